@@ -1,0 +1,390 @@
+#!/usr/bin/env python
+"""bench.py -- K-means map throughput (points/s) on B200, the metric BASELINE.json names.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]            # this framework
+  python bench.py --impl reference [--gpus N] [--steps K] ...    # the reference's CPU path
+  torchrun --nproc-per-node N ... bench.py --gpus N ...          # one rank per GPU
+
+A "step" is one pass of the hot path (nearest-centroid assignment + combiner partial sums,
+one K-means iteration's map phase) over one split-set of synthetic 2-D points:
+BASELINE.json configs[1] = 200,000,000 points, d=2, k=128 per GPU ("weak" scaling: every
+GPU slot maps its own 200 M-point shard; the k*d sums + k counts are then sum-allreduced
+over NCCL).
+
+  value     whole-job points/s with the points resident in HBM (CUDA events on the
+            library's own stream; K steps between barriers; max over ranks)
+  e2e       the same through the reference-facing C-ABI call hgm_map_split with PINNED HOST
+            buffers: host->device copies of the whole split and the device->host read of
+            the partials are inside the timed region
+  roofline  the map kernel alone: algorithmic bytes (4*d per point)
+            over its average CUDA-event duration, against MEASURED_PEAKS.json's HBM copy rate
+  cpu_baseline  the reference-runtime CPU Pipes program (oracle/_ref) on a bounded sample
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, "hadoop-1.0.3-gpu_b200")
+sys.path[:0] = [PKG, os.path.join(ROOT, "tests")]
+
+import numpy as np  # noqa: E402
+
+METRIC = "kmeans_map_points_per_sec"
+UNIT = "points/s"
+FALLBACK_HBM_GBS = 6650.0  # /opt/skills/guides/B200_PROFILING.md fallback
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    ap.add_argument("--points", type=int, default=200_000_000, help="points per GPU (configs[1])")
+    ap.add_argument("--k", type=int, default=128)
+    ap.add_argument("--d", type=int, default=2)
+    ap.add_argument("--cpu-points", type=int, default=1 << 19, help="points per CPU process in the baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--kernel", type=int, default=0, help="force a kernel family (hgpumap.h HGM_KERNEL_*)")
+    return ap.parse_args()
+
+
+def workload_name(args):
+    return (f"K-means 1 iteration, {args.points:,} 2-D points per GPU, k={args.k}, single B200 GPU map slot"
+            if args.d == 2 else f"K-means 1 iteration, {args.points:,} points per GPU, d={args.d}, k={args.k}")
+
+
+# ---------------------------------------------------------------------------------------
+# CPU baseline / reference arm: the reference's own Pipes runtime, JVM-free
+# ---------------------------------------------------------------------------------------
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except AttributeError:
+        return os.cpu_count() or 1
+
+
+class CpuReference:
+    """P concurrent Pipes children = P CPU map slots (mapred.tasktracker.map.cpu.tasks.maximum),
+    each replaying a command file of `points` MAP_ITEM records through the reference's
+    HadoopPipes.cc (or, if oracle/_ref is absent, the C port called in-process)."""
+
+    def __init__(self, args, procs, points):
+        from hgpumap import synth
+
+        self.k, self.d, self.procs, self.points = args.k, args.d, procs, points
+        self.bin = os.path.join(ROOT, "oracle", "_ref", "kmeans-pipes-cpu")
+        self.kind = "reference" if os.path.exists(self.bin) else "port"
+        centres = synth.centres(synth.SEED_POINTS, self.k, self.d)
+        self.cent = synth.perturb(synth.SEED_CENTROIDS, centres)
+        self.tmp = tempfile.mkdtemp(prefix="hgm_cpu_")
+        self.splits = [synth.points(synth.SEED_POINTS, i * points, points, centres) for i in range(procs)]
+        if self.kind == "reference":
+            import pipes_harness as ph
+
+            cpath = os.path.join(self.tmp, "centroids.bin")
+            self.cent.astype("<f4").tofile(cpath)
+            self.cmds = []
+            for i, pts in enumerate(self.splits):
+                path = os.path.join(self.tmp, f"cmd{i}")
+                ph.kmeans_downlink(pts, cpath, self.k, self.d, "binary", 1, 1).write(path)
+                self.cmds.append(path)
+        else:
+            import ctypes as C
+
+            so = os.path.join(ROOT, "oracle", "libkmeans_oracle.so")
+            if not os.path.exists(so):
+                subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "oracle"], check=True, capture_output=True)
+            self.lib = C.CDLL(so)
+            self.procs = 1
+
+    def sample(self):
+        what = (f"{self.procs} concurrent Pipes children x {self.points:,} one-point MAP_ITEM records through the "
+                "reference runtime (HadoopPipes.cc record pump + CombineRunner), map time excludes the runtime's "
+                "5 s ping-thread join") if self.kind == "reference" else \
+               f"C port of the mapper+combiner, 1 thread, {self.points:,} points, no Pipes protocol"
+        return what
+
+    def step(self):
+        """Run one bounded sample; returns (points, seconds of map work = max over children)."""
+        if self.kind == "port":
+            import ctypes as C
+
+            pts = self.splits[0]
+            sums = np.zeros((self.k, self.d))
+            counts = np.zeros(self.k, np.int64)
+            p = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+            t0 = time.perf_counter()
+            self.lib.hgo_map_combine(p(pts), C.c_int64(len(pts)), self.d, p(self.cent), self.k, p(sums), p(counts), None, None)
+            return len(pts), time.perf_counter() - t0
+        children = []
+        for i, cmd in enumerate(self.cmds):
+            stats = os.path.join(self.tmp, f"stats{i}.json")
+            env = {"hadoop.pipes.command.file": cmd, "HGM_ORACLE_STATS": stats, "PATH": os.environ.get("PATH", "")}
+            children.append((subprocess.Popen([self.bin], env=env, stdout=subprocess.DEVNULL, stderr=subprocess.PIPE), stats))
+        total, worst = 0, 0.0
+        for proc, stats in children:
+            _, err = proc.communicate(timeout=600)
+            if proc.returncode != 1:  # runTask's `true` is the exit status (wordcount-simple.cc:63-66)
+                raise RuntimeError(f"reference child failed: {err.decode()[-300:]}")
+            rec = json.load(open(stats))
+            total += rec["points"]
+            worst = max(worst, rec["map_seconds"])
+        return total, worst
+
+
+def run_reference_arm(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = host_cores()
+    ref = CpuReference(args, procs=cores, points=1 << 18)
+    for _ in range(min(args.warmup, 1)):
+        ref.step()
+    pts, secs = 0, 0.0
+    for _ in range(args.steps):
+        p, s = ref.step()
+        pts += p
+        secs += s
+    value = pts / secs
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * secs / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": workload_name(args), "k": args.k, "d": args.d,
+                   "sample_points_per_step": pts // args.steps},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": ref.procs, "kind": ref.kind, "sample": ref.sample()},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------------------
+# clocks
+# ---------------------------------------------------------------------------------------
+
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+              "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.FIELDS}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.thread.join(timeout=2)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for row in self.rows:
+            parts = [p.strip() for p in row.split(",")]
+            if len(parts) != 6:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for name, val in zip(names, parts[2:]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------------------
+# this framework
+# ---------------------------------------------------------------------------------------
+
+def hbm_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            return float(json.load(open(path))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, copy)"
+        except Exception:
+            pass
+    return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+
+    from hgpumap import capi, synth
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}; launch with torch.distributed.run")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    n, k, d = args.points, args.k, args.d
+    centres = synth.centres(synth.SEED_POINTS, k, d)
+    centroids = synth.perturb(synth.SEED_CENTROIDS, centres)
+    slot = capi.GpuMapSlot(local_rank)
+    if args.kernel:
+        slot.set_kernel(args.kernel)
+    slot.set_centroids(centroids)
+    points = torch.empty(n * d, dtype=torch.float32, device=dev)  # device memory: plumbing only
+    slot.synth_points_device(synth.SEED_POINTS, rank * n, n, centres, points.data_ptr())
+    if world > 1:
+        box = [capi.GpuMapSlot.comm_id() if rank == 0 else None]
+        dist.broadcast_object_list(box, src=0)
+        slot.comm_init(world, rank, box[0])
+    stream = torch.cuda.ExternalStream(slot.stream(), device=dev)
+
+    def step():
+        slot.reset_partials()
+        slot.map_device(points.data_ptr(), n)
+        if world > 1:
+            slot.allreduce_partials()
+
+    for _ in range(max(args.warmup, 3)):
+        step()
+    slot.sync()
+    sums, counts = slot.read_partials()
+    assert int(counts.sum()) == n * world, f"partials count {int(counts.sum())} != {n * world}"
+    kernel_family = slot.last_kernel()
+
+    # ---- value: K steps, HBM-resident, CUDA events on the library's stream -------------
+    sampler = ClockSampler(local_rank)
+    k_a = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    k_b = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    launches0 = slot.launch_count()
+    barrier()
+    if rank == 0:
+        sampler.start()
+    ev0.record(stream)
+    for i in range(args.steps):
+        slot.reset_partials()
+        k_a[i].record(stream)
+        slot.map_device(points.data_ptr(), n)
+        k_b[i].record(stream)
+        if world > 1:
+            slot.allreduce_partials()
+    ev1.record(stream)
+    slot.sync()
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    launches = slot.launch_count() - launches0
+    elapsed_ms = ev0.elapsed_time(ev1)
+    kernel_ms = statistics.mean(a.elapsed_time(b) for a, b in zip(k_a, k_b))
+    t = torch.tensor([elapsed_ms, kernel_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    elapsed_ms, kernel_ms = t.tolist()
+    value = world * n * args.steps / (elapsed_ms * 1e-3)
+
+    # ---- e2e: the C-ABI call a Pipes child / JNI stub makes, host buffers ----------------
+    e2e = None
+    if not args.no_e2e:
+        host = torch.empty(n * d, dtype=torch.float32, pin_memory=True)
+        host.copy_(points)
+        torch.cuda.synchronize()
+        h_sums = np.zeros((k, d))
+        h_counts = np.zeros(k, np.int64)
+        nbytes = n * d * 4
+
+        def e2e_step():
+            slot.map_split_raw(host.data_ptr(), nbytes, h_sums, h_counts)
+            if world > 1:
+                slot.allreduce_partials()
+                return slot.read_partials()
+            return h_sums, h_counts
+
+        for _ in range(3):
+            e2e_step()
+        e2e_steps = max(3, min(args.steps, 10))
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            s_, c_ = e2e_step()
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        assert int(c_.sum()) == n * world
+        t = torch.tensor([dt], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dt = t.item()
+        e2e = {"value": world * n * e2e_steps / dt, "unit": UNIT, "h2d_bytes_per_step": nbytes,
+               "d2h_bytes_per_step": k * d * 8 + k * 8, "steps": e2e_steps, "ms_per_step": 1e3 * dt / e2e_steps,
+               "api": "hgm_map_split (pinned host split -> chunked async H2D -> kernel -> partials D2H)"}
+        del host
+
+    if rank == 0:
+        peak, peak_src = hbm_peak()
+        achieved = n * d * 4 / (kernel_ms * 1e-3) / 1e9
+        fam = {capi.KERNEL_GRID2D: "grid2d_map_kernel", capi.KERNEL_EXACT: "exact_map_kernel"}.get(kernel_family, "?")
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(args), "points_per_gpu": n, "k": k, "d": d, "kernel": fam,
+                       "l2": f"inputs ({n * d * 4 / 1e6:.0f} MB per GPU) larger than the 126 MB L2; no flush needed",
+                       "parallelism": f"{world} GPU map slot(s), split-sharded; NCCL allreduce of k*d sums + k counts"
+                       if world > 1 else "1 GPU map slot"},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": None, "kernel": fam, "kernel_ms": kernel_ms, "peak_source": peak_src,
+                         "algorithmic_bytes_per_point": 4 * d},
+            "clocks": clocks,
+            "gpu_launches": launches,
+        }
+        if e2e:
+            line["e2e"] = e2e
+        if world == 1 and not args.no_cpu_baseline:
+            cores = min(host_cores(), 32)
+            ref = CpuReference(args, procs=cores, points=args.cpu_points)
+            p, s = ref.step()
+            line["cpu_baseline"] = {"value": p / s, "unit": UNIT, "cores": ref.procs, "kind": ref.kind,
+                                    "sample": ref.sample()}
+        print(json.dumps(line), flush=True)
+    slot.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference_arm(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

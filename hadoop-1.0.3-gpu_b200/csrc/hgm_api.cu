@@ -1,0 +1,591 @@
+// hgm_api.cu -- the C ABI of libhgpumap.so (include/hgpumap.h): context, staging, dispatch.
+//
+// One hgm_ctx is one GPU map slot (mapred/TaskTracker.java:2526-2562): a CUDA context on
+// one device, a compute stream, two copy streams with pinned bounce buffers, the centroid
+// table with its kernel-side index, and the device partials [k*d FP64 sums][k int64 counts].
+// A split is streamed through HBM in chunks: while chunk i is being mapped, chunk i+1 is
+// crossing PCIe; nothing is ever computed on the host.
+#include <errno.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdlib.h>
+
+#include <algorithm>
+#include <vector>
+
+#include "hgm_internal.h"
+
+using namespace hgm;
+
+namespace {
+thread_local char g_err[512] = "";
+
+constexpr size_t kChunkBytes = size_t(64) << 20;  // HBM chunk per pipeline stage
+constexpr int kStages = 3;
+constexpr size_t kBounceBytes = size_t(16) << 20;  // pinned bounce for pageable callers
+}  // namespace
+
+struct hgm_ctx {
+  int device = -1;
+  int sm_count = 0;
+  size_t smem_optin = 0;
+  cudaStream_t stream = nullptr;          // kernels
+  cudaStream_t copy[kStages] = {};        // H2D / D2H
+  cudaEvent_t ev_h2d[kStages] = {}, ev_free[kStages] = {}, ev_t0 = nullptr, ev_t1 = nullptr;
+  void *d_chunk[kStages] = {};            // kChunkBytes each
+  int32_t *d_assign_chunk[kStages] = {};  // lazily allocated
+  size_t assign_chunk_cap = 0;
+  void *h_bounce[kStages] = {};
+  cudaEvent_t ev_bounce[kStages] = {};
+
+  int k = 0, d = 0;
+  float *d_cent = nullptr;      // k*d floats (+ pad to 16 B)
+  void *d_partials = nullptr;   // [k*d double][k int64]
+  bool grid_ok = false;
+  Grid2D grid{};
+  uint16_t *d_table = nullptr;  // G*G
+  uint16_t *d_cand = nullptr;   // G*G*8
+  int forced = HGM_KERNEL_AUTO, last_kernel = HGM_KERNEL_AUTO;
+  int last_launches = 0;
+  int64_t total_launches = 0;
+  bool timing_open = false;
+  void *nccl_comm = nullptr;
+  char err[512] = "";
+};
+
+namespace {
+
+int fail(hgm_ctx *ctx, int code, const char *fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  snprintf(g_err, sizeof g_err, "%s", buf);
+  if (ctx) snprintf(ctx->err, sizeof ctx->err, "%s", buf);
+  return code;
+}
+
+#define CU(ctx, call)                                                                         \
+  do {                                                                                        \
+    cudaError_t e_ = (call);                                                                  \
+    if (e_ != cudaSuccess)                                                                    \
+      return fail(ctx, HGM_ECUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_),     \
+                  __FILE__, __LINE__);                                                        \
+  } while (0)
+
+#define NEED_CTX(ctx)                                             \
+  do {                                                            \
+    if (!(ctx)) return fail(nullptr, HGM_EINVAL, "ctx is NULL");  \
+    cudaError_t e_ = cudaSetDevice((ctx)->device);                \
+    if (e_ != cudaSuccess)                                        \
+      return fail(ctx, HGM_ECUDA, "cudaSetDevice(%d): %s", (ctx)->device, cudaGetErrorString(e_)); \
+  } while (0)
+
+double *sums_ptr(hgm_ctx *c) { return static_cast<double *>(c->d_partials); }
+unsigned long long *counts_ptr(hgm_ctx *c) {
+  return reinterpret_cast<unsigned long long *>(sums_ptr(c) + (size_t)c->k * c->d);
+}
+size_t partial_bytes(const hgm_ctx *c) { return (size_t)c->k * c->d * 8 + (size_t)c->k * 8; }
+
+void free_job(hgm_ctx *c) {
+  cudaFree(c->d_cent); c->d_cent = nullptr;
+  cudaFree(c->d_partials); c->d_partials = nullptr;
+  cudaFree(c->d_table); c->d_table = nullptr;
+  cudaFree(c->d_cand); c->d_cand = nullptr;
+  c->grid_ok = false;
+  c->k = c->d = 0;
+}
+
+// Choose the d == 2 cell grid for a centroid table; false if the table is not indexable
+// (non-finite or astronomically large coordinates) and the exact scan must be used.
+bool plan_grid2d(const float *cent, int k, size_t smem_optin, Grid2D *out) {
+  if (k > 1024) return false;
+  double lo[2] = {INFINITY, INFINITY}, hi[2] = {-INFINITY, -INFINITY};
+  for (int c = 0; c < k; ++c)
+    for (int j = 0; j < 2; ++j) {
+      const double v = cent[2 * c + j];
+      if (!std::isfinite(v) || fabs(v) > 1e18) return false;
+      lo[j] = std::min(lo[j], v);
+      hi[j] = std::max(hi[j], v);
+    }
+  int G = 256;
+  while (G > 64 && grid2d_map_smem_bytes(G, k) > smem_optin) G -= 32;
+  if (grid2d_map_smem_bytes(G, k) > smem_optin) return false;
+  float s[2], B[2];
+  int32_t b[2];
+  for (int j = 0; j < 2; ++j) {
+    double ext = hi[j] - lo[j];
+    const double mag = std::max(fabs(lo[j]), fabs(hi[j]));
+    if (!(ext > mag * 1e-4)) ext = std::max(mag * 1e-4, 1e-30);  // degenerate axis
+    const double margin = 0.125 * ext;
+    const double origin = lo[j] - margin;
+    const double scale = (double)(G - 1) / (ext + 2 * margin);
+    const float sf = (float)scale;
+    if (!(sf > 0.f) || !std::isfinite(sf)) return false;
+    const double off = -floor(origin * (double)sf + 0.5);  // RN(origin*s) + b == 0
+    if (fabs(off) > 4.0e6) return false;                   // keep b + 2^23 exact in FP32
+    s[j] = sf;
+    b[j] = (int32_t)off;
+    B[j] = (float)(off + 8388608.0);
+  }
+  out->sx = s[0]; out->sy = s[1];
+  out->Bx = B[0]; out->By = B[1];
+  out->bx = b[0]; out->by = b[1];
+  out->G = G;
+  return true;
+}
+
+int pick_kernel(hgm_ctx *c) {
+  if (c->forced == HGM_KERNEL_EXACT) return HGM_KERNEL_EXACT;
+  if (c->forced == HGM_KERNEL_GRID2D) return c->grid_ok ? HGM_KERNEL_GRID2D : -1;
+  if (c->forced == HGM_KERNEL_TENSOR) return -1;
+  return c->grid_ok ? HGM_KERNEL_GRID2D : HGM_KERNEL_EXACT;
+}
+
+// queue the map of n device-resident points on ctx->stream; adds into the partials
+int map_points_async(hgm_ctx *c, const float *d_pts, int64_t n, int32_t *d_assign) {
+  if (n == 0) return HGM_OK;
+  const int kern = pick_kernel(c);
+  if (kern < 0) return fail(c, HGM_EINVAL, "forced kernel %d does not fit k=%d d=%d", c->forced, c->k, c->d);
+  cudaError_t e;
+  if (kern == HGM_KERNEL_GRID2D) {
+    e = launch_grid2d_map(d_pts, n, c->d_cent, c->k, c->grid, c->d_table, c->d_cand, sums_ptr(c),
+                          counts_ptr(c), d_assign, c->sm_count, c->smem_optin, c->stream);
+  } else {
+    e = launch_exact_map(d_pts, n, c->d, c->d_cent, c->k, sums_ptr(c), counts_ptr(c), d_assign,
+                         c->sm_count, c->smem_optin, c->stream);
+  }
+  if (e != cudaSuccess) return fail(c, HGM_ECUDA, "map kernel launch failed: %s", cudaGetErrorString(e));
+  c->last_kernel = kern;
+  c->last_launches += 1;
+  c->total_launches += 1;
+  return HGM_OK;
+}
+
+bool is_pinned(const void *p) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return a.type == cudaMemoryTypeHost;
+}
+
+}  // namespace
+
+namespace hgm {
+void comm_destroy(void *comm);
+int ctx_shape(hgm_ctx *c, int *device, int *k, int *d, cudaStream_t *stream, void ***comm_slot) {
+  *device = c->device; *k = c->k; *d = c->d; *stream = c->stream; *comm_slot = &c->nccl_comm;
+  return 0;
+}
+int ctx_fail(hgm_ctx *c, int code, const char *msg) { return fail(c, code, "%s", msg); }
+}  // namespace hgm
+
+extern "C" {
+
+int hgm_version(void) { return 1000; }
+
+int hgm_device_count(int *count) {
+  if (!count) return fail(nullptr, HGM_EINVAL, "count is NULL");
+  CU(nullptr, cudaGetDeviceCount(count));
+  return HGM_OK;
+}
+
+const char *hgm_last_error(hgm_ctx *ctx) { return ctx ? ctx->err : g_err; }
+
+int hgm_open(int device_id, hgm_ctx **out) {
+  if (!out) return fail(nullptr, HGM_EINVAL, "out is NULL");
+  *out = nullptr;
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || ndev == 0)
+    return fail(nullptr, HGM_ENODEV, "no CUDA device: %s (there is no CPU fallback in a GPU map slot)",
+                e != cudaSuccess ? cudaGetErrorString(e) : "device count is 0");
+  if (device_id < 0 || device_id >= ndev)
+    return fail(nullptr, HGM_ENODEV, "device %d out of range (have %d)", device_id, ndev);
+  cudaDeviceProp prop;
+  CU(nullptr, cudaGetDeviceProperties(&prop, device_id));
+  if (prop.major != 10)
+    return fail(nullptr, HGM_ENODEV, "device %d is sm_%d%d; this library carries sm_100a code only",
+                device_id, prop.major, prop.minor);
+  CU(nullptr, cudaSetDevice(device_id));
+  hgm_ctx *c = new (std::nothrow) hgm_ctx();
+  if (!c) return fail(nullptr, HGM_ENOMEM, "out of host memory");
+  c->device = device_id;
+  c->sm_count = prop.multiProcessorCount;
+  c->smem_optin = prop.sharedMemPerBlockOptin;
+#define CUO(call)                                                                            \
+  do {                                                                                       \
+    cudaError_t e2_ = (call);                                                                \
+    if (e2_ != cudaSuccess) {                                                                \
+      fail(nullptr, HGM_ECUDA, "%s failed: %s", #call, cudaGetErrorString(e2_));             \
+      hgm_close(c);                                                                          \
+      return HGM_ECUDA;                                                                      \
+    }                                                                                        \
+  } while (0)
+  CUO(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
+  CUO(cudaEventCreate(&c->ev_t0));
+  CUO(cudaEventCreate(&c->ev_t1));
+  for (int i = 0; i < kStages; ++i) {
+    CUO(cudaStreamCreateWithFlags(&c->copy[i], cudaStreamNonBlocking));
+    CUO(cudaEventCreateWithFlags(&c->ev_h2d[i], cudaEventDisableTiming));
+    CUO(cudaEventCreateWithFlags(&c->ev_free[i], cudaEventDisableTiming));
+    CUO(cudaEventCreateWithFlags(&c->ev_bounce[i], cudaEventDisableTiming));
+  }
+#undef CUO
+  *out = c;
+  return HGM_OK;
+}
+
+void hgm_close(hgm_ctx *c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  if (c->stream) cudaStreamSynchronize(c->stream);
+  if (c->nccl_comm) { hgm::comm_destroy(c->nccl_comm); c->nccl_comm = nullptr; }
+  free_job(c);
+  for (int i = 0; i < kStages; ++i) {
+    if (c->copy[i]) { cudaStreamSynchronize(c->copy[i]); cudaStreamDestroy(c->copy[i]); }
+    if (c->ev_h2d[i]) cudaEventDestroy(c->ev_h2d[i]);
+    if (c->ev_free[i]) cudaEventDestroy(c->ev_free[i]);
+    if (c->ev_bounce[i]) cudaEventDestroy(c->ev_bounce[i]);
+    cudaFree(c->d_chunk[i]);
+    cudaFree(c->d_assign_chunk[i]);
+    if (c->h_bounce[i]) cudaFreeHost(c->h_bounce[i]);
+  }
+  if (c->ev_t0) cudaEventDestroy(c->ev_t0);
+  if (c->ev_t1) cudaEventDestroy(c->ev_t1);
+  if (c->stream) cudaStreamDestroy(c->stream);
+  delete c;
+}
+
+int hgm_set_centroids(hgm_ctx *c, const float *centroids, int32_t k, int32_t d) {
+  NEED_CTX(c);
+  if (!centroids || k <= 0 || d <= 0) return fail(c, HGM_EINVAL, "need centroids, k > 0, d > 0");
+  if ((int64_t)k * d > (int64_t(1) << 28)) return fail(c, HGM_EINVAL, "k*d too large");
+  CU(c, cudaStreamSynchronize(c->stream));
+  if (k != c->k || d != c->d) {
+    free_job(c);
+    const size_t cent_bytes = (((size_t)k * d * 4) + 15) & ~size_t(15);
+    CU(c, cudaMalloc(&c->d_cent, cent_bytes));
+    CU(c, cudaMemsetAsync(c->d_cent, 0, cent_bytes, c->stream));
+    c->k = k; c->d = d;
+    CU(c, cudaMalloc(&c->d_partials, partial_bytes(c)));
+  }
+  CU(c, cudaMemcpyAsync(c->d_cent, centroids, (size_t)k * d * 4, cudaMemcpyHostToDevice, c->stream));
+  CU(c, cudaMemsetAsync(c->d_partials, 0, partial_bytes(c), c->stream));
+  c->grid_ok = false;
+  if (d == 2) {
+    Grid2D g;
+    if (plan_grid2d(centroids, k, c->smem_optin, &g)) {
+      if (!c->d_table || g.G != c->grid.G) {
+        cudaFree(c->d_table); cudaFree(c->d_cand);
+        c->d_table = nullptr; c->d_cand = nullptr;
+        CU(c, cudaMalloc(&c->d_table, (size_t)g.G * g.G * 2 + 16));
+        CU(c, cudaMalloc(&c->d_cand, (size_t)g.G * g.G * kMaxCand * 2));
+      }
+      c->grid = g;
+      cudaError_t e = launch_grid2d_build(c->d_cent, k, g, c->d_table, c->d_cand, c->stream);
+      if (e != cudaSuccess) return fail(c, HGM_ECUDA, "grid2d build launch: %s", cudaGetErrorString(e));
+      c->total_launches += 1;
+      c->grid_ok = true;
+    }
+  }
+  // the caller's centroid buffer may be reused as soon as we return
+  CU(c, cudaStreamSynchronize(c->stream));
+  return HGM_OK;
+}
+
+int hgm_set_kernel(hgm_ctx *c, int32_t kernel) {
+  if (!c) return fail(nullptr, HGM_EINVAL, "ctx is NULL");
+  if (kernel < HGM_KERNEL_AUTO || kernel > HGM_KERNEL_TENSOR) return fail(c, HGM_EINVAL, "unknown kernel %d", kernel);
+  c->forced = kernel;
+  return HGM_OK;
+}
+
+int hgm_last_kernel(hgm_ctx *c, int32_t *kernel) {
+  if (!c || !kernel) return fail(c, HGM_EINVAL, "NULL argument");
+  *kernel = c->last_kernel;
+  return HGM_OK;
+}
+
+int hgm_reset_partials(hgm_ctx *c) {
+  NEED_CTX(c);
+  if (!c->d_partials) return fail(c, HGM_EINVAL, "hgm_set_centroids has not been called");
+  CU(c, cudaMemsetAsync(c->d_partials, 0, partial_bytes(c), c->stream));
+  return HGM_OK;
+}
+
+int hgm_map_device(hgm_ctx *c, const float *d_points, int64_t n, int32_t *d_assign) {
+  NEED_CTX(c);
+  if (!c->d_partials) return fail(c, HGM_EINVAL, "hgm_set_centroids has not been called");
+  if (n < 0 || (n > 0 && !d_points)) return fail(c, HGM_EINVAL, "bad points argument");
+  if (reinterpret_cast<uintptr_t>(d_points) & 7) return fail(c, HGM_EINVAL, "d_points must be 8-byte aligned");
+  c->last_launches = 0;
+  CU(c, cudaEventRecord(c->ev_t0, c->stream));
+  const int rc = map_points_async(c, d_points, n, d_assign);
+  if (rc != HGM_OK) return rc;
+  CU(c, cudaEventRecord(c->ev_t1, c->stream));
+  c->timing_open = true;
+  return HGM_OK;
+}
+
+int hgm_read_partials(hgm_ctx *c, double *sums, int64_t *counts) {
+  NEED_CTX(c);
+  if (!c->d_partials) return fail(c, HGM_EINVAL, "hgm_set_centroids has not been called");
+  if (!sums || !counts) return fail(c, HGM_EINVAL, "sums and counts are required");
+  CU(c, cudaMemcpyAsync(sums, sums_ptr(c), (size_t)c->k * c->d * 8, cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaMemcpyAsync(counts, counts_ptr(c), (size_t)c->k * 8, cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  return HGM_OK;
+}
+
+int hgm_partials_device(hgm_ctx *c, double **d_sums, int64_t **d_counts) {
+  if (!c || !c->d_partials) return fail(c, HGM_EINVAL, "hgm_set_centroids has not been called");
+  if (d_sums) *d_sums = sums_ptr(c);
+  if (d_counts) *d_counts = reinterpret_cast<int64_t *>(counts_ptr(c));
+  return HGM_OK;
+}
+
+int hgm_sync(hgm_ctx *c) {
+  NEED_CTX(c);
+  CU(c, cudaStreamSynchronize(c->stream));
+  return HGM_OK;
+}
+
+int hgm_stream(hgm_ctx *c, void **cuda_stream) {
+  if (!c || !cuda_stream) return fail(c, HGM_EINVAL, "NULL argument");
+  *cuda_stream = c->stream;
+  return HGM_OK;
+}
+
+int hgm_last_map_ms(hgm_ctx *c, float *ms, int32_t *launches) {
+  NEED_CTX(c);
+  if (!c->timing_open) return fail(c, HGM_EINVAL, "no map call has been timed yet");
+  CU(c, cudaEventSynchronize(c->ev_t1));
+  if (ms) CU(c, cudaEventElapsedTime(ms, c->ev_t0, c->ev_t1));
+  if (launches) *launches = c->last_launches;
+  return HGM_OK;
+}
+
+int hgm_launch_count(hgm_ctx *c, int64_t *launches) {
+  if (!c || !launches) return fail(c, HGM_EINVAL, "NULL argument");
+  *launches = c->total_launches;
+  return HGM_OK;
+}
+
+int hgm_device_alloc(hgm_ctx *c, size_t nbytes, void **d_ptr) {
+  NEED_CTX(c);
+  if (!d_ptr) return fail(c, HGM_EINVAL, "d_ptr is NULL");
+  cudaError_t e = cudaMalloc(d_ptr, nbytes ? nbytes : 1);
+  if (e != cudaSuccess) { cudaGetLastError(); return fail(c, HGM_ENOMEM, "cudaMalloc(%zu): %s", nbytes, cudaGetErrorString(e)); }
+  return HGM_OK;
+}
+int hgm_device_free(hgm_ctx *c, void *d_ptr) {
+  NEED_CTX(c);
+  CU(c, cudaStreamSynchronize(c->stream));
+  CU(c, cudaFree(d_ptr));
+  return HGM_OK;
+}
+int hgm_host_alloc(hgm_ctx *c, size_t nbytes, void **h_ptr) {
+  NEED_CTX(c);
+  if (!h_ptr) return fail(c, HGM_EINVAL, "h_ptr is NULL");
+  cudaError_t e = cudaHostAlloc(h_ptr, nbytes ? nbytes : 1, cudaHostAllocDefault);
+  if (e != cudaSuccess) { cudaGetLastError(); return fail(c, HGM_ENOMEM, "cudaHostAlloc(%zu): %s", nbytes, cudaGetErrorString(e)); }
+  return HGM_OK;
+}
+int hgm_host_free(hgm_ctx *c, void *h_ptr) {
+  NEED_CTX(c);
+  CU(c, cudaFreeHost(h_ptr));
+  return HGM_OK;
+}
+int hgm_memcpy_h2d(hgm_ctx *c, void *d_dst, const void *h_src, size_t nbytes) {
+  NEED_CTX(c);
+  CU(c, cudaMemcpyAsync(d_dst, h_src, nbytes, cudaMemcpyHostToDevice, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  return HGM_OK;
+}
+int hgm_memcpy_d2h(hgm_ctx *c, void *h_dst, const void *d_src, size_t nbytes) {
+  NEED_CTX(c);
+  CU(c, cudaMemcpyAsync(h_dst, d_src, nbytes, cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  return HGM_OK;
+}
+
+// ---- the streamed map task ---------------------------------------------------------------
+
+static int ensure_pipeline(hgm_ctx *c, bool want_assign, size_t rows_per_chunk, bool want_bounce) {
+  for (int i = 0; i < kStages; ++i) {
+    if (!c->d_chunk[i]) CU(c, cudaMalloc(&c->d_chunk[i], kChunkBytes));
+    if (want_bounce && !c->h_bounce[i]) CU(c, cudaHostAlloc(&c->h_bounce[i], kBounceBytes, cudaHostAllocDefault));
+  }
+  if (want_assign && c->assign_chunk_cap < rows_per_chunk) {
+    for (int i = 0; i < kStages; ++i) {
+      cudaFree(c->d_assign_chunk[i]);
+      c->d_assign_chunk[i] = nullptr;
+      CU(c, cudaMalloc(&c->d_assign_chunk[i], rows_per_chunk * 4));
+    }
+    c->assign_chunk_cap = rows_per_chunk;
+  }
+  return HGM_OK;
+}
+
+// Byte source of a split: host memory or a file region read through the bounce buffers.
+struct SplitSource {
+  const unsigned char *mem = nullptr;
+  FILE *file = nullptr;
+  size_t nbytes = 0;
+  bool pinned = false;
+};
+
+static int map_stream(hgm_ctx *c, SplitSource &src, int32_t fmt, double *sums, int64_t *counts,
+                      int32_t *assign, int64_t *n_points_out) {
+  if (!c->d_partials) return fail(c, HGM_EINVAL, "hgm_set_centroids has not been called");
+  if (!sums || !counts) return fail(c, HGM_EINVAL, "sums_kxd and counts_k are required");
+  if (fmt != HGM_FMT_F32LE && fmt != HGM_FMT_F32BE)
+    return fail(c, HGM_EFORMAT, "record format %d is not supported by this build", fmt);
+  const size_t row = (size_t)c->d * 4;
+  if (src.nbytes % row != 0)
+    return fail(c, HGM_EFORMAT, "split of %zu bytes is not a whole number of %zu-byte rows", src.nbytes, row);
+  const int64_t n = (int64_t)(src.nbytes / row);
+  if (n_points_out) *n_points_out = n;
+  size_t rows_per_chunk = kChunkBytes / row;
+  rows_per_chunk &= ~size_t(8191);  // whole tiles of every kernel, keeps 16-byte alignment
+  if (rows_per_chunk == 0) rows_per_chunk = kChunkBytes / row;
+  if (rows_per_chunk == 0) return fail(c, HGM_EINVAL, "a row of d=%d floats exceeds the staging chunk", c->d);
+  const bool bounce = !src.pinned;
+  int rc = ensure_pipeline(c, assign != nullptr, rows_per_chunk, bounce);
+  if (rc != HGM_OK) return rc;
+
+  c->last_launches = 0;
+  CU(c, cudaMemsetAsync(c->d_partials, 0, partial_bytes(c), c->stream));
+  CU(c, cudaEventRecord(c->ev_t0, c->stream));
+  int64_t done = 0;
+  int stage = 0;
+  int bounce_i = 0;
+  bool stage_used[kStages] = {};
+  bool bounce_used[kStages] = {};
+  while (done < n) {
+    const int64_t m = std::min<int64_t>((int64_t)rows_per_chunk, n - done);
+    const size_t bytes = (size_t)m * row;
+    cudaStream_t cs = c->copy[stage];
+    // the chunk buffer is free once the kernel that read it (and its assign D2H) is done
+    if (stage_used[stage]) CU(c, cudaStreamWaitEvent(cs, c->ev_free[stage], 0));
+    if (!bounce) {
+      CU(c, cudaMemcpyAsync(c->d_chunk[stage], src.mem + (size_t)done * row, bytes, cudaMemcpyHostToDevice, cs));
+    } else {
+      size_t off = 0;
+      while (off < bytes) {
+        const size_t piece = std::min(kBounceBytes, bytes - off);
+        if (bounce_used[bounce_i]) CU(c, cudaEventSynchronize(c->ev_bounce[bounce_i]));
+        if (src.file) {
+          if (fread(c->h_bounce[bounce_i], 1, piece, src.file) != piece)
+            return fail(c, HGM_EIO, "short read from split file: %s", strerror(errno));
+        } else {
+          memcpy(c->h_bounce[bounce_i], src.mem + (size_t)done * row + off, piece);
+        }
+        CU(c, cudaMemcpyAsync(static_cast<unsigned char *>(c->d_chunk[stage]) + off, c->h_bounce[bounce_i], piece,
+                              cudaMemcpyHostToDevice, cs));
+        CU(c, cudaEventRecord(c->ev_bounce[bounce_i], cs));
+        bounce_used[bounce_i] = true;
+        bounce_i = (bounce_i + 1) % kStages;
+        off += piece;
+      }
+    }
+    CU(c, cudaEventRecord(c->ev_h2d[stage], cs));
+    CU(c, cudaStreamWaitEvent(c->stream, c->ev_h2d[stage], 0));
+    if (fmt == HGM_FMT_F32BE) {  // K5: decode on the device, in place
+      cudaError_t e = launch_bswap32(static_cast<uint32_t *>(c->d_chunk[stage]), m * c->d, c->stream);
+      if (e != cudaSuccess) return fail(c, HGM_ECUDA, "decode launch: %s", cudaGetErrorString(e));
+      c->last_launches += 1;
+      c->total_launches += 1;
+    }
+    int32_t *d_asg = assign ? c->d_assign_chunk[stage] : nullptr;
+    rc = map_points_async(c, static_cast<const float *>(c->d_chunk[stage]), m, d_asg);
+    if (rc != HGM_OK) return rc;
+    if (assign)
+      CU(c, cudaMemcpyAsync(assign + done, d_asg, (size_t)m * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaEventRecord(c->ev_free[stage], c->stream));
+    stage_used[stage] = true;
+    stage = (stage + 1) % kStages;
+    done += m;
+  }
+  CU(c, cudaEventRecord(c->ev_t1, c->stream));
+  c->timing_open = true;
+  CU(c, cudaMemcpyAsync(sums, sums_ptr(c), (size_t)c->k * c->d * 8, cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaMemcpyAsync(counts, counts_ptr(c), (size_t)c->k * 8, cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  return HGM_OK;
+}
+
+int hgm_map_split(hgm_ctx *c, const void *host_bytes, size_t nbytes, int32_t fmt, double *sums,
+                  int64_t *counts, int32_t *assign, int64_t *n_points_out) {
+  NEED_CTX(c);
+  if (nbytes > 0 && !host_bytes) return fail(c, HGM_EINVAL, "host_bytes is NULL");
+  SplitSource src;
+  src.mem = static_cast<const unsigned char *>(host_bytes);
+  src.nbytes = nbytes;
+  src.pinned = nbytes > 0 && is_pinned(host_bytes);
+  return map_stream(c, src, fmt, sums, counts, assign, n_points_out);
+}
+
+int hgm_map_file(hgm_ctx *c, const char *path, int64_t offset, int64_t length, int32_t fmt,
+                 double *sums, int64_t *counts, int32_t *assign, int64_t *n_points_out) {
+  NEED_CTX(c);
+  if (!path || offset < 0) return fail(c, HGM_EINVAL, "bad path or offset");
+  FILE *f = fopen(path, "rb");
+  if (!f) return fail(c, HGM_EIO, "cannot open %s: %s", path, strerror(errno));
+  if (length < 0) {
+    fseeko(f, 0, SEEK_END);
+    length = (int64_t)ftello(f) - offset;
+    if (length < 0) length = 0;
+  }
+  if (fseeko(f, (off_t)offset, SEEK_SET) != 0) {
+    fclose(f);
+    return fail(c, HGM_EIO, "cannot seek %s to %lld", path, (long long)offset);
+  }
+  SplitSource src;
+  src.file = f;
+  src.nbytes = (size_t)length;
+  src.pinned = false;
+  const int rc = map_stream(c, src, fmt, sums, counts, assign, n_points_out);
+  fclose(f);
+  if (rc != HGM_OK) cudaStreamSynchronize(c->stream);
+  return rc;
+}
+
+// ---- synthetic workload ------------------------------------------------------------------
+
+int hgm_synth_centres(uint64_t seed, int32_t k, int32_t d, float *out) {
+  if (!out || k <= 0 || d <= 0) return fail(nullptr, HGM_EINVAL, "bad argument");
+  synth_centres_host(seed, k, d, out);
+  return HGM_OK;
+}
+int hgm_synth_perturb(uint64_t seed, int32_t k, int32_t d, const float *centres, float *out) {
+  if (!out || !centres || k <= 0 || d <= 0) return fail(nullptr, HGM_EINVAL, "bad argument");
+  synth_perturb_host(seed, k, d, centres, out);
+  return HGM_OK;
+}
+int hgm_synth_points_host(uint64_t seed, int64_t first, int64_t n, int32_t d, int32_t k,
+                          const float *centres, float *out) {
+  if (!out || !centres || k <= 0 || d <= 0 || n < 0) return fail(nullptr, HGM_EINVAL, "bad argument");
+  synth_points_host(seed, first, n, d, k, centres, out);
+  return HGM_OK;
+}
+int hgm_synth_points_device(hgm_ctx *c, uint64_t seed, int64_t first, int64_t n, int32_t d, int32_t k,
+                            const float *centres_host, float *d_out) {
+  NEED_CTX(c);
+  if (!centres_host || (!d_out && n > 0) || k <= 0 || d <= 0 || n < 0) return fail(c, HGM_EINVAL, "bad argument");
+  float *d_centres = nullptr;
+  CU(c, cudaMalloc(&d_centres, (size_t)k * d * 4));
+  cudaError_t e = cudaMemcpyAsync(d_centres, centres_host, (size_t)k * d * 4, cudaMemcpyHostToDevice, c->stream);
+  if (e == cudaSuccess) e = launch_synth_points(seed, first, n, d, k, d_centres, d_out, c->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+  cudaFree(d_centres);
+  if (e != cudaSuccess) return fail(c, HGM_ECUDA, "synth: %s", cudaGetErrorString(e));
+  c->total_launches += 1;
+  return HGM_OK;
+}
+
+}  // extern "C"

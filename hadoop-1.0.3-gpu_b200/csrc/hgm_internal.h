@@ -1,0 +1,61 @@
+// hgm_internal.h -- shared declarations of libhgpumap's translation units (not installed).
+#pragma once
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+
+#include "../../include/hgpumap.h"
+
+namespace hgm {
+
+// ---- arithmetic contract ------------------------------------
+// distance = FP32 sum_j (x_j - c_j)^2 with j ascending and every operation rounded on
+// its own.  nvcc contracts a*b+c into FMA by default, so the exact paths spell the
+// rounding out with intrinsics instead of relying on a compiler flag.
+__device__ __forceinline__ float sqdiff(float x, float c) {
+  float t = __fsub_rn(x, c);
+  return __fmul_rn(t, t);
+}
+
+// ---- d == 2 cell index (kernels_grid2d.cu) -------------------------------------------
+// cell coordinate of x:  bits(fma(x, s, B)) - 0x4B000000, where B = b + 2^23 with b an
+// integer, i.e. RN(x*s) + b obtained from the mantissa of one FMA.  NaN, +-inf and
+// out-of-range x all come out >= G as unsigned and take the brute-force path.
+struct Grid2D {
+  float sx, Bx, sy, By;
+  int32_t bx, by;  // the integer offsets inside Bx, By (builder needs them)
+  int32_t G;       // cells per side
+};
+
+constexpr uint32_t kMagicBits = 0x4B000000u;  // bits of 2^23
+constexpr uint16_t kCellBrute = 0xFFFFu;      // cell entry: scan all k centroids
+constexpr uint16_t kCellMulti = 0x8000u;      // cell entry: 0x8000 | candidate count (2..8)
+constexpr int kMaxCand = 8;
+
+// launchers (each returns the CUDA error of its launch)
+cudaError_t launch_grid2d_build(const float *d_cent, int k, const Grid2D &g, uint16_t *d_table,
+                                uint16_t *d_cand, cudaStream_t s);
+cudaError_t launch_grid2d_map(const float *d_pts, int64_t n, const float *d_cent, int k,
+                              const Grid2D &g, const uint16_t *d_table, const uint16_t *d_cand,
+                              double *d_sums, unsigned long long *d_counts, int32_t *d_assign,
+                              int sm_count, size_t smem_optin, cudaStream_t s);
+size_t grid2d_map_smem_bytes(int G, int k);
+
+cudaError_t launch_exact_map(const float *d_pts, int64_t n, int d, const float *d_cent, int k,
+                             double *d_sums, unsigned long long *d_counts, int32_t *d_assign,
+                             int sm_count, size_t smem_optin, cudaStream_t s);
+
+cudaError_t launch_bswap32(uint32_t *d_words, int64_t n_words, cudaStream_t s);
+
+cudaError_t launch_synth_points(uint64_t seed, int64_t first, int64_t n, int d, int k,
+                                const float *d_centres, float *d_out, cudaStream_t s);
+
+// host side of the synthetic generator (synth.cu)
+void synth_centres_host(uint64_t seed, int k, int d, float *out);
+void synth_perturb_host(uint64_t seed, int k, int d, const float *centres, float *out);
+void synth_points_host(uint64_t seed, int64_t first, int64_t n, int d, int k, const float *centres,
+                       float *out);
+
+}  // namespace hgm

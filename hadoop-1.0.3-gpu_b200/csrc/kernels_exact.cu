@@ -1,0 +1,159 @@
+// kernels_exact.cu -- the brute-force FP32 map kernel: any d, any k, no index.
+//
+// This is the reference scan itself (oracle/kmeans_oracle.c hgo_nearest states the same
+// contract on the CPU): one thread per point walks every centroid in ascending index,
+// distance = FP32 sum_j (x_j - c_j)^2 with j ascending and no FMA contraction, strict '<'
+// from (+inf, 0).  It fills the map-body slot Mapper::map (c++/pipes/api/hadoop/Pipes.hh:
+// 158-161) and the combiner slot Reducer::reduce (Pipes.hh:166-169) for shapes the
+// specialised kernels do not take, and it is the re-check kernel behind them.
+//
+// The per-(point, centroid) sum must run over j sequentially to round like the scan does,
+// so the parallel axes are points (threads) and nothing else; centroids stream through
+// shared memory in chunks and are read as warp-wide broadcasts.
+#include "hgm_internal.h"
+
+namespace hgm {
+namespace {
+
+constexpr int kThreads = 128;
+constexpr int kSmemAccLimit = 4096;  // use shared FP64 accumulators when k*d <= this
+
+template <int D>
+__global__ void __launch_bounds__(kThreads)
+    exact_map_kernel(const float *__restrict__ pts, long long n, int d_rt,
+                     const float *__restrict__ cent, int k, int kc, int smem_acc,
+                     double *__restrict__ g_sums, unsigned long long *__restrict__ g_counts,
+                     int32_t *__restrict__ assign) {
+  const int d = D > 0 ? D : d_rt;
+  extern __shared__ __align__(16) unsigned char raw[];
+  // layout: [acc doubles k*d][cnt u64 k] (if smem_acc) | centroid chunk kc*d | xT d*kThreads (D==0)
+  double *acc_s = reinterpret_cast<double *>(raw);
+  unsigned long long *cnt_s = reinterpret_cast<unsigned long long *>(acc_s + (smem_acc ? (size_t)k * d : 0));
+  float *cent_s = reinterpret_cast<float *>(cnt_s + (smem_acc ? k : 0));
+  float *xT = cent_s + (size_t)kc * d;
+  const int t = threadIdx.x;
+
+  if (smem_acc) {
+    for (int i = t; i < k * d; i += kThreads) acc_s[i] = 0.0;
+    for (int i = t; i < k; i += kThreads) cnt_s[i] = 0ull;
+  }
+  __syncthreads();
+
+  const long long ntiles = (n + kThreads - 1) / kThreads;
+  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const long long p = tile * kThreads + t;
+    const bool live = p < n;
+    float xr[D > 0 ? D : 1];
+    if (D > 0) {
+#pragma unroll
+      for (int j = 0; j < D; ++j) xr[j] = live ? pts[p * D + j] : 0.f;
+    } else {
+      // stage this tile's rows transposed: xT[j][thread]; coalesced global reads
+      const long long base = tile * kThreads * (long long)d;
+      const long long lim = n * (long long)d;
+      for (int i = t; i < kThreads * d; i += kThreads) {
+        const long long gidx = base + i;
+        const float v = gidx < lim ? pts[gidx] : 0.f;
+        xT[(i % d) * kThreads + (i / d)] = v;
+      }
+    }
+    float best = INFINITY;
+    int arg = 0;
+    for (int c0 = 0; c0 < k; c0 += kc) {
+      const int m = min(kc, k - c0);
+      __syncthreads();  // previous chunk fully consumed (and xT staged)
+      for (int i = t; i < m * d; i += kThreads) cent_s[i] = cent[(size_t)c0 * d + i];
+      __syncthreads();
+      for (int c = 0; c < m; ++c) {
+        float a = 0.0f;
+        if (D > 0) {
+#pragma unroll
+          for (int j = 0; j < D; ++j) a = __fadd_rn(a, sqdiff(xr[j], cent_s[c * D + j]));
+        } else {
+          for (int j = 0; j < d; ++j) a = __fadd_rn(a, sqdiff(xT[j * kThreads + t], cent_s[c * d + j]));
+        }
+        if (a < best) { best = a; arg = c0 + c; }
+      }
+    }
+    if (live) {
+      if (assign) assign[p] = arg;
+      double *sums = smem_acc ? acc_s : g_sums;
+      unsigned long long *cnts = smem_acc ? cnt_s : g_counts;
+      atomicAdd(&cnts[arg], 1ull);
+      if (D > 0) {
+#pragma unroll
+        for (int j = 0; j < D; ++j) atomicAdd(&sums[(size_t)arg * D + j], (double)xr[j]);
+      } else {
+        for (int j = 0; j < d; ++j) atomicAdd(&sums[(size_t)arg * d + j], (double)xT[j * kThreads + t]);
+      }
+    }
+    __syncthreads();  // xT is rewritten by the next tile
+  }
+  if (smem_acc) {
+    __syncthreads();
+    for (int i = t; i < k * d; i += kThreads)
+      if (acc_s[i] != 0.0) atomicAdd(&g_sums[i], acc_s[i]);
+    for (int i = t; i < k; i += kThreads)
+      if (cnt_s[i] != 0ull) atomicAdd(&g_counts[i], cnt_s[i]);
+  }
+}
+
+__global__ void bswap32_kernel(uint32_t *w, long long n) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride)
+    w[i] = __byte_perm(w[i], 0, 0x0123);
+}
+
+}  // namespace
+
+cudaError_t launch_exact_map(const float *d_pts, int64_t n, int d, const float *d_cent, int k,
+                             double *d_sums, unsigned long long *d_counts, int32_t *d_assign,
+                             int sm_count, size_t smem_optin, cudaStream_t s) {
+  if (n <= 0) return cudaSuccess;
+  const int smem_acc = ((long long)k * d <= kSmemAccLimit) ? 1 : 0;
+  const size_t acc_bytes = smem_acc ? ((size_t)k * d * 8 + (size_t)k * 8) : 0;
+  const bool reg_path = d <= 8;
+  const size_t xt_bytes = reg_path ? 0 : (size_t)d * kThreads * 4;
+  if (acc_bytes + xt_bytes + (size_t)d * 4 > smem_optin) return cudaErrorInvalidValue;
+  size_t room = smem_optin - acc_bytes - xt_bytes;
+  if (room > 64 * 1024) room = 64 * 1024;  // keep a few CTAs per SM
+  int kc = (int)(room / ((size_t)d * 4));
+  if (kc > k) kc = k;
+  if (kc < 1) return cudaErrorInvalidValue;
+  const size_t smem = acc_bytes + (size_t)kc * d * 4 + xt_bytes;
+
+  void (*kern)(const float *, long long, int, const float *, int, int, int, double *,
+               unsigned long long *, int32_t *) = nullptr;
+  switch (reg_path ? d : 0) {
+    case 1: kern = exact_map_kernel<1>; break;
+    case 2: kern = exact_map_kernel<2>; break;
+    case 3: kern = exact_map_kernel<3>; break;
+    case 4: kern = exact_map_kernel<4>; break;
+    case 5: kern = exact_map_kernel<5>; break;
+    case 6: kern = exact_map_kernel<6>; break;
+    case 7: kern = exact_map_kernel<7>; break;
+    case 8: kern = exact_map_kernel<8>; break;
+    default: kern = exact_map_kernel<0>; break;
+  }
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  const long long ntiles = (n + kThreads - 1) / kThreads;
+  int per_sm = (int)(smem_optin / (smem + 1024));
+  if (per_sm < 1) per_sm = 1;
+  if (per_sm > 8) per_sm = 8;
+  long long grid = (long long)sm_count * per_sm;
+  if (grid > ntiles) grid = ntiles;
+  kern<<<(int)grid, kThreads, smem, s>>>(d_pts, (long long)n, d, d_cent, k, kc, smem_acc, d_sums,
+                                         d_counts, d_assign);
+  return cudaGetLastError();
+}
+
+cudaError_t launch_bswap32(uint32_t *d_words, int64_t n_words, cudaStream_t s) {
+  if (n_words <= 0) return cudaSuccess;
+  long long blocks = (n_words + 255) / 256;
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  bswap32_kernel<<<(int)blocks, 256, 0, s>>>(d_words, (long long)n_words);
+  return cudaGetLastError();
+}
+
+}  // namespace hgm

@@ -1,0 +1,179 @@
+/* hgpumap.h -- C ABI of libhgpumap.so, the B200 (sm_100a) K-means map-task runtime.
+ *
+ * This is the drop-in boundary for the one path the millecker/hadoop-1.0.3-gpu fork
+ * accelerates: the K-means *map* function (nearest-centroid assignment + combiner
+ * partial sums) run as a GPU map task.  In the reference that path is reached through
+ * C++ virtuals and a socket protocol, not a C ABI:
+ *
+ *   Java task  --PipesGPUMapRunner.run-->  child process  --HadoopPipes::runTask-->
+ *   Mapper::map(MapContext&) per record, Reducer::reduce(ReduceContext&) as combiner
+ *
+ * so each entry point below names the reference interface it stands under
+ * (paths relative to /root/reference/hadoop-1.0.3/src).  Two hosts bind this header:
+ * the Pipes child `kmeans-pipes-gpu` (the -gpubin; csrc/pipes_gpu_main.cc) and a JNI
+ * stub inside the task JVM.
+ *
+ * Conventions: plain C, no C++ or torch types; every function returns 0 or a negative
+ * HGM_E* code and records a message readable with hgm_last_error(); the caller owns
+ * every host buffer; one hgm_ctx per GPU map slot, used by one thread at a time
+ * (mapred/TaskTracker.java:2526-2562 gives a slot to one task at a time); there is NO
+ * CPU fallback: without a usable sm_100 device hgm_open fails and the task must fail
+ * (the scheduler re-runs the split, mapred/JobInProgress.java:3146-3159).
+ */
+#ifndef HGPUMAP_H
+#define HGPUMAP_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct hgm_ctx hgm_ctx;
+
+#define HGM_OK 0
+#define HGM_EINVAL (-22)   /* bad argument or call order */
+#define HGM_ENOMEM (-12)   /* host or device allocation failed */
+#define HGM_ENODEV (-19)   /* no such device / not an sm_100 GPU */
+#define HGM_EIO (-5)       /* file or stream error */
+#define HGM_ECUDA (-1000)  /* CUDA runtime error; text in hgm_last_error */
+#define HGM_ENCCL (-1001)  /* NCCL missing or failed */
+#define HGM_EFORMAT (-1002)/* malformed input record */
+
+/* Record formats of a split (JobConf kmeans.input.format; the reference's map input is
+ * one std::string per record, c++/pipes/api/hadoop/Pipes.hh:89). */
+#define HGM_FMT_F32LE 0 /* rows of d little-endian IEEE float32 (primary format)           */
+#define HGM_FMT_F32BE 1 /* rows of d big-endian float32 (DataOutput.writeFloat order)       */
+#define HGM_FMT_TEXT 2  /* decimals separated by space, comma, tab or newline; each field   */
+                        /* means what HadoopUtils::toFloat (c++/utils/impl/StringUtils.cc:  */
+                        /* 49-56) would return for it                                       */
+
+/* Kernel families (hgm_set_kernel); AUTO picks by shape. */
+#define HGM_KERNEL_AUTO 0
+#define HGM_KERNEL_EXACT 1   /* brute-force FP32 scan, any d and k                          */
+#define HGM_KERNEL_GRID2D 2  /* d == 2: exact candidate pruning through a cell index        */
+#define HGM_KERNEL_TENSOR 3  /* tcgen05 distance GEMM + FP32 re-check of near ties          */
+
+/* ---- library / device ------------------------------------------------------------- */
+
+/* ABI version of this header (major*1000 + minor). */
+int hgm_version(void);
+
+/* Number of CUDA devices visible; the TaskTracker sizes
+ * mapred.tasktracker.map.gpu.tasks.maximum from it (mapred/TaskTracker.java:1428-1433). */
+int hgm_device_count(int *count);
+
+/* Open the GPU map slot on `device_id`.  Stands for the device id the Java side appends
+ * to the child's argv (mapred/pipes/Application.java:179-181; slot i <-> device i,
+ * mapred/TaskTrackerStatus.java:536-551).  Creates the CUDA context, one stream and the
+ * pinned staging ring once; keep the ctx alive across splits. */
+int hgm_open(int device_id, hgm_ctx **out);
+void hgm_close(hgm_ctx *ctx);
+
+/* Last error text of `ctx`, or of the calling thread when ctx is NULL (hgm_open failed).
+ * The Pipes adapter rethrows it as HadoopUtils::Error (c++/utils/api/hadoop/SerialUtils.hh:
+ * 29-63) so Hadoop sees a failed task. */
+const char *hgm_last_error(hgm_ctx *ctx);
+
+/* ---- job state ---------------------------------------------------------------------- */
+
+/* Install the k x d FP32 centroid table (row-major, host memory) for the following map
+ * calls and zero the partial sums.  Stands for what a Mapper constructor reads from the
+ * JobConf (c++/pipes/impl/HadoopPipes.cc:801 createMapper; JobConf access Pipes.hh:46-54).
+ * Builds the kernel-side index (cell table for d == 2) on the device. */
+int hgm_set_centroids(hgm_ctx *ctx, const float *centroids, int32_t k, int32_t d);
+
+/* Force a kernel family (tests and profiling); HGM_EINVAL if the shape does not fit it. */
+int hgm_set_kernel(hgm_ctx *ctx, int32_t kernel);
+/* Which family the last map call actually ran (one of HGM_KERNEL_*). */
+int hgm_last_kernel(hgm_ctx *ctx, int32_t *kernel);
+
+/* ---- the map task ------------------------------------------------------------------- */
+
+/* One map task over one input split held in HOST memory: stage to HBM through pinned
+ * buffers (async, chunked, overlapped with the kernel), decode records on the device,
+ * assign every point to its nearest centroid and leave the combiner's output.
+ *   sums_kxd[k*d]  FP64 per-cluster coordinate sums      (required)
+ *   counts_k[k]    int64 per-cluster point counts        (required)
+ *   assign_or_null int32 cluster index per point, or NULL
+ *   n_points_out   number of points decoded, or NULL
+ * Replaces, for a whole split at once: Mapper::map per record (Pipes.hh:158-161, called
+ * from HadoopPipes.cc:884-885), the CombineRunner buffer (HadoopPipes.cc:660-706) and the
+ * combiner Reducer::reduce (Pipes.hh:166-169, called from HadoopPipes.cc:700-702).
+ * Results are for THIS split only (the ctx partials are reset first). */
+int hgm_map_split(hgm_ctx *ctx, const void *host_bytes, size_t nbytes, int32_t fmt,
+                  double *sums_kxd, int64_t *counts_k, int32_t *assign_or_null,
+                  int64_t *n_points_out);
+
+/* Same, reading the split from a local file: the C++ RecordReader route
+ * (hadoop.pipes.java.recordreader=false; HadoopPipes.cc:793-799, example
+ * examples/pipes/impl/wordcount-nopipe.cc:67-113; FileSplit = path, start, length,
+ * mapred/FileSplit.java:81-85).  length < 0 means "to end of file". */
+int hgm_map_file(hgm_ctx *ctx, const char *path, int64_t offset, int64_t length, int32_t fmt,
+                 double *sums_kxd, int64_t *counts_k, int32_t *assign_or_null,
+                 int64_t *n_points_out);
+
+/* ---- device-resident splits (iterations >= 2 of a job, and the kernel-only bench) ---- */
+
+/* Map n points already in HBM (row-major FP32, 8-byte aligned at least) and ADD the
+ * result into the ctx's device partials.  Asynchronous on the ctx stream.
+ * d_assign_or_null is a device pointer to n int32, or NULL. */
+int hgm_map_device(hgm_ctx *ctx, const float *d_points, int64_t n_points,
+                   int32_t *d_assign_or_null);
+/* Zero the device partials (asynchronous). */
+int hgm_reset_partials(hgm_ctx *ctx);
+/* Copy the device partials to host memory (synchronises the ctx stream). */
+int hgm_read_partials(hgm_ctx *ctx, double *sums_kxd, int64_t *counts_k);
+/* Device addresses of the partials, laid out [k*d doubles][k int64] contiguously, for a
+ * caller that runs its own collective (torch.distributed) on them. */
+int hgm_partials_device(hgm_ctx *ctx, double **d_sums, int64_t **d_counts);
+/* Wait for everything queued on the ctx stream. */
+int hgm_sync(hgm_ctx *ctx);
+/* The ctx's compute stream as a cudaStream_t, so a host that has its own CUDA binding can
+ * order work or record events against the map kernels (bench.py times with CUDA events
+ * on exactly this stream). */
+int hgm_stream(hgm_ctx *ctx, void **cuda_stream);
+/* Device time of the last map call's kernels in milliseconds (CUDA events on the ctx
+ * stream; valid after hgm_sync / hgm_read_partials), and how many kernels it launched. */
+int hgm_last_map_ms(hgm_ctx *ctx, float *ms, int32_t *launches);
+/* Total kernels this ctx has launched since hgm_open. */
+int hgm_launch_count(hgm_ctx *ctx, int64_t *launches);
+
+/* Device / pinned-host memory for hosts that have no CUDA runtime of their own (JNI). */
+int hgm_device_alloc(hgm_ctx *ctx, size_t nbytes, void **d_ptr);
+int hgm_device_free(hgm_ctx *ctx, void *d_ptr);
+int hgm_host_alloc(hgm_ctx *ctx, size_t nbytes, void **h_ptr);
+int hgm_host_free(hgm_ctx *ctx, void *h_ptr);
+int hgm_memcpy_h2d(hgm_ctx *ctx, void *d_dst, const void *h_src, size_t nbytes);
+int hgm_memcpy_d2h(hgm_ctx *ctx, void *h_dst, const void *d_src, size_t nbytes);
+
+/* ---- multi-GPU: one ctx per device, partials combined over NVLink -------------------- */
+
+/* Replaces the intra-box part of the map->reduce shuffle of per-task partial records
+ * (mapred/TaskTracker.java:4050 MapOutputServlet) by ONE sum-allreduce of the
+ * [k*d] FP64 sums + [k] int64 counts across the GPU slots of a box.
+ * hgm_comm_id fills 128 bytes on rank 0, which the host distributes (JobConf / file /
+ * torch.distributed); every rank then calls hgm_comm_init and, per iteration,
+ * hgm_allreduce_partials.  NCCL is loaded with dlopen at hgm_comm_id/hgm_comm_init time;
+ * HGM_ENCCL if it is absent. */
+int hgm_comm_id(void *id128);
+int hgm_comm_init(hgm_ctx *ctx, int32_t n_ranks, int32_t rank, const void *id128);
+int hgm_allreduce_partials(hgm_ctx *ctx);
+
+/* ---- synthetic workload of the benchmark -------------------- */
+
+/* Integer-hash mixture-of-k-blobs generator; bit-identical on host and device.
+ * Not part of the reference (it publishes no workload); used by bench.py and tests. */
+int hgm_synth_centres(uint64_t seed, int32_t k, int32_t d, float *centres_out);
+int hgm_synth_perturb(uint64_t seed, int32_t k, int32_t d, const float *centres,
+                      float *centroids_out);
+int hgm_synth_points_host(uint64_t seed, int64_t first, int64_t n, int32_t d, int32_t k,
+                          const float *centres, float *points_out);
+int hgm_synth_points_device(hgm_ctx *ctx, uint64_t seed, int64_t first, int64_t n, int32_t d,
+                            int32_t k, const float *centres_host, float *d_points_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* HGPUMAP_H */
