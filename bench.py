@@ -192,16 +192,24 @@ class ClockSampler:
 
     def _pump(self):
         for line in self.proc.stdout:
-            self.rows.append(line.strip())
+            self.rows.append((time.perf_counter(), line.strip()))
 
-    def stop(self):
+    def wait_first(self, timeout=5.0):
+        t0 = time.perf_counter()
+        while self.proc and not self.rows and time.perf_counter() - t0 < timeout:
+            time.sleep(0.02)
+
+    def stop(self, t_lo=None, t_hi=None):
+        """Summarise the samples taken in [t_lo, t_hi] (host perf_counter times)."""
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
         self.thread.join(timeout=2)
         sm, mx, reasons = [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for row in self.rows:
+        for stamp, row in self.rows:
+            if (t_lo is not None and stamp < t_lo) or (t_hi is not None and stamp > t_hi + 0.05):
+                continue
             parts = [p.strip() for p in row.split(",")]
             if len(parts) != 6:
                 continue
@@ -285,10 +293,19 @@ def run_ours(args):
     k_a = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     k_b = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    launches0 = slot.launch_count()
-    barrier()
     if rank == 0:
         sampler.start()
+        sampler.wait_first()
+    # The K timed steps last only milliseconds, less than nvidia-smi's sampling period, so
+    # the clocks are sampled over >= 1 s of the identical load run back to back with (and
+    # including) the timed region; these extra steps are untimed warm-up.
+    t_load0 = time.perf_counter()
+    while time.perf_counter() - t_load0 < 1.0:
+        for _ in range(8):
+            step()
+        slot.sync()
+    launches0 = slot.launch_count()
+    barrier()
     ev0.record(stream)
     for i in range(args.steps):
         slot.reset_partials()
@@ -300,7 +317,7 @@ def run_ours(args):
     ev1.record(stream)
     slot.sync()
     barrier()
-    clocks = sampler.stop() if rank == 0 else None
+    clocks = sampler.stop(t_load0 + 0.2, time.perf_counter()) if rank == 0 else None
     launches = slot.launch_count() - launches0
     elapsed_ms = ev0.elapsed_time(ev1)
     kernel_ms = statistics.mean(a.elapsed_time(b) for a, b in zip(k_a, k_b))
