@@ -22,20 +22,32 @@
 // has a strictly larger COMPUTED distance than c0 everywhere in the cell and can never be a
 // minimiser of the scan, let alone its lowest-index one.
 //
-// Combiner: per tile of 8192 points a counting sort by cluster in shared memory (one native
+// Combiner: per tile of 4096 points a counting sort by cluster in shared memory (one native
 // integer ATOMS per point gives the rank; shared FP32/FP64 atomic adds are CAS loops on
 // sm_100), then each cluster's contiguous run is summed in FP64 by its owner threads.  The
 // per-CTA FP64 partials leave the SM once, as k*3 RED.ADD.F64/U64 to global.
+#include <stdlib.h>
+
 #include "hgm_internal.h"
 
 namespace hgm {
 
 namespace {
 
-constexpr int kThreads = 512;
-constexpr int kPPT = 16;                    // points per thread per tile
-constexpr int kTile = kThreads * kPPT;      // 8192 points = 64 KB of float2
 constexpr int kMaxK = 1024;
+constexpr int kPPT = 8;  // points per thread per tile
+
+// Shape of the map kernel: kGroups independent thread groups of kGroupThreads per CTA, each
+// working on tiles of kGroupThreads * kPPT points; kRegPrefetch keeps the next tile's loads
+// in registers, otherwise the next tile is pulled into L2 with prefetch instructions.
+template <int kGroupsT, int kGroupThreadsT, bool kRegPrefetchT>
+struct Shape {
+  static constexpr int kGroups = kGroupsT;
+  static constexpr int kGroupThreads = kGroupThreadsT;
+  static constexpr int kThreads = kGroupsT * kGroupThreadsT;
+  static constexpr int kTile = kGroupThreadsT * kPPT;
+  static constexpr bool kRegPrefetch = kRegPrefetchT;
+};
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
@@ -132,7 +144,9 @@ __global__ void __launch_bounds__(256) grid2d_build_kernel(const float *__restri
       ++cnt;
     }
   }
-  if (cnt == 1) {
+  if (ix == g.G - 1 || iy == g.G - 1) {
+    table[cell] = kCellBrute;  // the kernel clamps everything outside the grid onto this border
+  } else if (cnt == 1) {
     table[cell] = (uint16_t)c0;
   } else if (cnt <= kMaxCand) {
     table[cell] = (uint16_t)(kCellMulti | cnt);
@@ -143,37 +157,38 @@ __global__ void __launch_bounds__(256) grid2d_build_kernel(const float *__restri
 }
 
 // ---- the map kernel ---------------------------------------------------------------------
-struct Smem {
-  uint16_t *table;     // G*G
-  float2 *sorted;      // kTile
-  float2 *cent;        // k (padded to even)
-  int *hist;           // k
-  int *offs;           // k
-  double *acc;         // 2k
-  long long *cnt;      // k
-  uint64_t *bar;
-};
-
+// One persistent CTA per SM made of independent thread groups.  The groups share the cell
+// table and the centroids (read-only after the prologue) and nothing else: each owns its
+// tiles, its sort buffer, histogram and FP64 partials, and synchronises on its own named
+// barrier, so one group's scatter/sum phases overlap another's load/lookup phase.
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
 
-__device__ __forceinline__ Smem carve(unsigned char *base, int G, int k) {
-  Smem s;
-  size_t o = 0;
-  s.table = reinterpret_cast<uint16_t *>(base + o); o += align16((size_t)G * G * 2);
-  s.sorted = reinterpret_cast<float2 *>(base + o);  o += (size_t)kTile * 8;
-  s.cent = reinterpret_cast<float2 *>(base + o);    o += align16((size_t)k * 8);
-  s.acc = reinterpret_cast<double *>(base + o);     o += (size_t)k * 16;
-  s.cnt = reinterpret_cast<long long *>(base + o);  o += (size_t)k * 8;
-  s.hist = reinterpret_cast<int *>(base + o);       o += align16((size_t)k * 4);
-  s.offs = reinterpret_cast<int *>(base + o);       o += align16((size_t)k * 4);
-  s.bar = reinterpret_cast<uint64_t *>(base + o);
-  return s;
+// per-group shared memory: [sorted float2 tile][acc 2k f64][cnt k i64][hist k i32][offs k i32][qcount]
+__host__ __device__ inline size_t group_bytes(int tile, int k) {
+  return (size_t)tile * 8 + (size_t)k * 16 + (size_t)k * 8 + 2 * align16((size_t)k * 4) + 16;
+}
+__host__ __device__ inline size_t shared_head_bytes(int G, int k) {
+  return align16((size_t)G * G * 2) + align16((size_t)k * 8) + 16;
 }
 
-// nearest centroid of one point given its cell entry; exact scan over the candidates
-__device__ __forceinline__ int resolve_slow(float x, float y, uint32_t entry, uint32_t cell,
-                                            const float2 *cent_s, int k,
-                                            const uint16_t *__restrict__ cand) {
+__device__ __forceinline__ void group_sync(int group, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(group + 1), "r"(nthreads) : "memory");
+}
+
+// cell entry of a point: one FMA per axis lands RN(x*s)+b in the mantissa; the unsigned min
+// folds every out-of-range / NaN / inf value onto the last row or column, which the builder
+// marks "scan everything".
+__device__ __forceinline__ uint32_t cell_of(float x, float y, const Grid2D &g) {
+  const uint32_t ux = min(__float_as_uint(__fmaf_rn(x, g.sx, g.Bx)) - kMagicBits, (uint32_t)(g.G - 1));
+  const uint32_t uy = min(__float_as_uint(__fmaf_rn(y, g.sy, g.By)) - kMagicBits, (uint32_t)(g.G - 1));
+  return uy * (uint32_t)g.G + ux;
+}
+
+// exact scan of one point over its cell's candidates (or over all k): ascending index,
+// strict '<' from (+inf, 0) -- the reference scan restricted to a superset of its winners
+__device__ __noinline__ int resolve_slow(float x, float y, uint32_t entry, uint32_t cell,
+                                         const float2 *cent_s, int k,
+                                         const uint16_t *__restrict__ cand) {
   float best = INFINITY;
   int arg = 0;
   if (entry == kCellBrute) {
@@ -197,67 +212,88 @@ __device__ __forceinline__ int resolve_slow(float x, float y, uint32_t entry, ui
   return arg;
 }
 
-template <bool kVec4, bool kAssign>
-__global__ void __launch_bounds__(kThreads, 1)
+constexpr uint32_t kKeyNone = 0xFFFFFFFFu;    // no point in this slot (ragged last tile)
+constexpr uint32_t kKeyQueued = 0x80000000u;  // | queue slot: resolved in phase A2
+
+template <class S, bool kVec4, bool kAssign>
+__global__ void __launch_bounds__(S::kThreads, 1)
     grid2d_map_kernel(const float *__restrict__ pts, long long n, const float *__restrict__ cent,
                       int k, Grid2D g, const uint16_t *__restrict__ table,
                       const uint16_t *__restrict__ cand, double *__restrict__ g_sums,
                       unsigned long long *__restrict__ g_counts, int32_t *__restrict__ assign) {
+  constexpr int kGT = S::kGroupThreads;
+  constexpr int kTile = S::kTile;
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  const Smem s = carve(smem_raw, g.G, k);
-  const int t = threadIdx.x;
-  const int G = g.G;
+  const int group = threadIdx.x / kGT;
+  const int t = threadIdx.x % kGT;  // thread within the group
+  const int lane = threadIdx.x & 31;
 
-  // stage the cell table and the centroids with TMA bulk copies
-  const uint32_t table_bytes = (uint32_t)align16((size_t)G * G * 2);
+  // carve shared memory (pointers computed, not looked up: no local-memory struct)
+  uint16_t *const table_s = reinterpret_cast<uint16_t *>(smem_raw);
+  float2 *const cent_s = reinterpret_cast<float2 *>(smem_raw + align16((size_t)g.G * g.G * 2));
+  uint64_t *const bar = reinterpret_cast<uint64_t *>(reinterpret_cast<unsigned char *>(cent_s) + align16((size_t)k * 8));
+  unsigned char *const gb = smem_raw + shared_head_bytes(g.G, k) + (size_t)group * group_bytes(kTile, k);
+  float2 *const sorted = reinterpret_cast<float2 *>(gb);
+  double *const acc = reinterpret_cast<double *>(gb + (size_t)kTile * 8);
+  long long *const cnt = reinterpret_cast<long long *>(acc + 2 * k);
+  int *const hist = reinterpret_cast<int *>(cnt + k);
+  int *const offs = reinterpret_cast<int *>(reinterpret_cast<unsigned char *>(hist) + align16((size_t)k * 4));
+  int *const qcount = reinterpret_cast<int *>(reinterpret_cast<unsigned char *>(offs) + align16((size_t)k * 4));
+
+  // stage the cell table and the centroids with TMA bulk copies (SASS: UBLKCP)
+  const uint32_t table_bytes = (uint32_t)align16((size_t)g.G * g.G * 2);
   const uint32_t cent_bytes = (uint32_t)align16((size_t)k * 8);
-  if (t == 0) mbar_init(s.bar, 1);
+  if (threadIdx.x == 0) mbar_init(bar, 1);
   __syncthreads();
-  if (t == 0) {
-    mbar_expect_tx(s.bar, table_bytes + cent_bytes);
+  if (threadIdx.x == 0) {
+    mbar_expect_tx(bar, table_bytes + cent_bytes);
     for (uint32_t o = 0; o < table_bytes; o += 32768) {
       const uint32_t sz = table_bytes - o < 32768 ? table_bytes - o : 32768;
-      tma_bulk_g2s(reinterpret_cast<unsigned char *>(s.table) + o,
-                   reinterpret_cast<const unsigned char *>(table) + o, sz, s.bar);
+      tma_bulk_g2s(reinterpret_cast<unsigned char *>(table_s) + o,
+                   reinterpret_cast<const unsigned char *>(table) + o, sz, bar);
     }
-    tma_bulk_g2s(s.cent, cent, cent_bytes, s.bar);
+    tma_bulk_g2s(cent_s, cent, cent_bytes, bar);
   }
-  for (int c = t; c < k; c += kThreads) {
-    s.hist[c] = 0;
-    s.acc[2 * c] = 0.0;
-    s.acc[2 * c + 1] = 0.0;
-    s.cnt[c] = 0;
+  for (int c = t; c < k; c += kGT) {
+    hist[c] = 0;
+    acc[2 * c] = 0.0;
+    acc[2 * c + 1] = 0.0;
+    cnt[c] = 0;
   }
-  mbar_wait(s.bar, 0);
+  if (t == 0) *qcount = 0;
+  mbar_wait(bar, 0);
   __syncthreads();
 
-  // threads per cluster in the segment-sum phase (power of two, <= 32)
+  // threads per cluster in the run-sum phase (power of two, <= 32)
   int tpc = 1;
-  while (tpc < 32 && tpc * 2 * k <= kThreads) tpc *= 2;
-  const int groups = kThreads / tpc;
+  while (tpc < 32 && tpc * 2 * k <= kGT) tpc *= 2;
+  const int groups_of_tpc = kGT / tpc;
 
   const long long ntiles = (n + kTile - 1) / kTile;
+  const long long tile_stride = (long long)gridDim.x * S::kGroups;
+  const long long tile0 = (long long)blockIdx.x * S::kGroups + group;
 
-  // raw tile loads: thread t owns the point pairs (i*kThreads + t), i = 0..kPPT/2-1
+  // raw tile loads: thread t owns the point pairs (i*kGT + t), i = 0..kPPT/2-1
   auto load_tile = [&](long long tile, float4 (&buf)[kPPT / 2]) {
     const long long base = tile * kTile;
+    const bool full = base + kTile <= n;
 #pragma unroll
     for (int i = 0; i < kPPT / 2; ++i) {
-      const long long p = base + 2ll * (i * kThreads + t);
+      const long long p = base + 2ll * (i * kGT + t);
       float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
       if (kVec4) {
-        if (p + 1 < n) {
+        if (full || p + 1 < n) {
           v = __ldcs(reinterpret_cast<const float4 *>(pts + 2 * p));
         } else if (p < n) {
           const float2 h = __ldcs(reinterpret_cast<const float2 *>(pts + 2 * p));
           v.x = h.x; v.y = h.y;
         }
       } else {
-        if (p < n) {
+        if (full || p < n) {
           const float2 h = __ldcs(reinterpret_cast<const float2 *>(pts + 2 * p));
           v.x = h.x; v.y = h.y;
         }
-        if (p + 1 < n) {
+        if (full || p + 1 < n) {
           const float2 h = __ldcs(reinterpret_cast<const float2 *>(pts + 2 * p + 2));
           v.z = h.x; v.w = h.y;
         }
@@ -265,67 +301,105 @@ __global__ void __launch_bounds__(kThreads, 1)
       buf[i] = v;
     }
   };
+  // pull a whole tile into L2 ahead of use: one 128-byte line per prefetch
+  auto prefetch_tile = [&](long long tile) {
+    const char *b = reinterpret_cast<const char *>(pts + 2 * tile * kTile);
+    const long long lim = 8 * n;
+    for (int o = t * 128; o < kTile * 8; o += kGT * 128)
+      if (8 * tile * kTile + o < lim) asm volatile("prefetch.global.L2 [%0];" ::"l"(b + o));
+  };
 
-  float4 nxt[kPPT / 2];
-  if ((long long)blockIdx.x < ntiles) load_tile(blockIdx.x, nxt);
-  for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+  float4 buf[kPPT / 2];
+  if (S::kRegPrefetch) {
+    if (tile0 < ntiles) load_tile(tile0, buf);
+  } else {
+    if (tile0 < ntiles) prefetch_tile(tile0);
+  }
+  for (long long tile = tile0; tile < ntiles; tile += tile_stride) {
     const long long base = tile * kTile;  // first point of the tile (even)
+    const int live = (int)min((long long)kTile, n - base);  // points in this tile
     float xs[kPPT], ys[kPPT];
-    uint32_t key[kPPT];  // cluster | rank << 16, or 0xFFFFFFFF for "no point"
+    uint32_t key[kPPT];  // cluster | rank << 16
 
-    // ---- phase A: cell lookup, exact resolve, rank (loads were issued a tile ahead) ------
+    if (!S::kRegPrefetch) {
+      load_tile(tile, buf);
+      if (tile + tile_stride < ntiles) prefetch_tile(tile + tile_stride);
+    }
 #pragma unroll
     for (int i = 0; i < kPPT / 2; ++i) {
-      xs[2 * i] = nxt[i].x; ys[2 * i] = nxt[i].y; xs[2 * i + 1] = nxt[i].z; ys[2 * i + 1] = nxt[i].w;
+      xs[2 * i] = buf[i].x; ys[2 * i] = buf[i].y; xs[2 * i + 1] = buf[i].z; ys[2 * i + 1] = buf[i].w;
     }
-    if (tile + gridDim.x < ntiles) load_tile(tile + gridDim.x, nxt);
-    uint32_t entry[kPPT];
-    uint32_t cellv[kPPT];
+    if (S::kRegPrefetch && tile + tile_stride < ntiles) load_tile(tile + tile_stride, buf);
+
+    // ---- phase A1: cell lookup; single-candidate points get their rank at once, the rest
+    // are queued (warp-aggregated slot allocation) for dense resolution in A2 -----------
 #pragma unroll
     for (int i = 0; i < kPPT; ++i) {
-      const uint32_t ux = __float_as_uint(__fmaf_rn(xs[i], g.sx, g.Bx)) - kMagicBits;
-      const uint32_t uy = __float_as_uint(__fmaf_rn(ys[i], g.sy, g.By)) - kMagicBits;
-      const bool inside = (ux < (uint32_t)G) && (uy < (uint32_t)G);
-      const uint32_t cell = inside ? uy * G + ux : 0u;
-      cellv[i] = cell;
-      const uint32_t e = s.table[cell];
-      entry[i] = inside ? e : (uint32_t)kCellBrute;
-    }
-#pragma unroll
-    for (int i = 0; i < kPPT; ++i) {
-      const long long p = base + 2ll * ((i >> 1) * kThreads + t) + (i & 1);
-      int c = (int)entry[i];
-      if (entry[i] >= kCellMulti) c = resolve_slow(xs[i], ys[i], entry[i], cellv[i], s.cent, k, cand);
-      if (p < n) {
-        const int r = atomicAdd(&s.hist[c], 1);
-        key[i] = (uint32_t)c | ((uint32_t)r << 16);
+      const int local = 2 * ((i >> 1) * kGT + t) + (i & 1);  // index within the tile
+      const uint32_t e = table_s[cell_of(xs[i], ys[i], g)];
+      const bool valid = local < live;
+      const bool slow = valid && e >= kCellMulti;
+      const uint32_t m = __ballot_sync(0xFFFFFFFFu, slow);
+      if (valid && !slow) {
+        const int r = atomicAdd(&hist[e], 1);
+        key[i] = e | ((uint32_t)r << 16);
       } else {
-        key[i] = 0xFFFFFFFFu;
+        key[i] = kKeyNone;
+      }
+      if (m) {
+        int qbase = 0;
+        if (lane == 0) qbase = atomicAdd(qcount, __popc(m));
+        qbase = __shfl_sync(0xFFFFFFFFu, qbase, 0);
+        if (slow) {
+          const int q = qbase + __popc(m & ((1u << lane) - 1));
+          sorted[q] = make_float2(xs[i], ys[i]);
+          key[i] = kKeyQueued | (uint32_t)q;
+        }
       }
     }
+    group_sync(group, kGT);
+
+    // ---- phase A2: the queued points, one per thread, exact candidate scan --------------
+    const int nq = *qcount;
+    if (nq) {
+      for (int q = t; q < nq; q += kGT) {
+        const float2 v = sorted[q];
+        const uint32_t cell = cell_of(v.x, v.y, g);
+        const int c = resolve_slow(v.x, v.y, table_s[cell], cell, cent_s, k, cand);
+        const int r = atomicAdd(&hist[c], 1);
+        sorted[q].x = __uint_as_float((uint32_t)c | ((uint32_t)r << 16));
+      }
+      group_sync(group, kGT);
+#pragma unroll
+      for (int i = 0; i < kPPT; ++i)
+        if (key[i] != kKeyNone && (key[i] & kKeyQueued)) key[i] = __float_as_uint(sorted[key[i] & 0xFFFF].x);
+      if (t == 0) *qcount = 0;
+      group_sync(group, kGT);  // keys are out of the queue before phase C overwrites it
+    }
+
     if (kAssign) {
       const bool assign8 = (reinterpret_cast<uintptr_t>(assign) & 7) == 0;
 #pragma unroll
       for (int i = 0; i < kPPT / 2; ++i) {
-        const long long p = base + 2ll * (i * kThreads + t);
-        if (p + 1 < n && assign8) {
+        const int local = 2 * (i * kGT + t);
+        const long long p = base + local;
+        if (local + 1 < live && assign8) {
           *reinterpret_cast<int2 *>(assign + p) =
               make_int2((int)(key[2 * i] & 0xFFFF), (int)(key[2 * i + 1] & 0xFFFF));
         } else {
-          if (p < n) assign[p] = (int)(key[2 * i] & 0xFFFF);
-          if (p + 1 < n) assign[p + 1] = (int)(key[2 * i + 1] & 0xFFFF);
+          if (local < live) assign[p] = (int)(key[2 * i] & 0xFFFF);
+          if (local + 1 < live) assign[p + 1] = (int)(key[2 * i + 1] & 0xFFFF);
         }
       }
     }
-    __syncthreads();
 
-    // ---- phase B: exclusive scan of the tile histogram (warp 0) ------------------------
+    // ---- phase B: exclusive scan of the tile histogram (first warp of the group) ---------
     if (t < 32) {
       const int per = (k + 31) / 32;
       const int lo = t * per;
       int sum = 0;
       for (int j = 0; j < per; ++j)
-        if (lo + j < k) sum += s.hist[lo + j];
+        if (lo + j < k) sum += hist[lo + j];
       int incl = sum;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
@@ -334,66 +408,113 @@ __global__ void __launch_bounds__(kThreads, 1)
       }
       int run = incl - sum;
       for (int j = 0; j < per; ++j)
-        if (lo + j < k) { s.offs[lo + j] = run; run += s.hist[lo + j]; }
+        if (lo + j < k) { offs[lo + j] = run; run += hist[lo + j]; }
     }
-    __syncthreads();
+    group_sync(group, kGT);
 
     // ---- phase C: scatter the points into cluster order --------------------------------
 #pragma unroll
     for (int i = 0; i < kPPT; ++i) {
-      if (key[i] != 0xFFFFFFFFu) {
+      if (key[i] != kKeyNone) {
         const int c = key[i] & 0xFFFF;
-        s.sorted[s.offs[c] + (int)(key[i] >> 16)] = make_float2(xs[i], ys[i]);
+        sorted[offs[c] + (int)(key[i] >> 16)] = make_float2(xs[i], ys[i]);
       }
     }
-    __syncthreads();
+    group_sync(group, kGT);
 
-    // ---- phase D: FP64 run sums, owner threads fold them into the CTA partials ---------
+    // ---- phase D: FP64 run sums, owner lanes fold them into the group partials and clear
+    // the histogram for the next tile ------------------------------------------------------
     {
       const int sub = t & (tpc - 1);
-      for (int c0 = 0; c0 < k; c0 += groups) {  // uniform trip count: the shuffles need all lanes
+      for (int c0 = 0; c0 < k; c0 += groups_of_tpc) {  // uniform trip count: shuffles need all lanes
         const int c = c0 + t / tpc;
-        const bool live = c < k;
-        const int start = live ? s.offs[c] : 0, m = live ? s.hist[c] : 0;
+        const bool on = c < k;
+        const int start = on ? offs[c] : 0, m = on ? hist[c] : 0;
         double ax = 0.0, ay = 0.0;
-        for (int j = sub; j < m; j += tpc) {
-          const float2 v = s.sorted[start + j];
-          ax += (double)v.x;
-          ay += (double)v.y;
+        int j = sub;
+        for (; j + tpc < m; j += 2 * tpc) {  // two independent loads per trip
+          const float2 v0 = sorted[start + j];
+          const float2 v1 = sorted[start + j + tpc];
+          ax += (double)v0.x; ay += (double)v0.y;
+          ax += (double)v1.x; ay += (double)v1.y;
+        }
+        if (j < m) {
+          const float2 v = sorted[start + j];
+          ax += (double)v.x; ay += (double)v.y;
         }
         for (int o = tpc >> 1; o > 0; o >>= 1) {
           ax += __shfl_xor_sync(0xFFFFFFFFu, ax, o);
           ay += __shfl_xor_sync(0xFFFFFFFFu, ay, o);
         }
-        if (live && sub == 0) {
-          s.acc[2 * c] += ax;
-          s.acc[2 * c + 1] += ay;
-          s.cnt[c] += m;
+        if (on && sub == 0) {
+          acc[2 * c] += ax;
+          acc[2 * c + 1] += ay;
+          cnt[c] += m;
+          hist[c] = 0;  // every lane of this cluster has read m (the shuffles above)
         }
       }
     }
-    __syncthreads();
-    for (int c = t; c < k; c += kThreads) s.hist[c] = 0;
-    // the next tile's phase A only touches hist after its loads; the barrier that follows
-    // phase A orders this zeroing against phase B.  It must not race the atomics though:
-    __syncthreads();
+    group_sync(group, kGT);  // sorted/hist are free for the next tile
   }
 
-  // ---- CTA partials -> global (one RED per value per CTA) ------------------------------
-  for (int c = t; c < k; c += kThreads) {
-    if (s.cnt[c] != 0) {
-      atomicAdd(&g_sums[2 * c], s.acc[2 * c]);
-      atomicAdd(&g_sums[2 * c + 1], s.acc[2 * c + 1]);
-      atomicAdd(&g_counts[c], (unsigned long long)s.cnt[c]);
+  // ---- group partials -> global (one RED per value per group) ----------------------------
+  for (int c = t; c < k; c += kGT) {
+    if (cnt[c] != 0) {
+      atomicAdd(&g_sums[2 * c], acc[2 * c]);
+      atomicAdd(&g_sums[2 * c + 1], acc[2 * c + 1]);
+      atomicAdd(&g_counts[c], (unsigned long long)cnt[c]);
     }
   }
 }
 
+using ShapeA = Shape<2, 512, false>;  // 1024 threads, L2 prefetch
+using ShapeB = Shape<2, 512, true>;   // 1024 threads, register prefetch
+using ShapeC = Shape<4, 256, false>;  // 1024 threads, four groups
+using ShapeD = Shape<3, 256, true>;   // 768 threads, register prefetch
+
+int active_variant() {
+  static const int variant = [] {
+    const char *v = getenv("HGM_GRID2D_VARIANT");  // tuning knob; the default is the measured best
+    return v ? atoi(v) : 0;
+  }();
+  return variant;
+}
+template <class S>
+size_t shape_smem_bytes(int G, int k) {
+  return shared_head_bytes(G, k) + S::kGroups * group_bytes(S::kTile, k);
+}
+
+template <class S>
+cudaError_t launch_shape(const float *d_pts, int64_t n, const float *d_cent, int k, const Grid2D &g,
+                         const uint16_t *d_table, const uint16_t *d_cand, double *d_sums,
+                         unsigned long long *d_counts, int32_t *d_assign, int sm_count,
+                         size_t smem_optin, cudaStream_t s) {
+  const size_t smem = shared_head_bytes(g.G, k) + S::kGroups * group_bytes(S::kTile, k);
+  if (smem > smem_optin) return cudaErrorInvalidValue;
+  const bool vec4 = (reinterpret_cast<uintptr_t>(d_pts) & 15) == 0;
+  const bool asg = d_assign != nullptr;
+  auto kern = vec4 ? (asg ? grid2d_map_kernel<S, true, true> : grid2d_map_kernel<S, true, false>)
+                   : (asg ? grid2d_map_kernel<S, false, true> : grid2d_map_kernel<S, false, false>);
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  const long long ntiles = (n + S::kTile - 1) / S::kTile;
+  const long long want = (ntiles + S::kGroups - 1) / S::kGroups;
+  const int grid = (int)(want < sm_count ? want : sm_count);
+  kern<<<grid, S::kThreads, smem, s>>>(d_pts, (long long)n, d_cent, k, g, d_table, d_cand, d_sums,
+                                       d_counts, d_assign);
+  return cudaGetLastError();
+}
+
 }  // namespace
 
+// shared memory the map kernel needs for a G x G table and k clusters; plan_grid2d sizes G by it
 size_t grid2d_map_smem_bytes(int G, int k) {
-  return align16((size_t)G * G * 2) + (size_t)kTile * 8 + align16((size_t)k * 8) + (size_t)k * 16 +
-         (size_t)k * 8 + 2 * align16((size_t)k * 4) + 16;
+  switch (active_variant()) {
+    case 1: return shape_smem_bytes<ShapeB>(G, k);
+    case 2: return shape_smem_bytes<ShapeC>(G, k);
+    case 3: return shape_smem_bytes<ShapeD>(G, k);
+    default: return shape_smem_bytes<ShapeA>(G, k);
+  }
 }
 
 cudaError_t launch_grid2d_build(const float *d_cent, int k, const Grid2D &g, uint16_t *d_table,
@@ -410,19 +531,14 @@ cudaError_t launch_grid2d_map(const float *d_pts, int64_t n, const float *d_cent
                               int sm_count, size_t smem_optin, cudaStream_t s) {
   if (n <= 0) return cudaSuccess;
   if (k > kMaxK) return cudaErrorInvalidValue;
-  const size_t smem = grid2d_map_smem_bytes(g.G, k);
-  if (smem > smem_optin) return cudaErrorInvalidValue;
-  const bool vec4 = (reinterpret_cast<uintptr_t>(d_pts) & 15) == 0;
-  const bool asg = d_assign != nullptr;
-  auto kern = vec4 ? (asg ? grid2d_map_kernel<true, true> : grid2d_map_kernel<true, false>)
-                   : (asg ? grid2d_map_kernel<false, true> : grid2d_map_kernel<false, false>);
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  if (e != cudaSuccess) return e;
-  const long long ntiles = (n + kTile - 1) / kTile;
-  const int grid = (int)(ntiles < sm_count ? ntiles : sm_count);
-  kern<<<grid, kThreads, smem, s>>>(d_pts, (long long)n, d_cent, k, g, d_table, d_cand, d_sums,
-                                    d_counts, d_assign);
-  return cudaGetLastError();
+#define HGM_ARGS d_pts, n, d_cent, k, g, d_table, d_cand, d_sums, d_counts, d_assign, sm_count, smem_optin, s
+  switch (active_variant()) {
+    case 1: return launch_shape<ShapeB>(HGM_ARGS);
+    case 2: return launch_shape<ShapeC>(HGM_ARGS);
+    case 3: return launch_shape<ShapeD>(HGM_ARGS);
+    default: return launch_shape<ShapeA>(HGM_ARGS);
+  }
+#undef HGM_ARGS
 }
 
 }  // namespace hgm

@@ -1,0 +1,305 @@
+// kmeans_pipes_gpu.cc -- the K-means GPU map task as a Hadoop Pipes program (the -gpubin).
+//
+// Submitted exactly like the reference expects (pipes/Submitter.java:419-420, 349-379):
+//   bin/hadoop pipes -cpubin kmeans-pipes-cpu -gpubin kmeans-pipes-gpu -input ... -output ...
+//        -jobconf kmeans.k=128,kmeans.d=2,kmeans.centroids=centroids.bin
+// and started by pipes/Application.java:156-194 as `kmeans-pipes-gpu <GPUDeviceId>`.
+// It is written against the Pipes C++ API only (hadoop/Pipes.hh), so it builds against the
+// reference's libhadooppipes.a as well as against this repository's runtime, and reaches
+// CUDA only through the C ABI of libhgpumap.so (include/hgpumap.h).
+//
+// Same record contract as the CPU program of the job (JobConf keys kmeans.k, kmeans.d,
+// kmeans.centroids, kmeans.input.format; map output key = decimal cluster id, value =
+// "count s0 s1 ..."), with one difference the protocol allows: the mapper buffers its
+// input, maps whole batches on the GPU and emits ALREADY COMBINED records from close(), so
+// createCombiner() returns NULL and the runtime's CombineRunner (HadoopPipes.cc:660-706)
+// never buffers a pair.  Records leave in the byte order of their keys, like a combiner
+// spill would emit them.
+//
+// Input routes:
+//   piped (hadoop.pipes.java.recordreader=true):  MAP_ITEM values are appended to a pinned
+//       batch; kmeans.input.format = binary (rows of d LE float32) | path (value names a
+//       file [\t offset \t length], the shipped NLineInputFormat config,
+//       conf/mapred-site.xml:13-22);
+//   C++ reader (=false): the FileSplit (mapred/FileSplit.java:81-85) is handed to
+//       hgm_map_file and read straight into pinned memory -- no per-record traffic at all.
+// There is no CPU fallback: any hgm_* failure throws HadoopUtils::Error and the task fails.
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <algorithm>
+#include <string>
+#include <vector>
+
+#include "hadoop/Pipes.hh"
+#include "hadoop/SerialUtils.hh"
+#include "hadoop/StringUtils.hh"
+#include "hadoop/TemplateFactory.hh"
+#include "hgpumap.h"
+
+static int g_device = 0;
+
+namespace {
+
+const std::string KMEANS = "KMEANS";
+
+void check(hgm_ctx *ctx, int rc, const char *what) {
+  if (rc != HGM_OK) throw HadoopUtils::Error(std::string(what) + ": " + hgm_last_error(ctx));
+}
+
+std::string partialToString(long long count, const double *sums, int d) {
+  char buf[64];
+  snprintf(buf, sizeof buf, "%lld", count);
+  std::string out(buf);
+  for (int j = 0; j < d; ++j) {
+    snprintf(buf, sizeof buf, " %.17g", sums[j]);
+    out += buf;
+  }
+  return out;
+}
+
+// FileSplit as Java serialises it: UTF8.writeString(path) = 2-byte BE length + bytes, then
+// two big-endian longs (mapred/FileSplit.java:81-85).  Also accepts the vint-length form the
+// reference's test fixture uses (test/.../pipes/WordCountInputFormat.java:42-44).
+struct Split {
+  std::string path;
+  int64_t start = 0, length = -1;
+};
+Split parseSplit(const std::string &raw) {
+  Split s;
+  const unsigned char *p = reinterpret_cast<const unsigned char *>(raw.data());
+  const size_t n = raw.size();
+  if (n >= 2) {
+    const size_t len = ((size_t)p[0] << 8) | p[1];
+    if (2 + len + 16 == n) {
+      s.path.assign(raw, 2, len);
+      auto be64 = [](const unsigned char *q) { int64_t v = 0; for (int i = 0; i < 8; ++i) v = (v << 8) | q[i]; return v; };
+      s.start = be64(p + 2 + len);
+      s.length = be64(p + 2 + len + 8);
+      return s;
+    }
+  }
+  HadoopUtils::StringInStream in(raw);
+  HadoopUtils::deserializeString(s.path, in);
+  return s;
+}
+std::string stripScheme(const std::string &uri) {  // "file:/x" -> "/x"
+  if (uri.compare(0, 5, "file:") == 0) {
+    std::string rest = uri.substr(5);
+    while (rest.size() > 1 && rest[0] == '/' && rest[1] == '/') rest.erase(0, 1);
+    return rest;
+  }
+  return uri;
+}
+
+}  // namespace
+
+class KMeansGpuMap : public HadoopPipes::Mapper {
+  HadoopPipes::MapContext *ctx_;
+  hgm_ctx *gpu_ = nullptr;
+  int k_, d_;
+  enum { BINARY, PATH, SPLIT } format_ = BINARY;
+  int fmt_code_ = HGM_FMT_F32LE;
+  std::vector<double> sums_, part_sums_;
+  std::vector<int64_t> counts_, part_counts_;
+  unsigned char *batch_ = nullptr;  // pinned
+  size_t batch_cap_ = 0, batch_used_ = 0;
+  int64_t points_ = 0;
+  HadoopPipes::TaskContext::Counter *pointsIn_, *gpuMicros_, *batches_;
+
+  void fold() {
+    for (size_t i = 0; i < sums_.size(); ++i) sums_[i] += part_sums_[i];
+    for (size_t i = 0; i < counts_.size(); ++i) counts_[i] += part_counts_[i];
+  }
+  void account(int64_t n) {
+    float ms = 0;
+    int32_t launches = 0;
+    hgm_last_map_ms(gpu_, &ms, &launches);
+    points_ += n;
+    ctx_->incrementCounter(pointsIn_, (uint64_t)n);
+    ctx_->incrementCounter(gpuMicros_, (uint64_t)(ms * 1000.0f));
+    ctx_->incrementCounter(batches_, 1);
+  }
+  void flush() {
+    if (batch_used_ == 0) return;
+    int64_t n = 0;
+    check(gpu_, hgm_map_split(gpu_, batch_, batch_used_, fmt_code_, part_sums_.data(), part_counts_.data(), nullptr, &n),
+          "hgm_map_split");
+    fold();
+    account(n);
+    batch_used_ = 0;
+  }
+  void mapFile(const std::string &path, int64_t off, int64_t len) {
+    int64_t n = 0;
+    check(gpu_, hgm_map_file(gpu_, path.c_str(), off, len, fmt_code_, part_sums_.data(), part_counts_.data(), nullptr, &n),
+          "hgm_map_file");
+    fold();
+    account(n);
+  }
+
+ public:
+  explicit KMeansGpuMap(HadoopPipes::MapContext &context) : ctx_(&context) {
+    const HadoopPipes::JobConf *conf = context.getJobConf();
+    k_ = conf->getInt("kmeans.k");
+    d_ = conf->getInt("kmeans.d");
+    HADOOP_ASSERT(k_ > 0 && d_ > 0, "kmeans.k and kmeans.d must be positive");
+    if (conf->hasKey("kmeans.input.format")) {
+      const std::string &f = conf->get("kmeans.input.format");
+      if (f == "path") format_ = PATH;
+      else if (f == "binary-be") fmt_code_ = HGM_FMT_F32BE;
+      else HADOOP_ASSERT(f == "binary", "kmeans.input.format " + f + " is not supported on a GPU slot");
+    }
+    if (conf->hasKey("hadoop.pipes.java.recordreader") && !conf->getBoolean("hadoop.pipes.java.recordreader"))
+      format_ = SPLIT;
+    if (conf->hasKey("kmeans.gpu.device")) g_device = conf->getInt("kmeans.gpu.device");
+
+    const std::string &cpath = conf->get("kmeans.centroids");
+    FILE *f = fopen(cpath.c_str(), "rb");
+    HADOOP_ASSERT(f != NULL, "cannot open centroid file " + cpath);
+    std::vector<float> cent((size_t)k_ * d_);
+    const size_t got = fread(cent.data(), sizeof(float), cent.size(), f);
+    fclose(f);
+    HADOOP_ASSERT(got == cent.size(), "centroid file " + cpath + " is shorter than k*d floats");
+
+    check(nullptr, hgm_open(g_device, &gpu_), "hgm_open");
+    check(gpu_, hgm_set_centroids(gpu_, cent.data(), k_, d_), "hgm_set_centroids");
+    sums_.assign((size_t)k_ * d_, 0.0);
+    part_sums_.assign((size_t)k_ * d_, 0.0);
+    counts_.assign(k_, 0);
+    part_counts_.assign(k_, 0);
+    if (format_ == BINARY) {
+      const size_t row = 4 * (size_t)d_;
+      batch_cap_ = std::max<size_t>(row, ((size_t(64) << 20) / row) * row);
+      void *p = nullptr;
+      check(gpu_, hgm_host_alloc(gpu_, batch_cap_, &p), "hgm_host_alloc");
+      batch_ = static_cast<unsigned char *>(p);
+    }
+    pointsIn_ = context.getCounter(KMEANS, "POINTS");
+    gpuMicros_ = context.getCounter(KMEANS, "GPU_MAP_MICROS");
+    batches_ = context.getCounter(KMEANS, "GPU_BATCHES");
+  }
+
+  ~KMeansGpuMap() {
+    if (gpu_) {
+      if (batch_) hgm_host_free(gpu_, batch_);
+      hgm_close(gpu_);
+    }
+  }
+
+  void map(HadoopPipes::MapContext &context) {
+    const std::string &v = context.getInputValue();
+    if (format_ == BINARY) {
+      HADOOP_ASSERT(v.size() % (4 * (size_t)d_) == 0, "binary record is not a whole number of rows");
+      size_t off = 0;
+      while (off < v.size()) {
+        if (batch_used_ == batch_cap_) flush();
+        const size_t take = std::min(v.size() - off, batch_cap_ - batch_used_);
+        memcpy(batch_ + batch_used_, v.data() + off, take);
+        batch_used_ += take;
+        off += take;
+      }
+    } else if (format_ == PATH) {
+      std::vector<std::string> parts = HadoopUtils::splitString(v, "\t");
+      HADOOP_ASSERT(parts.size() == 1 || parts.size() == 3, "path record must be file[\\toffset\\tlength]: " + v);
+      mapFile(stripScheme(parts[0]), parts.size() == 3 ? atoll(parts[1].c_str()) : 0,
+              parts.size() == 3 ? atoll(parts[2].c_str()) : -1);
+    } else {  // SPLIT: the reader hands over the split descriptor as the key
+      const Split s = parseSplit(context.getInputKey());
+      mapFile(stripScheme(s.path), s.start, s.length);
+    }
+  }
+
+  // emit the combined output of the whole task (HadoopPipes.cc:1007-1020 calls close() on
+  // the mapper before the uplink says DONE)
+  void close() {
+    flush();
+    std::vector<std::string> keys;
+    for (int c = 0; c < k_; ++c)
+      if (counts_[c] != 0) keys.push_back(HadoopUtils::toString(c));
+    std::sort(keys.begin(), keys.end());  // byte order of std::map<string,...> in CombineRunner
+    for (const std::string &key : keys) {
+      const int c = atoi(key.c_str());
+      ctx_->emit(key, partialToString((long long)counts_[c], &sums_[(size_t)c * d_], d_));
+    }
+  }
+};
+
+// Hands the mapper one record: the serialised split itself (C++ reader route,
+// HadoopPipes.cc:793-799, 874-882).
+class WholeSplitReader : public HadoopPipes::RecordReader {
+  std::string split_;
+  bool given_ = false;
+
+ public:
+  explicit WholeSplitReader(HadoopPipes::MapContext &context) : split_(context.getInputSplit()) {}
+  bool next(std::string &key, std::string &value) {
+    if (given_) return false;
+    key = split_;
+    value.clear();
+    given_ = true;
+    return true;
+  }
+  float getProgress() { return given_ ? 1.0f : 0.0f; }
+};
+
+// Reduce side = centroid update; identical to the CPU program's (it normally runs from the
+// -cpubin, pipes/PipesReducer.java:59-93 starts the child with runOnGPU=false).
+class KMeansReduce : public HadoopPipes::Reducer {
+  int d_;
+
+ public:
+  explicit KMeansReduce(HadoopPipes::TaskContext &context) : d_(context.getJobConf()->getInt("kmeans.d")) {}
+  void reduce(HadoopPipes::ReduceContext &context) {
+    long long count = 0;
+    std::vector<double> sums(d_, 0.0);
+    while (context.nextValue()) {
+      const char *s = context.getInputValue().c_str();
+      char *end;
+      count += strtoll(s, &end, 10);
+      for (int j = 0; j < d_; ++j) {
+        s = end;
+        sums[j] += strtod(s, &end);
+        HADOOP_ASSERT(end != s, "malformed partial record " + context.getInputValue());
+      }
+    }
+    char buf[64];
+    snprintf(buf, sizeof buf, "%lld", count);
+    std::string out(buf);
+    for (int j = 0; j < d_; ++j) {
+      snprintf(buf, sizeof buf, " %.9g", (float)(sums[j] / (double)count));
+      out += buf;
+    }
+    context.emit(context.getInputKey(), out);
+  }
+};
+
+class KMeansPartitioner : public HadoopPipes::Partitioner {
+ public:
+  explicit KMeansPartitioner(HadoopPipes::TaskContext &) {}
+  int partition(const std::string &key, int numOfReduces) { return HadoopUtils::toInt(key) % numOfReduces; }
+};
+
+// The C++ reader is created only when Java says the input is not piped.
+class GpuFactory : public HadoopPipes::Factory {
+ public:
+  HadoopPipes::Mapper *createMapper(HadoopPipes::MapContext &c) const { return new KMeansGpuMap(c); }
+  HadoopPipes::Reducer *createReducer(HadoopPipes::ReduceContext &c) const { return new KMeansReduce(c); }
+  HadoopPipes::Partitioner *createPartitioner(HadoopPipes::MapContext &c) const { return new KMeansPartitioner(c); }
+  HadoopPipes::RecordReader *createRecordReader(HadoopPipes::MapContext &c) const {
+    const HadoopPipes::JobConf *conf = c.getJobConf();
+    if (conf->hasKey("hadoop.pipes.java.recordreader") && !conf->getBoolean("hadoop.pipes.java.recordreader"))
+      return new WholeSplitReader(c);
+    return NULL;
+  }
+};
+
+int main(int argc, char **argv) {
+  // pipes/Application.java:179-181 appends the GPU device id to the command line
+  if (argc > 1) g_device = atoi(argv[argc - 1]);
+  else if (const char *env = getenv("HGM_DEVICE")) g_device = atoi(env);
+  // As in the shipped examples the bool is the exit status (wordcount-simple.cc:63-66);
+  // Hadoop ignores it and waits for DONE.
+  return HadoopPipes::runTask(GpuFactory());
+}
