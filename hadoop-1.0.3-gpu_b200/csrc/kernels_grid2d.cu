@@ -161,11 +161,24 @@ __global__ void __launch_bounds__(256) grid2d_build_kernel(const float *__restri
 // table and the centroids (read-only after the prologue) and nothing else: each owns its
 // tiles, its sort buffer, histogram and FP64 partials, and synchronises on its own named
 // barrier, so one group's scatter/sum phases overlap another's load/lookup phase.
+//
+// Per tile and group (a counting sort by cluster, then balanced run sums):
+//   A  load 8 points per thread, look their cells up; every point takes a rank in its bin
+//      with one native integer ATOMS.  Bins 0..k-1 are the clusters of single-candidate
+//      cells; bin k collects the points of multi-candidate cells ("unresolved").  No branch.
+//   B  warp 0: exclusive scan of the k+1 bin sizes; sizes are folded into the counts
+//   C  scatter the points to offset[bin] + rank
+//   D  every thread sums a 9-point chunk of the sorted buffer in FP64 (odd stride: the
+//      LDS.64 are conflict-free, every thread does the same work) and flushes a partial to
+//      the group's accumulators whenever the cluster changes;
+//   D' the unresolved run, one point per thread: exact candidate scan, then the same flush.
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
 
-// per-group shared memory: [sorted float2 tile][acc 2k f64][cnt k i64][hist k i32][offs k i32][qcount]
-__host__ __device__ inline size_t group_bytes(int tile, int k) {
-  return (size_t)tile * 8 + (size_t)k * 16 + (size_t)k * 8 + 2 * align16((size_t)k * 4) + 16;
+// per-group shared memory:
+// [sort buffer tile float2][acc 2k f64][cnt k i64][hist k+1 i32][offs k+1 i32][late k i32][lidx tile u16]
+__host__ __device__ inline size_t group_bytes(int tile, int k, bool with_assign) {
+  return (size_t)tile * 8 + (size_t)k * 16 + (size_t)k * 8 + 2 * align16((size_t)(k + 1) * 4) +
+         align16((size_t)k * 4) + (with_assign ? align16((size_t)tile * 2) : 0);
 }
 __host__ __device__ inline size_t shared_head_bytes(int G, int k) {
   return align16((size_t)G * G * 2) + align16((size_t)k * 8) + 16;
@@ -212,8 +225,7 @@ __device__ __noinline__ int resolve_slow(float x, float y, uint32_t entry, uint3
   return arg;
 }
 
-constexpr uint32_t kKeyNone = 0xFFFFFFFFu;    // no point in this slot (ragged last tile)
-constexpr uint32_t kKeyQueued = 0x80000000u;  // | queue slot: resolved in phase A2
+constexpr int kChunk = kPPT + 1;  // 9: odd stride of 8-byte slots = conflict-free LDS.64
 
 template <class S, bool kVec4, bool kAssign>
 __global__ void __launch_bounds__(S::kThreads, 1)
@@ -223,22 +235,23 @@ __global__ void __launch_bounds__(S::kThreads, 1)
                       unsigned long long *__restrict__ g_counts, int32_t *__restrict__ assign) {
   constexpr int kGT = S::kGroupThreads;
   constexpr int kTile = S::kTile;
+  static_assert(kGT * kChunk >= kTile, "phase D must cover the tile in one pass");
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int group = threadIdx.x / kGT;
   const int t = threadIdx.x % kGT;  // thread within the group
-  const int lane = threadIdx.x & 31;
 
   // carve shared memory (pointers computed, not looked up: no local-memory struct)
   uint16_t *const table_s = reinterpret_cast<uint16_t *>(smem_raw);
   float2 *const cent_s = reinterpret_cast<float2 *>(smem_raw + align16((size_t)g.G * g.G * 2));
   uint64_t *const bar = reinterpret_cast<uint64_t *>(reinterpret_cast<unsigned char *>(cent_s) + align16((size_t)k * 8));
-  unsigned char *const gb = smem_raw + shared_head_bytes(g.G, k) + (size_t)group * group_bytes(kTile, k);
+  unsigned char *const gb = smem_raw + shared_head_bytes(g.G, k) + (size_t)group * group_bytes(kTile, k, kAssign);
   float2 *const sorted = reinterpret_cast<float2 *>(gb);
   double *const acc = reinterpret_cast<double *>(gb + (size_t)kTile * 8);
   long long *const cnt = reinterpret_cast<long long *>(acc + 2 * k);
-  int *const hist = reinterpret_cast<int *>(cnt + k);
-  int *const offs = reinterpret_cast<int *>(reinterpret_cast<unsigned char *>(hist) + align16((size_t)k * 4));
-  int *const qcount = reinterpret_cast<int *>(reinterpret_cast<unsigned char *>(offs) + align16((size_t)k * 4));
+  int *const hist = reinterpret_cast<int *>(cnt + k);  // k+1 bins; bin k = unresolved
+  int *const offs = reinterpret_cast<int *>(reinterpret_cast<unsigned char *>(hist) + align16((size_t)(k + 1) * 4));
+  int *const late = reinterpret_cast<int *>(reinterpret_cast<unsigned char *>(offs) + align16((size_t)(k + 1) * 4));
+  uint16_t *const lidx = reinterpret_cast<uint16_t *>(reinterpret_cast<unsigned char *>(late) + align16((size_t)k * 4));
 
   // stage the cell table and the centroids with TMA bulk copies (SASS: UBLKCP)
   const uint32_t table_bytes = (uint32_t)align16((size_t)g.G * g.G * 2);
@@ -256,18 +269,14 @@ __global__ void __launch_bounds__(S::kThreads, 1)
   }
   for (int c = t; c < k; c += kGT) {
     hist[c] = 0;
+    late[c] = 0;
     acc[2 * c] = 0.0;
     acc[2 * c + 1] = 0.0;
     cnt[c] = 0;
   }
-  if (t == 0) *qcount = 0;
+  if (t == 0) hist[k] = 0;
   mbar_wait(bar, 0);
   __syncthreads();
-
-  // threads per cluster in the run-sum phase (power of two, <= 32)
-  int tpc = 1;
-  while (tpc < 32 && tpc * 2 * k <= kGT) tpc *= 2;
-  const int groups_of_tpc = kGT / tpc;
 
   const long long ntiles = (n + kTile - 1) / kTile;
   const long long tile_stride = (long long)gridDim.x * S::kGroups;
@@ -308,6 +317,12 @@ __global__ void __launch_bounds__(S::kThreads, 1)
     for (int o = t * 128; o < kTile * 8; o += kGT * 128)
       if (8 * tile * kTile + o < lim) asm volatile("prefetch.global.L2 [%0];" ::"l"(b + o));
   };
+  // add one run partial to the group's accumulators (shared FP64 atomic = CAS loop; runs
+  // are ~16 points, so this is a small fraction of the work and rarely contended)
+  auto flush = [&](int c, double ax, double ay) {
+    atomicAdd(&acc[2 * c], ax);
+    atomicAdd(&acc[2 * c + 1], ay);
+  };
 
   float4 buf[kPPT / 2];
   if (S::kRegPrefetch) {
@@ -319,7 +334,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
     const long long base = tile * kTile;  // first point of the tile (even)
     const int live = (int)min((long long)kTile, n - base);  // points in this tile
     float xs[kPPT], ys[kPPT];
-    uint32_t key[kPPT];  // cluster | rank << 16
+    uint32_t key[kPPT];  // bin | rank << 16
 
     if (!S::kRegPrefetch) {
       load_tile(tile, buf);
@@ -331,75 +346,49 @@ __global__ void __launch_bounds__(S::kThreads, 1)
     }
     if (S::kRegPrefetch && tile + tile_stride < ntiles) load_tile(tile + tile_stride, buf);
 
-    // ---- phase A1: cell lookup; single-candidate points get their rank at once, the rest
-    // are queued (warp-aggregated slot allocation) for dense resolution in A2 -----------
+    // ---- phase A: cell -> bin, rank within the bin ------------------------------------------
+    if (live == kTile) {  // full tile: no per-point bounds checks
 #pragma unroll
-    for (int i = 0; i < kPPT; ++i) {
-      const int local = 2 * ((i >> 1) * kGT + t) + (i & 1);  // index within the tile
-      const uint32_t e = table_s[cell_of(xs[i], ys[i], g)];
-      const bool valid = local < live;
-      const bool slow = valid && e >= kCellMulti;
-      const uint32_t m = __ballot_sync(0xFFFFFFFFu, slow);
-      if (valid && !slow) {
-        const int r = atomicAdd(&hist[e], 1);
-        key[i] = e | ((uint32_t)r << 16);
-      } else {
-        key[i] = kKeyNone;
+      for (int i = 0; i < kPPT; ++i) {
+        const uint32_t e = table_s[cell_of(xs[i], ys[i], g)];
+        const uint32_t bin = e < kCellMulti ? e : (uint32_t)k;
+        key[i] = bin | ((uint32_t)atomicAdd(&hist[bin], 1) << 16);
       }
-      if (m) {
-        int qbase = 0;
-        if (lane == 0) qbase = atomicAdd(qcount, __popc(m));
-        qbase = __shfl_sync(0xFFFFFFFFu, qbase, 0);
-        if (slow) {
-          const int q = qbase + __popc(m & ((1u << lane) - 1));
-          sorted[q] = make_float2(xs[i], ys[i]);
-          key[i] = kKeyQueued | (uint32_t)q;
-        }
+    } else {
+#pragma unroll
+      for (int i = 0; i < kPPT; ++i) {
+        const int local = 2 * ((i >> 1) * kGT + t) + (i & 1);  // index within the tile
+        const uint32_t e = table_s[cell_of(xs[i], ys[i], g)];
+        const uint32_t bin = e < kCellMulti ? e : (uint32_t)k;
+        key[i] = 0xFFFFFFFFu;
+        if (local < live) key[i] = bin | ((uint32_t)atomicAdd(&hist[bin], 1) << 16);
       }
     }
-    group_sync(group, kGT);
-
-    // ---- phase A2: the queued points, one per thread, exact candidate scan --------------
-    const int nq = *qcount;
-    if (nq) {
-      for (int q = t; q < nq; q += kGT) {
-        const float2 v = sorted[q];
-        const uint32_t cell = cell_of(v.x, v.y, g);
-        const int c = resolve_slow(v.x, v.y, table_s[cell], cell, cent_s, k, cand);
-        const int r = atomicAdd(&hist[c], 1);
-        sorted[q].x = __uint_as_float((uint32_t)c | ((uint32_t)r << 16));
-      }
-      group_sync(group, kGT);
-#pragma unroll
-      for (int i = 0; i < kPPT; ++i)
-        if (key[i] != kKeyNone && (key[i] & kKeyQueued)) key[i] = __float_as_uint(sorted[key[i] & 0xFFFF].x);
-      if (t == 0) *qcount = 0;
-      group_sync(group, kGT);  // keys are out of the queue before phase C overwrites it
-    }
-
-    if (kAssign) {
+    if (kAssign) {  // resolved points: the owner knows the cluster already
       const bool assign8 = (reinterpret_cast<uintptr_t>(assign) & 7) == 0;
 #pragma unroll
       for (int i = 0; i < kPPT / 2; ++i) {
         const int local = 2 * (i * kGT + t);
         const long long p = base + local;
-        if (local + 1 < live && assign8) {
-          *reinterpret_cast<int2 *>(assign + p) =
-              make_int2((int)(key[2 * i] & 0xFFFF), (int)(key[2 * i + 1] & 0xFFFF));
+        const int c0 = (int)(key[2 * i] & 0xFFFF), c1 = (int)(key[2 * i + 1] & 0xFFFF);
+        if (local + 1 < live && assign8 && c0 != k && c1 != k) {
+          *reinterpret_cast<int2 *>(assign + p) = make_int2(c0, c1);
         } else {
-          if (local < live) assign[p] = (int)(key[2 * i] & 0xFFFF);
-          if (local + 1 < live) assign[p + 1] = (int)(key[2 * i + 1] & 0xFFFF);
+          if (local < live && c0 != k) assign[p] = c0;
+          if (local + 1 < live && c1 != k) assign[p + 1] = c1;
         }
       }
     }
+    group_sync(group, kGT);
 
-    // ---- phase B: exclusive scan of the tile histogram (first warp of the group) ---------
+    // ---- phase B (warp 0): exclusive scan of the k+1 bins; fold sizes into the counts ------
     if (t < 32) {
-      const int per = (k + 31) / 32;
+      const int nb = k + 1;
+      const int per = (nb + 31) / 32;
       const int lo = t * per;
       int sum = 0;
       for (int j = 0; j < per; ++j)
-        if (lo + j < k) sum += hist[lo + j];
+        if (lo + j < nb) sum += hist[lo + j];
       int incl = sum;
 #pragma unroll
       for (int o = 1; o < 32; o <<= 1) {
@@ -407,62 +396,81 @@ __global__ void __launch_bounds__(S::kThreads, 1)
         if (t >= o) incl += up;
       }
       int run = incl - sum;
-      for (int j = 0; j < per; ++j)
-        if (lo + j < k) { offs[lo + j] = run; run += hist[lo + j]; }
+      for (int j = 0; j < per; ++j) {
+        const int c = lo + j;
+        if (c < nb) {
+          const int h = hist[c];
+          offs[c] = run;
+          run += h;
+          hist[c] = 0;
+          if (c < k) { cnt[c] += h + late[c]; late[c] = 0; }
+        }
+      }
     }
     group_sync(group, kGT);
 
-    // ---- phase C: scatter the points into cluster order --------------------------------
+    // ---- phase C: scatter to offset[bin] + rank ----------------------------------------------
 #pragma unroll
     for (int i = 0; i < kPPT; ++i) {
-      if (key[i] != kKeyNone) {
-        const int c = key[i] & 0xFFFF;
-        sorted[offs[c] + (int)(key[i] >> 16)] = make_float2(xs[i], ys[i]);
+      if (live == kTile || key[i] != 0xFFFFFFFFu) {
+        const int pos = offs[key[i] & 0xFFFF] + (int)(key[i] >> 16);
+        sorted[pos] = make_float2(xs[i], ys[i]);
+        if (kAssign) lidx[pos] = (uint16_t)(2 * ((i >> 1) * kGT + t) + (i & 1));
       }
     }
     group_sync(group, kGT);
 
-    // ---- phase D: FP64 run sums, owner lanes fold them into the group partials and clear
-    // the histogram for the next tile ------------------------------------------------------
+    // ---- phase D: balanced FP64 run sums over the resolved part -----------------------------
+    const int nfast = offs[k];
     {
-      const int sub = t & (tpc - 1);
-      for (int c0 = 0; c0 < k; c0 += groups_of_tpc) {  // uniform trip count: shuffles need all lanes
-        const int c = c0 + t / tpc;
-        const bool on = c < k;
-        const int start = on ? offs[c] : 0, m = on ? hist[c] : 0;
+      int pos = t * kChunk;
+      if (pos < nfast) {
+        const int stop = min(nfast, pos + kChunk);
+        int lo = 0, hi = k;  // largest c with offs[c] <= pos
+        while (hi - lo > 1) {
+          const int mid = (lo + hi) >> 1;
+          if (offs[mid] <= pos) lo = mid; else hi = mid;
+        }
+        int c = lo;
+        int nextb = offs[c + 1];
         double ax = 0.0, ay = 0.0;
-        int j = sub;
-        for (; j + tpc < m; j += 2 * tpc) {  // two independent loads per trip
-          const float2 v0 = sorted[start + j];
-          const float2 v1 = sorted[start + j + tpc];
-          ax += (double)v0.x; ay += (double)v0.y;
-          ax += (double)v1.x; ay += (double)v1.y;
+#pragma unroll
+        for (int i = 0; i < kChunk; ++i, ++pos) {
+          if (pos < stop) {
+            if (pos >= nextb) {
+              flush(c, ax, ay);
+              ax = 0.0; ay = 0.0;
+              do { ++c; nextb = offs[c + 1]; } while (pos >= nextb);
+            }
+            const float2 v = sorted[pos];
+            ax += (double)v.x;
+            ay += (double)v.y;
+          }
         }
-        if (j < m) {
-          const float2 v = sorted[start + j];
-          ax += (double)v.x; ay += (double)v.y;
-        }
-        for (int o = tpc >> 1; o > 0; o >>= 1) {
-          ax += __shfl_xor_sync(0xFFFFFFFFu, ax, o);
-          ay += __shfl_xor_sync(0xFFFFFFFFu, ay, o);
-        }
-        if (on && sub == 0) {
-          acc[2 * c] += ax;
-          acc[2 * c + 1] += ay;
-          cnt[c] += m;
-          hist[c] = 0;  // every lane of this cluster has read m (the shuffles above)
-        }
+        flush(c, ax, ay);
       }
     }
-    group_sync(group, kGT);  // sorted/hist are free for the next tile
+    // ---- phase D': the unresolved run, one point per thread, exact candidate scan -----------
+    for (int j = nfast + t; j < live; j += kGT) {
+      const float2 v = sorted[j];
+      const uint32_t cell = cell_of(v.x, v.y, g);
+      const int c = resolve_slow(v.x, v.y, table_s[cell], cell, cent_s, k, cand);
+      flush(c, (double)v.x, (double)v.y);
+      atomicAdd(&late[c], 1);
+      if (kAssign) assign[base + lidx[j]] = c;
+    }
+    // No barrier here: the next tile's phase A only touches hist (zeroed in B), and every
+    // thread passes that phase's barrier before B/C rewrite offs/late/sorted.
   }
+  group_sync(group, kGT);
 
   // ---- group partials -> global (one RED per value per group) ----------------------------
   for (int c = t; c < k; c += kGT) {
-    if (cnt[c] != 0) {
+    const long long m = cnt[c] + late[c];
+    if (m != 0) {
       atomicAdd(&g_sums[2 * c], acc[2 * c]);
       atomicAdd(&g_sums[2 * c + 1], acc[2 * c + 1]);
-      atomicAdd(&g_counts[c], (unsigned long long)cnt[c]);
+      atomicAdd(&g_counts[c], (unsigned long long)m);
     }
   }
 }
@@ -480,8 +488,8 @@ int active_variant() {
   return variant;
 }
 template <class S>
-size_t shape_smem_bytes(int G, int k) {
-  return shared_head_bytes(G, k) + S::kGroups * group_bytes(S::kTile, k);
+size_t shape_smem_bytes(int G, int k, bool with_assign) {
+  return shared_head_bytes(G, k) + S::kGroups * group_bytes(S::kTile, k, with_assign);
 }
 
 template <class S>
@@ -489,7 +497,7 @@ cudaError_t launch_shape(const float *d_pts, int64_t n, const float *d_cent, int
                          const uint16_t *d_table, const uint16_t *d_cand, double *d_sums,
                          unsigned long long *d_counts, int32_t *d_assign, int sm_count,
                          size_t smem_optin, cudaStream_t s) {
-  const size_t smem = shared_head_bytes(g.G, k) + S::kGroups * group_bytes(S::kTile, k);
+  const size_t smem = shape_smem_bytes<S>(g.G, k, d_assign != nullptr);
   if (smem > smem_optin) return cudaErrorInvalidValue;
   const bool vec4 = (reinterpret_cast<uintptr_t>(d_pts) & 15) == 0;
   const bool asg = d_assign != nullptr;
@@ -510,10 +518,10 @@ cudaError_t launch_shape(const float *d_pts, int64_t n, const float *d_cent, int
 // shared memory the map kernel needs for a G x G table and k clusters; plan_grid2d sizes G by it
 size_t grid2d_map_smem_bytes(int G, int k) {
   switch (active_variant()) {
-    case 1: return shape_smem_bytes<ShapeB>(G, k);
-    case 2: return shape_smem_bytes<ShapeC>(G, k);
-    case 3: return shape_smem_bytes<ShapeD>(G, k);
-    default: return shape_smem_bytes<ShapeA>(G, k);
+    case 1: return shape_smem_bytes<ShapeB>(G, k, true);
+    case 2: return shape_smem_bytes<ShapeC>(G, k, true);
+    case 3: return shape_smem_bytes<ShapeD>(G, k, true);
+    default: return shape_smem_bytes<ShapeA>(G, k, true);
   }
 }
 
