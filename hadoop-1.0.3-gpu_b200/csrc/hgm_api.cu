@@ -109,9 +109,8 @@ bool plan_grid2d(const float *cent, int k, size_t smem_optin, Grid2D *out) {
       lo[j] = std::min(lo[j], v);
       hi[j] = std::max(hi[j], v);
     }
-  int G = 256;
-  while (G > 64 && grid2d_map_smem_bytes(G, k) > smem_optin) G -= 32;
-  if (grid2d_map_smem_bytes(G, k) > smem_optin) return false;
+  int G = 0, shape = 0;
+  if (!grid2d_plan(k, smem_optin, &G, &shape)) return false;
   float s[2], B[2];
   int32_t b[2];
   for (int j = 0; j < 2; ++j) {
@@ -133,6 +132,7 @@ bool plan_grid2d(const float *cent, int k, size_t smem_optin, Grid2D *out) {
   out->Bx = B[0]; out->By = B[1];
   out->bx = b[0]; out->by = b[1];
   out->G = G;
+  out->shape = shape;
   return true;
 }
 

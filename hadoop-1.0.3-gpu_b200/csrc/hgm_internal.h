@@ -27,6 +27,7 @@ struct Grid2D {
   float sx, Bx, sy, By;
   int32_t bx, by;  // the integer offsets inside Bx, By (builder needs them)
   int32_t G;       // cells per side
+  int32_t shape;   // map-kernel shape picked for this job (kernels_grid2d.cu)
 };
 
 constexpr uint32_t kMagicBits = 0x4B000000u;  // bits of 2^23
@@ -41,7 +42,7 @@ cudaError_t launch_grid2d_map(const float *d_pts, int64_t n, const float *d_cent
                               const Grid2D &g, const uint16_t *d_table, const uint16_t *d_cand,
                               double *d_sums, unsigned long long *d_counts, int32_t *d_assign,
                               int sm_count, size_t smem_optin, cudaStream_t s);
-size_t grid2d_map_smem_bytes(int G, int k);
+bool grid2d_plan(int k, size_t smem_optin, int *G_out, int *shape_out);
 
 cudaError_t launch_exact_map(const float *d_pts, int64_t n, int d, const float *d_cent, int k,
                              double *d_sums, unsigned long long *d_counts, int32_t *d_assign,

@@ -159,26 +159,38 @@ __global__ void __launch_bounds__(256) grid2d_build_kernel(const float *__restri
 // ---- the map kernel ---------------------------------------------------------------------
 // One persistent CTA per SM made of independent thread groups.  The groups share the cell
 // table and the centroids (read-only after the prologue) and nothing else: each owns its
-// tiles, its sort buffer, histogram and FP64 partials, and synchronises on its own named
-// barrier, so one group's scatter/sum phases overlap another's load/lookup phase.
+// tiles, its sort buffer, bin counters and FP64 partials, and synchronises on its own named
+// barrier, so one group's sum phase overlaps another's load/lookup/scatter phase.
 //
-// Per tile and group (a counting sort by cluster, then balanced run sums):
-//   A  load 8 points per thread, look their cells up; every point takes a rank in its bin
-//      with one native integer ATOMS.  Bins 0..k-1 are the clusters of single-candidate
-//      cells; bin k collects the points of multi-candidate cells ("unresolved").  No branch.
-//   B  warp 0: exclusive scan of the k+1 bin sizes; sizes are folded into the counts
-//   C  scatter the points to offset[bin] + rank
-//   D  every thread sums a 9-point chunk of the sorted buffer in FP64 (odd stride: the
-//      LDS.64 are conflict-free, every thread does the same work) and flushes a partial to
-//      the group's accumulators whenever the cluster changes;
-//   D' the unresolved run, one point per thread: exact candidate scan, then the same flush.
+// The sort buffer is a [rank][bin] "striped" array, W = k + 16 bins wide and R rows high:
+// bins 0..k-1 are the clusters; bins k..k+15 are two alternating sets of eight "unresolved"
+// bins for the points of multi-candidate cells.  A point's slot is rank*W + bin, the rank
+// coming from one native integer ATOMS on the bin's counter: no offsets, no scan.
+//
+// Per tile (kGroupThreads * 8 points) and group, two phases and two barriers:
+//   1a each thread takes 8 points: cell -> bin -> rank -> store.  Straight-line code.
+//   1b the unresolved points the PREVIOUS tile left behind are resolved, one per thread, by
+//      the exact candidate scan, and stored into this tile's columns like any other point.
+//   2  owner lanes walk their cluster's column (consecutive lanes = consecutive addresses,
+//      conflict-free) and add it in FP64 to partials they keep in registers for the whole
+//      kernel.
+// A point whose rank is >= R (a cluster much longer than the average in this tile) goes to
+// an overflow region at the top of the buffer and is added with a shared-memory CAS instead;
+// a tile that fills even that region is redone by the packed counting-sort path.
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
 
+constexpr int kUnres = 8;            // unresolved bins per parity (power of two)
+constexpr int kExtra = 2 * kUnres;   // extra columns of the striped layout
+
 // per-group shared memory:
-// [sort buffer tile float2][acc 2k f64][cnt k i64][hist k+1 i32][offs k+1 i32][late k i32][lidx tile u16]
-__host__ __device__ inline size_t group_bytes(int tile, int k, bool with_assign) {
-  return (size_t)tile * 8 + (size_t)k * 16 + (size_t)k * 8 + 2 * align16((size_t)(k + 1) * 4) +
-         align16((size_t)k * 4) + (with_assign ? align16((size_t)tile * 2) : 0);
+// [sort buffer slots float2][acc 2k f64][cnt k i64][hist k+kExtra+2 i32][offs k+1 i32][late k i32]
+// [flag 16 B][lidx (slots) u16, assign only]
+__host__ __device__ inline size_t group_small_bytes(int k) {
+  return (size_t)k * 16 + (size_t)k * 8 + align16((size_t)(k + kExtra + 2) * 4) +
+         align16((size_t)(k + 1) * 4) + align16((size_t)k * 4) + 16;
+}
+__host__ __device__ inline size_t group_bytes(int slots, int k, bool with_assign) {
+  return (size_t)slots * 8 + group_small_bytes(k) + (with_assign ? align16((size_t)slots * 2) : 0);
 }
 __host__ __device__ inline size_t shared_head_bytes(int G, int k) {
   return align16((size_t)G * G * 2) + align16((size_t)k * 8) + 16;
@@ -225,33 +237,36 @@ __device__ __noinline__ int resolve_slow(float x, float y, uint32_t entry, uint3
   return arg;
 }
 
-constexpr int kChunk = kPPT + 1;  // 9: odd stride of 8-byte slots = conflict-free LDS.64
+constexpr uint16_t kNoIndex = 0xFFFF;  // lidx value: this entry's assignment is already written
 
 template <class S, bool kVec4, bool kAssign>
 __global__ void __launch_bounds__(S::kThreads, 1)
     grid2d_map_kernel(const float *__restrict__ pts, long long n, const float *__restrict__ cent,
-                      int k, Grid2D g, const uint16_t *__restrict__ table,
+                      int k, Grid2D g, int slots, int rcap, const uint16_t *__restrict__ table,
                       const uint16_t *__restrict__ cand, double *__restrict__ g_sums,
                       unsigned long long *__restrict__ g_counts, int32_t *__restrict__ assign) {
   constexpr int kGT = S::kGroupThreads;
   constexpr int kTile = S::kTile;
-  static_assert(kGT * kChunk >= kTile, "phase D must cover the tile in one pass");
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int group = threadIdx.x / kGT;
   const int t = threadIdx.x % kGT;  // thread within the group
+  const int lane = threadIdx.x & 31;
+  const int W = k + kExtra;            // bins per row of the striped layout
+  const int tend = slots - rcap * W;   // capacity of the overflow region (slots-1 downwards)
 
   // carve shared memory (pointers computed, not looked up: no local-memory struct)
   uint16_t *const table_s = reinterpret_cast<uint16_t *>(smem_raw);
   float2 *const cent_s = reinterpret_cast<float2 *>(smem_raw + align16((size_t)g.G * g.G * 2));
   uint64_t *const bar = reinterpret_cast<uint64_t *>(reinterpret_cast<unsigned char *>(cent_s) + align16((size_t)k * 8));
-  unsigned char *const gb = smem_raw + shared_head_bytes(g.G, k) + (size_t)group * group_bytes(kTile, k, kAssign);
+  unsigned char *const gb = smem_raw + shared_head_bytes(g.G, k) + (size_t)group * group_bytes(slots, k, kAssign);
   float2 *const sorted = reinterpret_cast<float2 *>(gb);
-  double *const acc = reinterpret_cast<double *>(gb + (size_t)kTile * 8);
+  double *const acc = reinterpret_cast<double *>(gb + (size_t)slots * 8);
   long long *const cnt = reinterpret_cast<long long *>(acc + 2 * k);
-  int *const hist = reinterpret_cast<int *>(cnt + k);  // k+1 bins; bin k = unresolved
-  int *const offs = reinterpret_cast<int *>(reinterpret_cast<unsigned char *>(hist) + align16((size_t)(k + 1) * 4));
+  int *const hist = reinterpret_cast<int *>(cnt + k);  // W bin counters, then 2 overflow counters
+  int *const offs = reinterpret_cast<int *>(reinterpret_cast<unsigned char *>(hist) + align16((size_t)(W + 2) * 4));
   int *const late = reinterpret_cast<int *>(reinterpret_cast<unsigned char *>(offs) + align16((size_t)(k + 1) * 4));
-  uint16_t *const lidx = reinterpret_cast<uint16_t *>(reinterpret_cast<unsigned char *>(late) + align16((size_t)k * 4));
+  int *const flag = reinterpret_cast<int *>(reinterpret_cast<unsigned char *>(late) + align16((size_t)k * 4));
+  uint16_t *const lidx = reinterpret_cast<uint16_t *>(reinterpret_cast<unsigned char *>(flag) + 16);
 
   // stage the cell table and the centroids with TMA bulk copies (SASS: UBLKCP)
   const uint32_t table_bytes = (uint32_t)align16((size_t)g.G * g.G * 2);
@@ -268,15 +283,26 @@ __global__ void __launch_bounds__(S::kThreads, 1)
     tma_bulk_g2s(cent_s, cent, cent_bytes, bar);
   }
   for (int c = t; c < k; c += kGT) {
-    hist[c] = 0;
     late[c] = 0;
     acc[2 * c] = 0.0;
     acc[2 * c + 1] = 0.0;
     cnt[c] = 0;
   }
-  if (t == 0) hist[k] = 0;
+  for (int c = t; c < W + 2; c += kGT) hist[c] = 0;
+  if (t == 0) *flag = 0;
   mbar_wait(bar, 0);
   __syncthreads();
+
+  // threads per cluster in the column-sum phase (power of two, <= 32); when every cluster has
+  // its own fixed lanes (one pass) their partials stay in registers across tiles
+  int tpc = 1;
+  while (tpc < 32 && tpc * 2 * k <= kGT) tpc *= 2;
+  const int owners = kGT / tpc;  // clusters covered per pass
+  const int sub = t & (tpc - 1);
+  const bool one_pass = k <= owners;
+  const int my_c = t / tpc;
+  double reg_x = 0.0, reg_y = 0.0;
+  long long reg_n = 0;
 
   const long long ntiles = (n + kTile - 1) / kTile;
   const long long tile_stride = (long long)gridDim.x * S::kGroups;
@@ -317,11 +343,34 @@ __global__ void __launch_bounds__(S::kThreads, 1)
     for (int o = t * 128; o < kTile * 8; o += kGT * 128)
       if (8 * tile * kTile + o < lim) asm volatile("prefetch.global.L2 [%0];" ::"l"(b + o));
   };
-  // add one run partial to the group's accumulators (shared FP64 atomic = CAS loop; runs
-  // are ~16 points, so this is a small fraction of the work and rarely contended)
+  // add a partial to the group's accumulators from any thread (shared FP64 atomic = CAS loop;
+  // only overflow points and the packed path come here)
   auto flush = [&](int c, double ax, double ay) {
     atomicAdd(&acc[2 * c], ax);
     atomicAdd(&acc[2 * c + 1], ay);
+  };
+  // resolve one stored point exactly and add it with CAS (overflow region, packed path)
+  auto settle = [&](float2 v, long long base, uint16_t li) {
+    const uint32_t cell = cell_of(v.x, v.y, g);
+    const uint32_t e = table_s[cell];
+    const int c = e < kCellMulti ? (int)e : resolve_slow(v.x, v.y, e, cell, cent_s, k, cand);
+    flush(c, (double)v.x, (double)v.y);
+    atomicAdd(&late[c], 1);
+    if (kAssign && li != kNoIndex) assign[base + li] = c;
+  };
+  // rank a point in `bin` and store it; ranks beyond the striped rows go to the overflow
+  // region of parity `par`; returns false if even that is full
+  auto place = [&](float x, float y, int bin, int par, uint16_t li) -> bool {
+    const int r = atomicAdd(&hist[bin], 1);
+    int pos = r * W + bin;
+    if (r >= rcap) {
+      const int r2 = atomicAdd(&hist[W + par], 1);
+      if (r2 >= tend) return false;
+      pos = slots - 1 - r2;
+    }
+    sorted[pos] = make_float2(x, y);
+    if (kAssign) lidx[pos] = li;
+    return true;
   };
 
   float4 buf[kPPT / 2];
@@ -330,141 +379,245 @@ __global__ void __launch_bounds__(S::kThreads, 1)
   } else {
     if (tile0 < ntiles) prefetch_tile(tile0);
   }
-  for (long long tile = tile0; tile < ntiles; tile += tile_stride) {
+  int par = 0;
+  long long prev_base = 0;
+  bool pending = false;  // the previous tile left unresolved points in its parity's bins
+  for (long long tile = tile0; tile < ntiles || pending; tile += tile_stride, par ^= 1) {
+    const bool has_tile = tile < ntiles;
     const long long base = tile * kTile;  // first point of the tile (even)
-    const int live = (int)min((long long)kTile, n - base);  // points in this tile
+    const int live = has_tile ? (int)min((long long)kTile, n - base) : 0;
+    const int ubase = k + par * kUnres;         // this tile's unresolved bins
+    const int pbase = k + (par ^ 1) * kUnres;   // the previous tile's
     float xs[kPPT], ys[kPPT];
-    uint32_t key[kPPT];  // bin | rank << 16
 
-    if (!S::kRegPrefetch) {
-      load_tile(tile, buf);
-      if (tile + tile_stride < ntiles) prefetch_tile(tile + tile_stride);
-    }
+    if (has_tile) {
+      if (!S::kRegPrefetch) {
+        load_tile(tile, buf);
+        if (tile + tile_stride < ntiles) prefetch_tile(tile + tile_stride);
+      }
 #pragma unroll
-    for (int i = 0; i < kPPT / 2; ++i) {
-      xs[2 * i] = buf[i].x; ys[2 * i] = buf[i].y; xs[2 * i + 1] = buf[i].z; ys[2 * i + 1] = buf[i].w;
+      for (int i = 0; i < kPPT / 2; ++i) {
+        xs[2 * i] = buf[i].x; ys[2 * i] = buf[i].y; xs[2 * i + 1] = buf[i].z; ys[2 * i + 1] = buf[i].w;
+      }
+      if (S::kRegPrefetch && tile + tile_stride < ntiles) load_tile(tile + tile_stride, buf);
     }
-    if (S::kRegPrefetch && tile + tile_stride < ntiles) load_tile(tile + tile_stride, buf);
 
-    // ---- phase A: cell -> bin, rank within the bin ------------------------------------------
-    if (live == kTile) {  // full tile: no per-point bounds checks
+    // ---- phase 1a: cell -> bin -> rank -> slot ----------------------------------------------
+    bool lost = false;
+    const int ubin = ubase + (lane & (kUnres - 1));
+    if (live == kTile) {  // full tile: straight-line code, no bounds checks
 #pragma unroll
       for (int i = 0; i < kPPT; ++i) {
         const uint32_t e = table_s[cell_of(xs[i], ys[i], g)];
-        const uint32_t bin = e < kCellMulti ? e : (uint32_t)k;
-        key[i] = bin | ((uint32_t)atomicAdd(&hist[bin], 1) << 16);
+        const bool resolved = e < kCellMulti;
+        const int bin = resolved ? (int)e : ubin;
+        const int r = atomicAdd(&hist[bin], 1);
+        const int local = 2 * ((i >> 1) * kGT + t) + (i & 1);
+        if (kAssign && resolved) assign[base + local] = (int)e;
+        if (__any_sync(0xFFFFFFFFu, r >= rcap)) {  // rare: some lane's cluster outgrew the rows
+          int pos = r * W + bin;
+          bool ok = true;
+          if (r >= rcap) {
+            const int r2 = atomicAdd(&hist[W + par], 1);
+            ok = r2 < tend;
+            pos = slots - 1 - r2;
+          }
+          if (ok) {
+            sorted[pos] = make_float2(xs[i], ys[i]);
+            if (kAssign) lidx[pos] = resolved ? kNoIndex : (uint16_t)local;
+          }
+          lost |= !ok;
+        } else {
+          const int pos = r * W + bin;
+          sorted[pos] = make_float2(xs[i], ys[i]);
+          if (kAssign) lidx[pos] = resolved ? kNoIndex : (uint16_t)local;
+        }
       }
-    } else {
+    } else if (live > 0) {
 #pragma unroll
       for (int i = 0; i < kPPT; ++i) {
         const int local = 2 * ((i >> 1) * kGT + t) + (i & 1);  // index within the tile
-        const uint32_t e = table_s[cell_of(xs[i], ys[i], g)];
-        const uint32_t bin = e < kCellMulti ? e : (uint32_t)k;
-        key[i] = 0xFFFFFFFFu;
-        if (local < live) key[i] = bin | ((uint32_t)atomicAdd(&hist[bin], 1) << 16);
-      }
-    }
-    if (kAssign) {  // resolved points: the owner knows the cluster already
-      const bool assign8 = (reinterpret_cast<uintptr_t>(assign) & 7) == 0;
-#pragma unroll
-      for (int i = 0; i < kPPT / 2; ++i) {
-        const int local = 2 * (i * kGT + t);
-        const long long p = base + local;
-        const int c0 = (int)(key[2 * i] & 0xFFFF), c1 = (int)(key[2 * i + 1] & 0xFFFF);
-        if (local + 1 < live && assign8 && c0 != k && c1 != k) {
-          *reinterpret_cast<int2 *>(assign + p) = make_int2(c0, c1);
-        } else {
-          if (local < live && c0 != k) assign[p] = c0;
-          if (local + 1 < live && c1 != k) assign[p + 1] = c1;
+        if (local < live) {
+          const uint32_t e = table_s[cell_of(xs[i], ys[i], g)];
+          const bool resolved = e < kCellMulti;
+          if (kAssign && resolved) assign[base + local] = (int)e;
+          lost |= !place(xs[i], ys[i], resolved ? (int)e : ubin, par, resolved ? kNoIndex : (uint16_t)local);
         }
       }
     }
-    group_sync(group, kGT);
-
-    // ---- phase B (warp 0): exclusive scan of the k+1 bins; fold sizes into the counts ------
-    if (t < 32) {
-      const int nb = k + 1;
-      const int per = (nb + 31) / 32;
-      const int lo = t * per;
-      int sum = 0;
-      for (int j = 0; j < per; ++j)
-        if (lo + j < nb) sum += hist[lo + j];
-      int incl = sum;
-#pragma unroll
-      for (int o = 1; o < 32; o <<= 1) {
-        const int up = __shfl_up_sync(0xFFFFFFFFu, incl, o);
-        if (t >= o) incl += up;
-      }
-      int run = incl - sum;
-      for (int j = 0; j < per; ++j) {
-        const int c = lo + j;
-        if (c < nb) {
-          const int h = hist[c];
-          offs[c] = run;
-          run += h;
-          hist[c] = 0;
-          if (c < k) { cnt[c] += h + late[c]; late[c] = 0; }
+    // ---- phase 1b: resolve what the previous tile could not, into this tile's columns -------
+    if (pending) {
+      for (int u = t; u < kUnres * rcap; u += kGT) {
+        const int j = u & (kUnres - 1), r = u / kUnres;
+        if (r < min(hist[pbase + j], rcap)) {
+          const int pos = r * W + pbase + j;
+          const float2 v = sorted[pos];
+          const uint32_t cell = cell_of(v.x, v.y, g);
+          const int c = resolve_slow(v.x, v.y, table_s[cell], cell, cent_s, k, cand);
+          if (kAssign) assign[prev_base + lidx[pos]] = c;
+          lost |= !place(v.x, v.y, c, par, kNoIndex);
         }
       }
     }
+    if (lost) *flag = 1;
     group_sync(group, kGT);
 
-    // ---- phase C: scatter to offset[bin] + rank ----------------------------------------------
-#pragma unroll
-    for (int i = 0; i < kPPT; ++i) {
-      if (live == kTile || key[i] != 0xFFFFFFFFu) {
-        const int pos = offs[key[i] & 0xFFFF] + (int)(key[i] >> 16);
-        sorted[pos] = make_float2(xs[i], ys[i]);
-        if (kAssign) lidx[pos] = (uint16_t)(2 * ((i >> 1) * kGT + t) + (i & 1));
-      }
-    }
-    group_sync(group, kGT);
-
-    // ---- phase D: balanced FP64 run sums over the resolved part -----------------------------
-    const int nfast = offs[k];
-    {
-      int pos = t * kChunk;
-      if (pos < nfast) {
-        const int stop = min(nfast, pos + kChunk);
-        int lo = 0, hi = k;  // largest c with offs[c] <= pos
-        while (hi - lo > 1) {
-          const int mid = (lo + hi) >> 1;
-          if (offs[mid] <= pos) lo = mid; else hi = mid;
+    if (*flag == 0) {
+      // the other parity's unresolved and overflow counters were consumed before the barrier
+      if (t < kUnres) hist[pbase + t] = 0;
+      if (t == kUnres) hist[W + (par ^ 1)] = 0;
+      // ---- phase 2: FP64 column sums by the clusters' owner lanes ----------------------------
+      if (one_pass) {
+        const bool on = my_c < k;
+        const int h = on ? hist[my_c] : 0;
+        const int m = min(h, rcap);
+        const float2 *col = sorted + my_c;
+        int r = sub;
+        for (; r + tpc < m; r += 2 * tpc) {  // two rows per trip
+          const float2 v0 = col[r * W];
+          const float2 v1 = col[(r + tpc) * W];
+          reg_x += (double)v0.x; reg_y += (double)v0.y;
+          reg_x += (double)v1.x; reg_y += (double)v1.y;
         }
-        int c = lo;
-        int nextb = offs[c + 1];
-        double ax = 0.0, ay = 0.0;
-#pragma unroll
-        for (int i = 0; i < kChunk; ++i, ++pos) {
-          if (pos < stop) {
-            if (pos >= nextb) {
-              flush(c, ax, ay);
-              ax = 0.0; ay = 0.0;
-              do { ++c; nextb = offs[c + 1]; } while (pos >= nextb);
-            }
-            const float2 v = sorted[pos];
+        if (r < m) {
+          const float2 v = col[r * W];
+          reg_x += (double)v.x; reg_y += (double)v.y;
+        }
+        __syncwarp();  // all lanes of the cluster have read h
+        if (on && sub == 0) { reg_n += m; hist[my_c] = 0; }
+      } else {
+        for (int c0 = 0; c0 < k; c0 += owners) {  // uniform trip count: shuffles need all lanes
+          const int c = c0 + my_c;
+          const bool on = c < k;
+          const int h = on ? hist[c] : 0;
+          const int m = min(h, rcap);
+          double ax = 0.0, ay = 0.0;
+          const float2 *col = sorted + c;
+          for (int r = sub; r < m; r += tpc) {
+            const float2 v = col[r * W];
             ax += (double)v.x;
             ay += (double)v.y;
           }
+          for (int o = tpc >> 1; o > 0; o >>= 1) {
+            ax += __shfl_xor_sync(0xFFFFFFFFu, ax, o);
+            ay += __shfl_xor_sync(0xFFFFFFFFu, ay, o);
+          }
+          if (on && sub == 0 && h) {
+            acc[2 * c] += ax;
+            acc[2 * c + 1] += ay;
+            cnt[c] += m;
+            hist[c] = 0;
+          }
         }
-        flush(c, ax, ay);
       }
+      // overflow region: rare, one point per thread, CAS adds
+      const int nover = min(hist[W + par], tend);
+      for (int u = t; u < nover; u += kGT) {
+        const int pos = slots - 1 - u;
+        settle(sorted[pos], base, kAssign ? lidx[pos] : kNoIndex);
+      }
+      pending = has_tile;  // this tile's unresolved bins wait for the next phase 1b
+      prev_base = base;
+    } else {
+      // ---- packed path: redo this tile as histogram -> scan -> scatter -> run sums -----------
+      // Everything phase 1 stored is discarded; the tile's points are still in xs/ys, the
+      // previous tile's unresolved points still sit in their columns (settled here with CAS).
+      if (pending) {
+        for (int u = t; u < kUnres * rcap; u += kGT) {
+          const int j = u & (kUnres - 1), r = u / kUnres;
+          if (r < min(hist[pbase + j], rcap)) {
+            const int pos = r * W + pbase + j;
+            settle(sorted[pos], prev_base, kAssign ? lidx[pos] : kNoIndex);
+          }
+        }
+      }
+      group_sync(group, kGT);
+      for (int c = t; c < W + 2; c += kGT) hist[c] = 0;
+      group_sync(group, kGT);
+      int *const ucount = hist + k;  // bin k of the packed layout: every unresolved point
+      uint32_t key[kPPT];
+#pragma unroll
+      for (int i = 0; i < kPPT; ++i) {
+        const int local = 2 * ((i >> 1) * kGT + t) + (i & 1);
+        key[i] = 0xFFFFFFFFu;
+        if (local < live) {
+          const uint32_t e = table_s[cell_of(xs[i], ys[i], g)];
+          const bool resolved = e < kCellMulti;
+          const int r = atomicAdd(resolved ? &hist[e] : ucount, 1);
+          key[i] = (resolved ? e : (uint32_t)k) | ((uint32_t)r << 16);
+        }
+      }
+      group_sync(group, kGT);
+      if (t < 32) {  // exclusive scan of the k+1 bins
+        const int nb = k + 1;
+        const int per = (nb + 31) / 32;
+        const int lo = t * per;
+        int sum = 0;
+        for (int j = 0; j < per; ++j)
+          if (lo + j < nb) sum += hist[lo + j];
+        int incl = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) {
+          const int up = __shfl_up_sync(0xFFFFFFFFu, incl, o);
+          if (t >= o) incl += up;
+        }
+        int run = incl - sum;
+        for (int j = 0; j < per; ++j) {
+          const int c = lo + j;
+          if (c < nb) { offs[c] = run; run += hist[c]; }
+        }
+      }
+      group_sync(group, kGT);
+#pragma unroll
+      for (int i = 0; i < kPPT; ++i) {
+        if (key[i] != 0xFFFFFFFFu) {
+          const int pos = offs[key[i] & 0xFFFF] + (int)(key[i] >> 16);
+          sorted[pos] = make_float2(xs[i], ys[i]);
+          if (kAssign) lidx[pos] = (uint16_t)(2 * ((i >> 1) * kGT + t) + (i & 1));
+        }
+      }
+      group_sync(group, kGT);
+      for (int c0 = 0; c0 < k; c0 += owners) {
+        const int c = c0 + my_c;
+        const bool on = c < k;
+        const int start = on ? offs[c] : 0, m = on ? hist[c] : 0;
+        double ax = 0.0, ay = 0.0;
+        for (int j = sub; j < m; j += tpc) {
+          const float2 v = sorted[start + j];
+          ax += (double)v.x;
+          ay += (double)v.y;
+        }
+        for (int o = tpc >> 1; o > 0; o >>= 1) {
+          ax += __shfl_xor_sync(0xFFFFFFFFu, ax, o);
+          ay += __shfl_xor_sync(0xFFFFFFFFu, ay, o);
+        }
+        if (on && sub == 0 && m) {
+          acc[2 * c] += ax;
+          acc[2 * c + 1] += ay;
+          cnt[c] += m;
+        }
+      }
+      for (int j = offs[k] + t; j < live; j += kGT) settle(sorted[j], base, kAssign ? lidx[j] : kNoIndex);
+      group_sync(group, kGT);
+      for (int c = t; c < W + 2; c += kGT) hist[c] = 0;
+      if (t == 0) *flag = 0;
+      pending = false;
     }
-    // ---- phase D': the unresolved run, one point per thread, exact candidate scan -----------
-    for (int j = nfast + t; j < live; j += kGT) {
-      const float2 v = sorted[j];
-      const uint32_t cell = cell_of(v.x, v.y, g);
-      const int c = resolve_slow(v.x, v.y, table_s[cell], cell, cent_s, k, cand);
-      flush(c, (double)v.x, (double)v.y);
-      atomicAdd(&late[c], 1);
-      if (kAssign) assign[base + lidx[j]] = c;
-    }
-    // No barrier here: the next tile's phase A only touches hist (zeroed in B), and every
-    // thread passes that phase's barrier before B/C rewrite offs/late/sorted.
+    group_sync(group, kGT);  // sort buffer, counters and flag are free for the next tile
   }
-  group_sync(group, kGT);
 
-  // ---- group partials -> global (one RED per value per group) ----------------------------
+  // ---- partials -> global: registers first (one_pass), then the group's shared partials ----
+  if (one_pass && my_c < k) {
+    for (int o = tpc >> 1; o > 0; o >>= 1) {
+      reg_x += __shfl_xor_sync(0xFFFFFFFFu, reg_x, o);
+      reg_y += __shfl_xor_sync(0xFFFFFFFFu, reg_y, o);
+    }
+    if (sub == 0 && reg_n) {
+      atomicAdd(&g_sums[2 * my_c], reg_x);
+      atomicAdd(&g_sums[2 * my_c + 1], reg_y);
+      atomicAdd(&g_counts[my_c], (unsigned long long)reg_n);
+    }
+  }
   for (int c = t; c < k; c += kGT) {
     const long long m = cnt[c] + late[c];
     if (m != 0) {
@@ -475,21 +628,48 @@ __global__ void __launch_bounds__(S::kThreads, 1)
   }
 }
 
-using ShapeA = Shape<2, 512, false>;  // 1024 threads, L2 prefetch
+using ShapeA = Shape<2, 512, false>;  // 1024 threads, two groups, L2 prefetch
 using ShapeB = Shape<2, 512, true>;   // 1024 threads, register prefetch
-using ShapeC = Shape<4, 256, false>;  // 1024 threads, four groups
+using ShapeC = Shape<4, 256, false>;  // 1024 threads, four groups, L2 prefetch
 using ShapeD = Shape<3, 256, true>;   // 768 threads, register prefetch
 
-int active_variant() {
+// HGM_GRID2D_VARIANT forces a shape (tuning knob); otherwise the shape is picked per job.
+int forced_variant() {
   static const int variant = [] {
-    const char *v = getenv("HGM_GRID2D_VARIANT");  // tuning knob; the default is the measured best
-    return v ? atoi(v) : 0;
+    const char *v = getenv("HGM_GRID2D_VARIANT");
+    return v ? atoi(v) : -1;
   }();
   return variant;
 }
+
+// How the shared memory left after the table is split: slots of the sort buffer per group and
+// rows of the striped layout.  The overflow region keeps at least a quarter tile.
+struct Plan {
+  int slots, rcap;
+  size_t smem;
+  bool ok;
+};
 template <class S>
-size_t shape_smem_bytes(int G, int k, bool with_assign) {
-  return shared_head_bytes(G, k) + S::kGroups * group_bytes(S::kTile, k, with_assign);
+Plan make_plan(int G, int k, bool with_assign, size_t smem_optin) {
+  Plan p{0, 0, 0, false};
+  const size_t head = shared_head_bytes(G, k);
+  if (head >= smem_optin) return p;
+  const size_t per_group = (smem_optin - head) / S::kGroups;
+  const size_t fixed = group_small_bytes(k) + 32;
+  if (per_group <= fixed) return p;
+  size_t slots = (per_group - fixed) / (with_assign ? 10 : 8);
+  slots &= ~size_t(7);
+  if (slots > 65536) slots = 65536;  // lidx and slot arithmetic are 16-bit
+  if ((long long)slots < S::kTile) return p;  // the packed path needs a whole tile
+  const int W = k + kExtra;
+  int rcap = (int)((slots - S::kTile / 4) / W);
+  if (rcap < 1) rcap = 0;  // no striped rows: every tile takes the packed path
+  if (rcap > 1023) rcap = 1023;
+  p.slots = (int)slots;
+  p.rcap = rcap;
+  p.smem = head + S::kGroups * group_bytes((int)slots, k, with_assign);
+  p.ok = p.smem <= smem_optin;
+  return p;
 }
 
 template <class S>
@@ -497,32 +677,54 @@ cudaError_t launch_shape(const float *d_pts, int64_t n, const float *d_cent, int
                          const uint16_t *d_table, const uint16_t *d_cand, double *d_sums,
                          unsigned long long *d_counts, int32_t *d_assign, int sm_count,
                          size_t smem_optin, cudaStream_t s) {
-  const size_t smem = shape_smem_bytes<S>(g.G, k, d_assign != nullptr);
-  if (smem > smem_optin) return cudaErrorInvalidValue;
+  const Plan plan = make_plan<S>(g.G, k, d_assign != nullptr, smem_optin);
+  if (!plan.ok) return cudaErrorInvalidValue;
   const bool vec4 = (reinterpret_cast<uintptr_t>(d_pts) & 15) == 0;
   const bool asg = d_assign != nullptr;
   auto kern = vec4 ? (asg ? grid2d_map_kernel<S, true, true> : grid2d_map_kernel<S, true, false>)
                    : (asg ? grid2d_map_kernel<S, false, true> : grid2d_map_kernel<S, false, false>);
-  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.smem);
   if (e != cudaSuccess) return e;
   const long long ntiles = (n + S::kTile - 1) / S::kTile;
   const long long want = (ntiles + S::kGroups - 1) / S::kGroups;
   const int grid = (int)(want < sm_count ? want : sm_count);
-  kern<<<grid, S::kThreads, smem, s>>>(d_pts, (long long)n, d_cent, k, g, d_table, d_cand, d_sums,
-                                       d_counts, d_assign);
+  kern<<<grid, S::kThreads, plan.smem, s>>>(d_pts, (long long)n, d_cent, k, g, plan.slots, plan.rcap,
+                                            d_table, d_cand, d_sums, d_counts, d_assign);
   return cudaGetLastError();
+}
+
+template <class S>
+bool shape_fits(int G, int k, size_t smem_optin) {
+  // a table is usable if the assign variant fits and the plain variant gets >= 2 tiles of slots
+  const Plan a = make_plan<S>(G, k, true, smem_optin);
+  const Plan b = make_plan<S>(G, k, false, smem_optin);
+  return a.ok && b.ok && b.slots >= 2 * S::kTile;
 }
 
 }  // namespace
 
-// shared memory the map kernel needs for a G x G table and k clusters; plan_grid2d sizes G by it
-size_t grid2d_map_smem_bytes(int G, int k) {
-  switch (active_variant()) {
-    case 1: return shape_smem_bytes<ShapeB>(G, k, true);
-    case 2: return shape_smem_bytes<ShapeC>(G, k, true);
-    case 3: return shape_smem_bytes<ShapeD>(G, k, true);
-    default: return shape_smem_bytes<ShapeA>(G, k, true);
+// Pick the table size and kernel shape for k clusters: four groups of 256 threads (the
+// measured best at k = 128) while the table can stay at 160+ cells per side, otherwise two
+// groups of 512, whose per-group arrays cost half as much shared memory.
+bool grid2d_plan(int k, size_t smem_optin, int *G_out, int *shape_out) {
+  const int forced = forced_variant();
+  auto fits = [&](int shape, int G) {
+    switch (shape) {
+      case 0: return shape_fits<ShapeA>(G, k, smem_optin);
+      case 1: return shape_fits<ShapeB>(G, k, smem_optin);
+      case 3: return shape_fits<ShapeD>(G, k, smem_optin);
+      default: return shape_fits<ShapeC>(G, k, smem_optin);
+    }
+  };
+  const int order[2] = {2, 0};
+  for (int pass = 0; pass < 2; ++pass) {
+    const int shape = forced >= 0 ? forced : order[pass];
+    const int gmin = (forced >= 0 || pass == 1) ? 64 : 160;
+    for (int G = 256; G >= gmin; G -= 32)
+      if (fits(shape, G)) { *G_out = G; *shape_out = shape; return true; }
+    if (forced >= 0) break;
   }
+  return false;
 }
 
 cudaError_t launch_grid2d_build(const float *d_cent, int k, const Grid2D &g, uint16_t *d_table,
@@ -540,11 +742,11 @@ cudaError_t launch_grid2d_map(const float *d_pts, int64_t n, const float *d_cent
   if (n <= 0) return cudaSuccess;
   if (k > kMaxK) return cudaErrorInvalidValue;
 #define HGM_ARGS d_pts, n, d_cent, k, g, d_table, d_cand, d_sums, d_counts, d_assign, sm_count, smem_optin, s
-  switch (active_variant()) {
+  switch (g.shape) {
+    case 0: return launch_shape<ShapeA>(HGM_ARGS);
     case 1: return launch_shape<ShapeB>(HGM_ARGS);
-    case 2: return launch_shape<ShapeC>(HGM_ARGS);
     case 3: return launch_shape<ShapeD>(HGM_ARGS);
-    default: return launch_shape<ShapeA>(HGM_ARGS);
+    default: return launch_shape<ShapeC>(HGM_ARGS);
   }
 #undef HGM_ARGS
 }
