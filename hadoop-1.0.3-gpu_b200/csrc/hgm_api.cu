@@ -181,6 +181,11 @@ int ctx_shape(hgm_ctx *c, int *device, int *k, int *d, cudaStream_t *stream, voi
   return 0;
 }
 int ctx_fail(hgm_ctx *c, int code, const char *msg) { return fail(c, code, "%s", msg); }
+// for entry points that live in other translation units and have no ctx
+int report_error(int code, const char *msg) { return fail(nullptr, code, "%s", msg); }
+bool plan_grid2d_for(const float *cent, int k, size_t smem_optin, Grid2D *out) {
+  return plan_grid2d(cent, k, smem_optin, out);
+}
 }  // namespace hgm
 
 extern "C" {

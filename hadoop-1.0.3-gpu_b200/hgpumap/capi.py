@@ -57,6 +57,7 @@ SIGNATURES = {
     "hgm_stream": (C.c_int, [_c_ctx, C.POINTER(_p)]),
     "hgm_last_map_ms": (C.c_int, [_c_ctx, C.POINTER(C.c_float), C.POINTER(C.c_int32)]),
     "hgm_launch_count": (C.c_int, [_c_ctx, C.POINTER(C.c_int64)]),
+    "hgm_map_device_static": (C.c_int, [C.c_int, _p, C.c_int64, _p, C.c_int32, C.c_int32, _p, _p, _p, _p]),
     "hgm_device_alloc": (C.c_int, [_c_ctx, C.c_size_t, C.POINTER(_p)]),
     "hgm_device_free": (C.c_int, [_c_ctx, _p]),
     "hgm_host_alloc": (C.c_int, [_c_ctx, C.c_size_t, C.POINTER(_p)]),
@@ -272,6 +273,22 @@ class GpuMapSlot:
         c = np.ascontiguousarray(centres, dtype=np.float32)
         self._check(self._lib.hgm_synth_points_device(self._ctx, seed, first, n, c.shape[1], c.shape[0],
                                                       _ptr(c), d_out))
+
+
+def map_device_static(device: int, d_points: int, n_points: int, centroids: np.ndarray,
+                      d_assign: int | None = None, stream: int | None = None):
+    """hgm_map_device_static: the d == 2 map task without any device allocation (the scratch
+    is a static device array inside the library).  Returns (sums[k,2] f64, counts[k] i64)."""
+    lib = load_library()
+    c = np.ascontiguousarray(centroids, dtype=np.float32)
+    k, d = c.shape
+    sums = np.zeros((k, d), dtype=np.float64)
+    counts = np.zeros(k, dtype=np.int64)
+    rc = lib.hgm_map_device_static(device, d_points, n_points, _ptr(c), k, d, _ptr(sums), _ptr(counts),
+                                   d_assign, stream)
+    if rc != 0:
+        raise HgmError(rc, lib.hgm_last_error(None).decode())
+    return sums, counts
 
 
 def synth_centres(seed: int, k: int, d: int) -> np.ndarray:

@@ -140,6 +140,25 @@ int hgm_last_map_ms(hgm_ctx *ctx, float *ms, int32_t *launches);
 /* Total kernels this ctx has launched since hgm_open. */
 int hgm_launch_count(hgm_ctx *ctx, int64_t *launches);
 
+/* The d == 2 map task for a caller that is not allowed to allocate device memory -- a slot
+ * running inside an HBM budget someone else owns (a TaskTracker's per-slot arena, a JVM or
+ * pool allocator that holds every byte), where cudaMalloc is off limits and its device-wide
+ * synchronisation would stall the other slots.  It has no counterpart in the reference.
+ * Nothing is allocated: the cell index, the centroid copy and the partial sums live in one
+ * static device array of about 1.16 MiB that every GPU loading this library holds until the
+ * process exits.  Limits: d must be 2, 1 <= k <= 1024, and the centroid table must be
+ * indexable (finite, |coordinate| <= 1e18); otherwise HGM_EINVAL with an explanation.
+ * d_points (n_points rows, 8-byte aligned) and d_assign_or_null are device pointers;
+ * centroids (k*2 floats), sums_kxd and counts_k are host pointers; cuda_stream is a
+ * cudaStream_t or NULL.  The call returns after the results are in the host arrays.
+ * All calls on one GPU share that array, which keeps the previous call's contents (the call
+ * clears what it accumulates into): calls that overlap on a GPU race -- run them one at a
+ * time.  The first call on a device also looks up the array's device address; make that
+ * first call before starting any stream capture. */
+int hgm_map_device_static(int device_id, const float *d_points, int64_t n_points,
+                          const float *centroids, int32_t k, int32_t d, double *sums_kxd,
+                          int64_t *counts_k, int32_t *d_assign_or_null, void *cuda_stream);
+
 /* Device / pinned-host memory for hosts that have no CUDA runtime of their own (JNI). */
 int hgm_device_alloc(hgm_ctx *ctx, size_t nbytes, void **d_ptr);
 int hgm_device_free(hgm_ctx *ctx, void *d_ptr);
