@@ -108,3 +108,60 @@ def kmeans_downlink(points, centroid_path, k, d, fmt="binary", num_reduces=1, pe
     else:
         raise ValueError(fmt)
     return dl.close()
+
+
+# ---- socket mode: play the Java task (pipes/Application.java:130-215) --------------------------
+
+def java_digest(password: bytes, msg: bytes) -> bytes:
+    """base64(HMAC-SHA1(password, msg)) as SecureShuffleUtils.hashFromString / the child's
+    createDigest (HadoopPipes.cc:421-448) compute it."""
+    import base64
+    import hashlib
+    import hmac
+
+    return base64.b64encode(hmac.new(password, msg, hashlib.sha1).digest())
+
+
+def run_child_over_socket(binary, downlink_after_auth: wire.Downlink, password=b"job-token-secret",
+                          challenge=b"1234567890123456", bad_digest=False, timeout=60, args=()):
+    """Listen on a loopback port, start the child with hadoop.pipes.command.port and the
+    password file, authenticate, send the downlink, collect the uplink until EOF."""
+    import socket
+
+    tmp = tempfile.mkdtemp(prefix="pipes_sock_")
+    secret = os.path.join(tmp, "jobTokenPassword")
+    with open(secret, "wb") as f:
+        f.write(password)
+    os.chmod(secret, 0o400)
+    server = socket.socket(socket.AF_INET, socket.SOCK_STREAM)
+    server.bind(("127.0.0.1", 0))
+    server.listen(4)
+    port = server.getsockname()[1]
+    env = {"hadoop.pipes.command.port": str(port), "hadoop.pipes.shared.secret.location": secret,
+           "TMPDIR": tmp, "PATH": os.environ.get("PATH", "")}
+    for key in ("LD_LIBRARY_PATH", "CUDA_VISIBLE_DEVICES"):
+        if key in os.environ:
+            env[key] = os.environ[key]
+    proc = subprocess.Popen([binary, *args], env=env, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+    server.settimeout(timeout)
+    conn, _ = server.accept()
+    conn.settimeout(timeout)
+    digest = java_digest(password, challenge)
+    if bad_digest:
+        digest = b"A" + digest[1:]
+    expected = java_digest(password, digest)
+    auth = wire.Downlink().authenticate(digest.decode(), challenge.decode()).to_bytes()
+    conn.sendall(auth + downlink_after_auth.to_bytes())
+    chunks = []
+    try:
+        while True:
+            data = conn.recv(1 << 16)
+            if not data:
+                break
+            chunks.append(data)
+    except (socket.timeout, ConnectionResetError):
+        pass
+    out, err = proc.communicate(timeout=timeout)
+    conn.close()
+    server.close()
+    return proc.returncode, b"".join(chunks), err, expected
