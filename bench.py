@@ -297,13 +297,21 @@ def run_ours(args):
         sampler.start()
         sampler.wait_first()
     # The K timed steps last only milliseconds, less than nvidia-smi's sampling period, so
-    # the clocks are sampled over >= 1 s of the identical load run back to back with (and
-    # including) the timed region; these extra steps are untimed warm-up.
+    # the clocks are sampled over ~1 s of the identical load run back to back with (and
+    # including) the timed region; these extra steps are untimed warm-up.  Every rank runs the
+    # SAME number of them (a step holds a collective): the count is agreed on first.
+    t_probe = time.perf_counter()
+    for _ in range(8):
+        step()
+    slot.sync()
+    per_step = torch.tensor([(time.perf_counter() - t_probe) / 8], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(per_step, op=dist.ReduceOp.MAX)
+    load_steps = int(min(4000, max(16, 1.0 / max(per_step.item(), 1e-5))))
     t_load0 = time.perf_counter()
-    while time.perf_counter() - t_load0 < 1.0:
-        for _ in range(8):
-            step()
-        slot.sync()
+    for _ in range(load_steps):
+        step()
+    slot.sync()
     launches0 = slot.launch_count()
     barrier()
     ev0.record(stream)
