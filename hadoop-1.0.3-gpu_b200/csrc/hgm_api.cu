@@ -287,7 +287,7 @@ int hgm_set_centroids(hgm_ctx *c, const float *centroids, int32_t k, int32_t d) 
       if (!c->d_table || g.G != c->grid.G) {
         cudaFree(c->d_table); cudaFree(c->d_cand);
         c->d_table = nullptr; c->d_cand = nullptr;
-        CU(c, cudaMalloc(&c->d_table, (size_t)g.G * g.G * 2 + 16));
+        CU(c, cudaMalloc(&c->d_table, grid2d_table_bytes(g.G)));
         CU(c, cudaMalloc(&c->d_cand, (size_t)g.G * g.G * kMaxCand * 2));
       }
       c->grid = g;

@@ -34,6 +34,11 @@ constexpr uint32_t kMagicBits = 0x4B000000u;  // bits of 2^23
 constexpr uint16_t kCellBrute = 0xFFFFu;      // cell entry: scan all k centroids
 constexpr uint16_t kCellMulti = 0x8000u;      // cell entry: 0x8000 | candidate count (2..8)
 constexpr int kMaxCand = 8;
+// 8-bit copy of the table for k <= kTable8MaxK: cluster id, or kTable8Multi = "look at the 16-bit entry"
+constexpr int kTable8MaxK = 254;
+constexpr uint8_t kTable8Multi = 0xFF;
+// bytes of the table buffer for a G x G grid: 16-bit table, then the 8-bit copy
+inline size_t grid2d_table_bytes(int G) { return (size_t)G * G * 3 + 32; }
 
 // launchers (each returns the CUDA error of its launch)
 cudaError_t launch_grid2d_build(const float *d_cent, int k, const Grid2D &g, uint16_t *d_table,

@@ -11,7 +11,7 @@
 // caller's buffers lives in ONE file-scope device array, `g_scratch` below.
 //
 // Consequences a caller must know:
-//  * every GPU that loads libhgpumap.so carries the array (kScratchBytes, ~1.16 MiB) until
+//  * every GPU that loads libhgpumap.so carries the array (kScratchBytes, ~1.22 MiB) until
 //    the process exits, whether this entry point is used or not;
 //  * the job is limited to what fits: d == 2, k <= kStaticMaxK, and a centroid table the cell
 //    index can hold (finite, |coordinate| <= 1e18); anything else is refused with a message;
@@ -37,7 +37,7 @@ namespace {
 
 constexpr int kStaticMaxK = 1024;
 constexpr int kStaticMaxG = 256;
-constexpr size_t kTableBytes = (size_t)kStaticMaxG * kStaticMaxG * 2;                  // 128 KiB
+constexpr size_t kTableBytes = ((size_t)kStaticMaxG * kStaticMaxG * 3 + 32 + 255) & ~size_t(255);  // 192 KiB: 16-bit table + 8-bit copy
 constexpr size_t kCandBytes = (size_t)kStaticMaxG * kStaticMaxG * hgm::kMaxCand * 2;   // 1 MiB
 constexpr size_t kCentBytes = (size_t)kStaticMaxK * 2 * 4;                             // 8 KiB
 constexpr size_t kPartialBytes = (size_t)kStaticMaxK * (2 * 8 + 8);                    // 24 KiB

@@ -28,6 +28,8 @@
 // per-CTA FP64 partials leave the SM once, as k*3 RED.ADD.F64/U64 to global.
 #include <stdlib.h>
 
+#include <type_traits>
+
 #include "hgm_internal.h"
 
 namespace hgm {
@@ -94,6 +96,8 @@ __device__ __forceinline__ float dist2(float x, float y, float2 c) {
 __global__ void __launch_bounds__(256) grid2d_build_kernel(const float *__restrict__ cent, int k,
                                                            Grid2D g, uint16_t *__restrict__ table,
                                                            uint16_t *__restrict__ cand) {
+  // table8 (one byte per cell, for k <= kTable8MaxK) follows the 16-bit table in the same buffer
+  uint8_t *const table8 = reinterpret_cast<uint8_t *>(table + (size_t)g.G * g.G);
   extern __shared__ double2 sc[];
   for (int c = threadIdx.x; c < k; c += blockDim.x)
     sc[c] = make_double2((double)cent[2 * c], (double)cent[2 * c + 1]);
@@ -144,16 +148,19 @@ __global__ void __launch_bounds__(256) grid2d_build_kernel(const float *__restri
       ++cnt;
     }
   }
+  uint16_t entry;
   if (ix == g.G - 1 || iy == g.G - 1) {
-    table[cell] = kCellBrute;  // the kernel clamps everything outside the grid onto this border
+    entry = kCellBrute;  // the kernel clamps everything outside the grid onto this border
   } else if (cnt == 1) {
-    table[cell] = (uint16_t)c0;
+    entry = (uint16_t)c0;
   } else if (cnt <= kMaxCand) {
-    table[cell] = (uint16_t)(kCellMulti | cnt);
+    entry = (uint16_t)(kCellMulti | cnt);
     for (int i = 0; i < kMaxCand; ++i) cand[(size_t)cell * kMaxCand + i] = i < cnt ? list[i] : 0;
   } else {
-    table[cell] = kCellBrute;
+    entry = kCellBrute;
   }
+  table[cell] = entry;
+  table8[cell] = entry < kCellMulti ? (uint8_t)(entry < kTable8Multi ? entry : kTable8Multi) : kTable8Multi;
 }
 
 // ---- the map kernel ---------------------------------------------------------------------
@@ -162,38 +169,38 @@ __global__ void __launch_bounds__(256) grid2d_build_kernel(const float *__restri
 // tiles, its sort buffer, bin counters and FP64 partials, and synchronises on its own named
 // barrier, so one group's sum phase overlaps another's load/lookup/scatter phase.
 //
-// The sort buffer is a [rank][bin] "striped" array, W = k + 16 bins wide and R rows high:
-// bins 0..k-1 are the clusters; bins k..k+15 are two alternating sets of eight "unresolved"
-// bins for the points of multi-candidate cells.  A point's slot is rank*W + bin, the rank
-// coming from one native integer ATOMS on the bin's counter: no offsets, no scan.
+// The sort buffer holds, per group:
+//   - a [rank][cluster] "striped" array, k clusters wide and R rows high: a point of a
+//     single-candidate cell goes to slot rank*k + cluster, its rank coming from one native
+//     integer ATOMS on the cluster's counter -- no offsets, no scan;
+//   - two queues (they alternate by tile) for the points of multi-candidate cells;
+//   - an overflow region at the top for ranks that do not fit (heavy skew).
 //
 // Per tile (kGroupThreads * 8 points) and group, two phases and two barriers:
-//   1a each thread takes 8 points: cell -> bin -> rank -> store.  Straight-line code.
-//   1b the unresolved points the PREVIOUS tile left behind are resolved, one per thread, by
-//      the exact candidate scan, and stored into this tile's columns like any other point.
+//   1a each thread takes 8 points: cell -> (cluster | queue) -> rank -> store.  Straight line.
+//   1b the queue the PREVIOUS tile filled is drained, one point per thread: exact candidate
+//      scan, then the point is stored into this tile's striped array like any other.
 //   2  owner lanes walk their cluster's column (consecutive lanes = consecutive addresses,
 //      conflict-free) and add it in FP64 to partials they keep in registers for the whole
-//      kernel.
-// A point whose rank is >= R (a cluster much longer than the average in this tile) goes to
-// an overflow region at the top of the buffer and is added with a shared-memory CAS instead;
-// a tile that fills even that region is redone by the packed counting-sort path.
+//      kernel; overflow points are added with a shared-memory CAS.
+// A tile that fills even the overflow region is redone by the packed counting-sort path.
 __host__ __device__ inline size_t align16(size_t x) { return (x + 15) & ~size_t(15); }
 
-constexpr int kUnres = 8;            // unresolved bins per parity (power of two)
-constexpr int kExtra = 2 * kUnres;   // extra columns of the striped layout
+constexpr int kHistExtra = 4;  // queue counters [2], overflow counters [2]
 
 // per-group shared memory:
-// [sort buffer slots float2][acc 2k f64][cnt k i64][hist k+kExtra+2 i32][offs k+1 i32][late k i32]
+// [sort buffer slots float2][acc 2k f64][cnt k i64][hist k+4 i32][offs k+1 i32][late k i32]
 // [flag 16 B][lidx (slots) u16, assign only]
 __host__ __device__ inline size_t group_small_bytes(int k) {
-  return (size_t)k * 16 + (size_t)k * 8 + align16((size_t)(k + kExtra + 2) * 4) +
+  return (size_t)k * 16 + (size_t)k * 8 + align16((size_t)(k + kHistExtra) * 4) +
          align16((size_t)(k + 1) * 4) + align16((size_t)k * 4) + 16;
 }
 __host__ __device__ inline size_t group_bytes(int slots, int k, bool with_assign) {
   return (size_t)slots * 8 + group_small_bytes(k) + (with_assign ? align16((size_t)slots * 2) : 0);
 }
+__host__ __device__ inline bool use_table8(int k) { return k <= kTable8MaxK; }
 __host__ __device__ inline size_t shared_head_bytes(int G, int k) {
-  return align16((size_t)G * G * 2) + align16((size_t)k * 8) + 16;
+  return align16((size_t)G * G * (use_table8(k) ? 1 : 2)) + align16((size_t)k * 8) + 16;
 }
 
 __device__ __forceinline__ void group_sync(int group, int nthreads) {
@@ -210,10 +217,11 @@ __device__ __forceinline__ uint32_t cell_of(float x, float y, const Grid2D &g) {
 }
 
 // exact scan of one point over its cell's candidates (or over all k): ascending index,
-// strict '<' from (+inf, 0) -- the reference scan restricted to a superset of its winners
-__device__ __noinline__ int resolve_slow(float x, float y, uint32_t entry, uint32_t cell,
-                                         const float2 *cent_s, int k,
-                                         const uint16_t *__restrict__ cand) {
+// strict '<' from (+inf, 0) -- the reference scan restricted to a superset of its winners.
+// Multi-candidate cells list at least two candidates; two is by far the common case.
+__device__ __forceinline__ int resolve_exact(float x, float y, uint32_t entry, uint32_t cell,
+                                             const float2 *cent_s, int k,
+                                             const uint16_t *__restrict__ cand) {
   float best = INFINITY;
   int arg = 0;
   if (entry == kCellBrute) {
@@ -224,11 +232,15 @@ __device__ __noinline__ int resolve_slow(float x, float y, uint32_t entry, uint3
   } else {
     const int cnt = entry & 0x7FFF;
     const uint4 ids = __ldg(reinterpret_cast<const uint4 *>(cand + (size_t)cell * kMaxCand));
-    const uint32_t w[4] = {ids.x, ids.y, ids.z, ids.w};
-#pragma unroll
-    for (int i = 0; i < kMaxCand; ++i) {
-      if (i < cnt) {
-        const int c = (w[i >> 1] >> ((i & 1) * 16)) & 0xFFFF;
+    const int c0 = ids.x & 0xFFFF, c1 = ids.x >> 16;
+    const float d0 = dist2(x, y, cent_s[c0]), d1 = dist2(x, y, cent_s[c1]);
+    if (d0 < best) { best = d0; arg = c0; }
+    if (d1 < best) { best = d1; arg = c1; }
+    if (cnt > 2) {
+      const unsigned long long lo = ((unsigned long long)ids.y << 32) | ids.x;
+      const unsigned long long hi = ((unsigned long long)ids.w << 32) | ids.z;
+      for (int i = 2; i < cnt; ++i) {
+        const int c = (int)(((i < 4 ? lo : hi) >> (16 * (i & 3))) & 0xFFFF);
         const float dd = dist2(x, y, cent_s[c]);
         if (dd < best) { best = dd; arg = c; }
       }
@@ -239,37 +251,42 @@ __device__ __noinline__ int resolve_slow(float x, float y, uint32_t entry, uint3
 
 constexpr uint16_t kNoIndex = 0xFFFF;  // lidx value: this entry's assignment is already written
 
-template <class S, bool kVec4, bool kAssign>
+template <class S, bool kVec4, bool kAssign, bool kT8>
 __global__ void __launch_bounds__(S::kThreads, 1)
     grid2d_map_kernel(const float *__restrict__ pts, long long n, const float *__restrict__ cent,
-                      int k, Grid2D g, int slots, int rcap, const uint16_t *__restrict__ table,
-                      const uint16_t *__restrict__ cand, double *__restrict__ g_sums,
-                      unsigned long long *__restrict__ g_counts, int32_t *__restrict__ assign) {
+                      int k, Grid2D g, int slots, int rcap, int qcap,
+                      const uint16_t *__restrict__ table, const uint16_t *__restrict__ cand,
+                      double *__restrict__ g_sums, unsigned long long *__restrict__ g_counts,
+                      int32_t *__restrict__ assign) {
   constexpr int kGT = S::kGroupThreads;
   constexpr int kTile = S::kTile;
+  using entry_t = typename std::conditional<kT8, uint8_t, uint16_t>::type;
+  constexpr uint32_t kMulti = kT8 ? (uint32_t)kTable8Multi : (uint32_t)kCellMulti;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int group = threadIdx.x / kGT;
   const int t = threadIdx.x % kGT;  // thread within the group
-  const int lane = threadIdx.x & 31;
-  const int W = k + kExtra;            // bins per row of the striped layout
-  const int tend = slots - rcap * W;   // capacity of the overflow region (slots-1 downwards)
+  const int qoff = rcap * k;                      // queue 0 starts here, queue 1 at qoff + qcap
+  const int tend = slots - qoff - 2 * qcap;       // capacity of the overflow region (slots-1 downwards)
 
   // carve shared memory (pointers computed, not looked up: no local-memory struct)
-  uint16_t *const table_s = reinterpret_cast<uint16_t *>(smem_raw);
-  float2 *const cent_s = reinterpret_cast<float2 *>(smem_raw + align16((size_t)g.G * g.G * 2));
+  const size_t table_bytes_al = align16((size_t)g.G * g.G * sizeof(entry_t));
+  entry_t *const table_s = reinterpret_cast<entry_t *>(smem_raw);
+  float2 *const cent_s = reinterpret_cast<float2 *>(smem_raw + table_bytes_al);
   uint64_t *const bar = reinterpret_cast<uint64_t *>(reinterpret_cast<unsigned char *>(cent_s) + align16((size_t)k * 8));
   unsigned char *const gb = smem_raw + shared_head_bytes(g.G, k) + (size_t)group * group_bytes(slots, k, kAssign);
   float2 *const sorted = reinterpret_cast<float2 *>(gb);
   double *const acc = reinterpret_cast<double *>(gb + (size_t)slots * 8);
   long long *const cnt = reinterpret_cast<long long *>(acc + 2 * k);
-  int *const hist = reinterpret_cast<int *>(cnt + k);  // W bin counters, then 2 overflow counters
-  int *const offs = reinterpret_cast<int *>(reinterpret_cast<unsigned char *>(hist) + align16((size_t)(W + 2) * 4));
+  int *const hist = reinterpret_cast<int *>(cnt + k);  // k cluster counters, 2 queue counters, 2 overflow counters
+  int *const offs = reinterpret_cast<int *>(reinterpret_cast<unsigned char *>(hist) + align16((size_t)(k + kHistExtra) * 4));
   int *const late = reinterpret_cast<int *>(reinterpret_cast<unsigned char *>(offs) + align16((size_t)(k + 1) * 4));
   int *const flag = reinterpret_cast<int *>(reinterpret_cast<unsigned char *>(late) + align16((size_t)k * 4));
   uint16_t *const lidx = reinterpret_cast<uint16_t *>(reinterpret_cast<unsigned char *>(flag) + 16);
 
   // stage the cell table and the centroids with TMA bulk copies (SASS: UBLKCP)
-  const uint32_t table_bytes = (uint32_t)align16((size_t)g.G * g.G * 2);
+  const unsigned char *table_src = kT8 ? reinterpret_cast<const unsigned char *>(table + (size_t)g.G * g.G)
+                                       : reinterpret_cast<const unsigned char *>(table);
+  const uint32_t table_bytes = (uint32_t)table_bytes_al;
   const uint32_t cent_bytes = (uint32_t)align16((size_t)k * 8);
   if (threadIdx.x == 0) mbar_init(bar, 1);
   __syncthreads();
@@ -277,8 +294,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
     mbar_expect_tx(bar, table_bytes + cent_bytes);
     for (uint32_t o = 0; o < table_bytes; o += 32768) {
       const uint32_t sz = table_bytes - o < 32768 ? table_bytes - o : 32768;
-      tma_bulk_g2s(reinterpret_cast<unsigned char *>(table_s) + o,
-                   reinterpret_cast<const unsigned char *>(table) + o, sz, bar);
+      tma_bulk_g2s(reinterpret_cast<unsigned char *>(table_s) + o, table_src + o, sz, bar);
     }
     tma_bulk_g2s(cent_s, cent, cent_bytes, bar);
   }
@@ -288,7 +304,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
     acc[2 * c + 1] = 0.0;
     cnt[c] = 0;
   }
-  for (int c = t; c < W + 2; c += kGT) hist[c] = 0;
+  for (int c = t; c < k + kHistExtra; c += kGT) hist[c] = 0;
   if (t == 0) *flag = 0;
   mbar_wait(bar, 0);
   __syncthreads();
@@ -311,37 +327,41 @@ __global__ void __launch_bounds__(S::kThreads, 1)
   // raw tile loads: thread t owns the point pairs (i*kGT + t), i = 0..kPPT/2-1
   auto load_tile = [&](long long tile, float4 (&buf)[kPPT / 2]) {
     const long long base = tile * kTile;
-    const bool full = base + kTile <= n;
+    const float *src = pts + 2 * base + 4 * t;
+    if (base + kTile <= n) {  // full tile: no bounds checks
 #pragma unroll
-    for (int i = 0; i < kPPT / 2; ++i) {
-      const long long p = base + 2ll * (i * kGT + t);
-      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (kVec4) {
-        if (full || p + 1 < n) {
-          v = __ldcs(reinterpret_cast<const float4 *>(pts + 2 * p));
-        } else if (p < n) {
-          const float2 h = __ldcs(reinterpret_cast<const float2 *>(pts + 2 * p));
-          v.x = h.x; v.y = h.y;
-        }
-      } else {
-        if (full || p < n) {
-          const float2 h = __ldcs(reinterpret_cast<const float2 *>(pts + 2 * p));
-          v.x = h.x; v.y = h.y;
-        }
-        if (full || p + 1 < n) {
-          const float2 h = __ldcs(reinterpret_cast<const float2 *>(pts + 2 * p + 2));
-          v.z = h.x; v.w = h.y;
+      for (int i = 0; i < kPPT / 2; ++i) {
+        if (kVec4) {
+          buf[i] = __ldcs(reinterpret_cast<const float4 *>(src + 4 * i * kGT));
+        } else {
+          const float2 a = __ldcs(reinterpret_cast<const float2 *>(src + 4 * i * kGT));
+          const float2 b = __ldcs(reinterpret_cast<const float2 *>(src + 4 * i * kGT + 2));
+          buf[i] = make_float4(a.x, a.y, b.x, b.y);
         }
       }
-      buf[i] = v;
+    } else {
+      const int live = (int)(n - base);
+#pragma unroll
+      for (int i = 0; i < kPPT / 2; ++i) {
+        const int local = 2 * (i * kGT + t);
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (local < live) {
+          const float2 a = __ldcs(reinterpret_cast<const float2 *>(src + 4 * i * kGT));
+          v.x = a.x; v.y = a.y;
+        }
+        if (local + 1 < live) {
+          const float2 b = __ldcs(reinterpret_cast<const float2 *>(src + 4 * i * kGT + 2));
+          v.z = b.x; v.w = b.y;
+        }
+        buf[i] = v;
+      }
     }
   };
-  // pull a whole tile into L2 ahead of use: one 128-byte line per prefetch
+  // pull the next tile into L2 ahead of use: one 128-byte line per prefetch
   auto prefetch_tile = [&](long long tile) {
-    const char *b = reinterpret_cast<const char *>(pts + 2 * tile * kTile);
-    const long long lim = 8 * n;
-    for (int o = t * 128; o < kTile * 8; o += kGT * 128)
-      if (8 * tile * kTile + o < lim) asm volatile("prefetch.global.L2 [%0];" ::"l"(b + o));
+    constexpr int kLines = kTile * 8 / 128;
+    if (t < kLines && (tile + 1) * kTile <= n)
+      asm volatile("prefetch.global.L2 [%0];" ::"l"(reinterpret_cast<const char *>(pts + 2 * tile * kTile) + t * 128));
   };
   // add a partial to the group's accumulators from any thread (shared FP64 atomic = CAS loop;
   // only overflow points and the packed path come here)
@@ -349,22 +369,26 @@ __global__ void __launch_bounds__(S::kThreads, 1)
     atomicAdd(&acc[2 * c], ax);
     atomicAdd(&acc[2 * c + 1], ay);
   };
+  // the 16-bit entry of a cell (the 8-bit shared table only says "multi")
+  auto entry16 = [&](uint32_t cell) -> uint32_t {
+    return kT8 ? (uint32_t)__ldg(table + cell) : (uint32_t)table_s[cell];
+  };
   // resolve one stored point exactly and add it with CAS (overflow region, packed path)
   auto settle = [&](float2 v, long long base, uint16_t li) {
     const uint32_t cell = cell_of(v.x, v.y, g);
-    const uint32_t e = table_s[cell];
-    const int c = e < kCellMulti ? (int)e : resolve_slow(v.x, v.y, e, cell, cent_s, k, cand);
+    const uint32_t e = entry16(cell);
+    const int c = e < kCellMulti ? (int)e : resolve_exact(v.x, v.y, e, cell, cent_s, k, cand);
     flush(c, (double)v.x, (double)v.y);
     atomicAdd(&late[c], 1);
     if (kAssign && li != kNoIndex) assign[base + li] = c;
   };
-  // rank a point in `bin` and store it; ranks beyond the striped rows go to the overflow
-  // region of parity `par`; returns false if even that is full
-  auto place = [&](float x, float y, int bin, int par, uint16_t li) -> bool {
-    const int r = atomicAdd(&hist[bin], 1);
-    int pos = r * W + bin;
+  // rank a resolved point in cluster c and store it; ranks beyond the striped rows go to the
+  // overflow region of parity `par`; returns false if even that is full
+  auto place = [&](float x, float y, int c, int par, uint16_t li) -> bool {
+    const int r = atomicAdd(&hist[c], 1);
+    int pos = r * k + c;
     if (r >= rcap) {
-      const int r2 = atomicAdd(&hist[W + par], 1);
+      const int r2 = atomicAdd(&hist[k + 2 + par], 1);
       if (r2 >= tend) return false;
       pos = slots - 1 - r2;
     }
@@ -381,13 +405,13 @@ __global__ void __launch_bounds__(S::kThreads, 1)
   }
   int par = 0;
   long long prev_base = 0;
-  bool pending = false;  // the previous tile left unresolved points in its parity's bins
+  bool pending = false;  // the previous tile left points in its queue
   for (long long tile = tile0; tile < ntiles || pending; tile += tile_stride, par ^= 1) {
     const bool has_tile = tile < ntiles;
     const long long base = tile * kTile;  // first point of the tile (even)
     const int live = has_tile ? (int)min((long long)kTile, n - base) : 0;
-    const int ubase = k + par * kUnres;         // this tile's unresolved bins
-    const int pbase = k + (par ^ 1) * kUnres;   // the previous tile's
+    const int my_q = qoff + par * qcap;            // this tile's queue
+    const int prev_q = qoff + (par ^ 1) * qcap;    // the previous tile's
     float xs[kPPT], ys[kPPT];
 
     if (has_tile) {
@@ -402,33 +426,28 @@ __global__ void __launch_bounds__(S::kThreads, 1)
       if (S::kRegPrefetch && tile + tile_stride < ntiles) load_tile(tile + tile_stride, buf);
     }
 
-    // ---- phase 1a: cell -> bin -> rank -> slot ----------------------------------------------
+    // ---- phase 1a: cell -> (cluster | queue) -> rank -> slot --------------------------------
     bool lost = false;
-    const int ubin = ubase + (lane & (kUnres - 1));
+    int *const my_qcount = &hist[k + par];
     if (live == kTile) {  // full tile: straight-line code, no bounds checks
 #pragma unroll
       for (int i = 0; i < kPPT; ++i) {
         const uint32_t e = table_s[cell_of(xs[i], ys[i], g)];
-        const bool resolved = e < kCellMulti;
-        const int bin = resolved ? (int)e : ubin;
-        const int r = atomicAdd(&hist[bin], 1);
+        const bool resolved = e < kMulti;
+        const int r = atomicAdd(resolved ? &hist[e] : my_qcount, 1);
         const int local = 2 * ((i >> 1) * kGT + t) + (i & 1);
         if (kAssign && resolved) assign[base + local] = (int)e;
-        if (__any_sync(0xFFFFFFFFu, r >= rcap)) {  // rare: some lane's cluster outgrew the rows
-          int pos = r * W + bin;
-          bool ok = true;
-          if (r >= rcap) {
-            const int r2 = atomicAdd(&hist[W + par], 1);
+        int pos = resolved ? r * k + (int)e : my_q + r;
+        bool ok = true;
+        if (__any_sync(0xFFFFFFFFu, r >= (resolved ? rcap : qcap))) {  // rare: a bin outgrew its room
+          if (r >= (resolved ? rcap : qcap)) {
+            const int r2 = atomicAdd(&hist[k + 2 + par], 1);
             ok = r2 < tend;
             pos = slots - 1 - r2;
           }
-          if (ok) {
-            sorted[pos] = make_float2(xs[i], ys[i]);
-            if (kAssign) lidx[pos] = resolved ? kNoIndex : (uint16_t)local;
-          }
           lost |= !ok;
-        } else {
-          const int pos = r * W + bin;
+        }
+        if (ok) {
           sorted[pos] = make_float2(xs[i], ys[i]);
           if (kAssign) lidx[pos] = resolved ? kNoIndex : (uint16_t)local;
         }
@@ -439,48 +458,60 @@ __global__ void __launch_bounds__(S::kThreads, 1)
         const int local = 2 * ((i >> 1) * kGT + t) + (i & 1);  // index within the tile
         if (local < live) {
           const uint32_t e = table_s[cell_of(xs[i], ys[i], g)];
-          const bool resolved = e < kCellMulti;
-          if (kAssign && resolved) assign[base + local] = (int)e;
-          lost |= !place(xs[i], ys[i], resolved ? (int)e : ubin, par, resolved ? kNoIndex : (uint16_t)local);
+          if (e < kMulti) {
+            if (kAssign) assign[base + local] = (int)e;
+            lost |= !place(xs[i], ys[i], (int)e, par, kNoIndex);
+          } else {
+            const int r = atomicAdd(my_qcount, 1);
+            int pos = my_q + r;
+            bool ok = true;
+            if (r >= qcap) {
+              const int r2 = atomicAdd(&hist[k + 2 + par], 1);
+              ok = r2 < tend;
+              pos = slots - 1 - r2;
+            }
+            if (ok) {
+              sorted[pos] = make_float2(xs[i], ys[i]);
+              if (kAssign) lidx[pos] = (uint16_t)local;
+            }
+            lost |= !ok;
+          }
         }
       }
     }
-    // ---- phase 1b: resolve what the previous tile could not, into this tile's columns -------
+    // ---- phase 1b: drain the previous tile's queue into this tile's striped array ------------
     if (pending) {
-      for (int u = t; u < kUnres * rcap; u += kGT) {
-        const int j = u & (kUnres - 1), r = u / kUnres;
-        if (r < min(hist[pbase + j], rcap)) {
-          const int pos = r * W + pbase + j;
-          const float2 v = sorted[pos];
-          const uint32_t cell = cell_of(v.x, v.y, g);
-          const int c = resolve_slow(v.x, v.y, table_s[cell], cell, cent_s, k, cand);
-          if (kAssign) assign[prev_base + lidx[pos]] = c;
-          lost |= !place(v.x, v.y, c, par, kNoIndex);
-        }
+      const int nq = min(hist[k + (par ^ 1)], qcap);
+      for (int u = t; u < nq; u += kGT) {
+        const float2 v = sorted[prev_q + u];
+        const uint32_t cell = cell_of(v.x, v.y, g);
+        const int c = resolve_exact(v.x, v.y, entry16(cell), cell, cent_s, k, cand);
+        if (kAssign) assign[prev_base + lidx[prev_q + u]] = c;
+        lost |= !place(v.x, v.y, c, par, kNoIndex);
       }
     }
     if (lost) *flag = 1;
     group_sync(group, kGT);
 
     if (*flag == 0) {
-      // the other parity's unresolved and overflow counters were consumed before the barrier
-      if (t < kUnres) hist[pbase + t] = 0;
-      if (t == kUnres) hist[W + (par ^ 1)] = 0;
+      // the other parity's queue and overflow counters were consumed before the barrier
+      if (t == 0) { hist[k + (par ^ 1)] = 0; hist[k + 2 + (par ^ 1)] = 0; }
       // ---- phase 2: FP64 column sums by the clusters' owner lanes ----------------------------
       if (one_pass) {
         const bool on = my_c < k;
         const int h = on ? hist[my_c] : 0;
         const int m = min(h, rcap);
-        const float2 *col = sorted + my_c;
+        const int step = tpc * k;
+        const float2 *p = sorted + my_c + sub * k;
         int r = sub;
-        for (; r + tpc < m; r += 2 * tpc) {  // two rows per trip
-          const float2 v0 = col[r * W];
-          const float2 v1 = col[(r + tpc) * W];
+        for (; r + tpc < m; r += 2 * tpc, p += 2 * step) {  // two rows per trip
+          const float2 v0 = p[0];
+          const float2 v1 = p[step];
           reg_x += (double)v0.x; reg_y += (double)v0.y;
           reg_x += (double)v1.x; reg_y += (double)v1.y;
         }
         if (r < m) {
-          const float2 v = col[r * W];
+          const float2 v = p[0];
           reg_x += (double)v.x; reg_y += (double)v.y;
         }
         __syncwarp();  // all lanes of the cluster have read h
@@ -494,7 +525,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
           double ax = 0.0, ay = 0.0;
           const float2 *col = sorted + c;
           for (int r = sub; r < m; r += tpc) {
-            const float2 v = col[r * W];
+            const float2 v = col[r * k];
             ax += (double)v.x;
             ay += (double)v.y;
           }
@@ -510,29 +541,26 @@ __global__ void __launch_bounds__(S::kThreads, 1)
           }
         }
       }
-      // overflow region: rare, one point per thread, CAS adds
-      const int nover = min(hist[W + par], tend);
+      // overflow region: rare, one point per thread, CAS adds.  The owner lanes above update
+      // the shared partials without atomics when they are not register-resident: keep the two apart.
+      if (!one_pass) group_sync(group, kGT);
+      const int nover = min(hist[k + 2 + par], tend);
       for (int u = t; u < nover; u += kGT) {
         const int pos = slots - 1 - u;
         settle(sorted[pos], base, kAssign ? lidx[pos] : kNoIndex);
       }
-      pending = has_tile;  // this tile's unresolved bins wait for the next phase 1b
+      pending = has_tile;  // this tile's queue waits for the next phase 1b
       prev_base = base;
     } else {
       // ---- packed path: redo this tile as histogram -> scan -> scatter -> run sums -----------
       // Everything phase 1 stored is discarded; the tile's points are still in xs/ys, the
-      // previous tile's unresolved points still sit in their columns (settled here with CAS).
+      // previous tile's queue is still intact (settled here with CAS).
       if (pending) {
-        for (int u = t; u < kUnres * rcap; u += kGT) {
-          const int j = u & (kUnres - 1), r = u / kUnres;
-          if (r < min(hist[pbase + j], rcap)) {
-            const int pos = r * W + pbase + j;
-            settle(sorted[pos], prev_base, kAssign ? lidx[pos] : kNoIndex);
-          }
-        }
+        const int nq = min(hist[k + (par ^ 1)], qcap);
+        for (int u = t; u < nq; u += kGT) settle(sorted[prev_q + u], prev_base, kAssign ? lidx[prev_q + u] : kNoIndex);
       }
       group_sync(group, kGT);
-      for (int c = t; c < W + 2; c += kGT) hist[c] = 0;
+      for (int c = t; c < k + kHistExtra; c += kGT) hist[c] = 0;
       group_sync(group, kGT);
       int *const ucount = hist + k;  // bin k of the packed layout: every unresolved point
       uint32_t key[kPPT];
@@ -542,7 +570,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
         key[i] = 0xFFFFFFFFu;
         if (local < live) {
           const uint32_t e = table_s[cell_of(xs[i], ys[i], g)];
-          const bool resolved = e < kCellMulti;
+          const bool resolved = e < kMulti;
           const int r = atomicAdd(resolved ? &hist[e] : ucount, 1);
           key[i] = (resolved ? e : (uint32_t)k) | ((uint32_t)r << 16);
         }
@@ -597,9 +625,10 @@ __global__ void __launch_bounds__(S::kThreads, 1)
           cnt[c] += m;
         }
       }
+      group_sync(group, kGT);  // the run sums above write the partials without atomics
       for (int j = offs[k] + t; j < live; j += kGT) settle(sorted[j], base, kAssign ? lidx[j] : kNoIndex);
       group_sync(group, kGT);
-      for (int c = t; c < W + 2; c += kGT) hist[c] = 0;
+      for (int c = t; c < k + kHistExtra; c += kGT) hist[c] = 0;
       if (t == 0) *flag = 0;
       pending = false;
     }
@@ -607,12 +636,12 @@ __global__ void __launch_bounds__(S::kThreads, 1)
   }
 
   // ---- partials -> global: registers first (one_pass), then the group's shared partials ----
-  if (one_pass && my_c < k) {
-    for (int o = tpc >> 1; o > 0; o >>= 1) {
+  if (one_pass) {
+    for (int o = tpc >> 1; o > 0; o >>= 1) {  // every lane takes part in the shuffles
       reg_x += __shfl_xor_sync(0xFFFFFFFFu, reg_x, o);
       reg_y += __shfl_xor_sync(0xFFFFFFFFu, reg_y, o);
     }
-    if (sub == 0 && reg_n) {
+    if (my_c < k && sub == 0 && reg_n) {
       atomicAdd(&g_sums[2 * my_c], reg_x);
       atomicAdd(&g_sums[2 * my_c + 1], reg_y);
       atomicAdd(&g_counts[my_c], (unsigned long long)reg_n);
@@ -645,13 +674,13 @@ int forced_variant() {
 // How the shared memory left after the table is split: slots of the sort buffer per group and
 // rows of the striped layout.  The overflow region keeps at least a quarter tile.
 struct Plan {
-  int slots, rcap;
+  int slots, rcap, qcap;
   size_t smem;
   bool ok;
 };
 template <class S>
 Plan make_plan(int G, int k, bool with_assign, size_t smem_optin) {
-  Plan p{0, 0, 0, false};
+  Plan p{0, 0, 0, 0, false};
   const size_t head = shared_head_bytes(G, k);
   if (head >= smem_optin) return p;
   const size_t per_group = (smem_optin - head) / S::kGroups;
@@ -661,12 +690,14 @@ Plan make_plan(int G, int k, bool with_assign, size_t smem_optin) {
   slots &= ~size_t(7);
   if (slots > 65536) slots = 65536;  // lidx and slot arithmetic are 16-bit
   if ((long long)slots < S::kTile) return p;  // the packed path needs a whole tile
-  const int W = k + kExtra;
-  int rcap = (int)((slots - S::kTile / 4) / W);
+  // queues: 3/16 of a tile each (the benchmark queues ~5 %); overflow region: >= 1/4 tile
+  const int qcap = S::kTile * 3 / 16;
+  int rcap = ((int)slots - 2 * qcap - S::kTile / 4) / k;
   if (rcap < 1) rcap = 0;  // no striped rows: every tile takes the packed path
   if (rcap > 1023) rcap = 1023;
   p.slots = (int)slots;
   p.rcap = rcap;
+  p.qcap = qcap;
   p.smem = head + S::kGroups * group_bytes((int)slots, k, with_assign);
   p.ok = p.smem <= smem_optin;
   return p;
@@ -681,15 +712,23 @@ cudaError_t launch_shape(const float *d_pts, int64_t n, const float *d_cent, int
   if (!plan.ok) return cudaErrorInvalidValue;
   const bool vec4 = (reinterpret_cast<uintptr_t>(d_pts) & 15) == 0;
   const bool asg = d_assign != nullptr;
-  auto kern = vec4 ? (asg ? grid2d_map_kernel<S, true, true> : grid2d_map_kernel<S, true, false>)
-                   : (asg ? grid2d_map_kernel<S, false, true> : grid2d_map_kernel<S, false, false>);
+  const bool t8 = use_table8(k);
+  void (*kern)(const float *, long long, const float *, int, Grid2D, int, int, int, const uint16_t *,
+               const uint16_t *, double *, unsigned long long *, int32_t *);
+  if (t8) {
+    kern = vec4 ? (asg ? grid2d_map_kernel<S, true, true, true> : grid2d_map_kernel<S, true, false, true>)
+                : (asg ? grid2d_map_kernel<S, false, true, true> : grid2d_map_kernel<S, false, false, true>);
+  } else {
+    kern = vec4 ? (asg ? grid2d_map_kernel<S, true, true, false> : grid2d_map_kernel<S, true, false, false>)
+                : (asg ? grid2d_map_kernel<S, false, true, false> : grid2d_map_kernel<S, false, false, false>);
+  }
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)plan.smem);
   if (e != cudaSuccess) return e;
   const long long ntiles = (n + S::kTile - 1) / S::kTile;
   const long long want = (ntiles + S::kGroups - 1) / S::kGroups;
   const int grid = (int)(want < sm_count ? want : sm_count);
   kern<<<grid, S::kThreads, plan.smem, s>>>(d_pts, (long long)n, d_cent, k, g, plan.slots, plan.rcap,
-                                            d_table, d_cand, d_sums, d_counts, d_assign);
+                                            plan.qcap, d_table, d_cand, d_sums, d_counts, d_assign);
   return cudaGetLastError();
 }
 

@@ -145,7 +145,7 @@ int hgm_launch_count(hgm_ctx *ctx, int64_t *launches);
  * pool allocator that holds every byte), where cudaMalloc is off limits and its device-wide
  * synchronisation would stall the other slots.  It has no counterpart in the reference.
  * Nothing is allocated: the cell index, the centroid copy and the partial sums live in one
- * static device array of about 1.16 MiB that every GPU loading this library holds until the
+ * static device array of about 1.22 MiB that every GPU loading this library holds until the
  * process exits.  Limits: d must be 2, 1 <= k <= 1024, and the centroid table must be
  * indexable (finite, |coordinate| <= 1e18); otherwise HGM_EINVAL with an explanation.
  * d_points (n_points rows, 8-byte aligned) and d_assign_or_null are device pointers;
