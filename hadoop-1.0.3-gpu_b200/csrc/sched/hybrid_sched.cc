@@ -1,0 +1,142 @@
+// hybrid_sched.cc -- the fork's hybrid CPU/GPU map assignment rule and a one-TaskTracker
+// simulator around it (include/hgsched.h has the reference citations).
+#include "../../../include/hgsched.h"
+
+#include <algorithm>
+#include <queue>
+#include <vector>
+
+namespace {
+
+// JobQueueTaskScheduler.java:134-177: statistics over the running jobs
+struct QueueStats {
+  int pending = 0;
+  int cpu_mean = 0, gpu_mean = 0;
+  double accel = 0.0;
+};
+
+QueueStats queue_stats(const hgs_job *jobs, int n, int fixes) {
+  QueueStats s;
+  int remaining = 0;
+  long long cpu_sum = 0, gpu_sum = 0;
+  int cpu_jobs = 0, gpu_jobs = 0;
+  for (int i = 0; i < n; ++i) {
+    const hgs_job &j = jobs[i];
+    if (fixes & HGS_FIX_PENDING) {
+      s.pending += j.desired_maps - j.finished_maps - j.running_maps;
+    } else {
+      remaining += j.desired_maps - j.finished_maps;  // :137
+      s.pending += remaining - j.running_maps;        // :139 adds the RUNNING TOTAL, not this job's share
+    }
+    s.cpu_mean = j.cpu_mean_ms;  // :143-144 the last running job wins
+    s.gpu_mean = j.gpu_mean_ms;
+    if (j.cpu_mean_ms) { cpu_sum += j.cpu_mean_ms; ++cpu_jobs; }
+    if (j.gpu_mean_ms) { gpu_sum += j.gpu_mean_ms; ++gpu_jobs; }
+  }
+  if (fixes & HGS_FIX_PER_JOB_ACCEL) {
+    s.cpu_mean = cpu_jobs ? (int)(cpu_sum / cpu_jobs) : 0;
+    s.gpu_mean = gpu_jobs ? (int)(gpu_sum / gpu_jobs) : 0;
+  }
+  s.accel = (s.cpu_mean == 0 || s.gpu_mean == 0) ? 0.0 : (double)s.cpu_mean / (double)s.gpu_mean;  // :175-177
+  if (s.accel == 0.0 && (fixes & HGS_FIX_PRIOR_ACCEL))
+    for (int i = 0; i < n; ++i)
+      if (jobs[i].prior_acceleration > 0.0) s.accel = jobs[i].prior_acceleration;
+  return s;
+}
+
+}  // namespace
+
+extern "C" int hgs_assign(const hgs_job *jobs, int32_t n_jobs, const hgs_tracker *tt, int32_t num_trackers,
+                          int32_t optional, int32_t fixes, int32_t want, hgs_decision *out) {
+  if (!jobs || !tt || !out || n_jobs < 0 || num_trackers < 1 || tt->max_gpu_slots > HGS_MAX_DEVICES) return -22;
+  *out = hgs_decision{};
+  const QueueStats s = queue_stats(jobs, n_jobs, fixes);
+  out->acceleration = s.accel;
+  out->pending_map_load = s.pending;
+  int avail_cpu = tt->max_cpu_slots - tt->running_cpu;  // :257-258
+  int avail_gpu = tt->max_gpu_slots - tt->running_gpu;
+  if (avail_cpu < 0) avail_cpu = 0;
+  if (avail_gpu < 0) avail_gpu = 0;
+  int left = std::max(want, 0);
+
+  // CPU pass (:290-326): skipped near the tail of the job when GPUs alone finish sooner
+  const bool skip_cpu = optional && std::max(s.pending, 0) < s.accel * tt->max_gpu_slots * num_trackers;
+  out->cpu_pass_skipped = skip_cpu ? 1 : 0;
+  if (!skip_cpu) {
+    const int take = std::min(avail_cpu, left);
+    out->n_cpu = take;
+    left -= take;
+  }
+  // GPU pass (:334-387): always; a job without a GPU executable stops the pass (`break`)
+  bool gpu_ok = n_jobs > 0;
+  for (int i = 0; i < n_jobs && i < 1; ++i) gpu_ok = jobs[i].has_gpu_executable != 0;
+  if (gpu_ok) {
+    uint32_t busy = tt->busy_devices;
+    const int scan = tt->max_gpu_slots;  // node-local pick scans trackerGPUMapCapacity ids (:354)
+    const int take = std::min(avail_gpu, left);
+    for (int t = 0; t < take; ++t) {
+      int dev = 0;  // Task's default GPUDeviceId when no free id is found
+      for (int j = 0; j < scan; ++j)
+        if (!(busy & (1u << j))) { dev = j; busy |= 1u << j; break; }
+      out->gpu_device[out->n_gpu++] = dev;
+    }
+  }
+  return 0;
+}
+
+extern "C" int hgs_simulate(const hgs_sim_params *p, hgs_sim_result *out) {
+  if (!p || !out || p->n_splits < 0 || p->iterations < 1 || p->cpu_slots < 0 || p->gpu_slots < 0 ||
+      p->gpu_slots > HGS_MAX_DEVICES || p->heartbeat_ms <= 0)
+    return -22;
+  *out = hgs_sim_result{};
+  struct Running { double finish; bool gpu; int dev; double start; };
+  auto later = [](const Running &a, const Running &b) { return a.finish > b.finish; };
+  double now = 0.0;
+  for (int it = 0; it < p->iterations; ++it) {
+    std::priority_queue<Running, std::vector<Running>, decltype(later)> running(later);
+    int finished = 0, started = 0;
+    long long cpu_time = 0, gpu_time = 0;  // integer milliseconds like JobInProgress sums them
+    int cpu_done = 0, gpu_done = 0;
+    uint32_t busy = 0;
+    int run_cpu = 0, run_gpu = 0;
+    double next_hb = now;
+    const double gpu_ms = it == 0 ? p->gpu_task_ms_first : p->gpu_task_ms_cached;
+    while (finished < p->n_splits) {
+      // advance to the next event: a heartbeat, or (out-of-band) a task completion
+      double t_next = next_hb;
+      if (!running.empty() && running.top().finish <= t_next) {
+        const Running r = running.top();
+        running.pop();
+        now = std::max(now, r.finish);
+        ++finished;
+        const long long took = (long long)(r.finish - r.start);  // finishTime - startTime, ms
+        if (r.gpu) { gpu_time += took; ++gpu_done; --run_gpu; busy &= ~(1u << r.dev); }
+        else { cpu_time += took; ++cpu_done; --run_cpu; }
+        if (p->out_of_band_heartbeat) next_hb = now;
+        continue;
+      }
+      now = std::max(now, t_next);
+      next_hb = now + p->heartbeat_ms;
+      ++out->heartbeats;
+      hgs_job job{p->n_splits, finished, run_cpu + run_gpu, cpu_done ? (int)(cpu_time / cpu_done) : 0,
+                  gpu_done ? (int)(gpu_time / gpu_done) : 0, 1, p->prior_acceleration};
+      hgs_tracker tt{p->cpu_slots, p->gpu_slots, run_cpu, run_gpu, busy};
+      hgs_decision d;
+      hgs_assign(&job, 1, &tt, 1, p->optional_scheduling, p->fixes, p->n_splits - started, &d);
+      out->cpu_pass_skips += d.cpu_pass_skipped;
+      out->last_acceleration = d.acceleration;
+      for (int i = 0; i < d.n_cpu; ++i) {
+        running.push(Running{now + p->task_overhead_ms + p->cpu_task_ms, false, -1, now});
+        ++run_cpu; ++started; ++out->tasks_cpu;
+      }
+      for (int i = 0; i < d.n_gpu; ++i) {
+        running.push(Running{now + p->task_overhead_ms + gpu_ms, true, d.gpu_device[i], now});
+        busy |= 1u << d.gpu_device[i];
+        ++run_gpu; ++started; ++out->tasks_gpu;
+      }
+      if (running.empty() && started >= p->n_splits) break;
+    }
+  }
+  out->makespan_ms = now;
+  return 0;
+}

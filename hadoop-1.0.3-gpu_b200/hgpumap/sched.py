@@ -1,0 +1,78 @@
+"""ctypes binding of libhgsched.so (include/hgsched.h): the fork's hybrid CPU/GPU map
+assignment rule (JobQueueTaskScheduler.assignTasks) and the one-TaskTracker simulator."""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_PKG_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+MAX_DEVICES = 32
+FIX_PENDING, FIX_PER_JOB_ACCEL, FIX_PRIOR_ACCEL = 1, 2, 4
+
+
+class Job(C.Structure):
+    _fields_ = [("desired_maps", C.c_int32), ("finished_maps", C.c_int32), ("running_maps", C.c_int32),
+                ("cpu_mean_ms", C.c_int32), ("gpu_mean_ms", C.c_int32), ("has_gpu_executable", C.c_int32),
+                ("prior_acceleration", C.c_double)]
+
+
+class Tracker(C.Structure):
+    _fields_ = [("max_cpu_slots", C.c_int32), ("max_gpu_slots", C.c_int32), ("running_cpu", C.c_int32),
+                ("running_gpu", C.c_int32), ("busy_devices", C.c_uint32)]
+
+
+class Decision(C.Structure):
+    _fields_ = [("n_cpu", C.c_int32), ("n_gpu", C.c_int32), ("gpu_device", C.c_int32 * MAX_DEVICES),
+                ("cpu_pass_skipped", C.c_int32), ("pending_map_load", C.c_int32), ("acceleration", C.c_double)]
+
+
+class SimParams(C.Structure):
+    _fields_ = [("n_splits", C.c_int32), ("iterations", C.c_int32), ("cpu_slots", C.c_int32),
+                ("gpu_slots", C.c_int32), ("cpu_task_ms", C.c_double), ("gpu_task_ms_first", C.c_double),
+                ("gpu_task_ms_cached", C.c_double), ("task_overhead_ms", C.c_double), ("heartbeat_ms", C.c_double),
+                ("out_of_band_heartbeat", C.c_int32), ("optional_scheduling", C.c_int32), ("fixes", C.c_int32),
+                ("prior_acceleration", C.c_double)]
+
+
+class SimResult(C.Structure):
+    _fields_ = [("makespan_ms", C.c_double), ("tasks_cpu", C.c_int64), ("tasks_gpu", C.c_int64),
+                ("heartbeats", C.c_int64), ("cpu_pass_skips", C.c_int64), ("last_acceleration", C.c_double),
+                ("points_per_sec", C.c_double)]
+
+
+_LIB = None
+
+
+def load() -> C.CDLL:
+    global _LIB
+    if _LIB is None:
+        path = os.path.join(_PKG_ROOT, "libhgsched.so")
+        if not os.path.exists(path):
+            raise FileNotFoundError(f"{path} is not built; run `make -C {_PKG_ROOT}`")
+        lib = C.CDLL(path)
+        lib.hgs_assign.restype = C.c_int
+        lib.hgs_assign.argtypes = [C.POINTER(Job), C.c_int32, C.POINTER(Tracker), C.c_int32, C.c_int32,
+                                   C.c_int32, C.c_int32, C.POINTER(Decision)]
+        lib.hgs_simulate.restype = C.c_int
+        lib.hgs_simulate.argtypes = [C.POINTER(SimParams), C.POINTER(SimResult)]
+        _LIB = lib
+    return _LIB
+
+
+def assign(jobs: list[Job], tracker: Tracker, num_trackers: int = 1, optional: bool = True, fixes: int = 0,
+           want: int = 1 << 30) -> Decision:
+    arr = (Job * max(len(jobs), 1))(*jobs)
+    out = Decision()
+    rc = load().hgs_assign(arr, len(jobs), C.byref(tracker), num_trackers, int(optional), fixes, want, C.byref(out))
+    if rc != 0:
+        raise ValueError(f"hgs_assign returned {rc}")
+    return out
+
+
+def simulate(**kw) -> SimResult:
+    params = SimParams(**kw)
+    out = SimResult()
+    rc = load().hgs_simulate(C.byref(params), C.byref(out))
+    if rc != 0:
+        raise ValueError(f"hgs_simulate returned {rc}")
+    return out

@@ -1,0 +1,101 @@
+/* hgsched.h -- C ABI of libhgsched.so: the fork's hybrid CPU/GPU map scheduling rule, restated.
+ *
+ * The reference decides, on every TaskTracker heartbeat, how many map tasks go to CPU slots
+ * and how many to GPU slots (and on which device):
+ *   JobQueueTaskScheduler.assignTasks   mapred/org/apache/hadoop/mapred/JobQueueTaskScheduler.java:86-575
+ *     job statistics                    :134-169   (pendingMapLoad, mean CPU / GPU map times)
+ *     acceleration factor               :175-177   cpuMean / gpuMean, 0 if either is 0
+ *     CPU pass (suppressed near the tail) :290-326 skipped iff optionalscheduling &&
+ *                                                  max(pending,0) < accel * gpuSlots * trackers
+ *     GPU pass, device = first free id  :334-387
+ *   mean times (integer ms, finished tasks only)   mapred/JobInProgress.java:527-565
+ *   free device bitmap                             mapred/TaskTrackerStatus.java:536-551
+ *   slot counters the launcher blocks on           mapred/TaskTracker.java:2434-2629
+ * Java cannot be built in this image, so the rule lives here in C++ behind a C ABI (a JNI or
+ * test harness binds it); hgs_simulate drives it over one TaskTracker for BASELINE config 3.
+ */
+#ifndef HGSCHED_H
+#define HGSCHED_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define HGS_MAX_DEVICES 32
+
+/* One running job as assignTasks sees it (JobInProgress getters). */
+typedef struct {
+  int32_t desired_maps;       /* desiredMaps()                                   */
+  int32_t finished_maps;      /* finishedMaps()                                  */
+  int32_t running_maps;       /* runningMaps()                                   */
+  int32_t cpu_mean_ms;        /* getCPUMapTaskMeanTime(): int ms, 0 if none yet  */
+  int32_t gpu_mean_ms;        /* getGPUMapTaskMeanTime()                         */
+  int32_t has_gpu_executable; /* hadoop.pipes.gpu.executable is set (:342-347)   */
+  double prior_acceleration;  /* HGS_FIX_PRIOR_ACCEL: factor measured earlier (previous iteration /
+                                 job, or a calibration run), used until this job has finished
+                                 tasks of both kinds; 0 = none                  */
+} hgs_job;
+
+/* One TaskTracker heartbeat (TaskTrackerStatus). */
+typedef struct {
+  int32_t max_cpu_slots;   /* mapred.tasktracker.map.cpu.tasks.maximum */
+  int32_t max_gpu_slots;   /* mapred.tasktracker.map.gpu.tasks.maximum */
+  int32_t running_cpu;     /* countCPUMapTasks()                       */
+  int32_t running_gpu;     /* countGPUMapTasks()                       */
+  uint32_t busy_devices;   /* bit j set = device j runs a GPU map      */
+} hgs_tracker;
+
+/* Behaviour switches.  All 0 = the reference as written, quirks included. */
+#define HGS_FIX_PENDING 1     /* pendingMapLoad per job instead of the running total (:139)        */
+#define HGS_FIX_PER_JOB_ACCEL 2 /* factor from every job's times, not only the last job's (:143-144) */
+#define HGS_FIX_PRIOR_ACCEL 4 /* start from a measured factor instead of 0 ("fed by measured per-task
+                                 GPU acceleration"): without it every job begins by filling all CPU
+                                 slots, and a GPU task shorter than 1 ms (integer-ms means,
+                                 JobInProgress.java:527-565) keeps the factor at 0 forever */
+/* Not modelled: data locality.  Every task is handed out by the node-local branch (:350-366), so the
+ * non-local branch's shorter device-id scan (:373, availableGPUMapSlots instead of the capacity) and
+ * its one-task-per-heartbeat `break scheduleGPUMaps` never apply on the single node simulated here. */
+
+typedef struct {
+  int32_t n_cpu;                         /* map tasks handed to CPU slots                    */
+  int32_t n_gpu;                         /* map tasks handed to GPU slots                    */
+  int32_t gpu_device[HGS_MAX_DEVICES];   /* device id stamped on each GPU task (setGPUDeviceId) */
+  int32_t cpu_pass_skipped;              /* 1 if the optional-scheduling rule suppressed CPUs */
+  int32_t pending_map_load;
+  double acceleration;
+} hgs_decision;
+
+/* One assignTasks call.  `want` = how many more map tasks the job queue could hand out (the
+ * obtainNew*MapTask calls return null beyond it); all tasks are taken as node-local.
+ * Returns 0, or -22 on a bad argument. */
+int hgs_assign(const hgs_job *jobs, int32_t n_jobs, const hgs_tracker *tracker, int32_t num_trackers,
+               int32_t optional_scheduling, int32_t fixes, int32_t want, hgs_decision *out);
+
+/* Discrete-event run of `iterations` K-means map phases of `n_splits` map tasks each on ONE
+ * TaskTracker with the given slots, driven by hgs_assign at every heartbeat. */
+typedef struct {
+  int32_t n_splits, iterations;
+  int32_t cpu_slots, gpu_slots;
+  double cpu_task_ms;        /* one split on one CPU slot                              */
+  double gpu_task_ms_first;  /* one split on a GPU slot, iteration 1 (staged from host) */
+  double gpu_task_ms_cached; /* iterations >= 2 (split resident in HBM)                */
+  double task_overhead_ms;   /* per-task launch cost (child JVM + Pipes child + handshake) */
+  double heartbeat_ms;       /* TaskTracker heartbeat period                           */
+  int32_t out_of_band_heartbeat; /* 1 = also heartbeat when a task finishes            */
+  int32_t optional_scheduling, fixes;
+  double prior_acceleration; /* handed to every job when HGS_FIX_PRIOR_ACCEL is set */
+} hgs_sim_params;
+
+typedef struct {
+  double makespan_ms;
+  int64_t tasks_cpu, tasks_gpu, heartbeats, cpu_pass_skips;
+  double last_acceleration;
+  double points_per_sec;     /* filled by the caller's points-per-split if > 0 */
+} hgs_sim_result;
+
+int hgs_simulate(const hgs_sim_params *params, hgs_sim_result *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

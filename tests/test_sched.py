@@ -1,0 +1,102 @@
+"""CPU: the hybrid CPU/GPU assignment rule restated from JobQueueTaskScheduler.assignTasks
+(mapred/JobQueueTaskScheduler.java:86-575).  The reference has no test for its GPU branch
+(SURVEY.md section 4), so these pin the rule as the source states it, quirks included."""
+import pytest
+
+from hgpumap import sched
+from hgpumap.sched import Job, Tracker
+
+
+def job(desired=100, finished=0, running=0, cpu=0, gpu=0, exe=1):
+    return Job(desired, finished, running, cpu, gpu, exe, 0.0)
+
+
+def test_acceleration_factor_is_cpu_over_gpu_and_zero_until_both_are_known():
+    tt = Tracker(3, 1, 0, 0, 0)
+    assert sched.assign([job(cpu=0, gpu=50)], tt).acceleration == 0.0          # :175-177
+    assert sched.assign([job(cpu=4000, gpu=0)], tt).acceleration == 0.0
+    assert sched.assign([job(cpu=4000, gpu=50)], tt).acceleration == 80.0
+
+
+def test_shipped_config_fills_three_cpu_slots_and_one_gpu_slot():
+    """conf/mapred-site.xml:23-44: 3 CPU + 1 GPU map slots, optionalscheduling=true."""
+    d = sched.assign([job()], Tracker(3, 1, 0, 0, 0))
+    assert (d.n_cpu, d.n_gpu, d.gpu_device[0], d.cpu_pass_skipped) == (3, 1, 0, 0)
+    d = sched.assign([job(running=3)], Tracker(3, 1, 2, 1, 0b1))
+    assert (d.n_cpu, d.n_gpu) == (1, 0)
+
+
+def test_cpu_pass_is_suppressed_near_the_tail_only_with_optional_scheduling():
+    """:290-291: skip CPUs iff optional && max(pending,0) < accel * gpuSlots * trackers."""
+    tt = Tracker(3, 1, 0, 0, 0)
+    tail = job(desired=100, finished=85, running=0, cpu=4000, gpu=200)   # pending 15 < 20*1*1
+    d = sched.assign([tail], tt, optional=True)
+    assert d.cpu_pass_skipped == 1 and (d.n_cpu, d.n_gpu) == (0, 1) and d.pending_map_load == 15
+    d = sched.assign([tail], tt, optional=False)
+    assert d.cpu_pass_skipped == 0 and (d.n_cpu, d.n_gpu) == (3, 1)
+    early = job(desired=100, finished=10, cpu=4000, gpu=200)             # pending 90 >= 20
+    assert sched.assign([early], tt).cpu_pass_skipped == 0
+    # more trackers raise the threshold: 15 < 20*1*1 but 90 < 20*1*8
+    assert sched.assign([early], tt, num_trackers=8).cpu_pass_skipped == 1
+    # before any GPU task has finished the factor is 0, so CPUs are never suppressed
+    assert sched.assign([job(desired=5, finished=4, cpu=4000, gpu=0)], tt).cpu_pass_skipped == 0
+
+
+def test_gpu_task_gets_the_first_free_device_id():
+    """:354-361 with the bitmap of TaskTrackerStatus.availableGPUDevices (:536-551)."""
+    d = sched.assign([job()], Tracker(0, 8, 0, 3, 0b00001011))
+    assert d.n_gpu == 5 and list(d.gpu_device[:5]) == [2, 4, 5, 6, 7]
+    d = sched.assign([job()], Tracker(0, 8, 0, 0, 0), want=2)
+    assert d.n_gpu == 2 and list(d.gpu_device[:2]) == [0, 1]
+
+
+def test_job_without_gpu_executable_gets_no_gpu_slot():
+    d = sched.assign([job(exe=0)], Tracker(2, 2, 0, 0, 0))                # :342-347
+    assert (d.n_cpu, d.n_gpu) == (2, 0)
+
+
+def test_pending_load_quirk_and_its_fix():
+    """:137-139 adds the RUNNING TOTAL of remaining maps for every job; the factor comes from
+    the last job only (:143-144)."""
+    jobs = [job(desired=10, finished=0, running=2, cpu=1000, gpu=100), job(desired=20, finished=5, running=1)]
+    d = sched.assign(jobs, Tracker(1, 1, 0, 0, 0))
+    assert d.pending_map_load == (10 - 2) + (10 + 15 - 1) and d.acceleration == 0.0
+    d = sched.assign(jobs, Tracker(1, 1, 0, 0, 0), fixes=sched.FIX_PENDING | sched.FIX_PER_JOB_ACCEL)
+    assert d.pending_map_load == (10 - 2) + (15 - 1) and d.acceleration == 10.0
+
+
+def test_simulation_hybrid_beats_cpu_only_and_tail_rule_helps():
+    base = dict(n_splits=120, iterations=1, cpu_task_ms=4000.0, gpu_task_ms_first=200.0, gpu_task_ms_cached=200.0,
+                task_overhead_ms=0.0, heartbeat_ms=50.0, out_of_band_heartbeat=1, fixes=0, prior_acceleration=0.0)
+    cpu_only = sched.simulate(cpu_slots=3, gpu_slots=0, optional_scheduling=0, **base)
+    hybrid = sched.simulate(cpu_slots=3, gpu_slots=1, optional_scheduling=0, **base)
+    tail = sched.simulate(cpu_slots=3, gpu_slots=1, optional_scheduling=1, **base)
+    assert cpu_only.tasks_gpu == 0 and cpu_only.tasks_cpu == 120
+    assert hybrid.makespan_ms < cpu_only.makespan_ms / 4
+    assert tail.makespan_ms <= hybrid.makespan_ms and tail.cpu_pass_skips > 0
+    assert hybrid.tasks_cpu + hybrid.tasks_gpu == 120 == tail.tasks_cpu + tail.tasks_gpu
+    assert 15 < tail.last_acceleration <= 20  # integer-millisecond means like JobInProgress.java:527-565
+
+
+def test_prior_acceleration_skips_the_cold_start():
+    """Without a prior every job starts by filling all CPU slots (factor 0 until tasks of both
+    kinds have finished); fed with a measured factor the rule suppresses them from the start."""
+    tt = Tracker(3, 1, 0, 0, 0)
+    fresh = Job(50, 0, 0, 0, 0, 1, 80.0)
+    assert sched.assign([fresh], tt).cpu_pass_skipped == 0
+    d = sched.assign([fresh], tt, fixes=sched.FIX_PRIOR_ACCEL)
+    assert d.cpu_pass_skipped == 1 and d.acceleration == 80.0 and (d.n_cpu, d.n_gpu) == (0, 1)
+    base = dict(n_splits=60, iterations=3, cpu_slots=8, gpu_slots=8, cpu_task_ms=14000.0, gpu_task_ms_first=1.2,
+                gpu_task_ms_cached=0.05, task_overhead_ms=1.0, heartbeat_ms=3000.0, out_of_band_heartbeat=1,
+                optional_scheduling=1)
+    cold = sched.simulate(fixes=0, prior_acceleration=0.0, **base)
+    warm = sched.simulate(fixes=sched.FIX_PRIOR_ACCEL, prior_acceleration=14000.0 / 2.2, **base)
+    assert cold.tasks_cpu == 24 and cold.makespan_ms > 3 * 14000
+    assert warm.tasks_cpu == 0 and warm.makespan_ms < 100
+
+
+def test_simulation_rejects_bad_arguments():
+    with pytest.raises(ValueError):
+        sched.simulate(n_splits=1, iterations=0, cpu_slots=1, gpu_slots=1, cpu_task_ms=1, gpu_task_ms_first=1,
+                       gpu_task_ms_cached=1, task_overhead_ms=0, heartbeat_ms=1, out_of_band_heartbeat=0,
+                       optional_scheduling=0, fixes=0, prior_acceleration=0.0)

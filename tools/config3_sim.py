@@ -1,0 +1,84 @@
+#!/usr/bin/env python
+"""BASELINE config 3 (K-means 10 iterations, 20 GB = 2.5 G 2-D points in 64 MiB splits, 8 GPU map
+slots + host CPU slots on one TaskTracker) through the restated hybrid scheduler.
+
+This is a SIMULATION of the scheduling (libhgsched.so, include/hgsched.h) fed with per-task times
+MEASURED on the GPU box by bench.py (profiles/r01_v7_bench_line.json); no JVM exists in this
+environment, so no real TaskTracker can be run.  It answers what the reference's per-heartbeat,
+per-task-process design costs on this path, and what the persistent per-GPU worker removes
+(SURVEY.md section 7 H3).
+
+  python tools/config3_sim.py [bench_line.json] > profiles/r01_config3_sim.md
+"""
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, os.path.join(ROOT, "hadoop-1.0.3-gpu_b200"))
+from hgpumap import sched  # noqa: E402
+
+SPLIT_BYTES = 64 << 20
+POINTS_PER_SPLIT = SPLIT_BYTES // 8
+TOTAL_POINTS = 2_500_000_000
+N_SPLITS = -(-TOTAL_POINTS // POINTS_PER_SPLIT)  # 299 (the last one partial)
+ITERATIONS = 10
+
+
+def main():
+    path = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "profiles", "r01_v7_bench_line.json")
+    line = json.loads(open(path).read().strip().splitlines()[-1])
+    gpu_resident = line["value"]                      # points/s, HBM-resident
+    gpu_staged = line["e2e"]["value"]                 # points/s, split staged from pinned host memory
+    cpu_all = line["cpu_baseline"]["value"]
+    cores = line["cpu_baseline"]["cores"]
+    cpu_per_core = cpu_all / cores
+    gpu_first_ms = 1e3 * POINTS_PER_SPLIT / gpu_staged
+    gpu_cached_ms = 1e3 * POINTS_PER_SPLIT / gpu_resident
+    cpu_ms = 1e3 * POINTS_PER_SPLIT / cpu_per_core
+    cpu_slots = max(cores - 8, 0)  # leave a core per GPU slot for its feeder thread
+
+    def run(label, **kw):
+        base = dict(n_splits=N_SPLITS, iterations=ITERATIONS, cpu_task_ms=cpu_ms, gpu_task_ms_first=gpu_first_ms,
+                    gpu_task_ms_cached=gpu_cached_ms, fixes=0, prior_acceleration=0.0)
+        base.update(kw)
+        r = sched.simulate(**base)
+        pts = TOTAL_POINTS * ITERATIONS / (r.makespan_ms * 1e-3)
+        return (label, r.makespan_ms / 1e3, pts, r.tasks_cpu, r.tasks_gpu, r.cpu_pass_skips, r.heartbeats)
+
+    rows = [
+        run("CPU slots only (reference CPU Pipes mapper), 3 s heartbeat, 2 s task launch",
+            cpu_slots=cores, gpu_slots=0, task_overhead_ms=2000, heartbeat_ms=3000, out_of_band_heartbeat=0, optional_scheduling=0),
+        run("reference scheduler as written: 8 GPU + CPU slots, 3 s heartbeat, 2 s task launch (JVM + child + CUDA context)",
+            cpu_slots=cpu_slots, gpu_slots=8, task_overhead_ms=2000, heartbeat_ms=3000, out_of_band_heartbeat=0, optional_scheduling=1),
+        run("same, out-of-band heartbeat on task completion",
+            cpu_slots=cpu_slots, gpu_slots=8, task_overhead_ms=2000, heartbeat_ms=3000, out_of_band_heartbeat=1, optional_scheduling=1),
+        run("persistent per-GPU worker (ctx kept, ~1 ms per task), out-of-band heartbeat, hybrid",
+            cpu_slots=cpu_slots, gpu_slots=8, task_overhead_ms=1, heartbeat_ms=3000, out_of_band_heartbeat=1, optional_scheduling=1),
+        run("persistent worker, hybrid, scheduler fed with the measured acceleration (HGS_FIX_PRIOR_ACCEL)",
+            cpu_slots=cpu_slots, gpu_slots=8, task_overhead_ms=1, heartbeat_ms=3000, out_of_band_heartbeat=1, optional_scheduling=1,
+            fixes=sched.FIX_PRIOR_ACCEL, prior_acceleration=cpu_ms / (gpu_first_ms + 1)),
+        run("persistent per-GPU worker, GPU slots only",
+            cpu_slots=0, gpu_slots=8, task_overhead_ms=1, heartbeat_ms=3000, out_of_band_heartbeat=1, optional_scheduling=1),
+    ]
+    print("# BASELINE config 3 through the restated hybrid scheduler (simulation, measured task times)\n")
+    print(f"Inputs from `{os.path.relpath(path, ROOT)}`: GPU map {gpu_resident / 1e9:.1f} G points/s HBM-resident, "
+          f"{gpu_staged / 1e9:.2f} G points/s staged from pinned host memory; CPU Pipes mapper "
+          f"{cpu_per_core / 1e6:.3f} M points/s per core ({cores} cores measured).")
+    print(f"One 64 MiB split = {POINTS_PER_SPLIT:,} points: GPU {gpu_first_ms:.2f} ms staged / {gpu_cached_ms:.3f} ms "
+          f"cached, CPU {cpu_ms / 1e3:.1f} s.  {N_SPLITS} splits x {ITERATIONS} iterations; iteration 1 staged, 2-10 from "
+          "the HBM split cache.  Scheduler = `hgs_simulate` (JobQueueTaskScheduler.assignTasks restated, "
+          "`include/hgsched.h`), `mapred.jobtracker.map.optionalscheduling=true`.\n")
+    print("| scenario | job time (s) | points/s | CPU tasks | GPU tasks | CPU-pass skips | heartbeats |")
+    print("|---|---|---|---|---|---|---|")
+    for label, secs, pts, tc, tg, skips, hb in rows:
+        print(f"| {label} | {secs:,.1f} | {pts / 1e9:.3f} G | {tc} | {tg} | {skips} | {hb} |")
+    print("\nReading: with a 3 s heartbeat and a process launch per task, a GPU slot that maps a split in ~1 ms is idle "
+          ">99.9 % of the time, and the CPU slots' 14 s tasks set the tail unless the acceleration-factor rule "
+          "suppresses them -- and that rule starts every job with factor 0, so each iteration first fills the CPU slots
+unless it is fed the factor measured before; the persistent worker turns the job into ~3000 sub-millisecond calls.  These are "
+          "scheduling simulations, not measured job runs: no JVM is available here.")
+
+
+if __name__ == "__main__":
+    main()
