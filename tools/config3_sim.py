@@ -75,8 +75,8 @@ def main():
         print(f"| {label} | {secs:,.1f} | {pts / 1e9:.3f} G | {tc} | {tg} | {skips} | {hb} |")
     print("\nReading: with a 3 s heartbeat and a process launch per task, a GPU slot that maps a split in ~1 ms is idle "
           ">99.9 % of the time, and the CPU slots' 14 s tasks set the tail unless the acceleration-factor rule "
-          "suppresses them -- and that rule starts every job with factor 0, so each iteration first fills the CPU slots
-unless it is fed the factor measured before; the persistent worker turns the job into ~3000 sub-millisecond calls.  These are "
+          "suppresses them -- and that rule starts every job with factor 0, so each iteration first fills the CPU slots "
+          "unless it is fed the factor measured before; the persistent worker turns the job into ~3000 sub-millisecond calls.  These are "
           "scheduling simulations, not measured job runs: no JVM is available here.")
 
 
