@@ -45,6 +45,12 @@ struct hgm_ctx {
   Grid2D grid{};
   uint16_t *d_table = nullptr;  // G*G
   uint16_t *d_cand = nullptr;   // G*G*8
+  bool tensor_ok = false;       // tcgen05 path prepared for this centroid table
+  float *d_caug = nullptr;      // [k_pad][d+32] augmented centroid matrix
+  unsigned int *d_tflags = nullptr;  // [0] max |c| bits, [1] re-check counter
+  int32_t *d_tassign = nullptr, *d_tlist = nullptr;  // scratch: assignments / re-check list
+  size_t tscratch_rows = 0;
+  unsigned long long last_rechecks = 0;
   int forced = HGM_KERNEL_AUTO, last_kernel = HGM_KERNEL_AUTO;
   int last_launches = 0;
   int64_t total_launches = 0;
@@ -93,6 +99,12 @@ void free_job(hgm_ctx *c) {
   cudaFree(c->d_partials); c->d_partials = nullptr;
   cudaFree(c->d_table); c->d_table = nullptr;
   cudaFree(c->d_cand); c->d_cand = nullptr;
+  cudaFree(c->d_caug); c->d_caug = nullptr;
+  cudaFree(c->d_tflags); c->d_tflags = nullptr;
+  cudaFree(c->d_tassign); c->d_tassign = nullptr;
+  cudaFree(c->d_tlist); c->d_tlist = nullptr;
+  c->tscratch_rows = 0;
+  c->tensor_ok = false;
   c->grid_ok = false;
   c->k = c->d = 0;
 }
@@ -139,8 +151,11 @@ bool plan_grid2d(const float *cent, int k, size_t smem_optin, Grid2D *out) {
 int pick_kernel(hgm_ctx *c) {
   if (c->forced == HGM_KERNEL_EXACT) return HGM_KERNEL_EXACT;
   if (c->forced == HGM_KERNEL_GRID2D) return c->grid_ok ? HGM_KERNEL_GRID2D : -1;
-  if (c->forced == HGM_KERNEL_TENSOR) return -1;
-  return c->grid_ok ? HGM_KERNEL_GRID2D : HGM_KERNEL_EXACT;
+  if (c->forced == HGM_KERNEL_TENSOR) return c->tensor_ok ? HGM_KERNEL_TENSOR : -1;
+  if (c->grid_ok) return HGM_KERNEL_GRID2D;
+  // the GEMM-shaped path pays off once a point meets a few thousand centroid coordinates
+  if (c->tensor_ok && (long long)c->k * c->d >= 8192) return HGM_KERNEL_TENSOR;
+  return HGM_KERNEL_EXACT;
 }
 
 // queue the map of n device-resident points on ctx->stream; adds into the partials
@@ -149,7 +164,24 @@ int map_points_async(hgm_ctx *c, const float *d_pts, int64_t n, int32_t *d_assig
   const int kern = pick_kernel(c);
   if (kern < 0) return fail(c, HGM_EINVAL, "forced kernel %d does not fit k=%d d=%d", c->forced, c->k, c->d);
   cudaError_t e;
-  if (kern == HGM_KERNEL_GRID2D) {
+  int launches = 1;
+  if (kern == HGM_KERNEL_TENSOR) {
+    if (reinterpret_cast<uintptr_t>(d_pts) & 15)
+      return fail(c, HGM_EINVAL, "the tensor path needs 16-byte aligned points");
+    if (c->tscratch_rows < (size_t)n) {  // scratch for assignments and the re-check list
+      CU(c, cudaStreamSynchronize(c->stream));
+      cudaFree(c->d_tassign); cudaFree(c->d_tlist);
+      c->d_tassign = c->d_tlist = nullptr;
+      c->tscratch_rows = 0;
+      CU(c, cudaMalloc(&c->d_tassign, (size_t)n * 4));
+      CU(c, cudaMalloc(&c->d_tlist, (size_t)n * 4));
+      c->tscratch_rows = (size_t)n;
+    }
+    e = launch_tensor_map(d_pts, n, c->d, c->d_cent, c->k, c->d_caug, c->d_tflags, d_assign ? d_assign : c->d_tassign,
+                          c->d_tlist, c->d_tflags + 1, sums_ptr(c), counts_ptr(c), c->sm_count, c->smem_optin,
+                          c->stream);
+    launches = 3;
+  } else if (kern == HGM_KERNEL_GRID2D) {
     e = launch_grid2d_map(d_pts, n, c->d_cent, c->k, c->grid, c->d_table, c->d_cand, sums_ptr(c),
                           counts_ptr(c), d_assign, c->sm_count, c->smem_optin, c->stream);
   } else {
@@ -158,8 +190,8 @@ int map_points_async(hgm_ctx *c, const float *d_pts, int64_t n, int32_t *d_assig
   }
   if (e != cudaSuccess) return fail(c, HGM_ECUDA, "map kernel launch failed: %s", cudaGetErrorString(e));
   c->last_kernel = kern;
-  c->last_launches += 1;
-  c->total_launches += 1;
+  c->last_launches += launches;
+  c->total_launches += launches;
   return HGM_OK;
 }
 
@@ -297,6 +329,17 @@ int hgm_set_centroids(hgm_ctx *c, const float *centroids, int32_t k, int32_t d) 
       c->grid_ok = true;
     }
   }
+  c->tensor_ok = false;
+  if (tensor_shape_ok(k, d, c->smem_optin)) {
+    if (!c->d_caug) {
+      CU(c, cudaMalloc(&c->d_caug, tensor_caug_floats(k, d) * 4));
+      CU(c, cudaMalloc(&c->d_tflags, 16));
+    }
+    cudaError_t e = launch_tensor_prep(c->d_cent, k, d, c->d_caug, c->d_tflags, c->stream);
+    if (e != cudaSuccess) return fail(c, HGM_ECUDA, "tensor prep launch: %s", cudaGetErrorString(e));
+    c->total_launches += 1;
+    c->tensor_ok = true;
+  }
   // the caller's centroid buffer may be reused as soon as we return
   CU(c, cudaStreamSynchronize(c->stream));
   return HGM_OK;
@@ -371,6 +414,18 @@ int hgm_last_map_ms(hgm_ctx *c, float *ms, int32_t *launches) {
   CU(c, cudaEventSynchronize(c->ev_t1));
   if (ms) CU(c, cudaEventElapsedTime(ms, c->ev_t0, c->ev_t1));
   if (launches) *launches = c->last_launches;
+  return HGM_OK;
+}
+
+int hgm_last_rechecks(hgm_ctx *c, int64_t *points) {
+  NEED_CTX(c);
+  if (!points) return fail(c, HGM_EINVAL, "points is NULL");
+  *points = 0;
+  if (c->last_kernel != HGM_KERNEL_TENSOR || !c->d_tflags) return HGM_OK;
+  unsigned int n = 0;
+  CU(c, cudaMemcpyAsync(&n, c->d_tflags + 1, 4, cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  *points = n;
   return HGM_OK;
 }
 

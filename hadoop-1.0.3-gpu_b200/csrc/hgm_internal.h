@@ -53,6 +53,16 @@ cudaError_t launch_exact_map(const float *d_pts, int64_t n, int d, const float *
                              double *d_sums, unsigned long long *d_counts, int32_t *d_assign,
                              int sm_count, size_t smem_optin, cudaStream_t s);
 
+// tcgen05 path (kernels_tensor.cu)
+bool tensor_shape_ok(int k, int d, size_t smem_optin);
+size_t tensor_caug_floats(int k, int d);
+cudaError_t launch_tensor_prep(const float *d_cent, int k, int d, float *d_caug, unsigned int *d_cmax_bits,
+                               cudaStream_t s);
+cudaError_t launch_tensor_map(const float *d_pts, int64_t n, int d, const float *d_cent, int k, const float *d_caug,
+                              const unsigned int *d_cmax_bits, int32_t *d_assign, int32_t *d_flag_list,
+                              unsigned int *d_flag_count, double *d_sums, unsigned long long *d_counts, int sm_count,
+                              size_t smem_optin, cudaStream_t s);
+
 cudaError_t launch_bswap32(uint32_t *d_words, int64_t n_words, cudaStream_t s);
 
 cudaError_t launch_synth_points(uint64_t seed, int64_t first, int64_t n, int d, int k,

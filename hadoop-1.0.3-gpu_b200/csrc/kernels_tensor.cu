@@ -1,0 +1,440 @@
+// kernels_tensor.cu -- K2/K3/K4: the GEMM-shaped map task (d = 32..128, k >= 128) on tcgen05.
+//
+// Fills the same two slots as the other kernels -- Mapper::map (c++/pipes/api/hadoop/Pipes.hh:
+// 158-161) and the combiner Reducer::reduce (Pipes.hh:166-169) -- for the shapes where the
+// distance step is a dense contraction (BASELINE configs 4 and 5: d=64/k=1024, d=128/k=4096).
+//
+//   K2  tensor_assign_kernel   scores S[i][c] = |c|^2 - 2 x_i.c on the 5th-gen tensor cores
+//       (tcgen05.mma kind::tf32, FP32 accumulators in TMEM), operands staged by TMA with the
+//       128-byte swizzle; the epilogue warps read the accumulators back with tcgen05.ld and
+//       keep, per point, the best and second-best score.  |c|^2 rides in the GEMM as one more
+//       K-block (x side = [1,1,1,0..], c side = |c|^2 split into three TF32-exact pieces).
+//   K3  recheck_kernel         TF32 carries ~2^-10 per operand, so a point whose top-2 margin
+//       is inside the rounding bound is re-scanned with the exact FP32 arithmetic of the
+//       reference scan (ascending index, strict '<'): assignments stay bit-identical.
+//   K4  accumulate_kernel      per-cluster FP64 sums / int64 counts from the final assignments.
+//
+// Rounding bound: the score of (x, c) is off by at most 2^-8 |x| |c| (x truncated to TF32 by
+// the tensor core: 2^-10; c rounded to TF32 here: 2^-11; doubled by the factor 2) plus FP32
+// accumulation and the scan's own rounding, d 2^-22 (|x| + |c|)^2.  If the best and the
+// second-best score are further apart than twice that, no other centroid can be the scan's
+// winner; otherwise K3 decides.
+#include <cuda.h>
+#include <math.h>
+
+#include "hgm_internal.h"
+
+namespace hgm {
+namespace {
+
+constexpr int kBlockK = 32;    // FP32 elements per K-block = one 128-byte swizzle row
+constexpr int kUmmaK = 8;      // K of one kind::tf32 instruction (32 bytes)
+constexpr int kTileM = 256;    // points per CTA tile: two 128-row accumulators share every B stage
+constexpr int kTileN = 128;    // centroids per MMA
+constexpr int kStages = 4;     // B pipeline depth
+constexpr int kABytes = 128 * kBlockK * 4;       // one 128-row K-block of A: 16 KiB
+constexpr int kBBytes = kTileN * kBlockK * 4;    // one B stage: 16 KiB
+constexpr int kEpiWarps = 8;
+constexpr int kThreads = (4 + kEpiWarps) * 32;   // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 spare, 4..11 epilogue
+constexpr uint32_t kTmemCols = 512;              // 2 buffers x 2 halves x 128 columns
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// Bounded wait: a protocol bug must end as a trapped kernel, never as a hung GPU.
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+  uint32_t done = 0;
+  for (uint32_t spins = 0; !done; ++spins) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    if (spins > 50u * 1000u * 1000u) __trap();
+  }
+}
+__device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, int c0, int c1, uint64_t *bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::
+          "r"(smem_u32(dst)),
+      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+// K-major, 128-byte-swizzled operand tile: rows of 128 bytes, 8-row groups 1024 bytes apart
+// (cute/arch/mma_sm100_desc.hpp SmemDescriptor: start>>4 | LBO<<16 | SBO<<32 | version 1<<46 | layout 2<<61)
+__device__ __forceinline__ uint64_t umma_desc(const void *tile, int k_step) {
+  const uint32_t addr = smem_u32(tile) + k_step * kUmmaK * 4;
+  return (uint64_t)((addr >> 4) & 0x3FFF) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) |
+         ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+}
+// kind::tf32, FP32 accumulate, A and B K-major, M = 128, N = kTileN (InstrDescriptor bit layout)
+constexpr uint32_t kIdesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kTileN >> 3) << 17) | ((128u >> 4) << 24);
+
+__device__ __forceinline__ void umma_tf32(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(kIdesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit(uint64_t *bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
+  uint32_t r[32];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+      "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// ---- prep: augmented centroid matrix C'[k_pad][d + 32] and max |c| ----------------------------
+__device__ __forceinline__ float tf32_rn(float f) {
+  uint32_t u = __float_as_uint(f);
+  u = (u + 0xFFFu + ((u >> 13) & 1u)) & ~0x1FFFu;
+  return __uint_as_float(u);
+}
+__global__ void tensor_prep_kernel(const float *__restrict__ cent, int k, int k_pad, int d, float *__restrict__ caug,
+                                   unsigned int *__restrict__ cmax_bits) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= k_pad) return;
+  float *row = caug + (size_t)c * (d + kBlockK);
+  if (c >= k) {  // padding rows: a score no real centroid can undercut
+    for (int j = 0; j < d + kBlockK; ++j) row[j] = 0.f;
+    row[d] = 3.0e38f;
+    return;
+  }
+  double n = 0.0;
+  for (int j = 0; j < d; ++j) {
+    const float v = cent[(size_t)c * d + j];
+    n += (double)v * (double)v;
+    row[j] = tf32_rn(-2.0f * v);
+  }
+  const float hi = tf32_rn((float)n);
+  const double r1 = n - (double)hi;
+  const float mid = tf32_rn((float)r1);
+  const float lo = tf32_rn((float)(r1 - (double)mid));
+  row[d] = hi; row[d + 1] = mid; row[d + 2] = lo;
+  for (int j = 3; j < kBlockK; ++j) row[d + j] = 0.f;
+  atomicMax(cmax_bits, __float_as_uint((float)sqrt(n)));  // non-negative floats order like their bits
+}
+
+// ---- K2 ------------------------------------------------------------------------------------------
+struct TensorArgs {
+  long long n;
+  int k, k_pad, d;
+  const unsigned int *cmax_bits;
+  int32_t *assign;        // [n] best index per point
+  int32_t *flag_list;     // indices of points that need the exact re-check
+  unsigned int *flag_count;
+};
+
+__global__ void __launch_bounds__(kThreads, 1)
+    tensor_assign_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_c,
+                         const TensorArgs a) {
+  extern __shared__ unsigned char smem_raw[];
+  // the 128-byte swizzle needs tiles on 1024-byte boundaries; the launch adds 1 KiB of slack
+  unsigned char *smem = reinterpret_cast<unsigned char *>(
+      (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int kblocks = a.d / kBlockK;           // real K-blocks; one more carries |c|^2
+  const int ntiles_n = a.k_pad / kTileN;
+  unsigned char *a_res = smem;                                  // [2 halves][kblocks] x 16 KiB
+  unsigned char *a_aug = a_res + (size_t)2 * kblocks * kABytes; // 16 KiB constant tile
+  unsigned char *b_stage = a_aug + kABytes;                     // kStages x 16 KiB
+  uint64_t *bars = reinterpret_cast<uint64_t *>(b_stage + (size_t)kStages * kBBytes);
+  uint64_t *full = bars, *empty = bars + kStages;
+  uint64_t *a_full = bars + 2 * kStages, *a_empty = a_full + 1;
+  uint64_t *t_full = a_empty + 1, *t_empty = t_full + 2;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(t_empty + 2);
+
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    mbar_init(a_full, 1);
+    mbar_init(a_empty, 1 + kEpiWarps);
+    for (int b = 0; b < 2; ++b) { mbar_init(&t_full[b], 1); mbar_init(&t_empty[b], kEpiWarps); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  // the |c|^2 K-block of the x side: every row = [1, 1, 1, 0, ...]; 16-byte chunk 0 of row r sits at
+  // chunk (0 ^ (r % 8)) under the 128-byte swizzle
+  for (int i = threadIdx.x; i < kABytes / 16; i += kThreads) {
+    const int r = i / 8, chunk = i % 8;
+    const float4 val = chunk == (r % 8) ? make_float4(1.f, 1.f, 1.f, 0.f) : make_float4(0.f, 0.f, 0.f, 0.f);
+    reinterpret_cast<float4 *>(a_aug)[i] = val;
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the MMA's async reads
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"(kTmemCols));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+
+  const long long tiles_m = (a.n + kTileM - 1) / kTileM;
+
+  if (warp == 0 && lane == 0) {
+    // ===== TMA producer =====
+    uint32_t stage = 0, phase = 0, a_phase = 0;
+    for (long long tm = blockIdx.x; tm < tiles_m; tm += gridDim.x) {
+      mbar_wait(a_empty, a_phase ^ 1);
+      mbar_expect_tx(a_full, 2 * kblocks * kABytes);
+      for (int h = 0; h < 2; ++h)
+        for (int kb = 0; kb < kblocks; ++kb)
+          tma_load_2d(a_res + ((size_t)h * kblocks + kb) * kABytes, &map_x, kb * kBlockK,
+                      (int)(tm * kTileM + h * 128), a_full);
+      a_phase ^= 1;
+      for (int tn = 0; tn < ntiles_n; ++tn)
+        for (int kb = 0; kb <= kblocks; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          mbar_expect_tx(&full[stage], kBBytes);
+          tma_load_2d(b_stage + (size_t)stage * kBBytes, &map_c, kb * kBlockK, tn * kTileN, &full[stage]);
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+    }
+  } else if (warp == 1 && lane == 0) {
+    // ===== MMA issuer =====
+    uint32_t stage = 0, phase = 0, a_phase = 0, t_phase[2] = {0, 0};
+    int buf = 0;
+    for (long long tm = blockIdx.x; tm < tiles_m; tm += gridDim.x) {
+      mbar_wait(a_full, a_phase);
+      a_phase ^= 1;
+      for (int tn = 0; tn < ntiles_n; ++tn) {
+        mbar_wait(&t_empty[buf], t_phase[buf] ^ 1);
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        for (int kb = 0; kb <= kblocks; ++kb) {
+          mbar_wait(&full[stage], phase);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const unsigned char *btile = b_stage + (size_t)stage * kBBytes;
+          const int ksteps = kb < kblocks ? kBlockK / kUmmaK : 1;  // the |c|^2 block has 3 live columns
+          for (int h = 0; h < 2; ++h) {
+            const unsigned char *atile = kb < kblocks ? a_res + ((size_t)h * kblocks + kb) * kABytes : a_aug;
+            const uint32_t tacc = tmem_base + (uint32_t)((buf * 2 + h) * kTileN);
+            for (int ks = 0; ks < ksteps; ++ks)
+              umma_tf32(tacc, umma_desc(atile, ks), umma_desc(btile, ks), (kb | ks) != 0);
+          }
+          umma_commit(&empty[stage]);  // the B stage is free once these MMAs have read it
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&t_full[buf]);     // accumulators of this centroid tile are complete
+        t_phase[buf] ^= 1;
+        buf ^= 1;
+      }
+      umma_commit(a_empty);            // every MMA that reads this point tile has retired
+    }
+  } else if (warp >= 4) {
+    // ===== epilogue: thread = one point (TMEM lane), scans the score columns =====
+    const int ew = warp - 4;
+    const int quarter = warp % 4;      // a warp may only touch TMEM lanes 32*(warp % 4) .. +31
+    const int half = ew / 4;           // which 128-row accumulator
+    const int row = half * 128 + quarter * 32 + lane;  // row within the CTA tile
+    const float cmax = __uint_as_float(*a.cmax_bits);
+    uint32_t a_phase = 0, t_phase[2] = {0, 0};
+    int buf = 0;
+    for (long long tm = blockIdx.x; tm < tiles_m; tm += gridDim.x) {
+      // |x|^2 of my row from the swizzled A tile
+      mbar_wait(a_full, a_phase);
+      a_phase ^= 1;
+      float xn = 0.f;
+      {
+        const int r = row % 128;
+        for (int kb = 0; kb < kblocks; ++kb) {
+          const float4 *tile = reinterpret_cast<const float4 *>(a_res + ((size_t)half * kblocks + kb) * kABytes);
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) {
+            const float4 v = tile[r * 8 + (ch ^ (r % 8))];
+            xn += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(a_empty);
+      float best = INFINITY, second = INFINITY;
+      int bidx = 0;
+      for (int tn = 0; tn < ntiles_n; ++tn) {
+        mbar_wait(&t_full[buf], t_phase[buf]);
+        t_phase[buf] ^= 1;
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)((buf * 2 + half) * kTileN);
+#pragma unroll 1
+        for (int ch = 0; ch < kTileN / 32; ++ch) {
+          float v[32];
+          tmem_ld32(taddr + ch * 32, v);
+          const int cbase = tn * kTileN + ch * 32;
+#pragma unroll
+          for (int i = 0; i < 32; ++i) {
+            const float s = v[i];
+            second = fminf(second, fmaxf(s, best));
+            bidx = s < best ? cbase + i : bidx;
+            best = fminf(s, best);
+          }
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&t_empty[buf]);
+        buf ^= 1;
+      }
+      const long long p = tm * kTileM + row;
+      if (p < a.n) {
+        const float xnorm = sqrtf(xn);
+        const float reach = xnorm + cmax;
+        const float thr = 0.0078125f * xnorm * cmax + (float)a.d * 2.3841858e-07f * reach * reach;
+        a.assign[p] = bidx;
+        if (!(second - best > thr)) {  // also catches NaN / inf rows
+          const unsigned int slot = atomicAdd(a.flag_count, 1u);
+          a.flag_list[slot] = (int32_t)p;  // p < 2^31 per launch (the host chunks larger inputs)
+        }
+      }
+    }
+  }
+  __syncthreads();
+  if (warp == 2) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols));
+  }
+}
+
+// ---- K3: exact re-check of flagged points, one warp per point ---------------------------------
+__global__ void recheck_kernel(const float *__restrict__ pts, int d, const float *__restrict__ cent, int k,
+                               const int32_t *__restrict__ flag_list, const unsigned int *__restrict__ flag_count,
+                               int32_t *__restrict__ assign) {
+  const unsigned int nflag = *flag_count;
+  const int lane = threadIdx.x % 32;
+  const unsigned int warps = (gridDim.x * blockDim.x) / 32;
+  for (unsigned int f = (blockIdx.x * blockDim.x + threadIdx.x) / 32; f < nflag; f += warps) {
+    const long long p = flag_list[f];
+    const float *x = pts + p * d;
+    float best = INFINITY;
+    int arg = 0x7FFFFFFF;
+    for (int c = lane; c < k; c += 32) {  // each lane scans its centroids in ascending order
+      const float *cc = cent + (size_t)c * d;
+      float acc = 0.0f;
+      for (int j = 0; j < d; ++j) acc = __fadd_rn(acc, sqdiff(x[j], cc[j]));
+      if (acc < best) { best = acc; arg = c; }
+    }
+    for (int o = 16; o > 0; o >>= 1) {    // lexicographic (distance, index) minimum = the scan's winner
+      const float ob = __shfl_xor_sync(0xFFFFFFFFu, best, o);
+      const int oa = __shfl_xor_sync(0xFFFFFFFFu, arg, o);
+      if (ob < best || (ob == best && oa < arg)) { best = ob; arg = oa; }
+    }
+    if (lane == 0) assign[p] = (best < INFINITY) ? arg : 0;  // nothing beat +inf: the scan keeps index 0
+  }
+}
+
+// ---- K4: FP64 sums and counts from the assignments, one warp per point -------------------------
+__global__ void accumulate_kernel(const float *__restrict__ pts, long long n, int d, const int32_t *__restrict__ assign,
+                                  double *__restrict__ sums, unsigned long long *__restrict__ counts) {
+  const int lane = threadIdx.x % 32;
+  const long long warps = ((long long)gridDim.x * blockDim.x) / 32;
+  for (long long p = ((long long)blockIdx.x * blockDim.x + threadIdx.x) / 32; p < n; p += warps) {
+    const int c = assign[p];
+    const float *x = pts + p * d;
+    double *dst = sums + (size_t)c * d;
+    for (int j = lane; j < d; j += 32) atomicAdd(&dst[j], (double)x[j]);
+    if (lane == 0) atomicAdd(&counts[c], 1ull);
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
+                                  const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = [] {
+    void *p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+        q != cudaDriverEntryPointSuccess)
+      p = nullptr;
+    return reinterpret_cast<EncodeTiledFn>(p);
+  }();
+  return fn;
+}
+
+// rows x cols FP32 row-major matrix, box = 128 rows x 32 columns, 128-byte swizzle, OOB reads as 0
+bool make_map(CUtensorMap *map, const float *base, uint64_t rows, uint64_t cols) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return false;
+  const cuuint64_t dims[2] = {cols, rows};
+  const cuuint64_t strides[1] = {cols * 4};
+  const cuuint32_t box[2] = {kBlockK, 128};
+  const cuuint32_t estr[2] = {1, 1};
+  return fn(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(base), dims, strides, box, estr,
+            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+size_t tensor_smem_bytes(int d) {
+  const int kblocks = d / kBlockK;
+  return (size_t)2 * kblocks * kABytes + kABytes + (size_t)kStages * kBBytes + 256;
+}
+
+}  // namespace
+
+bool tensor_shape_ok(int k, int d, size_t smem_optin) {
+  return d % kBlockK == 0 && d >= kBlockK && d <= 128 && k >= 128 && tensor_smem_bytes(d) + 1024 <= smem_optin;
+}
+int tensor_k_pad(int k) { return (k + kTileN - 1) / kTileN * kTileN; }
+size_t tensor_caug_floats(int k, int d) { return (size_t)tensor_k_pad(k) * (d + kBlockK); }
+
+cudaError_t launch_tensor_prep(const float *d_cent, int k, int d, float *d_caug, unsigned int *d_cmax_bits,
+                               cudaStream_t s) {
+  cudaError_t e = cudaMemsetAsync(d_cmax_bits, 0, 4, s);
+  if (e != cudaSuccess) return e;
+  const int k_pad = tensor_k_pad(k);
+  tensor_prep_kernel<<<(k_pad + 127) / 128, 128, 0, s>>>(d_cent, k, k_pad, d, d_caug, d_cmax_bits);
+  return cudaGetLastError();
+}
+
+// assign + re-check + accumulate for n device-resident points; 3 kernels on stream s
+cudaError_t launch_tensor_map(const float *d_pts, int64_t n, int d, const float *d_cent, int k, const float *d_caug,
+                              const unsigned int *d_cmax_bits, int32_t *d_assign, int32_t *d_flag_list,
+                              unsigned int *d_flag_count, double *d_sums, unsigned long long *d_counts, int sm_count,
+                              size_t smem_optin, cudaStream_t s) {
+  if (n <= 0) return cudaSuccess;
+  if (n > 0x7FFFFFFFll) return cudaErrorInvalidValue;
+  if ((reinterpret_cast<uintptr_t>(d_pts) & 15) != 0) return cudaErrorInvalidValue;
+  CUtensorMap map_x, map_c;
+  const int k_pad = tensor_k_pad(k);
+  if (!make_map(&map_x, d_pts, (uint64_t)n, (uint64_t)d) ||
+      !make_map(&map_c, d_caug, (uint64_t)k_pad, (uint64_t)(d + kBlockK)))
+    return cudaErrorInvalidValue;
+  cudaError_t e = cudaMemsetAsync(d_flag_count, 0, 4, s);
+  if (e != cudaSuccess) return e;
+  const size_t smem = tensor_smem_bytes(d) + 1024;  // + slack to align the base to 1024 B
+  e = cudaFuncSetAttribute(tensor_assign_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  TensorArgs a{(long long)n, k, k_pad, d, d_cmax_bits, d_assign, d_flag_list, d_flag_count};
+  const long long tiles = (n + kTileM - 1) / kTileM;
+  const int grid = (int)(tiles < sm_count ? tiles : sm_count);
+  tensor_assign_kernel<<<grid, kThreads, smem, s>>>(map_x, map_c, a);
+  if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  recheck_kernel<<<sm_count * 4, 256, 0, s>>>(d_pts, d, d_cent, k, d_flag_list, d_flag_count, d_assign);
+  if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  accumulate_kernel<<<sm_count * 8, 256, 0, s>>>(d_pts, (long long)n, d, d_assign, d_sums, d_counts);
+  return cudaGetLastError();
+}
+
+}  // namespace hgm

@@ -56,6 +56,7 @@ SIGNATURES = {
     "hgm_sync": (C.c_int, [_c_ctx]),
     "hgm_stream": (C.c_int, [_c_ctx, C.POINTER(_p)]),
     "hgm_last_map_ms": (C.c_int, [_c_ctx, C.POINTER(C.c_float), C.POINTER(C.c_int32)]),
+    "hgm_last_rechecks": (C.c_int, [_c_ctx, C.POINTER(C.c_int64)]),
     "hgm_launch_count": (C.c_int, [_c_ctx, C.POINTER(C.c_int64)]),
     "hgm_map_device_static": (C.c_int, [C.c_int, _p, C.c_int64, _p, C.c_int32, C.c_int32, _p, _p, _p, _p]),
     "hgm_device_alloc": (C.c_int, [_c_ctx, C.c_size_t, C.POINTER(_p)]),
@@ -222,6 +223,11 @@ class GpuMapSlot:
         ms, n = C.c_float(), C.c_int32()
         self._check(self._lib.hgm_last_map_ms(self._ctx, C.byref(ms), C.byref(n)))
         return ms.value, n.value
+
+    def last_rechecks(self) -> int:
+        n = C.c_int64()
+        self._check(self._lib.hgm_last_rechecks(self._ctx, C.byref(n)))
+        return n.value
 
     def launch_count(self) -> int:
         n = C.c_int64()

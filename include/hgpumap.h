@@ -137,6 +137,10 @@ int hgm_stream(hgm_ctx *ctx, void **cuda_stream);
 /* Device time of the last map call's kernels in milliseconds (CUDA events on the ctx
  * stream; valid after hgm_sync / hgm_read_partials), and how many kernels it launched. */
 int hgm_last_map_ms(hgm_ctx *ctx, float *ms, int32_t *launches);
+/* How many points of the last map call on the tensor-core path had a top-2 score margin
+ * inside the TF32 rounding bound and were re-scanned with the exact FP32 arithmetic
+ * (0 for the other kernel families).  Synchronises the ctx stream. */
+int hgm_last_rechecks(hgm_ctx *ctx, int64_t *points);
 /* Total kernels this ctx has launched since hgm_open. */
 int hgm_launch_count(hgm_ctx *ctx, int64_t *launches);
 

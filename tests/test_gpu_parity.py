@@ -237,3 +237,65 @@ def test_idempotent_and_centroid_update_roundtrip(slot, oracle):
     slot.set_centroids(new)
     s3, c3, a3 = slot.map_split(pts, want_assign=True)
     np.testing.assert_array_equal(a3, oracle.assign(pts, new))
+
+
+# ---- the tcgen05 path (K2 scores + K3 exact re-check + K4 accumulate) ---------------------------
+
+@pytest.mark.parametrize("d,k,n", [(32, 128, 5000), (64, 1024, 20011), (128, 512, 6001), (96, 300, 4097),
+                                   (64, 129, 255), (64, 256, 256), (64, 256, 1)])
+def test_tensor_path_matches_oracle(slot, oracle, d, k, n):
+    """BASELINE config 4/5 shapes at test size: assignments bit-exact through the TF32 GEMM +
+    FP32 re-check, counts exact, sums within tolerance."""
+    pts, cent = cases.general_d(n, d, k, seed=d + k)
+    run_case(slot, oracle, pts, cent, capi.KERNEL_TENSOR)
+
+
+def test_tensor_path_decides_almost_everything_on_the_tensor_cores(slot, oracle):
+    """If the GEMM scores were wrong every point would be flagged and the exact re-check would
+    hide it: on well-separated data the re-check must stay rare, on duplicated centroids it
+    must take (at least) the points of the duplicated clusters."""
+    pts, cent = cases.general_d(50000, 64, 1024, seed=77)
+    slot.set_kernel(capi.KERNEL_TENSOR)
+    slot.set_centroids(cent)
+    sums, counts, assign = slot.map_split(pts, want_assign=True)
+    rechecks = slot.last_rechecks()
+    np.testing.assert_array_equal(assign, oracle.assign(pts, cent))
+    assert rechecks < 0.02 * len(pts), f"{rechecks} of {len(pts)} points re-checked"
+    dup = cent.copy()
+    dup[1] = dup[0]
+    slot.set_centroids(dup)
+    _, counts, assign = slot.map_split(pts, want_assign=True)
+    np.testing.assert_array_equal(assign, oracle.assign(pts, dup))
+    assert slot.last_rechecks() >= counts[0] > 0
+    slot.set_kernel(capi.KERNEL_AUTO)
+
+
+def test_tensor_path_is_the_default_for_gemm_shapes(slot, oracle):
+    pts, cent = cases.general_d(3000, 64, 1024, seed=3)
+    run_case(slot, oracle, pts, cent, capi.KERNEL_AUTO, want_kernel=capi.KERNEL_TENSOR)
+    pts, cent = cases.general_d(3000, 64, 100, seed=4)  # k < 128: not a tensor shape
+    run_case(slot, oracle, pts, cent, capi.KERNEL_AUTO, want_kernel=capi.KERNEL_EXACT)
+
+
+def test_tensor_path_near_ties_are_rechecked_exactly(slot, oracle):
+    """Duplicated and nearly-duplicated centroids, points on centroids and on bisectors: the
+    TF32 scores cannot separate them, the exact re-check must (lowest index wins ties)."""
+    rng = np.random.default_rng(9)
+    d, k = 64, 256
+    cent = rng.normal(0, 4, size=(k, d)).astype(np.float32)
+    cent[17] = cent[5]                                   # exact duplicate
+    cent[200] = cent[5]
+    cent[33] = cent[32] + np.float32(1e-4)               # closer than TF32 can see
+    cent[64] = np.nextafter(cent[63], np.float32(np.inf))  # one ulp apart
+    pts = [cent[rng.integers(0, k, 2000)] + rng.normal(0, 1.0, size=(2000, d)).astype(np.float32)]
+    pts.append(cent.copy())                              # points exactly on centroids
+    pts.append(((cent[:-1].astype(np.float64) + cent[1:]) / 2).astype(np.float32))  # bisector points
+    nan_row = np.zeros((3, d), np.float32)
+    nan_row[0, 3] = np.nan
+    nan_row[1, 0] = np.inf
+    nan_row[2] = 1e30
+    pts.append(nan_row)
+    pts = np.concatenate(pts).astype(np.float32)
+    run_case(slot, oracle, pts, cent, capi.KERNEL_TENSOR)
+    a = oracle.assign(pts, cent)
+    assert not np.isin(a, [17, 200]).any()
