@@ -170,17 +170,15 @@ int map_points_async(hgm_ctx *c, const float *d_pts, int64_t n, int32_t *d_assig
       return fail(c, HGM_EINVAL, "the tensor path needs 16-byte aligned points");
     if (c->tscratch_rows < (size_t)n) {  // scratch for assignments and the re-check list
       CU(c, cudaStreamSynchronize(c->stream));
-      cudaFree(c->d_tassign); cudaFree(c->d_tlist);
-      c->d_tassign = c->d_tlist = nullptr;
+      cudaFree(c->d_tlist);
+      c->d_tlist = nullptr;
       c->tscratch_rows = 0;
-      CU(c, cudaMalloc(&c->d_tassign, (size_t)n * 4));
       CU(c, cudaMalloc(&c->d_tlist, (size_t)n * 4));
       c->tscratch_rows = (size_t)n;
     }
-    e = launch_tensor_map(d_pts, n, c->d, c->d_cent, c->k, c->d_caug, c->d_tflags, d_assign ? d_assign : c->d_tassign,
-                          c->d_tlist, c->d_tflags + 1, sums_ptr(c), counts_ptr(c), c->sm_count, c->smem_optin,
-                          c->stream);
-    launches = 3;
+    e = launch_tensor_map(d_pts, n, c->d, c->d_cent, c->k, c->d_caug, c->d_tflags, d_assign, c->d_tlist,
+                          c->d_tflags + 1, sums_ptr(c), counts_ptr(c), c->sm_count, c->smem_optin, c->stream);
+    launches = 2;
   } else if (kern == HGM_KERNEL_GRID2D) {
     e = launch_grid2d_map(d_pts, n, c->d_cent, c->k, c->grid, c->d_table, c->d_cand, sums_ptr(c),
                           counts_ptr(c), d_assign, c->sm_count, c->smem_optin, c->stream);

@@ -12,7 +12,8 @@
 //   K3  recheck_kernel         TF32 carries ~2^-10 per operand, so a point whose top-2 margin
 //       is inside the rounding bound is re-scanned with the exact FP32 arithmetic of the
 //       reference scan (ascending index, strict '<'): assignments stay bit-identical.
-//   K4  accumulate_kernel      per-cluster FP64 sums / int64 counts from the final assignments.
+//   K4  accumulation           per-cluster FP64 sums / int64 counts: a decided point is added by its
+//       epilogue thread (RED.ADD.F64, row re-read from L2), a re-checked one by K3.
 //
 // Rounding bound: the score of (x, c) is off by at most 2^-8 |x| |c| (x truncated to TF32 by
 // the tensor core: 2^-10; c rounded to TF32 here: 2^-11; doubled by the factor 2) plus FP32
@@ -21,6 +22,7 @@
 // winner; otherwise K3 decides.
 #include <cuda.h>
 #include <math.h>
+#include <stdlib.h>
 
 #include "hgm_internal.h"
 
@@ -31,11 +33,11 @@ constexpr int kBlockK = 32;    // FP32 elements per K-block = one 128-byte swizz
 constexpr int kUmmaK = 8;      // K of one kind::tf32 instruction (32 bytes)
 constexpr int kTileM = 256;    // points per CTA tile: two 128-row accumulators share every B stage
 constexpr int kTileN = 128;    // centroids per MMA
-constexpr int kStages = 4;     // B pipeline depth
+constexpr int kMaxStages = 8;  // B pipeline depth: as many 16 KiB stages as shared memory leaves (L2 latency is long)
 constexpr int kABytes = 128 * kBlockK * 4;       // one 128-row K-block of A: 16 KiB
 constexpr int kBBytes = kTileN * kBlockK * 4;    // one B stage: 16 KiB
-constexpr int kEpiWarps = 8;
-constexpr int kThreads = (4 + kEpiWarps) * 32;   // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 spare, 4..11 epilogue
+constexpr int kEpiWarps = 16;                    // two per (accumulator half, TMEM lane quarter): 64 columns each
+constexpr int kThreads = (4 + kEpiWarps) * 32;   // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 spare, 4..19 epilogue
 constexpr uint32_t kTmemCols = 512;              // 2 buffers x 2 halves x 128 columns
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
@@ -71,6 +73,13 @@ __device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, i
       "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
       : "memory");
 }
+// one lane of a converged warp (the others skip the statement); keeps the surrounding code
+// warp-uniform so that descriptors and addresses live in uniform registers
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+  return pred != 0;
+}
 // K-major, 128-byte-swizzled operand tile: rows of 128 bytes, 8-row groups 1024 bytes apart
 // (cute/arch/mma_sm100_desc.hpp SmemDescriptor: start>>4 | LBO<<16 | SBO<<32 | version 1<<46 | layout 2<<61)
 __device__ __forceinline__ uint64_t umma_desc(const void *tile, int k_step) {
@@ -92,8 +101,8 @@ __device__ __forceinline__ void umma_commit(uint64_t *bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
                : "memory");
 }
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
-  uint32_t r[32];
+// issue a 32-column TMEM load for this warp's 32 lanes; the registers are valid after tmem_wait()
+__device__ __forceinline__ void tmem_ld32_issue(uint32_t taddr, uint32_t (&r)[32]) {
   asm volatile(
       "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
       "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
@@ -103,10 +112,24 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32]) {
         "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
         "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
       : "r"(taddr));
-  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-#pragma unroll
-  for (int i = 0; i < 32; ++i) v[i] = __uint_as_float(r[i]);
 }
+__device__ __forceinline__ void tmem_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// Top-2 of a stream of scores with the column index riding in the 7 low mantissa bits of the
+// score ("key"): one LOP3 + three FMNMX per element instead of compare/select chains.  The
+// low bits cost 2^-16 of relative precision, far inside the TF32 rounding bound.
+struct Top2 {
+  float best = INFINITY, second = INFINITY;
+  __device__ __forceinline__ void push(uint32_t raw, uint32_t col7) {
+    const float key = __uint_as_float((raw & ~0x7Fu) | col7);
+    second = fminf(second, fmaxf(key, best));
+    best = fminf(key, best);
+  }
+  __device__ __forceinline__ void merge(const Top2 &o) {
+    second = fminf(fminf(second, o.second), fmaxf(best, o.best));
+    best = fminf(best, o.best);
+  }
+};
 
 // ---- prep: augmented centroid matrix C'[k_pad][d + 32] and max |c| ----------------------------
 __device__ __forceinline__ float tf32_rn(float f) {
@@ -142,10 +165,13 @@ __global__ void tensor_prep_kernel(const float *__restrict__ cent, int k, int k_
 // ---- K2 ------------------------------------------------------------------------------------------
 struct TensorArgs {
   long long n;
-  int k, k_pad, d;
+  int k, k_pad, d, stages;
   const unsigned int *cmax_bits;
-  int32_t *assign;        // [n] best index per point
-  int32_t *flag_list;     // indices of points that need the exact re-check
+  const float *pts;
+  double *sums;                 // [k*d] partial sums (RED.ADD.F64)
+  unsigned long long *counts;   // [k]
+  int32_t *assign;              // [n] best index per point, or NULL
+  int32_t *flag_list;           // indices of points that need the exact re-check
   unsigned int *flag_count;
 };
 
@@ -160,10 +186,11 @@ __global__ void __launch_bounds__(kThreads, 1)
   const int ntiles_n = a.k_pad / kTileN;
   unsigned char *a_res = smem;                                  // [2 halves][kblocks] x 16 KiB
   unsigned char *a_aug = a_res + (size_t)2 * kblocks * kABytes; // 16 KiB constant tile
-  unsigned char *b_stage = a_aug + kABytes;                     // kStages x 16 KiB
+  const int kStages = a.stages;
+  unsigned char *b_stage = a_aug + kABytes;                     // stages x 16 KiB
   uint64_t *bars = reinterpret_cast<uint64_t *>(b_stage + (size_t)kStages * kBBytes);
-  uint64_t *full = bars, *empty = bars + kStages;
-  uint64_t *a_full = bars + 2 * kStages, *a_empty = a_full + 1;
+  uint64_t *full = bars, *empty = bars + kMaxStages;
+  uint64_t *a_full = bars + 2 * kMaxStages, *a_empty = a_full + 1;
   uint64_t *t_full = a_empty + 1, *t_empty = t_full + 2;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(t_empty + 2);
 
@@ -196,27 +223,37 @@ __global__ void __launch_bounds__(kThreads, 1)
 
   const long long tiles_m = (a.n + kTileM - 1) / kTileM;
 
-  if (warp == 0 && lane == 0) {
-    // ===== TMA producer =====
+  if (warp == 0) {
+    // ===== TMA producer (whole warp walks the loop, one elected lane issues) =====
     uint32_t stage = 0, phase = 0, a_phase = 0;
     for (long long tm = blockIdx.x; tm < tiles_m; tm += gridDim.x) {
       mbar_wait(a_empty, a_phase ^ 1);
-      mbar_expect_tx(a_full, 2 * kblocks * kABytes);
-      for (int h = 0; h < 2; ++h)
-        for (int kb = 0; kb < kblocks; ++kb)
-          tma_load_2d(a_res + ((size_t)h * kblocks + kb) * kABytes, &map_x, kb * kBlockK,
-                      (int)(tm * kTileM + h * 128), a_full);
+      if (elect_one()) {
+        mbar_expect_tx(a_full, 2 * kblocks * kABytes);
+        for (int h = 0; h < 2; ++h)
+          for (int kb = 0; kb < kblocks; ++kb)
+            tma_load_2d(a_res + ((size_t)h * kblocks + kb) * kABytes, &map_x, kb * kBlockK,
+                        (int)(tm * kTileM + h * 128), a_full);
+      }
+      __syncwarp();
       a_phase ^= 1;
       for (int tn = 0; tn < ntiles_n; ++tn)
         for (int kb = 0; kb <= kblocks; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
-          mbar_expect_tx(&full[stage], kBBytes);
-          tma_load_2d(b_stage + (size_t)stage * kBBytes, &map_c, kb * kBlockK, tn * kTileN, &full[stage]);
+          if (elect_one()) {
+            mbar_expect_tx(&full[stage], kBBytes);
+            tma_load_2d(b_stage + (size_t)stage * kBBytes, &map_c, kb * kBlockK, tn * kTileN, &full[stage]);
+          }
+          __syncwarp();
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
     }
-  } else if (warp == 1 && lane == 0) {
-    // ===== MMA issuer =====
+  } else if (warp == 1) {
+    // ===== MMA issuer (whole warp walks the loop, one elected lane issues) =====
+    // One thread feeds the tensor core, so every instruction between two tcgen05.mma counts:
+    // the shared-memory descriptors are built once and only advanced (16-byte units in the
+    // low bits: a tile = kABytes >> 4, a K-step of 32 bytes = 2).
+    const uint64_t a_desc0 = umma_desc(a_res, 0), aug_desc = umma_desc(a_aug, 0), b_desc0 = umma_desc(b_stage, 0);
     uint32_t stage = 0, phase = 0, a_phase = 0, t_phase[2] = {0, 0};
     int buf = 0;
     for (long long tm = blockIdx.x; tm < tiles_m; tm += gridDim.x) {
@@ -225,33 +262,51 @@ __global__ void __launch_bounds__(kThreads, 1)
       for (int tn = 0; tn < ntiles_n; ++tn) {
         mbar_wait(&t_empty[buf], t_phase[buf] ^ 1);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        for (int kb = 0; kb <= kblocks; ++kb) {
+        const uint32_t tacc0 = tmem_base + (uint32_t)(buf * 2 * kTileN), tacc1 = tacc0 + kTileN;
+        for (int kb = 0; kb < kblocks; ++kb) {
           mbar_wait(&full[stage], phase);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-          const unsigned char *btile = b_stage + (size_t)stage * kBBytes;
-          const int ksteps = kb < kblocks ? kBlockK / kUmmaK : 1;  // the |c|^2 block has 3 live columns
-          for (int h = 0; h < 2; ++h) {
-            const unsigned char *atile = kb < kblocks ? a_res + ((size_t)h * kblocks + kb) * kABytes : a_aug;
-            const uint32_t tacc = tmem_base + (uint32_t)((buf * 2 + h) * kTileN);
-            for (int ks = 0; ks < ksteps; ++ks)
-              umma_tf32(tacc, umma_desc(atile, ks), umma_desc(btile, ks), (kb | ks) != 0);
+          const uint64_t bd = b_desc0 + (uint64_t)(stage * (kBBytes >> 4));
+          const uint64_t ad0 = a_desc0 + (uint64_t)(kb * (kABytes >> 4));
+          const uint64_t ad1 = ad0 + (uint64_t)(kblocks * (kABytes >> 4));
+          if (elect_one()) {
+#pragma unroll
+            for (int ks = 0; ks < kBlockK / kUmmaK; ++ks) umma_tf32(tacc0, ad0 + 2 * ks, bd + 2 * ks, (kb | ks) != 0);
+#pragma unroll
+            for (int ks = 0; ks < kBlockK / kUmmaK; ++ks) umma_tf32(tacc1, ad1 + 2 * ks, bd + 2 * ks, (kb | ks) != 0);
+            umma_commit(&empty[stage]);  // the B stage is free once these MMAs have read it
           }
-          umma_commit(&empty[stage]);  // the B stage is free once these MMAs have read it
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
+          __syncwarp();
+          if (++stage == (uint32_t)kStages) { stage = 0; phase ^= 1; }
         }
-        umma_commit(&t_full[buf]);     // accumulators of this centroid tile are complete
+        {  // the |c|^2 K-block: x side = the constant tile, 3 live columns = one K-step
+          mbar_wait(&full[stage], phase);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint64_t bd = b_desc0 + (uint64_t)(stage * (kBBytes >> 4));
+          if (elect_one()) {
+            umma_tf32(tacc0, aug_desc, bd, 1);
+            umma_tf32(tacc1, aug_desc, bd, 1);
+            umma_commit(&empty[stage]);
+            umma_commit(&t_full[buf]);  // accumulators of this centroid tile are complete
+          }
+          __syncwarp();
+          if (++stage == (uint32_t)kStages) { stage = 0; phase ^= 1; }
+        }
         t_phase[buf] ^= 1;
         buf ^= 1;
       }
-      umma_commit(a_empty);            // every MMA that reads this point tile has retired
+      if (elect_one()) umma_commit(a_empty);  // every MMA that reads this point tile has retired
+      __syncwarp();
     }
   } else if (warp >= 4) {
-    // ===== epilogue: thread = one point (TMEM lane), scans the score columns =====
+    // ===== epilogue: a thread owns one point (TMEM lane) and half of each tile's score columns =====
     const int ew = warp - 4;
     const int quarter = warp % 4;      // a warp may only touch TMEM lanes 32*(warp % 4) .. +31
-    const int half = ew / 4;           // which 128-row accumulator
+    const int half = ew / 8;           // which 128-row accumulator
+    const int colhalf = (ew / 4) % 2;  // columns [64*colhalf, +64) of every centroid tile
     const int row = half * 128 + quarter * 32 + lane;  // row within the CTA tile
     const float cmax = __uint_as_float(*a.cmax_bits);
+    float4 *const xchg = reinterpret_cast<float4 *>(tmem_slot + 4);  // [256 rows] partner results
     uint32_t a_phase = 0, t_phase[2] = {0, 0};
     int buf = 0;
     for (long long tm = blockIdx.x; tm < tiles_m; tm += gridDim.x) {
@@ -259,7 +314,7 @@ __global__ void __launch_bounds__(kThreads, 1)
       mbar_wait(a_full, a_phase);
       a_phase ^= 1;
       float xn = 0.f;
-      {
+      if (colhalf == 0) {
         const int r = row % 128;
         for (int kb = 0; kb < kblocks; ++kb) {
           const float4 *tile = reinterpret_cast<const float4 *>(a_res + ((size_t)half * kblocks + kb) * kABytes);
@@ -272,42 +327,82 @@ __global__ void __launch_bounds__(kThreads, 1)
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(a_empty);
-      float best = INFINITY, second = INFINITY;
-      int bidx = 0;
+      Top2 even, odd;          // two independent chains for instruction-level parallelism
+      int best_tile = 0;
       for (int tn = 0; tn < ntiles_n; ++tn) {
         mbar_wait(&t_full[buf], t_phase[buf]);
         t_phase[buf] ^= 1;
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)((buf * 2 + half) * kTileN);
-#pragma unroll 1
-        for (int ch = 0; ch < kTileN / 32; ++ch) {
-          float v[32];
-          tmem_ld32(taddr + ch * 32, v);
-          const int cbase = tn * kTileN + ch * 32;
-#pragma unroll
-          for (int i = 0; i < 32; ++i) {
-            const float s = v[i];
-            second = fminf(second, fmaxf(s, best));
-            bidx = s < best ? cbase + i : bidx;
-            best = fminf(s, best);
-          }
-        }
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) +
+                               (uint32_t)((buf * 2 + half) * kTileN + colhalf * 64);
+        uint32_t r0[32], r1[32];
+        tmem_ld32_issue(taddr, r0);
+        tmem_ld32_issue(taddr + 32, r1);
+        const float before = fminf(even.best, odd.best);
+        tmem_wait();
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
         __syncwarp();
-        if (lane == 0) mbar_arrive(&t_empty[buf]);
+        if (lane == 0) mbar_arrive(&t_empty[buf]);  // the scores are in registers: free the accumulator
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          even.push(r0[i], colhalf * 64 + i);
+          odd.push(r0[i + 1], colhalf * 64 + i + 1);
+        }
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          even.push(r1[i], colhalf * 64 + 32 + i);
+          odd.push(r1[i + 1], colhalf * 64 + 32 + i + 1);
+        }
+        if (fminf(even.best, odd.best) < before) best_tile = tn;
         buf ^= 1;
       }
-      const long long p = tm * kTileM + row;
-      if (p < a.n) {
-        const float xnorm = sqrtf(xn);
-        const float reach = xnorm + cmax;
-        const float thr = 0.0078125f * xnorm * cmax + (float)a.d * 2.3841858e-07f * reach * reach;
-        a.assign[p] = bidx;
-        if (!(second - best > thr)) {  // also catches NaN / inf rows
-          const unsigned int slot = atomicAdd(a.flag_count, 1u);
-          a.flag_list[slot] = (int32_t)p;  // p < 2^31 per launch (the host chunks larger inputs)
+      even.merge(odd);
+      // the two column-halves of a row meet in shared memory; colhalf 0 decides the point
+      const int pair_bar = 1 + half * 4 + quarter;
+      if (colhalf == 1) xchg[row] = make_float4(even.best, even.second, __int_as_float(best_tile), 0.f);
+      asm volatile("bar.sync %0, %1;" ::"r"(pair_bar), "r"(64) : "memory");
+      if (colhalf == 0) {
+        const float4 o = xchg[row];
+        if (o.x < even.best) best_tile = __float_as_int(o.z);
+        Top2 other;
+        other.best = o.x; other.second = o.y;
+        even.merge(other);
+        const long long p = tm * kTileM + row;
+        int decided = -1;  // cluster of a point decided on the tensor cores, else -1
+        if (p < a.n) {
+          const int bidx = best_tile * kTileN + (int)(__float_as_uint(even.best) & 0x7Fu);
+          const float xnorm = sqrtf(xn);
+          const float reach = xnorm + cmax;
+          // 2^-7 |x||c| (TF32 operands, both sides of the margin) + (d 2^-22 + 2^-14)(|x|+|c|)^2
+          // (FP32 accumulation, the scan's own rounding, the 7 index bits of the keys)
+          const float thr = 0.0078125f * xnorm * cmax + ((float)a.d * 2.3841858e-07f + 6.1035156e-05f) * reach * reach;
+          if (a.assign) a.assign[p] = bidx;
+          if (even.second - even.best > thr) {
+            decided = bidx;
+          } else {  // inside the rounding bound (or NaN / inf): the exact scan decides
+            const unsigned int slot = atomicAdd(a.flag_count, 1u);
+            a.flag_list[slot] = (int32_t)p;  // p < 2^31 per launch (the host chunks larger inputs)
+          }
+        }
+        xchg[row].w = __int_as_float(decided);
+      }
+      asm volatile("bar.sync %0, %1;" ::"r"(pair_bar), "r"(64) : "memory");
+      // K4 for the decided points: both warps of the pair take 16 rows each; a row is added by
+      // the whole warp, lane j adding coordinates j, j+32, ... (coalesced FP64 REDs; the row was
+      // TMA-loaded microseconds ago and is still in L2)
+      {
+        const int row0 = half * 128 + quarter * 32 + colhalf * 16;
+        for (int i = 0; i < 16; ++i) {
+          const int c = __float_as_int(xchg[row0 + i].w);
+          if (c >= 0) {
+            const float *x = a.pts + (tm * kTileM + row0 + i) * a.d;
+            double *dst = a.sums + (size_t)c * a.d;
+            for (int j = lane; j < a.d; j += 32) atomicAdd(dst + j, (double)__ldg(x + j));
+            if (lane == 0) atomicAdd(a.counts + c, 1ull);
+          }
         }
       }
+      asm volatile("bar.sync %0, %1;" ::"r"(pair_bar), "r"(64) : "memory");  // xchg reusable
     }
   }
   __syncthreads();
@@ -316,10 +411,12 @@ __global__ void __launch_bounds__(kThreads, 1)
   }
 }
 
-// ---- K3: exact re-check of flagged points, one warp per point ---------------------------------
+// ---- K3: exact re-check of the flagged points, one warp per point; it also adds them to the
+// partial sums (K4 for these points) --------------------------------------------------------------
 __global__ void recheck_kernel(const float *__restrict__ pts, int d, const float *__restrict__ cent, int k,
                                const int32_t *__restrict__ flag_list, const unsigned int *__restrict__ flag_count,
-                               int32_t *__restrict__ assign) {
+                               int32_t *__restrict__ assign, double *__restrict__ sums,
+                               unsigned long long *__restrict__ counts) {
   const unsigned int nflag = *flag_count;
   const int lane = threadIdx.x % 32;
   const unsigned int warps = (gridDim.x * blockDim.x) / 32;
@@ -339,21 +436,12 @@ __global__ void recheck_kernel(const float *__restrict__ pts, int d, const float
       const int oa = __shfl_xor_sync(0xFFFFFFFFu, arg, o);
       if (ob < best || (ob == best && oa < arg)) { best = ob; arg = oa; }
     }
-    if (lane == 0) assign[p] = (best < INFINITY) ? arg : 0;  // nothing beat +inf: the scan keeps index 0
-  }
-}
-
-// ---- K4: FP64 sums and counts from the assignments, one warp per point -------------------------
-__global__ void accumulate_kernel(const float *__restrict__ pts, long long n, int d, const int32_t *__restrict__ assign,
-                                  double *__restrict__ sums, unsigned long long *__restrict__ counts) {
-  const int lane = threadIdx.x % 32;
-  const long long warps = ((long long)gridDim.x * blockDim.x) / 32;
-  for (long long p = ((long long)blockIdx.x * blockDim.x + threadIdx.x) / 32; p < n; p += warps) {
-    const int c = assign[p];
-    const float *x = pts + p * d;
-    double *dst = sums + (size_t)c * d;
-    for (int j = lane; j < d; j += 32) atomicAdd(&dst[j], (double)x[j]);
-    if (lane == 0) atomicAdd(&counts[c], 1ull);
+    const int c = (best < INFINITY) ? arg : 0;  // nothing beat +inf: the scan keeps index 0
+    if (lane == 0) {
+      if (assign) assign[p] = c;
+      atomicAdd(&counts[c], 1ull);
+    }
+    for (int j = lane; j < d; j += 32) atomicAdd(&sums[(size_t)c * d + j], (double)x[j]);
   }
 }
 
@@ -386,15 +474,22 @@ bool make_map(CUtensorMap *map, const float *base, uint64_t rows, uint64_t cols)
             CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
-size_t tensor_smem_bytes(int d) {
+size_t tensor_smem_bytes(int d, int stages) {
   const int kblocks = d / kBlockK;
-  return (size_t)2 * kblocks * kABytes + kABytes + (size_t)kStages * kBBytes + 256;
+  return (size_t)2 * kblocks * kABytes + kABytes + (size_t)stages * kBBytes + 512 + kTileM * 16 + 1024;
+}
+int tensor_stages(int d, size_t smem_optin) {
+  int stages = kMaxStages;
+  if (const char *v = getenv("HGM_TENSOR_STAGES")) stages = atoi(v);  // tuning knob
+  if (stages > kMaxStages) stages = kMaxStages;
+  while (stages > 2 && tensor_smem_bytes(d, stages) > smem_optin) --stages;
+  return stages;
 }
 
 }  // namespace
 
 bool tensor_shape_ok(int k, int d, size_t smem_optin) {
-  return d % kBlockK == 0 && d >= kBlockK && d <= 128 && k >= 128 && tensor_smem_bytes(d) + 1024 <= smem_optin;
+  return d % kBlockK == 0 && d >= kBlockK && d <= 128 && k >= 128 && tensor_smem_bytes(d, 2) <= smem_optin;
 }
 int tensor_k_pad(int k) { return (k + kTileN - 1) / kTileN * kTileN; }
 size_t tensor_caug_floats(int k, int d) { return (size_t)tensor_k_pad(k) * (d + kBlockK); }
@@ -408,7 +503,7 @@ cudaError_t launch_tensor_prep(const float *d_cent, int k, int d, float *d_caug,
   return cudaGetLastError();
 }
 
-// assign + re-check + accumulate for n device-resident points; 3 kernels on stream s
+// scores + assignment + accumulation (K2), then the exact re-check of the flagged points (K3)
 cudaError_t launch_tensor_map(const float *d_pts, int64_t n, int d, const float *d_cent, int k, const float *d_caug,
                               const unsigned int *d_cmax_bits, int32_t *d_assign, int32_t *d_flag_list,
                               unsigned int *d_flag_count, double *d_sums, unsigned long long *d_counts, int sm_count,
@@ -423,17 +518,17 @@ cudaError_t launch_tensor_map(const float *d_pts, int64_t n, int d, const float 
     return cudaErrorInvalidValue;
   cudaError_t e = cudaMemsetAsync(d_flag_count, 0, 4, s);
   if (e != cudaSuccess) return e;
-  const size_t smem = tensor_smem_bytes(d) + 1024;  // + slack to align the base to 1024 B
+  const int stages = tensor_stages(d, smem_optin);
+  const size_t smem = tensor_smem_bytes(d, stages);  // includes 1 KiB of slack to align the base
   e = cudaFuncSetAttribute(tensor_assign_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  TensorArgs a{(long long)n, k, k_pad, d, d_cmax_bits, d_assign, d_flag_list, d_flag_count};
+  TensorArgs a{(long long)n, k, k_pad, d, stages, d_cmax_bits, d_pts, d_sums, d_counts, d_assign, d_flag_list, d_flag_count};
   const long long tiles = (n + kTileM - 1) / kTileM;
   const int grid = (int)(tiles < sm_count ? tiles : sm_count);
   tensor_assign_kernel<<<grid, kThreads, smem, s>>>(map_x, map_c, a);
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
-  recheck_kernel<<<sm_count * 4, 256, 0, s>>>(d_pts, d, d_cent, k, d_flag_list, d_flag_count, d_assign);
-  if ((e = cudaGetLastError()) != cudaSuccess) return e;
-  accumulate_kernel<<<sm_count * 8, 256, 0, s>>>(d_pts, (long long)n, d, d_assign, d_sums, d_counts);
+  recheck_kernel<<<sm_count * 4, 256, 0, s>>>(d_pts, d, d_cent, k, d_flag_list, d_flag_count, d_assign, d_sums,
+                                              d_counts);
   return cudaGetLastError();
 }
 
