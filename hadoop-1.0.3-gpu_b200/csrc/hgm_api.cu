@@ -11,6 +11,7 @@
 #include <stdlib.h>
 
 #include <algorithm>
+#include <unordered_map>
 #include <vector>
 
 #include "hgm_internal.h"
@@ -56,6 +57,8 @@ struct hgm_ctx {
   int64_t total_launches = 0;
   bool timing_open = false;
   void *nccl_comm = nullptr;
+  struct CachedSplit { void *d_rows; int64_t n_points; size_t nbytes; };
+  std::unordered_map<int64_t, CachedSplit> cache;  // HBM-resident splits by id
   char err[512] = "";
 };
 
@@ -279,6 +282,8 @@ void hgm_close(hgm_ctx *c) {
   cudaSetDevice(c->device);
   if (c->stream) cudaStreamSynchronize(c->stream);
   if (c->nccl_comm) { hgm::comm_destroy(c->nccl_comm); c->nccl_comm = nullptr; }
+  for (auto &kv : c->cache) cudaFree(kv.second.d_rows);
+  c->cache.clear();
   free_job(c);
   for (int i = 0; i < kStages; ++i) {
     if (c->copy[i]) { cudaStreamSynchronize(c->copy[i]); cudaStreamDestroy(c->copy[i]); }
@@ -611,6 +616,128 @@ int hgm_map_file(hgm_ctx *c, const char *path, int64_t offset, int64_t length, i
   fclose(f);
   if (rc != HGM_OK) cudaStreamSynchronize(c->stream);
   return rc;
+}
+
+// ---- HBM-resident split cache -------------------------------------------------------------
+
+static void cache_erase(hgm_ctx *c, int64_t id) {
+  auto it = c->cache.find(id);
+  if (it == c->cache.end()) return;
+  cudaFree(it->second.d_rows);
+  c->cache.erase(it);
+}
+
+static int cache_store(hgm_ctx *c, int64_t split_id, SplitSource &src, int32_t fmt) {
+  if (!c->d_partials) return fail(c, HGM_EINVAL, "hgm_set_centroids has not been called (d is unknown)");
+  if (split_id < 0) return fail(c, HGM_EINVAL, "split_id must be >= 0");
+  if (fmt != HGM_FMT_F32LE && fmt != HGM_FMT_F32BE)
+    return fail(c, HGM_EFORMAT, "record format %d is not supported by this build", fmt);
+  const size_t row = (size_t)c->d * 4;
+  if (src.nbytes % row != 0)
+    return fail(c, HGM_EFORMAT, "split of %zu bytes is not a whole number of %zu-byte rows", src.nbytes, row);
+  CU(c, cudaStreamSynchronize(c->stream));
+  cache_erase(c, split_id);
+  void *d_rows = nullptr;
+  cudaError_t e = cudaMalloc(&d_rows, src.nbytes ? src.nbytes : 16);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return fail(c, HGM_ENOMEM, "split %lld (%zu bytes) does not fit the HBM cache: %s", (long long)split_id,
+                src.nbytes, cudaGetErrorString(e));
+  }
+  int rc = HGM_OK;
+  if (src.file) {  // through the pinned bounce buffers
+    rc = ensure_pipeline(c, false, 1, true);
+    size_t off = 0;
+    int bi = 0;
+    while (rc == HGM_OK && off < src.nbytes) {
+      const size_t piece = std::min(kBounceBytes, src.nbytes - off);
+      if (cudaEventSynchronize(c->ev_bounce[bi]) != cudaSuccess) cudaGetLastError();
+      if (fread(c->h_bounce[bi], 1, piece, src.file) != piece) {
+        rc = fail(c, HGM_EIO, "short read from split file: %s", strerror(errno));
+        break;
+      }
+      e = cudaMemcpyAsync(static_cast<unsigned char *>(d_rows) + off, c->h_bounce[bi], piece, cudaMemcpyHostToDevice,
+                          c->stream);
+      if (e == cudaSuccess) e = cudaEventRecord(c->ev_bounce[bi], c->stream);
+      if (e != cudaSuccess) rc = fail(c, HGM_ECUDA, "cache copy: %s", cudaGetErrorString(e));
+      bi = (bi + 1) % kStages;
+      off += piece;
+    }
+  } else if (src.nbytes) {
+    e = cudaMemcpyAsync(d_rows, src.mem, src.nbytes, cudaMemcpyHostToDevice, c->stream);
+    if (e != cudaSuccess) rc = fail(c, HGM_ECUDA, "cache copy: %s", cudaGetErrorString(e));
+  }
+  if (rc == HGM_OK && fmt == HGM_FMT_F32BE) {
+    e = launch_bswap32(static_cast<uint32_t *>(d_rows), (int64_t)(src.nbytes / 4), c->stream);
+    if (e != cudaSuccess) rc = fail(c, HGM_ECUDA, "decode launch: %s", cudaGetErrorString(e));
+    else c->total_launches += 1;
+  }
+  if (rc == HGM_OK && cudaStreamSynchronize(c->stream) != cudaSuccess) rc = fail(c, HGM_ECUDA, "cache copy failed");
+  if (rc != HGM_OK) {
+    cudaFree(d_rows);
+    return rc;
+  }
+  c->cache[split_id] = hgm_ctx::CachedSplit{d_rows, (int64_t)(src.nbytes / row), src.nbytes};
+  return HGM_OK;
+}
+
+int hgm_cache_put(hgm_ctx *c, int64_t split_id, const void *host_bytes, size_t nbytes, int32_t fmt) {
+  NEED_CTX(c);
+  if (nbytes > 0 && !host_bytes) return fail(c, HGM_EINVAL, "host_bytes is NULL");
+  SplitSource src;
+  src.mem = static_cast<const unsigned char *>(host_bytes);
+  src.nbytes = nbytes;
+  return cache_store(c, split_id, src, fmt);
+}
+
+int hgm_cache_put_file(hgm_ctx *c, int64_t split_id, const char *path, int64_t offset, int64_t length, int32_t fmt) {
+  NEED_CTX(c);
+  if (!path || offset < 0) return fail(c, HGM_EINVAL, "bad path or offset");
+  FILE *f = fopen(path, "rb");
+  if (!f) return fail(c, HGM_EIO, "cannot open %s: %s", path, strerror(errno));
+  if (length < 0) {
+    fseeko(f, 0, SEEK_END);
+    length = std::max<int64_t>((int64_t)ftello(f) - offset, 0);
+  }
+  if (fseeko(f, (off_t)offset, SEEK_SET) != 0) {
+    fclose(f);
+    return fail(c, HGM_EIO, "cannot seek %s to %lld", path, (long long)offset);
+  }
+  SplitSource src;
+  src.file = f;
+  src.nbytes = (size_t)length;
+  const int rc = cache_store(c, split_id, src, fmt);
+  fclose(f);
+  return rc;
+}
+
+int hgm_cache_map(hgm_ctx *c, int64_t split_id, int32_t *d_assign, int64_t *n_points_out) {
+  NEED_CTX(c);
+  auto it = c->cache.find(split_id);
+  if (it == c->cache.end()) return fail(c, HGM_EINVAL, "split %lld is not in the cache", (long long)split_id);
+  if (n_points_out) *n_points_out = it->second.n_points;
+  return hgm_map_device(c, static_cast<const float *>(it->second.d_rows), it->second.n_points, d_assign);
+}
+
+int hgm_cache_drop(hgm_ctx *c, int64_t split_id) {
+  NEED_CTX(c);
+  CU(c, cudaStreamSynchronize(c->stream));
+  if (split_id >= 0) {
+    cache_erase(c, split_id);
+  } else {
+    for (auto &kv : c->cache) cudaFree(kv.second.d_rows);
+    c->cache.clear();
+  }
+  return HGM_OK;
+}
+
+int hgm_cache_info(hgm_ctx *c, int64_t *n_splits, int64_t *bytes) {
+  if (!c) return fail(nullptr, HGM_EINVAL, "ctx is NULL");
+  int64_t total = 0;
+  for (auto &kv : c->cache) total += (int64_t)kv.second.nbytes;
+  if (n_splits) *n_splits = (int64_t)c->cache.size();
+  if (bytes) *bytes = total;
+  return HGM_OK;
 }
 
 // ---- synthetic workload ------------------------------------------------------------------

@@ -53,6 +53,11 @@ SIGNATURES = {
     "hgm_reset_partials": (C.c_int, [_c_ctx]),
     "hgm_read_partials": (C.c_int, [_c_ctx, _p, _p]),
     "hgm_partials_device": (C.c_int, [_c_ctx, C.POINTER(_p), C.POINTER(_p)]),
+    "hgm_cache_put": (C.c_int, [_c_ctx, C.c_int64, _p, C.c_size_t, C.c_int32]),
+    "hgm_cache_put_file": (C.c_int, [_c_ctx, C.c_int64, C.c_char_p, C.c_int64, C.c_int64, C.c_int32]),
+    "hgm_cache_map": (C.c_int, [_c_ctx, C.c_int64, _p, C.POINTER(C.c_int64)]),
+    "hgm_cache_drop": (C.c_int, [_c_ctx, C.c_int64]),
+    "hgm_cache_info": (C.c_int, [_c_ctx, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "hgm_sync": (C.c_int, [_c_ctx]),
     "hgm_stream": (C.c_int, [_c_ctx, C.POINTER(_p)]),
     "hgm_last_map_ms": (C.c_int, [_c_ctx, C.POINTER(C.c_float), C.POINTER(C.c_int32)]),
@@ -192,6 +197,29 @@ class GpuMapSlot:
                                            _ptr(counts), _ptr(assign), C.byref(n)))
         self.last_points = n.value
         return sums, counts, assign
+
+    # -- HBM-resident split cache -------------------------------------------------------
+    def cache_put(self, split_id: int, split, fmt: int = FMT_F32LE) -> None:
+        buf = np.frombuffer(split, dtype=np.uint8) if not isinstance(split, np.ndarray) else split
+        buf = np.ascontiguousarray(buf)
+        self._check(self._lib.hgm_cache_put(self._ctx, split_id, _ptr(buf) if buf.nbytes else None, buf.nbytes, fmt))
+
+    def cache_put_file(self, split_id: int, path: str, offset: int = 0, length: int = -1,
+                       fmt: int = FMT_F32LE) -> None:
+        self._check(self._lib.hgm_cache_put_file(self._ctx, split_id, path.encode(), offset, length, fmt))
+
+    def cache_map(self, split_id: int, d_assign: int | None = None) -> int:
+        n = C.c_int64()
+        self._check(self._lib.hgm_cache_map(self._ctx, split_id, d_assign, C.byref(n)))
+        return n.value
+
+    def cache_drop(self, split_id: int = -1) -> None:
+        self._check(self._lib.hgm_cache_drop(self._ctx, split_id))
+
+    def cache_info(self) -> tuple[int, int]:
+        n, b = C.c_int64(), C.c_int64()
+        self._check(self._lib.hgm_cache_info(self._ctx, C.byref(n), C.byref(b)))
+        return n.value, b.value
 
     # -- device-resident splits ---------------------------------------------------------
     def map_device(self, d_points: int, n_points: int, d_assign: int | None = None) -> None:

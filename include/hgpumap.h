@@ -128,6 +128,25 @@ int hgm_read_partials(hgm_ctx *ctx, double *sums_kxd, int64_t *counts_k);
 /* Device addresses of the partials, laid out [k*d doubles][k int64] contiguously, for a
  * caller that runs its own collective (torch.distributed) on them. */
 int hgm_partials_device(hgm_ctx *ctx, double **d_sums, int64_t **d_counts);
+/* The HBM-resident split cache: iteration 1 of a job stages each split once and keeps the
+ * decoded rows on the device; iterations 2.. map them from HBM (BASELINE config 3: 10
+ * iterations over the same 20 GB).  It is a cache only -- the unit of recovery stays the
+ * split (the reference re-runs a failed map from its input, mapred/JobInProgress.java:
+ * 3146-3159): a put that does not fit returns HGM_ENOMEM and the caller maps the split with
+ * hgm_map_split instead; hgm_close drops everything.
+ *   hgm_cache_put       stage + decode a split held in host memory, keep it under split_id
+ *                       (replacing an older entry of that id)
+ *   hgm_cache_put_file  same from a FileSplit byte range (mapred/FileSplit.java:81-85)
+ *   hgm_cache_map       hgm_map_device on the cached rows: ADDS into the partials, async
+ *   hgm_cache_drop      forget one split, or all of them with split_id < 0
+ *   hgm_cache_info      number of cached splits and their bytes */
+int hgm_cache_put(hgm_ctx *ctx, int64_t split_id, const void *host_bytes, size_t nbytes, int32_t fmt);
+int hgm_cache_put_file(hgm_ctx *ctx, int64_t split_id, const char *path, int64_t offset, int64_t length,
+                       int32_t fmt);
+int hgm_cache_map(hgm_ctx *ctx, int64_t split_id, int32_t *d_assign_or_null, int64_t *n_points_out);
+int hgm_cache_drop(hgm_ctx *ctx, int64_t split_id);
+int hgm_cache_info(hgm_ctx *ctx, int64_t *n_splits, int64_t *bytes);
+
 /* Wait for everything queued on the ctx stream. */
 int hgm_sync(hgm_ctx *ctx);
 /* The ctx's compute stream as a cudaStream_t, so a host that has its own CUDA binding can
