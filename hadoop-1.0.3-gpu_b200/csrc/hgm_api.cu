@@ -38,6 +38,10 @@ struct hgm_ctx {
   size_t assign_chunk_cap = 0;
   void *h_bounce[kStages] = {};
   cudaEvent_t ev_bounce[kStages] = {};
+  void *d_text[kStages] = {};             // staged text pieces (kBounceBytes each), lazily allocated
+  unsigned int *d_tblocks[kStages] = {};  // field counts / offsets per 4 KiB of text
+  TextStats *d_tstats[kStages] = {};
+  TextStats *h_tstats = nullptr;          // pinned, kStages entries
 
   int k = 0, d = 0;
   float *d_cent = nullptr;      // k*d floats (+ pad to 16 B)
@@ -293,7 +297,11 @@ void hgm_close(hgm_ctx *c) {
     cudaFree(c->d_chunk[i]);
     cudaFree(c->d_assign_chunk[i]);
     if (c->h_bounce[i]) cudaFreeHost(c->h_bounce[i]);
+    cudaFree(c->d_text[i]);
+    cudaFree(c->d_tblocks[i]);
+    cudaFree(c->d_tstats[i]);
   }
+  if (c->h_tstats) cudaFreeHost(c->h_tstats);
   if (c->ev_t0) cudaEventDestroy(c->ev_t0);
   if (c->ev_t1) cudaEventDestroy(c->ev_t1);
   if (c->stream) cudaStreamDestroy(c->stream);
@@ -582,6 +590,260 @@ static int map_stream(hgm_ctx *c, SplitSource &src, int32_t fmt, double *sums, i
   return HGM_OK;
 }
 
+// ---- HBM-resident split cache -------------------------------------------------------------
+
+static void cache_erase(hgm_ctx *c, int64_t id) {
+  auto it = c->cache.find(id);
+  if (it == c->cache.end()) return;
+  cudaFree(it->second.d_rows);
+  c->cache.erase(it);
+}
+
+// ---- text splits: LineRecordReader framing on the host, decode on the device ----------------
+
+static int ensure_text(hgm_ctx *c) {
+  for (int i = 0; i < kStages; ++i) {
+    if (!c->d_text[i]) CU(c, cudaMalloc(&c->d_text[i], kBounceBytes));
+    if (!c->d_tblocks[i]) CU(c, cudaMalloc(&c->d_tblocks[i], text_block_count(kBounceBytes) * sizeof(unsigned int)));
+    if (!c->d_tstats[i]) CU(c, cudaMalloc(&c->d_tstats[i], sizeof(TextStats)));
+  }
+  if (!c->h_tstats) CU(c, cudaHostAlloc(&c->h_tstats, kStages * sizeof(TextStats), cudaHostAllocDefault));
+  return HGM_OK;
+}
+
+// Bytes LineReader.readLine (core/org/apache/hadoop/util/LineReader.java:106-167) consumes from
+// file position pos: through the first LF, or the first CR and an LF right behind it; to EOF if
+// neither shows up.
+static int64_t line_bytes_from(FILE *f, int64_t pos) {
+  if (fseeko(f, (off_t)pos, SEEK_SET) != 0) return 0;
+  int64_t n = 0;
+  for (;;) {
+    const int ch = fgetc(f);
+    if (ch == EOF) return n;
+    ++n;
+    if (ch == '\n') return n;
+    if (ch == '\r') {
+      const int nx = fgetc(f);
+      return nx == '\n' ? n + 1 : n;
+    }
+  }
+}
+
+// The byte range of the records LineRecordReader hands out for FileSplit(off, len)
+// (mapred/org/apache/hadoop/mapred/LineRecordReader.java:79-95 and :137-157): a split that does
+// not start at 0 gives its first (partial or whole) line to its predecessor -- found by reading
+// one line from off-1 -- and every line that STARTS before off+len is read to its end.
+static void text_split_bounds(FILE *f, int64_t off, int64_t len, int64_t *start_out, int64_t *stop_out) {
+  fseeko(f, 0, SEEK_END);
+  const int64_t size = (int64_t)ftello(f);
+  int64_t end = len < 0 ? size : off + len;
+  if (end > size) end = size;
+  int64_t start = off;
+  if (off != 0) start = (off - 1) + line_bytes_from(f, off - 1);
+  if (start > size) start = size;
+  int64_t stop = start;
+  if (start < end) stop = (end - 1) + line_bytes_from(f, end - 1);
+  *start_out = start;
+  *stop_out = stop;
+}
+
+// Where to cut a staged window so that it ends at a line end (0 = no line end inside).
+static size_t text_cut(const unsigned char *buf, size_t n) {
+  for (size_t p = n; p > 0; --p)
+    if (buf[p - 1] == '\n') return p;
+  for (size_t p = n > 0 ? n - 1 : 0; p > 0; --p)  // CR-only files; a CR in the last byte may have its LF outside
+    if (buf[p - 1] == '\r') return p;
+  return 0;
+}
+
+static int text_error(hgm_ctx *c, const TextStats &st, int64_t origin) {
+  const unsigned code = (unsigned)(st.first_error & 15u);
+  const long long pos = (long long)(st.first_error >> 4) + origin;
+  switch (code) {
+    case HGM_TEXT_MALFORMED:
+      return fail(c, HGM_EFORMAT, "text split: the field at byte %lld is not a number sscanf(\"%%f\") accepts", pos);
+    case HGM_TEXT_RAGGED:
+      return fail(c, HGM_EFORMAT, "text split: the line ending at byte %lld does not hold a whole number of d=%d points",
+                  pos, c->d);
+    case HGM_TEXT_LONG:
+      return fail(c, HGM_EFORMAT, "text split: the field at byte %lld is longer than 127 bytes", pos);
+    default:
+      return fail(c, HGM_ECUDA, "text split: decoder ran out of room at byte %lld", pos);
+  }
+}
+
+static int map_text_stream(hgm_ctx *c, SplitSource &src, double *sums, int64_t *counts, int32_t *assign,
+                           int64_t *n_points_out) {
+  if (!c->d_partials) return fail(c, HGM_EINVAL, "hgm_set_centroids has not been called");
+  if (!sums || !counts) return fail(c, HGM_EINVAL, "sums_kxd and counts_k are required");
+  if (assign)
+    return fail(c, HGM_EINVAL, "assignments of a text split are not returned (the caller cannot size the array); "
+                               "cache the split and map it from HBM instead");
+  int rc = ensure_pipeline(c, false, 1, true);
+  if (rc == HGM_OK) rc = ensure_text(c);
+  if (rc != HGM_OK) return rc;
+
+  c->last_launches = 0;
+  CU(c, cudaMemsetAsync(c->d_partials, 0, partial_bytes(c), c->stream));
+  CU(c, cudaEventRecord(c->ev_t0, c->stream));
+  size_t remaining = src.nbytes, src_pos = 0;  // src_pos: source offset of the next fresh byte
+  const unsigned char *carry = nullptr;
+  size_t carry_len = 0;
+  int64_t points = 0;
+  int stage = 0;
+  bool used[kStages] = {};
+  while (remaining > 0 || carry_len > 0) {
+    cudaStream_t cs = c->copy[stage];
+    unsigned char *buf = static_cast<unsigned char *>(c->h_bounce[stage]);
+    if (used[stage]) CU(c, cudaEventSynchronize(c->ev_bounce[stage]));
+    if (carry_len) memmove(buf, carry, carry_len);  // the unfinished line of the previous window
+    const int64_t origin = (int64_t)src_pos - (int64_t)carry_len;
+    const size_t fresh = std::min(remaining, kBounceBytes - carry_len);
+    if (src.file) {
+      if (fresh && fread(buf + carry_len, 1, fresh, src.file) != fresh)
+        return fail(c, HGM_EIO, "short read from split file: %s", strerror(errno));
+    } else if (fresh) {
+      memcpy(buf + carry_len, src.mem + src_pos, fresh);
+    }
+    src_pos += fresh;
+    remaining -= fresh;
+    const size_t n = carry_len + fresh;
+    const size_t cut = remaining == 0 ? n : text_cut(buf, n);
+    if (cut == 0) return fail(c, HGM_EFORMAT, "text split: a line longer than %zu bytes at byte %lld", kBounceBytes, (long long)origin);
+    carry = buf + cut;
+    carry_len = n - cut;
+
+    CU(c, cudaMemcpyAsync(c->d_text[stage], buf, cut, cudaMemcpyHostToDevice, cs));
+    CU(c, cudaEventRecord(c->ev_bounce[stage], cs));
+    if (used[stage]) CU(c, cudaStreamWaitEvent(cs, c->ev_free[stage], 0));  // rows still being mapped
+    cudaError_t e = launch_text_decode(static_cast<const unsigned char *>(c->d_text[stage]), cut, c->d,
+                                       static_cast<float *>(c->d_chunk[stage]), kChunkBytes / 4, c->d_tblocks[stage],
+                                       c->d_tstats[stage], cs);
+    if (e != cudaSuccess) return fail(c, HGM_ECUDA, "text decode launch: %s", cudaGetErrorString(e));
+    c->last_launches += 3;
+    c->total_launches += 3;
+    CU(c, cudaMemcpyAsync(&c->h_tstats[stage], c->d_tstats[stage], sizeof(TextStats), cudaMemcpyDeviceToHost, cs));
+    CU(c, cudaEventRecord(c->ev_h2d[stage], cs));
+    CU(c, cudaStreamSynchronize(cs));  // only this copy stream: the previous piece keeps mapping meanwhile
+    const TextStats st = c->h_tstats[stage];
+    if (st.first_error != ~0ull) return text_error(c, st, origin);
+    if (st.n_fields % (unsigned long long)c->d != 0)
+      return fail(c, HGM_EFORMAT, "text split: the line ending at byte %lld does not hold a whole number of d=%d points",
+                  (long long)(origin + (int64_t)cut), c->d);
+    const int64_t m = (int64_t)(st.n_fields / (unsigned long long)c->d);
+    CU(c, cudaStreamWaitEvent(c->stream, c->ev_h2d[stage], 0));
+    rc = map_points_async(c, static_cast<const float *>(c->d_chunk[stage]), m, nullptr);
+    if (rc != HGM_OK) return rc;
+    CU(c, cudaEventRecord(c->ev_free[stage], c->stream));
+    used[stage] = true;
+    stage = (stage + 1) % kStages;
+    points += m;
+  }
+  if (n_points_out) *n_points_out = points;
+  CU(c, cudaEventRecord(c->ev_t1, c->stream));
+  c->timing_open = true;
+  CU(c, cudaMemcpyAsync(sums, sums_ptr(c), (size_t)c->k * c->d * 8, cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaMemcpyAsync(counts, counts_ptr(c), (size_t)c->k * 8, cudaMemcpyDeviceToHost, c->stream));
+  CU(c, cudaStreamSynchronize(c->stream));
+  return HGM_OK;
+}
+
+// A whole text split decoded into exactly-sized rows for the HBM cache.
+static int cache_store_text(hgm_ctx *c, int64_t split_id, SplitSource &src) {
+  if (!c->d_partials) return fail(c, HGM_EINVAL, "hgm_set_centroids has not been called (d is unknown)");
+  if (split_id < 0) return fail(c, HGM_EINVAL, "split_id must be >= 0");
+  if (src.nbytes >= (size_t(1) << 33)) return fail(c, HGM_EINVAL, "a text split must be smaller than 8 GiB");
+  int rc = ensure_pipeline(c, false, 1, true);
+  if (rc != HGM_OK) return rc;
+  CU(c, cudaStreamSynchronize(c->stream));
+  cache_erase(c, split_id);
+  unsigned char *d_text = nullptr;
+  unsigned int *d_blocks = nullptr;
+  TextStats *d_stats = nullptr;
+  float *d_rows = nullptr;
+  TextStats st = {0ull, ~0ull};
+  auto cleanup = [&](int code) {
+    cudaFree(d_text);
+    cudaFree(d_blocks);
+    cudaFree(d_stats);
+    if (code != HGM_OK) cudaFree(d_rows);
+    return code;
+  };
+  auto no_room = [&](cudaError_t e) {
+    cudaGetLastError();
+    return cleanup(fail(c, HGM_ENOMEM, "split %lld (%zu bytes of text) does not fit the HBM cache: %s",
+                        (long long)split_id, src.nbytes, cudaGetErrorString(e)));
+  };
+  cudaError_t e = cudaMalloc(&d_text, src.nbytes + 16);
+  if (e != cudaSuccess) return no_room(e);
+  e = cudaMalloc(&d_blocks, (text_block_count(src.nbytes) + 1) * sizeof(unsigned int));
+  if (e != cudaSuccess) return no_room(e);
+  e = cudaMalloc(&d_stats, sizeof(TextStats));
+  if (e != cudaSuccess) return no_room(e);
+  size_t off = 0;
+  int bi = 0;
+  while (off < src.nbytes) {
+    const size_t piece = std::min(kBounceBytes, src.nbytes - off);
+    if (cudaEventSynchronize(c->ev_bounce[bi]) != cudaSuccess) cudaGetLastError();
+    if (src.file) {
+      if (fread(c->h_bounce[bi], 1, piece, src.file) != piece)
+        return cleanup(fail(c, HGM_EIO, "short read from split file: %s", strerror(errno)));
+    } else {
+      memcpy(c->h_bounce[bi], src.mem + off, piece);
+    }
+    e = cudaMemcpyAsync(d_text + off, c->h_bounce[bi], piece, cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) e = cudaEventRecord(c->ev_bounce[bi], c->stream);
+    if (e != cudaSuccess) return cleanup(fail(c, HGM_ECUDA, "cache copy: %s", cudaGetErrorString(e)));
+    bi = (bi + 1) % kStages;
+    off += piece;
+  }
+  // pass 1 counts the fields so that the rows can be allocated exactly; pass 2 parses
+  for (int pass = 0; pass < 2; ++pass) {
+    e = launch_text_decode(d_text, src.nbytes, c->d, pass ? d_rows : nullptr, pass ? (size_t)st.n_fields : 0, d_blocks,
+                           d_stats, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&st, d_stats, sizeof st, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    if (e != cudaSuccess) return cleanup(fail(c, HGM_ECUDA, "text decode: %s", cudaGetErrorString(e)));
+    c->total_launches += pass ? 3 : 2;
+    if (pass == 0) {
+      if (st.n_fields % (unsigned long long)c->d != 0)
+        return cleanup(fail(c, HGM_EFORMAT, "text split: %llu numbers are not a whole number of d=%d points",
+                            st.n_fields, c->d));
+      e = cudaMalloc(&d_rows, st.n_fields ? (size_t)st.n_fields * 4 : 16);
+      if (e != cudaSuccess) return no_room(e);
+    } else if (st.first_error != ~0ull) {
+      return cleanup(text_error(c, st, 0));
+    }
+  }
+  c->cache[split_id] = hgm_ctx::CachedSplit{d_rows, (int64_t)(st.n_fields / (unsigned long long)c->d), (size_t)st.n_fields * 4};
+  return cleanup(HGM_OK);
+}
+
+// Opens path and frames the split: exact bytes for binary rows, LineRecordReader's rule for text.
+static int open_split_file(hgm_ctx *c, const char *path, int64_t offset, int64_t length, int32_t fmt, SplitSource *src) {
+  if (!path || offset < 0) return fail(c, HGM_EINVAL, "bad path or offset");
+  FILE *f = fopen(path, "rb");
+  if (!f) return fail(c, HGM_EIO, "cannot open %s: %s", path, strerror(errno));
+  int64_t start = offset, stop;
+  if (fmt == HGM_FMT_TEXT) {
+    text_split_bounds(f, offset, length, &start, &stop);
+  } else {
+    if (length < 0) {
+      fseeko(f, 0, SEEK_END);
+      length = std::max<int64_t>((int64_t)ftello(f) - offset, 0);
+    }
+    stop = offset + length;
+  }
+  if (fseeko(f, (off_t)start, SEEK_SET) != 0) {
+    fclose(f);
+    return fail(c, HGM_EIO, "cannot seek %s to %lld", path, (long long)start);
+  }
+  src->file = f;
+  src->nbytes = (size_t)(stop - start);
+  src->pinned = false;
+  return HGM_OK;
+}
+
 int hgm_map_split(hgm_ctx *c, const void *host_bytes, size_t nbytes, int32_t fmt, double *sums,
                   int64_t *counts, int32_t *assign, int64_t *n_points_out) {
   NEED_CTX(c);
@@ -590,41 +852,24 @@ int hgm_map_split(hgm_ctx *c, const void *host_bytes, size_t nbytes, int32_t fmt
   src.mem = static_cast<const unsigned char *>(host_bytes);
   src.nbytes = nbytes;
   src.pinned = nbytes > 0 && is_pinned(host_bytes);
+  if (fmt == HGM_FMT_TEXT) return map_text_stream(c, src, sums, counts, assign, n_points_out);
   return map_stream(c, src, fmt, sums, counts, assign, n_points_out);
 }
 
 int hgm_map_file(hgm_ctx *c, const char *path, int64_t offset, int64_t length, int32_t fmt,
                  double *sums, int64_t *counts, int32_t *assign, int64_t *n_points_out) {
   NEED_CTX(c);
-  if (!path || offset < 0) return fail(c, HGM_EINVAL, "bad path or offset");
-  FILE *f = fopen(path, "rb");
-  if (!f) return fail(c, HGM_EIO, "cannot open %s: %s", path, strerror(errno));
-  if (length < 0) {
-    fseeko(f, 0, SEEK_END);
-    length = (int64_t)ftello(f) - offset;
-    if (length < 0) length = 0;
-  }
-  if (fseeko(f, (off_t)offset, SEEK_SET) != 0) {
-    fclose(f);
-    return fail(c, HGM_EIO, "cannot seek %s to %lld", path, (long long)offset);
-  }
   SplitSource src;
-  src.file = f;
-  src.nbytes = (size_t)length;
-  src.pinned = false;
-  const int rc = map_stream(c, src, fmt, sums, counts, assign, n_points_out);
-  fclose(f);
-  if (rc != HGM_OK) cudaStreamSynchronize(c->stream);
+  int rc = open_split_file(c, path, offset, length, fmt, &src);
+  if (rc != HGM_OK) return rc;
+  rc = fmt == HGM_FMT_TEXT ? map_text_stream(c, src, sums, counts, assign, n_points_out)
+                           : map_stream(c, src, fmt, sums, counts, assign, n_points_out);
+  fclose(src.file);
+  if (rc != HGM_OK) {
+    for (int i = 0; i < kStages; ++i) cudaStreamSynchronize(c->copy[i]);
+    cudaStreamSynchronize(c->stream);
+  }
   return rc;
-}
-
-// ---- HBM-resident split cache -------------------------------------------------------------
-
-static void cache_erase(hgm_ctx *c, int64_t id) {
-  auto it = c->cache.find(id);
-  if (it == c->cache.end()) return;
-  cudaFree(it->second.d_rows);
-  c->cache.erase(it);
 }
 
 static int cache_store(hgm_ctx *c, int64_t split_id, SplitSource &src, int32_t fmt) {
@@ -687,27 +932,17 @@ int hgm_cache_put(hgm_ctx *c, int64_t split_id, const void *host_bytes, size_t n
   SplitSource src;
   src.mem = static_cast<const unsigned char *>(host_bytes);
   src.nbytes = nbytes;
+  if (fmt == HGM_FMT_TEXT) return cache_store_text(c, split_id, src);
   return cache_store(c, split_id, src, fmt);
 }
 
 int hgm_cache_put_file(hgm_ctx *c, int64_t split_id, const char *path, int64_t offset, int64_t length, int32_t fmt) {
   NEED_CTX(c);
-  if (!path || offset < 0) return fail(c, HGM_EINVAL, "bad path or offset");
-  FILE *f = fopen(path, "rb");
-  if (!f) return fail(c, HGM_EIO, "cannot open %s: %s", path, strerror(errno));
-  if (length < 0) {
-    fseeko(f, 0, SEEK_END);
-    length = std::max<int64_t>((int64_t)ftello(f) - offset, 0);
-  }
-  if (fseeko(f, (off_t)offset, SEEK_SET) != 0) {
-    fclose(f);
-    return fail(c, HGM_EIO, "cannot seek %s to %lld", path, (long long)offset);
-  }
   SplitSource src;
-  src.file = f;
-  src.nbytes = (size_t)length;
-  const int rc = cache_store(c, split_id, src, fmt);
-  fclose(f);
+  int rc = open_split_file(c, path, offset, length, fmt, &src);
+  if (rc != HGM_OK) return rc;
+  rc = fmt == HGM_FMT_TEXT ? cache_store_text(c, split_id, src) : cache_store(c, split_id, src, fmt);
+  fclose(src.file);
   return rc;
 }
 
@@ -717,6 +952,22 @@ int hgm_cache_map(hgm_ctx *c, int64_t split_id, int32_t *d_assign, int64_t *n_po
   if (it == c->cache.end()) return fail(c, HGM_EINVAL, "split %lld is not in the cache", (long long)split_id);
   if (n_points_out) *n_points_out = it->second.n_points;
   return hgm_map_device(c, static_cast<const float *>(it->second.d_rows), it->second.n_points, d_assign);
+}
+
+int hgm_cache_read(hgm_ctx *c, int64_t split_id, float *rows_out, int64_t cap_floats, int64_t *n_floats_out) {
+  NEED_CTX(c);
+  auto it = c->cache.find(split_id);
+  if (it == c->cache.end()) return fail(c, HGM_EINVAL, "split %lld is not in the cache", (long long)split_id);
+  const int64_t n = (int64_t)(it->second.nbytes / 4);
+  if (n_floats_out) *n_floats_out = n;
+  if (n > cap_floats || (n > 0 && !rows_out))
+    return fail(c, HGM_EINVAL, "split %lld holds %lld floats, the buffer %lld", (long long)split_id, (long long)n,
+                (long long)cap_floats);
+  if (n > 0) {
+    CU(c, cudaMemcpyAsync(rows_out, it->second.d_rows, (size_t)n * 4, cudaMemcpyDeviceToHost, c->stream));
+    CU(c, cudaStreamSynchronize(c->stream));
+  }
+  return HGM_OK;
 }
 
 int hgm_cache_drop(hgm_ctx *c, int64_t split_id) {

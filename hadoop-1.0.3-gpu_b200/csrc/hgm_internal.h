@@ -63,6 +63,16 @@ cudaError_t launch_tensor_map(const float *d_pts, int64_t n, int d, const float 
                               unsigned int *d_flag_count, double *d_sums, unsigned long long *d_counts, int sm_count,
                               size_t smem_optin, cudaStream_t s);
 
+// text decode (kernels_text.cu)
+struct TextStats {
+  unsigned long long n_fields;     // floats written by the last decode
+  unsigned long long first_error;  // (byte position << 4) | HGM_TEXT_*, all ones = none
+};
+enum { HGM_TEXT_MALFORMED = 1, HGM_TEXT_RAGGED = 2, HGM_TEXT_LONG = 3, HGM_TEXT_INTERNAL = 4 };
+size_t text_block_count(size_t nbytes);
+cudaError_t launch_text_decode(const unsigned char *d_text, size_t nbytes, int d, float *d_out, size_t out_cap,
+                               unsigned int *d_block_counts, TextStats *d_stats, cudaStream_t s);
+
 cudaError_t launch_bswap32(uint32_t *d_words, int64_t n_words, cudaStream_t s);
 
 cudaError_t launch_synth_points(uint64_t seed, int64_t first, int64_t n, int d, int k,

@@ -18,11 +18,13 @@
 //
 // Input routes:
 //   piped (hadoop.pipes.java.recordreader=true):  MAP_ITEM values are appended to a pinned
-//       batch; kmeans.input.format = binary (rows of d LE float32) | path (value names a
-//       file [\t offset \t length], the shipped NLineInputFormat config,
-//       conf/mapred-site.xml:13-22);
+//       batch; kmeans.input.format = binary (rows of d LE float32) | binary-be | text (one
+//       TextInputFormat line per record, decoded on the device: kernels_text.cu) | path
+//       (value names a file [\t offset \t length] of kmeans.file.format rows, the shipped
+//       NLineInputFormat config, conf/mapred-site.xml:13-22);
 //   C++ reader (=false): the FileSplit (mapred/FileSplit.java:81-85) is handed to
-//       hgm_map_file and read straight into pinned memory -- no per-record traffic at all.
+//       hgm_map_file and read straight into pinned memory -- no per-record traffic at all
+//       (text: framed like LineRecordReader, mapred/LineRecordReader.java:79-95).
 // There is no CPU fallback: any hgm_* failure throws HadoopUtils::Error and the task fails.
 #include <stdint.h>
 #include <stdio.h>
@@ -96,6 +98,13 @@ std::string stripScheme(const std::string &uri) {  // "file:/x" -> "/x"
 
 }  // namespace
 
+static int formatCode(const std::string &f) {
+  if (f == "binary") return HGM_FMT_F32LE;
+  if (f == "binary-be") return HGM_FMT_F32BE;
+  HADOOP_ASSERT(f == "text", "record format " + f + " is not one of binary, binary-be, text");
+  return HGM_FMT_TEXT;
+}
+
 class KMeansGpuMap : public HadoopPipes::Mapper {
   HadoopPipes::MapContext *ctx_;
   hgm_ctx *gpu_ = nullptr;
@@ -147,9 +156,12 @@ class KMeansGpuMap : public HadoopPipes::Mapper {
     HADOOP_ASSERT(k_ > 0 && d_ > 0, "kmeans.k and kmeans.d must be positive");
     if (conf->hasKey("kmeans.input.format")) {
       const std::string &f = conf->get("kmeans.input.format");
-      if (f == "path") format_ = PATH;
-      else if (f == "binary-be") fmt_code_ = HGM_FMT_F32BE;
-      else HADOOP_ASSERT(f == "binary", "kmeans.input.format " + f + " is not supported on a GPU slot");
+      if (f == "path") {
+        format_ = PATH;
+        if (conf->hasKey("kmeans.file.format")) fmt_code_ = formatCode(conf->get("kmeans.file.format"));
+      } else {
+        fmt_code_ = formatCode(f);
+      }
     }
     if (conf->hasKey("hadoop.pipes.java.recordreader") && !conf->getBoolean("hadoop.pipes.java.recordreader"))
       format_ = SPLIT;
@@ -171,7 +183,7 @@ class KMeansGpuMap : public HadoopPipes::Mapper {
     part_counts_.assign(k_, 0);
     if (format_ == BINARY) {
       const size_t row = 4 * (size_t)d_;
-      batch_cap_ = std::max<size_t>(row, ((size_t(64) << 20) / row) * row);
+      batch_cap_ = fmt_code_ == HGM_FMT_TEXT ? (size_t(64) << 20) : std::max<size_t>(row, ((size_t(64) << 20) / row) * row);
       void *p = nullptr;
       check(gpu_, hgm_host_alloc(gpu_, batch_cap_, &p), "hgm_host_alloc");
       batch_ = static_cast<unsigned char *>(p);
@@ -190,7 +202,15 @@ class KMeansGpuMap : public HadoopPipes::Mapper {
 
   void map(HadoopPipes::MapContext &context) {
     const std::string &v = context.getInputValue();
-    if (format_ == BINARY) {
+    if (format_ == BINARY && fmt_code_ == HGM_FMT_TEXT) {
+      // one TextInputFormat line per record: batch the lines, the device splits and parses them
+      HADOOP_ASSERT(v.find_first_of("\r\n") == std::string::npos, "text record holds a line end");
+      HADOOP_ASSERT(v.size() + 1 <= batch_cap_, "text record longer than the staging batch");
+      if (batch_used_ + v.size() + 1 > batch_cap_) flush();
+      memcpy(batch_ + batch_used_, v.data(), v.size());
+      batch_used_ += v.size();
+      batch_[batch_used_++] = '\n';
+    } else if (format_ == BINARY) {
       HADOOP_ASSERT(v.size() % (4 * (size_t)d_) == 0, "binary record is not a whole number of rows");
       size_t off = 0;
       while (off < v.size()) {

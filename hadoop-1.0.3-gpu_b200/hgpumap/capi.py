@@ -58,6 +58,7 @@ SIGNATURES = {
     "hgm_cache_map": (C.c_int, [_c_ctx, C.c_int64, _p, C.POINTER(C.c_int64)]),
     "hgm_cache_drop": (C.c_int, [_c_ctx, C.c_int64]),
     "hgm_cache_info": (C.c_int, [_c_ctx, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "hgm_cache_read": (C.c_int, [_c_ctx, C.c_int64, C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]),
     "hgm_sync": (C.c_int, [_c_ctx]),
     "hgm_stream": (C.c_int, [_c_ctx, C.POINTER(_p)]),
     "hgm_last_map_ms": (C.c_int, [_c_ctx, C.POINTER(C.c_float), C.POINTER(C.c_int32)]),
@@ -212,6 +213,14 @@ class GpuMapSlot:
         n = C.c_int64()
         self._check(self._lib.hgm_cache_map(self._ctx, split_id, d_assign, C.byref(n)))
         return n.value
+
+    def cache_read(self, split_id: int) -> np.ndarray:
+        """The cached split's decoded rows, [n, d] float32."""
+        n = C.c_int64()
+        self._lib.hgm_cache_read(self._ctx, split_id, None, 0, C.byref(n))  # size query
+        rows = np.empty(n.value, dtype=np.float32)
+        self._check(self._lib.hgm_cache_read(self._ctx, split_id, _ptr(rows) if n.value else None, n.value, C.byref(n)))
+        return rows.reshape(-1, self.d)
 
     def cache_drop(self, split_id: int = -1) -> None:
         self._check(self._lib.hgm_cache_drop(self._ctx, split_id))

@@ -45,9 +45,16 @@ typedef struct hgm_ctx hgm_ctx;
  * one std::string per record, c++/pipes/api/hadoop/Pipes.hh:89). */
 #define HGM_FMT_F32LE 0 /* rows of d little-endian IEEE float32 (primary format)           */
 #define HGM_FMT_F32BE 1 /* rows of d big-endian float32 (DataOutput.writeFloat order)       */
-#define HGM_FMT_TEXT 2  /* decimals separated by space, comma, tab or newline; each field   */
-                        /* means what HadoopUtils::toFloat (c++/utils/impl/StringUtils.cc:  */
-                        /* 49-56) would return for it                                       */
+#define HGM_FMT_TEXT 2  /* TextInputFormat lines (LF, CR or CR LF ends), each a whole number */
+                        /* of points; fields split at space, comma, tab as splitString does */
+                        /* (c++/utils/impl/StringUtils.cc:80-95); a field means what        */
+                        /* HadoopUtils::toFloat (:49-56, sscanf "%f") returns for it, bit   */
+                        /* for bit, and what toFloat rejects fails the call (HGM_EFORMAT).  */
+                        /* Decoded on the device.  hgm_map_file / hgm_cache_put_file frame  */
+                        /* (offset, length) the way LineRecordReader does (mapred/          */
+                        /* LineRecordReader.java:79-95,137-157): the first line belongs to  */
+                        /* the previous split unless offset == 0, the last one is read to   */
+                        /* its end.  Assignments are not returned for text (pass NULL).     */
 
 /* Kernel families (hgm_set_kernel); AUTO picks by shape. */
 #define HGM_KERNEL_AUTO 0
@@ -139,13 +146,17 @@ int hgm_partials_device(hgm_ctx *ctx, double **d_sums, int64_t **d_counts);
  *   hgm_cache_put_file  same from a FileSplit byte range (mapred/FileSplit.java:81-85)
  *   hgm_cache_map       hgm_map_device on the cached rows: ADDS into the partials, async
  *   hgm_cache_drop      forget one split, or all of them with split_id < 0
- *   hgm_cache_info      number of cached splits and their bytes */
+ *   hgm_cache_info      number of cached splits and their bytes
+ *   hgm_cache_read      copy a cached split's decoded rows (LE float32) back to the host:
+ *                       rows_out holds cap_floats floats; *n_floats_out = floats the split
+ *                       has (HGM_EINVAL, nothing copied, if that is more than cap_floats) */
 int hgm_cache_put(hgm_ctx *ctx, int64_t split_id, const void *host_bytes, size_t nbytes, int32_t fmt);
 int hgm_cache_put_file(hgm_ctx *ctx, int64_t split_id, const char *path, int64_t offset, int64_t length,
                        int32_t fmt);
 int hgm_cache_map(hgm_ctx *ctx, int64_t split_id, int32_t *d_assign_or_null, int64_t *n_points_out);
 int hgm_cache_drop(hgm_ctx *ctx, int64_t split_id);
 int hgm_cache_info(hgm_ctx *ctx, int64_t *n_splits, int64_t *bytes);
+int hgm_cache_read(hgm_ctx *ctx, int64_t split_id, float *rows_out, int64_t cap_floats, int64_t *n_floats_out);
 
 /* Wait for everything queued on the ctx stream. */
 int hgm_sync(hgm_ctx *ctx);

@@ -150,6 +150,66 @@ int32_t hgo_decode_text_record(const char *rec, int64_t len, float *out, int32_t
   return n;
 }
 
+/* a7 in bulk: field i is buf[off[i] .. off[i+1]) (at most 127 bytes); rc[i] = 0 or -1 */
+void hgo_to_float_many(const char *buf, const int64_t *off, int64_t n, float *out, int32_t *rc) {
+  char field[128];
+  for (int64_t i = 0; i < n; ++i) {
+    int64_t len = off[i + 1] - off[i];
+    if (len < 0 || len >= (int64_t)sizeof(field)) { rc[i] = -1; continue; }
+    memcpy(field, buf + off[i], (size_t)len);
+    field[len] = 0;
+    out[i] = 0.0f;
+    rc[i] = hgo_to_float(field, &out[i]);
+  }
+}
+
+/* ---- section 8(f)3: TextInputFormat framing --------------------------------
+ * LineReader.readLine (core/org/apache/hadoop/util/LineReader.java:106-167) over
+ * a file held in memory: returns the bytes consumed from pos (content plus the
+ * terminator LF, CR or CR LF; a CR is only joined with an LF right behind it),
+ * *content = bytes before the terminator. 0 at end of file. */
+int64_t hgo_read_line(const char *file, int64_t size, int64_t pos, int64_t *content) {
+  int64_t i = pos;
+  while (i < size && file[i] != '\n' && file[i] != '\r') ++i;
+  *content = i - pos;
+  if (i >= size) return i - pos;
+  if (file[i] == '\n') return i - pos + 1;
+  return (i + 1 < size && file[i + 1] == '\n') ? i - pos + 2 : i - pos + 1;
+}
+
+/* LineRecordReader for FileSplit(off, len)
+ * (mapred/org/apache/hadoop/mapred/LineRecordReader.java:79-95 constructor,
+ * :137-157 next): a split that does not start at byte 0 backs up one byte and
+ * throws away one line; records are the lines that START before off+len.
+ * Every record is decoded as a K-means text record (hgo_decode_text_record) of
+ * whole d-dimensional points, as the CPU mapper does. Returns the number of
+ * floats written, -1 - (record index) if that record is malformed or ragged,
+ * INT64_MIN if out is too small. *n_records = records seen. */
+int64_t hgo_text_split_decode(const char *file, int64_t size, int64_t off, int64_t len, int32_t d,
+                              float *out, int64_t cap, int64_t *n_records) {
+  int64_t start = off, end = off + len, content = 0, total = 0, rec = 0;
+  if (start != 0) {
+    --start;
+    start += hgo_read_line(file, size, start, &content);
+  }
+  int64_t pos = start;
+  while (pos < end) {
+    int64_t used = hgo_read_line(file, size, pos, &content);
+    if (used == 0) break;
+    if (cap - total < content) { /* a record of c bytes holds fewer than c numbers */
+      if (cap - total < (content + 1) / 2) return INT64_MIN;
+    }
+    int64_t room = cap - total > 0x7fffffff ? 0x7fffffff : cap - total;
+    int32_t n = hgo_decode_text_record(file + pos, content, out + total, (int32_t)room);
+    if (n < 0 || n % d != 0) { if (n_records) *n_records = rec; return -1 - rec; }
+    total += n;
+    pos += used;
+    ++rec;
+  }
+  if (n_records) *n_records = rec;
+  return total;
+}
+
 /* XDR float as on the wire (progress messages): 4 bytes, big-endian */
 void hgo_xdr_float(float f, uint8_t out[4]) {
   uint32_t bits;

@@ -108,6 +108,28 @@ class Oracle:
         rc = self.lib.hgo_to_float(s.encode() if isinstance(s, str) else s, C.byref(f))
         return None if rc != 0 else np.float32(f.value)
 
+    def to_float_many(self, fields):
+        """fields: list of bytes -> (float32 bits as uint32 array, rc array)"""
+        buf = b"".join(fields)
+        off = np.zeros(len(fields) + 1, np.int64)
+        np.cumsum([len(f) for f in fields], out=off[1:])
+        out = np.zeros(len(fields), np.float32)
+        rc = np.zeros(len(fields), np.int32)
+        self.lib.hgo_to_float_many(buf, self._p(off), C.c_int64(len(fields)), self._p(out), self._p(rc))
+        return out.view(np.uint32), rc
+
+    def text_split_decode(self, file_bytes, off, length, d):
+        """LineRecordReader + text record decode of FileSplit(off, length): (rows [n][d], records)."""
+        cap = len(file_bytes) // 2 + 8
+        out = np.empty(cap, np.float32)
+        nrec = C.c_int64(0)
+        self.lib.hgo_text_split_decode.restype = C.c_int64
+        n = self.lib.hgo_text_split_decode(file_bytes, C.c_int64(len(file_bytes)), C.c_int64(off), C.c_int64(length),
+                                           C.c_int32(d), self._p(out), C.c_int64(cap), C.byref(nrec))
+        if n < 0:
+            raise ValueError("record %d is malformed or ragged" % (-1 - n))
+        return out[:n].reshape(-1, d).copy(), nrec.value
+
     def synth_centres(self, seed, k, d):
         out = np.empty((k, d), np.float32)
         self.lib.hgo_synth_centres(seed, k, d, self._p(out))

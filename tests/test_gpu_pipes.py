@@ -144,3 +144,68 @@ def test_gpubin_fails_the_task_loudly(tmp_path):
           .run_map(b"s", 1, True).map_item(b"k", b"\x00" * 12).close())
     proc, out, _ = ph.run_child(GPU_BIN, dl, args=("0",))
     assert not wire.parse_uplink(out).done and b"whole number of rows" in proc.stderr
+
+
+def test_gpubin_text_records_match_the_cpubin(oracle, tmp_path):
+    """kmeans.input.format=text on both programs: the CPU one parses every line with
+    sscanf on the host, the GPU one batches the lines and decodes them on the device."""
+    cpu = os.path.join(REF_DIR, "kmeans-pipes-cpu")
+    if not os.path.exists(cpu):
+        pytest.skip("oracle/_ref not built")
+    pts, cent = cases.blobs(8000, 2, 128, seed=37)
+    cpath = str(tmp_path / "cent.bin")
+    cent.astype("<f4").tofile(cpath)
+    dl = ph.kmeans_downlink(pts, cpath, 128, 2, "text", 2)
+    res = ph.run_children([(cpu, dl, None), (GPU_BIN, dl, None)])
+    cpu_up, gpu_up = wire.parse_uplink(res[0][1]), wire.parse_uplink(res[1][1])
+    assert cpu_up.done and gpu_up.done, (res[0][0].stderr, res[1][0].stderr)
+    assert [(p, k) for p, k, _ in cpu_up.partitioned] == [(p, k) for p, k, _ in gpu_up.partitioned]
+    for (_, _, cv), (_, _, gv) in zip(cpu_up.partitioned, gpu_up.partitioned):
+        cf, gf = cv.split(), gv.split()
+        assert cf[0] == gf[0]
+        np.testing.assert_allclose([float(x) for x in gf[1:]], [float(x) for x in cf[1:]], rtol=1e-9, atol=1e-6)
+    assert gpu_up.counter("KMEANS", "POINTS") == len(pts)
+
+
+def test_gpubin_text_filesplits_cover_the_file_once(oracle, tmp_path):
+    """C++ reader route over a text file cut at arbitrary bytes: LineRecordReader's rule gives
+    every line to exactly one split."""
+    pts, cent = cases.blobs(20000, 2, 64, seed=41)
+    cpath = str(tmp_path / "cent.bin")
+    cent.astype("<f4").tofile(cpath)
+    text = "".join("%.7g,%.7g\n" % (x, y) for x, y in pts).encode()
+    data = str(tmp_path / "points.txt")
+    open(data, "wb").write(text)
+    conf = gpu_conf(cpath, 64, 2, "text")
+    conf["hadoop.pipes.java.recordreader"] = "false"
+    cuts = [0, 12345, len(text) // 2 + 3, len(text)]
+    total_counts = np.zeros(64, np.int64)
+    total_sums = np.zeros((64, 2))
+    for a, b in zip(cuts, cuts[1:]):
+        dl = (wire.Downlink().authenticate().start().set_job_conf(conf).set_input_types("k", "v")
+              .run_map(wire.file_split("file:" + data, a, b - a), 1, False))
+        proc, out, _ = ph.run_child(GPU_BIN, dl, args=("0",))
+        up = wire.parse_uplink(out)
+        assert up.done, proc.stderr
+        c, s = wire.kmeans_partials([(k, v) for _, k, v in up.partitioned], 64, 2)
+        rows, _ = oracle.text_split_decode(text, a, b - a, 2)
+        assert c.sum() == len(rows) == up.counter("KMEANS", "POINTS")
+        total_counts += c
+        total_sums += s
+    rows, _ = oracle.text_split_decode(text, 0, len(text), 2)
+    o = oracle.map_combine(rows, cent)
+    check_partials(total_sums, total_counts, o[0], o[1], o[2])
+
+
+def test_gpubin_malformed_text_fails_the_task(tmp_path):
+    cent = np.zeros((4, 2), np.float32)
+    cpath = str(tmp_path / "cent.bin")
+    cent.tofile(cpath)
+    dl = (wire.Downlink().authenticate().start().set_job_conf(gpu_conf(cpath, 4, 2, "text"))
+          .set_input_types("org.apache.hadoop.io.LongWritable", "org.apache.hadoop.io.Text")
+          .run_map(b"ignored", 1, True))
+    dl.map_item((0).to_bytes(8, "big"), "1.0 2.0")
+    dl.map_item((8).to_bytes(8, "big"), "3.0 4.0 5.0")
+    proc, out, _ = ph.run_child(GPU_BIN, dl.close(), args=("0",))
+    up = wire.parse_uplink(out)
+    assert not up.done and b"whole number" in proc.stderr
