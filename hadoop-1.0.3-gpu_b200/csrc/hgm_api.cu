@@ -24,6 +24,7 @@ thread_local char g_err[512] = "";
 constexpr size_t kChunkBytes = size_t(64) << 20;  // HBM chunk per pipeline stage
 constexpr int kStages = 3;
 constexpr size_t kBounceBytes = size_t(16) << 20;  // pinned bounce for pageable callers
+constexpr size_t kArenaBytes = size_t(2) << 30;    // split-cache arena block
 }  // namespace
 
 struct hgm_ctx {
@@ -61,8 +62,13 @@ struct hgm_ctx {
   int64_t total_launches = 0;
   bool timing_open = false;
   void *nccl_comm = nullptr;
-  struct CachedSplit { void *d_rows; int64_t n_points; size_t nbytes; };
-  std::unordered_map<int64_t, CachedSplit> cache;  // HBM-resident splits by id
+  // HBM-resident splits by id.  Rows live in arena blocks (one cudaMalloc per kArenaBytes, not per
+  // split) and are appended back to back, so that neighbours can be mapped by ONE launch
+  // (hgm_cache_map_all); a block is returned to the driver when its last split is dropped.
+  struct ArenaBlock { unsigned char *base; size_t cap, used; int live; };
+  struct CachedSplit { void *d_rows; int64_t n_points; size_t nbytes; int block; };
+  std::vector<ArenaBlock> arena;
+  std::unordered_map<int64_t, CachedSplit> cache;
   char err[512] = "";
 };
 
@@ -114,6 +120,55 @@ void free_job(hgm_ctx *c) {
   c->tensor_ok = false;
   c->grid_ok = false;
   c->k = c->d = 0;
+}
+
+// ---- split-cache arena ----------------------------------------------------------------------
+void *arena_alloc(hgm_ctx *c, size_t nbytes, int *block_out, cudaError_t *err) {
+  const size_t need = nbytes ? nbytes : 16;
+  *err = cudaSuccess;
+  for (int b = (int)c->arena.size() - 1; b >= 0; --b) {  // newest first: appends stay contiguous
+    hgm_ctx::ArenaBlock &blk = c->arena[b];
+    if (blk.base && blk.cap - blk.used >= need) {
+      void *p = blk.base + blk.used;
+      blk.used += (need + 15) & ~size_t(15);  // rows of whole 16-byte groups stay back to back
+      if (blk.used > blk.cap) blk.used = blk.cap;
+      blk.live += 1;
+      *block_out = b;
+      return p;
+    }
+    break;  // only the newest block is appended to
+  }
+  void *base = nullptr;
+  size_t cap = std::max(kArenaBytes, need);
+  cudaError_t e = cudaMalloc(&base, cap);
+  if (e != cudaSuccess && cap > need) {  // HBM is nearly full: take what this split needs
+    cudaGetLastError();
+    cap = need;
+    e = cudaMalloc(&base, cap);
+  }
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    *err = e;
+    return nullptr;
+  }
+  c->arena.push_back(hgm_ctx::ArenaBlock{static_cast<unsigned char *>(base), cap, std::min(cap, (need + 15) & ~size_t(15)), 1});
+  *block_out = (int)c->arena.size() - 1;
+  return base;
+}
+
+void arena_release(hgm_ctx *c, int block) {
+  hgm_ctx::ArenaBlock &blk = c->arena[block];
+  if (--blk.live == 0) {
+    cudaFree(blk.base);
+    blk.base = nullptr;
+    blk.cap = blk.used = 0;
+  }
+}
+
+void cache_clear(hgm_ctx *c) {
+  for (auto &blk : c->arena) cudaFree(blk.base);
+  c->arena.clear();
+  c->cache.clear();
 }
 
 // Choose the d == 2 cell grid for a centroid table; false if the table is not indexable
@@ -286,8 +341,7 @@ void hgm_close(hgm_ctx *c) {
   cudaSetDevice(c->device);
   if (c->stream) cudaStreamSynchronize(c->stream);
   if (c->nccl_comm) { hgm::comm_destroy(c->nccl_comm); c->nccl_comm = nullptr; }
-  for (auto &kv : c->cache) cudaFree(kv.second.d_rows);
-  c->cache.clear();
+  cache_clear(c);
   free_job(c);
   for (int i = 0; i < kStages; ++i) {
     if (c->copy[i]) { cudaStreamSynchronize(c->copy[i]); cudaStreamDestroy(c->copy[i]); }
@@ -314,6 +368,7 @@ int hgm_set_centroids(hgm_ctx *c, const float *centroids, int32_t k, int32_t d) 
   if ((int64_t)k * d > (int64_t(1) << 28)) return fail(c, HGM_EINVAL, "k*d too large");
   CU(c, cudaStreamSynchronize(c->stream));
   if (k != c->k || d != c->d) {
+    if (d != c->d) cache_clear(c);  // cached rows are rows of the old d
     free_job(c);
     const size_t cent_bytes = (((size_t)k * d * 4) + 15) & ~size_t(15);
     CU(c, cudaMalloc(&c->d_cent, cent_bytes));
@@ -595,7 +650,7 @@ static int map_stream(hgm_ctx *c, SplitSource &src, int32_t fmt, double *sums, i
 static void cache_erase(hgm_ctx *c, int64_t id) {
   auto it = c->cache.find(id);
   if (it == c->cache.end()) return;
-  cudaFree(it->second.d_rows);
+  arena_release(c, it->second.block);
   c->cache.erase(it);
 }
 
@@ -761,12 +816,13 @@ static int cache_store_text(hgm_ctx *c, int64_t split_id, SplitSource &src) {
   unsigned int *d_blocks = nullptr;
   TextStats *d_stats = nullptr;
   float *d_rows = nullptr;
+  int block = -1;
   TextStats st = {0ull, ~0ull};
   auto cleanup = [&](int code) {
     cudaFree(d_text);
     cudaFree(d_blocks);
     cudaFree(d_stats);
-    if (code != HGM_OK) cudaFree(d_rows);
+    if (code != HGM_OK && block >= 0) arena_release(c, block);
     return code;
   };
   auto no_room = [&](cudaError_t e) {
@@ -809,13 +865,14 @@ static int cache_store_text(hgm_ctx *c, int64_t split_id, SplitSource &src) {
       if (st.n_fields % (unsigned long long)c->d != 0)
         return cleanup(fail(c, HGM_EFORMAT, "text split: %llu numbers are not a whole number of d=%d points",
                             st.n_fields, c->d));
-      e = cudaMalloc(&d_rows, st.n_fields ? (size_t)st.n_fields * 4 : 16);
-      if (e != cudaSuccess) return no_room(e);
+      d_rows = static_cast<float *>(arena_alloc(c, (size_t)st.n_fields * 4, &block, &e));
+      if (!d_rows) return no_room(e);
     } else if (st.first_error != ~0ull) {
       return cleanup(text_error(c, st, 0));
     }
   }
-  c->cache[split_id] = hgm_ctx::CachedSplit{d_rows, (int64_t)(st.n_fields / (unsigned long long)c->d), (size_t)st.n_fields * 4};
+  c->cache[split_id] = hgm_ctx::CachedSplit{d_rows, (int64_t)(st.n_fields / (unsigned long long)c->d),
+                                            (size_t)st.n_fields * 4, block};
   return cleanup(HGM_OK);
 }
 
@@ -882,13 +939,12 @@ static int cache_store(hgm_ctx *c, int64_t split_id, SplitSource &src, int32_t f
     return fail(c, HGM_EFORMAT, "split of %zu bytes is not a whole number of %zu-byte rows", src.nbytes, row);
   CU(c, cudaStreamSynchronize(c->stream));
   cache_erase(c, split_id);
-  void *d_rows = nullptr;
-  cudaError_t e = cudaMalloc(&d_rows, src.nbytes ? src.nbytes : 16);
-  if (e != cudaSuccess) {
-    cudaGetLastError();
+  int block = -1;
+  cudaError_t e = cudaSuccess;
+  void *d_rows = arena_alloc(c, src.nbytes, &block, &e);
+  if (!d_rows)
     return fail(c, HGM_ENOMEM, "split %lld (%zu bytes) does not fit the HBM cache: %s", (long long)split_id,
                 src.nbytes, cudaGetErrorString(e));
-  }
   int rc = HGM_OK;
   if (src.file) {  // through the pinned bounce buffers
     rc = ensure_pipeline(c, false, 1, true);
@@ -919,10 +975,10 @@ static int cache_store(hgm_ctx *c, int64_t split_id, SplitSource &src, int32_t f
   }
   if (rc == HGM_OK && cudaStreamSynchronize(c->stream) != cudaSuccess) rc = fail(c, HGM_ECUDA, "cache copy failed");
   if (rc != HGM_OK) {
-    cudaFree(d_rows);
+    arena_release(c, block);
     return rc;
   }
-  c->cache[split_id] = hgm_ctx::CachedSplit{d_rows, (int64_t)(src.nbytes / row), src.nbytes};
+  c->cache[split_id] = hgm_ctx::CachedSplit{d_rows, (int64_t)(src.nbytes / row), src.nbytes, block};
   return HGM_OK;
 }
 
@@ -954,6 +1010,40 @@ int hgm_cache_map(hgm_ctx *c, int64_t split_id, int32_t *d_assign, int64_t *n_po
   return hgm_map_device(c, static_cast<const float *>(it->second.d_rows), it->second.n_points, d_assign);
 }
 
+int hgm_cache_map_all(hgm_ctx *c, int64_t *n_points_out, int32_t *n_launch_groups_out) {
+  NEED_CTX(c);
+  if (!c->d_partials) return fail(c, HGM_EINVAL, "hgm_set_centroids has not been called");
+  std::vector<const hgm_ctx::CachedSplit *> order;
+  order.reserve(c->cache.size());
+  for (auto &kv : c->cache) order.push_back(&kv.second);
+  std::sort(order.begin(), order.end(),
+            [](const hgm_ctx::CachedSplit *a, const hgm_ctx::CachedSplit *b) { return a->d_rows < b->d_rows; });
+  int64_t total = 0;
+  int32_t groups = 0;
+  size_t i = 0;
+  while (i < order.size()) {  // splits that sit back to back in an arena block go out as one launch
+    const unsigned char *begin = static_cast<const unsigned char *>(order[i]->d_rows);
+    const unsigned char *end = begin + order[i]->nbytes;
+    int64_t n = order[i]->n_points;
+    size_t j = i + 1;
+    while (j < order.size() && order[j]->block == order[i]->block && order[j]->d_rows == end) {
+      end += order[j]->nbytes;
+      n += order[j]->n_points;
+      ++j;
+    }
+    if (n > 0) {
+      const int rc = hgm_map_device(c, reinterpret_cast<const float *>(begin), n, nullptr);
+      if (rc != HGM_OK) return rc;
+      ++groups;
+    }
+    total += n;
+    i = j;
+  }
+  if (n_points_out) *n_points_out = total;
+  if (n_launch_groups_out) *n_launch_groups_out = groups;
+  return HGM_OK;
+}
+
 int hgm_cache_read(hgm_ctx *c, int64_t split_id, float *rows_out, int64_t cap_floats, int64_t *n_floats_out) {
   NEED_CTX(c);
   auto it = c->cache.find(split_id);
@@ -976,8 +1066,7 @@ int hgm_cache_drop(hgm_ctx *c, int64_t split_id) {
   if (split_id >= 0) {
     cache_erase(c, split_id);
   } else {
-    for (auto &kv : c->cache) cudaFree(kv.second.d_rows);
-    c->cache.clear();
+    cache_clear(c);
   }
   return HGM_OK;
 }

@@ -57,6 +57,7 @@ SIGNATURES = {
     "hgm_cache_put_file": (C.c_int, [_c_ctx, C.c_int64, C.c_char_p, C.c_int64, C.c_int64, C.c_int32]),
     "hgm_cache_map": (C.c_int, [_c_ctx, C.c_int64, _p, C.POINTER(C.c_int64)]),
     "hgm_cache_drop": (C.c_int, [_c_ctx, C.c_int64]),
+    "hgm_cache_map_all": (C.c_int, [_c_ctx, C.POINTER(C.c_int64), C.POINTER(C.c_int32)]),
     "hgm_cache_info": (C.c_int, [_c_ctx, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "hgm_cache_read": (C.c_int, [_c_ctx, C.c_int64, C.c_void_p, C.c_int64, C.POINTER(C.c_int64)]),
     "hgm_sync": (C.c_int, [_c_ctx]),
@@ -213,6 +214,12 @@ class GpuMapSlot:
         n = C.c_int64()
         self._check(self._lib.hgm_cache_map(self._ctx, split_id, d_assign, C.byref(n)))
         return n.value
+
+    def cache_map_all(self) -> tuple[int, int]:
+        """Map every cached split; returns (points, launch groups)."""
+        n, g = C.c_int64(), C.c_int32()
+        self._check(self._lib.hgm_cache_map_all(self._ctx, C.byref(n), C.byref(g)))
+        return n.value, g.value
 
     def cache_read(self, split_id: int) -> np.ndarray:
         """The cached split's decoded rows, [n, d] float32."""

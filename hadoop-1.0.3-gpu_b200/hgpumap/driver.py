@@ -3,8 +3,9 @@ iteration in the reference (one MapReduce job per iteration; the reduce side is 
 centroid update, pipes/PipesReducer.java:59-124 driving the program's Reducer), with the
 input kept in the slot's HBM split cache from the second iteration on.
 
-    iteration 1:   every split is staged from the host (hgm_cache_put) and mapped
-    iterations 2+: every split is mapped from HBM (hgm_cache_map)
+    iteration 1:   every split is staged from the host into the cache (hgm_cache_put)
+    every iteration: the cached splits are mapped from HBM (hgm_cache_map_all: neighbours in the
+                   cache's arena share a launch); what did not fit is streamed from the host
     each iteration: partials -> (allreduce across slots) -> centroid update -> hgm_set_centroids
 """
 from __future__ import annotations
@@ -22,23 +23,20 @@ def run_kmeans(slot: GpuMapSlot, splits: list, centroids: np.ndarray, iterations
     Returns (centroids, history) where history[i] = (sums, counts) of iteration i."""
     cent = np.ascontiguousarray(centroids, dtype=np.float32)
     history = []
-    cached = set()
+    slot.set_centroids(cent)
+    slot.cache_drop()  # the cache holds this job's splits only
+    streamed = []
+    for sid, split in enumerate(splits):
+        try:
+            slot.cache_put(sid, split, fmt)
+        except HgmError as err:
+            if err.code != -12:  # anything but "does not fit": a real failure
+                raise
+            streamed.append(split)
     for it in range(iterations):
         slot.set_centroids(cent)
         slot.reset_partials()
-        streamed = []
-        for sid, split in enumerate(splits):
-            if sid not in cached:
-                try:
-                    slot.cache_put(sid, split, fmt)
-                    cached.add(sid)
-                except HgmError as err:
-                    if err.code != -12:  # anything but "does not fit": a real failure
-                        raise
-            if sid in cached:
-                slot.cache_map(sid)  # adds into the slot's device partials
-            else:
-                streamed.append(split)
+        slot.cache_map_all()  # adds into the slot's device partials
         sums, counts = slot.read_partials()
         # the cache is only a cache: what did not fit is streamed from the host every iteration
         # (hgm_map_split starts from zeroed partials, hence after the read above)

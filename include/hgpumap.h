@@ -140,12 +140,17 @@ int hgm_partials_device(hgm_ctx *ctx, double **d_sums, int64_t **d_counts);
  * iterations over the same 20 GB).  It is a cache only -- the unit of recovery stays the
  * split (the reference re-runs a failed map from its input, mapred/JobInProgress.java:
  * 3146-3159): a put that does not fit returns HGM_ENOMEM and the caller maps the split with
- * hgm_map_split instead; hgm_close drops everything.
+ * hgm_map_split instead; hgm_close drops everything, and so does hgm_set_centroids with a
+ * different d.
  *   hgm_cache_put       stage + decode a split held in host memory, keep it under split_id
  *                       (replacing an older entry of that id)
  *   hgm_cache_put_file  same from a FileSplit byte range (mapred/FileSplit.java:81-85)
  *   hgm_cache_map       hgm_map_device on the cached rows: ADDS into the partials, async
- *   hgm_cache_drop      forget one split, or all of them with split_id < 0
+ *   hgm_cache_map_all   map every cached split; splits that lie back to back in the cache's
+ *                       arena (2 GiB blocks, filled in put order) share one launch, so an
+ *                       iteration over a resident input costs a handful of launches
+ *   hgm_cache_drop      forget one split, or all of them with split_id < 0 (an arena block
+ *                       goes back to the driver when its last split is dropped)
  *   hgm_cache_info      number of cached splits and their bytes
  *   hgm_cache_read      copy a cached split's decoded rows (LE float32) back to the host:
  *                       rows_out holds cap_floats floats; *n_floats_out = floats the split
@@ -154,6 +159,7 @@ int hgm_cache_put(hgm_ctx *ctx, int64_t split_id, const void *host_bytes, size_t
 int hgm_cache_put_file(hgm_ctx *ctx, int64_t split_id, const char *path, int64_t offset, int64_t length,
                        int32_t fmt);
 int hgm_cache_map(hgm_ctx *ctx, int64_t split_id, int32_t *d_assign_or_null, int64_t *n_points_out);
+int hgm_cache_map_all(hgm_ctx *ctx, int64_t *n_points_out, int32_t *n_launch_groups_out);
 int hgm_cache_drop(hgm_ctx *ctx, int64_t split_id);
 int hgm_cache_info(hgm_ctx *ctx, int64_t *n_splits, int64_t *bytes);
 int hgm_cache_read(hgm_ctx *ctx, int64_t split_id, float *rows_out, int64_t cap_floats, int64_t *n_floats_out);

@@ -41,6 +41,34 @@ def test_cache_put_map_drop(oracle, tmp_path):
         assert err.value.code == -1002
 
 
+def test_map_all_merges_neighbours_into_one_launch(oracle):
+    pts, cent = cases.blobs(6 * 40000, 2, 128, seed=53)
+    parts = np.array_split(pts, 6)  # 320000 bytes each: whole 16-byte groups, so they sit back to back
+    with capi.GpuMapSlot(0) as slot:
+        slot.set_centroids(cent)
+        for i, part in enumerate(parts):
+            slot.cache_put(10 + i, part)
+        slot.reset_partials()
+        assert slot.cache_map_all() == (len(pts), 1)
+        sums, counts = slot.read_partials()
+        o = oracle.map_combine(pts, cent)
+        check_partials(sums, counts, o[0], o[1], o[2])
+        slot.cache_drop(12)  # a hole: two runs now
+        slot.reset_partials()
+        n, groups = slot.cache_map_all()
+        assert (n, groups) == (len(pts) - 40000, 2)
+        keep = np.concatenate([parts[i] for i in (0, 1, 3, 4, 5)])
+        sums, counts = slot.read_partials()
+        o = oracle.map_combine(keep, cent)
+        check_partials(sums, counts, o[0], o[1], o[2])
+        slot.cache_put(12, parts[2][:1001])  # appended right behind the last split; odd size: padded at ITS end
+        slot.cache_put(99, parts[2][:10])    # ... so this one does not touch its neighbour
+        slot.reset_partials()
+        assert slot.cache_map_all() == (len(pts) - 40000 + 1011, 3)
+        slot.set_centroids(np.zeros((3, 5), np.float32))  # another d: the rows mean nothing now
+        assert slot.cache_info() == (0, 0)
+
+
 def test_ten_iterations_from_the_cache_follow_the_oracle(oracle):
     """Each iteration's assignments are checked against the oracle run on the SAME centroids the
     GPU path used (sums differ in their last bits, so free-running trajectories may part by an ulp)."""

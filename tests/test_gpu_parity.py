@@ -117,7 +117,10 @@ def test_unindexable_centroids_fall_to_exact_scan(slot, oracle):
                                    (16, 50, 6007), (64, 100, 4099), (128, 257, 2053), (300, 9, 777)])
 def test_general_dimensions_exact_scan(slot, oracle, d, k, n):
     pts, cent = cases.general_d(n, d, k, seed=d * 1000 + k)
-    run_case(slot, oracle, pts, cent, capi.KERNEL_AUTO, want_kernel=capi.KERNEL_EXACT)
+    tensor = d % 32 == 0 and 32 <= d <= 128 and k >= 128 and k * d >= 8192  # hgm_api.cu:pick_kernel
+    run_case(slot, oracle, pts, cent, capi.KERNEL_AUTO, want_kernel=capi.KERNEL_TENSOR if tensor else capi.KERNEL_EXACT)
+    if tensor:
+        run_case(slot, oracle, pts, cent, capi.KERNEL_EXACT)
 
 
 def test_big_endian_rows_are_decoded_on_device(slot, oracle):
