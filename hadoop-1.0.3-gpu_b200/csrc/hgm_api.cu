@@ -55,6 +55,8 @@ struct hgm_ctx {
   float *d_caug = nullptr;      // [k_pad][d+32] augmented centroid matrix
   unsigned int *d_tflags = nullptr;  // [0] max |c| bits, [1] re-check counter
   int32_t *d_tassign = nullptr, *d_tlist = nullptr;  // scratch: assignments / re-check list
+  int32_t *d_torder = nullptr;       // point indices grouped by cluster (K4)
+  unsigned int *d_tmeta = nullptr;   // [lcounts k][offsets k+1][cursor k][items k+1]
   size_t tscratch_rows = 0;
   unsigned long long last_rechecks = 0;
   int forced = HGM_KERNEL_AUTO, last_kernel = HGM_KERNEL_AUTO;
@@ -116,6 +118,8 @@ void free_job(hgm_ctx *c) {
   cudaFree(c->d_tflags); c->d_tflags = nullptr;
   cudaFree(c->d_tassign); c->d_tassign = nullptr;
   cudaFree(c->d_tlist); c->d_tlist = nullptr;
+  cudaFree(c->d_torder); c->d_torder = nullptr;
+  cudaFree(c->d_tmeta); c->d_tmeta = nullptr;
   c->tscratch_rows = 0;
   c->tensor_ok = false;
   c->grid_ok = false;
@@ -230,17 +234,21 @@ int map_points_async(hgm_ctx *c, const float *d_pts, int64_t n, int32_t *d_assig
   if (kern == HGM_KERNEL_TENSOR) {
     if (reinterpret_cast<uintptr_t>(d_pts) & 15)
       return fail(c, HGM_EINVAL, "the tensor path needs 16-byte aligned points");
-    if (c->tscratch_rows < (size_t)n) {  // scratch for assignments and the re-check list
+    if (c->tscratch_rows < (size_t)n) {  // scratch: assignments, re-check list, cluster order
       CU(c, cudaStreamSynchronize(c->stream));
-      cudaFree(c->d_tlist);
-      c->d_tlist = nullptr;
+      cudaFree(c->d_tlist); cudaFree(c->d_tassign); cudaFree(c->d_torder);
+      c->d_tlist = c->d_tassign = c->d_torder = nullptr;
       c->tscratch_rows = 0;
       CU(c, cudaMalloc(&c->d_tlist, (size_t)n * 4));
+      CU(c, cudaMalloc(&c->d_tassign, (size_t)n * 4));
+      CU(c, cudaMalloc(&c->d_torder, (size_t)n * 4));
       c->tscratch_rows = (size_t)n;
     }
-    e = launch_tensor_map(d_pts, n, c->d, c->d_cent, c->k, c->d_caug, c->d_tflags, d_assign, c->d_tlist,
-                          c->d_tflags + 1, sums_ptr(c), counts_ptr(c), c->sm_count, c->smem_optin, c->stream);
-    launches = 2;
+    if (!c->d_tmeta) CU(c, cudaMalloc(&c->d_tmeta, tensor_meta_words(c->k) * 4));
+    e = launch_tensor_map(d_pts, n, c->d, c->d_cent, c->k, c->d_caug, c->d_tflags, d_assign ? d_assign : c->d_tassign,
+                          c->d_tlist, c->d_tflags + 1, c->d_tmeta, c->d_torder, sums_ptr(c), counts_ptr(c), c->sm_count,
+                          c->smem_optin, c->stream);
+    launches = 5;
   } else if (kern == HGM_KERNEL_GRID2D) {
     e = launch_grid2d_map(d_pts, n, c->d_cent, c->k, c->grid, c->d_table, c->d_cand, sums_ptr(c),
                           counts_ptr(c), d_assign, c->sm_count, c->smem_optin, c->stream);

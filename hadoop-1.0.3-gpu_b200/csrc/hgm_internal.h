@@ -58,10 +58,11 @@ bool tensor_shape_ok(int k, int d, size_t smem_optin);
 size_t tensor_caug_floats(int k, int d);
 cudaError_t launch_tensor_prep(const float *d_cent, int k, int d, float *d_caug, unsigned int *d_cmax_bits,
                                cudaStream_t s);
+size_t tensor_meta_words(int k);  // uint32 words of per-launch cluster bookkeeping
 cudaError_t launch_tensor_map(const float *d_pts, int64_t n, int d, const float *d_cent, int k, const float *d_caug,
                               const unsigned int *d_cmax_bits, int32_t *d_assign, int32_t *d_flag_list,
-                              unsigned int *d_flag_count, double *d_sums, unsigned long long *d_counts, int sm_count,
-                              size_t smem_optin, cudaStream_t s);
+                              unsigned int *d_flag_count, unsigned int *d_meta, int32_t *d_order, double *d_sums,
+                              unsigned long long *d_counts, int sm_count, size_t smem_optin, cudaStream_t s);
 
 // text decode (kernels_text.cu)
 struct TextStats {

@@ -12,8 +12,13 @@
 //   K3  recheck_kernel         TF32 carries ~2^-10 per operand, so a point whose top-2 margin
 //       is inside the rounding bound is re-scanned with the exact FP32 arithmetic of the
 //       reference scan (ascending index, strict '<'): assignments stay bit-identical.
-//   K4  accumulation           per-cluster FP64 sums / int64 counts: a decided point is added by its
-//       epilogue thread (RED.ADD.F64, row re-read from L2), a re-checked one by K3.
+//   K4  accumulation           per-cluster FP64 sums / int64 counts, as a segmented reduction:
+//       K2/K3 only count the points of each cluster; cluster_offsets_kernel turns the counts into
+//       segment offsets, scatter_order_kernel writes the point indices cluster by cluster, and
+//       gather_reduce_kernel sums each segment's rows in registers (coalesced row reads, one
+//       FP64 RED per coordinate per 1024 points).  Adding every point with d REDs from K2's
+//       epilogue -- the first version -- was bound by the SM's RED issue rate (~41 cycles per
+//       warp instruction) and stalled the MMA pipeline behind the epilogue warps.
 //
 // Rounding bound: the score of (x, c) is off by at most 2^-8 |x| |c| (x truncated to TF32 by
 // the tensor core: 2^-10; c rounded to TF32 here: 2^-11; doubled by the factor 2) plus FP32
@@ -38,6 +43,8 @@ constexpr int kABytes = 128 * kBlockK * 4;       // one 128-row K-block of A: 16
 constexpr int kBBytes = kTileN * kBlockK * 4;    // one B stage: 16 KiB
 constexpr int kEpiWarps = 16;                    // two per (accumulator half, TMEM lane quarter): 64 columns each
 constexpr int kThreads = (4 + kEpiWarps) * 32;   // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 spare, 4..19 epilogue
+// (putting the single-lane roles ABOVE the epilogue warps, where the issue arbiter favours them, measured 3 % slower)
+constexpr int kTmaWarp = 0, kMmaWarp = 1, kAllocWarp = 2, kFirstEpiWarp = 4;
 constexpr uint32_t kTmemCols = 512;              // 2 buffers x 2 halves x 128 columns
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
@@ -64,6 +71,22 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
         : "r"(smem_u32(bar)), "r"(parity)
         : "memory");
     if (spins > 50u * 1000u * 1000u) __trap();
+  }
+}
+// Same for the single-lane roles (TMA producer, MMA issuer): their spin loops share the SM's ALU
+// pipe with the 16 epilogue warps, which are bound by it, so a failed probe backs off.
+__device__ __forceinline__ void mbar_wait_backoff(uint64_t *bar, uint32_t parity, unsigned ns) {
+  uint32_t done = 0;
+  for (uint32_t spins = 0; !done; ++spins) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(done)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    if (!done) __nanosleep(ns);
+    if (spins > 20u * 1000u * 1000u) __trap();
   }
 }
 __device__ __forceinline__ void tma_load_2d(void *dst, const CUtensorMap *map, int c0, int c1, uint64_t *bar) {
@@ -115,13 +138,18 @@ __device__ __forceinline__ void tmem_ld32_issue(uint32_t taddr, uint32_t (&r)[32
 }
 __device__ __forceinline__ void tmem_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
-// Top-2 of a stream of scores with the column index riding in the 7 low mantissa bits of the
-// score ("key"): one LOP3 + three FMNMX per element instead of compare/select chains.  The
-// low bits cost 2^-16 of relative precision, far inside the TF32 rounding bound.
+// Top-2 of a stream of scores with the column index riding in the 6 low mantissa bits of the
+// score ("key"): one LOP3 + 2.5 FMNMX/FMNMX3 per element instead of compare/select chains.  The
+// index must be a compile-time constant (a thread scans 64 columns of each centroid tile; which
+// half of the tile they are is known per warp and added at the end) -- a run-time part costs a
+// second LOP3 per element, and the epilogue is bound by exactly this ALU pipe.  The low bits
+// cost 2^-17 of relative precision, far inside the TF32 rounding bound.
 struct Top2 {
   float best = INFINITY, second = INFINITY;
-  __device__ __forceinline__ void push(uint32_t raw, uint32_t col7) {
-    const float key = __uint_as_float((raw & ~0x7Fu) | col7);
+  // keymask = ~0x3F, handed in as a kernel argument: as a literal the compiler splits the
+  // packing into AND-immediate + OR-immediate; from a register it is one LOP3 (a & mask) | imm
+  __device__ __forceinline__ void push(uint32_t raw, uint32_t col6, uint32_t keymask) {
+    const float key = __uint_as_float((raw & keymask) | col6);
     second = fminf(second, fmaxf(key, best));
     best = fminf(key, best);
   }
@@ -166,11 +194,12 @@ __global__ void tensor_prep_kernel(const float *__restrict__ cent, int k, int k_
 struct TensorArgs {
   long long n;
   int k, k_pad, d, stages;
+  uint32_t keymask;             // ~0x3F (see Top2::push)
+  int debug;                    // experiments only (HGM_TENSOR_DEBUG): 1 = no MMA issued, 2 = no TMEM loads, 3 = neither TMEM loads nor B tiles (stale operands)
   const unsigned int *cmax_bits;
   const float *pts;
-  double *sums;                 // [k*d] partial sums (RED.ADD.F64)
-  unsigned long long *counts;   // [k]
-  int32_t *assign;              // [n] best index per point, or NULL
+  unsigned int *lcounts;        // [k] points of this launch per cluster (decided ones here, the rest in K3)
+  int32_t *assign;              // [n] best index per point
   int32_t *flag_list;           // indices of points that need the exact re-check
   unsigned int *flag_count;
 };
@@ -211,7 +240,7 @@ __global__ void __launch_bounds__(kThreads, 1)
     reinterpret_cast<float4 *>(a_aug)[i] = val;
   }
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic-proxy writes -> visible to the MMA's async reads
-  if (warp == 2) {
+  if (warp == kAllocWarp) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
                  "r"(kTmemCols));
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
@@ -223,11 +252,11 @@ __global__ void __launch_bounds__(kThreads, 1)
 
   const long long tiles_m = (a.n + kTileM - 1) / kTileM;
 
-  if (warp == 0) {
+  if (warp == kTmaWarp) {
     // ===== TMA producer (whole warp walks the loop, one elected lane issues) =====
     uint32_t stage = 0, phase = 0, a_phase = 0;
     for (long long tm = blockIdx.x; tm < tiles_m; tm += gridDim.x) {
-      mbar_wait(a_empty, a_phase ^ 1);
+      mbar_wait_backoff(a_empty, a_phase ^ 1, 200);
       if (elect_one()) {
         mbar_expect_tx(a_full, 2 * kblocks * kABytes);
         for (int h = 0; h < 2; ++h)
@@ -237,9 +266,9 @@ __global__ void __launch_bounds__(kThreads, 1)
       }
       __syncwarp();
       a_phase ^= 1;
-      for (int tn = 0; tn < ntiles_n; ++tn)
+      for (int tn = 0; tn < (a.debug == 3 ? 0 : ntiles_n); ++tn)
         for (int kb = 0; kb <= kblocks; ++kb) {
-          mbar_wait(&empty[stage], phase ^ 1);
+          mbar_wait_backoff(&empty[stage], phase ^ 1, 100);
           if (elect_one()) {
             mbar_expect_tx(&full[stage], kBBytes);
             tma_load_2d(b_stage + (size_t)stage * kBBytes, &map_c, kb * kBlockK, tn * kTileN, &full[stage]);
@@ -248,7 +277,7 @@ __global__ void __launch_bounds__(kThreads, 1)
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
     }
-  } else if (warp == 1) {
+  } else if (warp == kMmaWarp) {
     // ===== MMA issuer (whole warp walks the loop, one elected lane issues) =====
     // One thread feeds the tensor core, so every instruction between two tcgen05.mma counts:
     // the shared-memory descriptors are built once and only advanced (16-byte units in the
@@ -257,35 +286,39 @@ __global__ void __launch_bounds__(kThreads, 1)
     uint32_t stage = 0, phase = 0, a_phase = 0, t_phase[2] = {0, 0};
     int buf = 0;
     for (long long tm = blockIdx.x; tm < tiles_m; tm += gridDim.x) {
-      mbar_wait(a_full, a_phase);
+      mbar_wait_backoff(a_full, a_phase, 40);
       a_phase ^= 1;
       for (int tn = 0; tn < ntiles_n; ++tn) {
-        mbar_wait(&t_empty[buf], t_phase[buf] ^ 1);
+        mbar_wait_backoff(&t_empty[buf], t_phase[buf] ^ 1, 40);
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const uint32_t tacc0 = tmem_base + (uint32_t)(buf * 2 * kTileN), tacc1 = tacc0 + kTileN;
         for (int kb = 0; kb < kblocks; ++kb) {
-          mbar_wait(&full[stage], phase);
+          if (a.debug != 3) mbar_wait_backoff(&full[stage], phase, 20);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           const uint64_t bd = b_desc0 + (uint64_t)(stage * (kBBytes >> 4));
           const uint64_t ad0 = a_desc0 + (uint64_t)(kb * (kABytes >> 4));
           const uint64_t ad1 = ad0 + (uint64_t)(kblocks * (kABytes >> 4));
           if (elect_one()) {
+            if (a.debug != 1) {
 #pragma unroll
             for (int ks = 0; ks < kBlockK / kUmmaK; ++ks) umma_tf32(tacc0, ad0 + 2 * ks, bd + 2 * ks, (kb | ks) != 0);
 #pragma unroll
             for (int ks = 0; ks < kBlockK / kUmmaK; ++ks) umma_tf32(tacc1, ad1 + 2 * ks, bd + 2 * ks, (kb | ks) != 0);
+            }
             umma_commit(&empty[stage]);  // the B stage is free once these MMAs have read it
           }
           __syncwarp();
           if (++stage == (uint32_t)kStages) { stage = 0; phase ^= 1; }
         }
         {  // the |c|^2 K-block: x side = the constant tile, 3 live columns = one K-step
-          mbar_wait(&full[stage], phase);
+          if (a.debug != 3) mbar_wait_backoff(&full[stage], phase, 20);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           const uint64_t bd = b_desc0 + (uint64_t)(stage * (kBBytes >> 4));
           if (elect_one()) {
-            umma_tf32(tacc0, aug_desc, bd, 1);
-            umma_tf32(tacc1, aug_desc, bd, 1);
+            if (a.debug != 1) {
+              umma_tf32(tacc0, aug_desc, bd, 1);
+              umma_tf32(tacc1, aug_desc, bd, 1);
+            }
             umma_commit(&empty[stage]);
             umma_commit(&t_full[buf]);  // accumulators of this centroid tile are complete
           }
@@ -298,17 +331,18 @@ __global__ void __launch_bounds__(kThreads, 1)
       if (elect_one()) umma_commit(a_empty);  // every MMA that reads this point tile has retired
       __syncwarp();
     }
-  } else if (warp >= 4) {
+  } else if (warp >= kFirstEpiWarp) {
     // ===== epilogue: a thread owns one point (TMEM lane) and half of each tile's score columns =====
-    const int ew = warp - 4;
+    const int ew = warp - kFirstEpiWarp;
     const int quarter = warp % 4;      // a warp may only touch TMEM lanes 32*(warp % 4) .. +31
     const int half = ew / 8;           // which 128-row accumulator
     const int colhalf = (ew / 4) % 2;  // columns [64*colhalf, +64) of every centroid tile
     const int row = half * 128 + quarter * 32 + lane;  // row within the CTA tile
     const float cmax = __uint_as_float(*a.cmax_bits);
-    float4 *const xchg = reinterpret_cast<float4 *>(tmem_slot + 4);  // [256 rows] partner results
+    const uint32_t keymask = a.keymask;
+    float4 *const xchg = reinterpret_cast<float4 *>(tmem_slot + 4);  // [2][256 rows] partner results
     uint32_t a_phase = 0, t_phase[2] = {0, 0};
-    int buf = 0;
+    int buf = 0, tile_parity = 0;
     for (long long tm = blockIdx.x; tm < tiles_m; tm += gridDim.x) {
       // |x|^2 of my row from the swizzled A tile
       mbar_wait(a_full, a_phase);
@@ -345,78 +379,64 @@ __global__ void __launch_bounds__(kThreads, 1)
         if (lane == 0) mbar_arrive(&t_empty[buf]);  // the scores are in registers: free the accumulator
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
-          even.push(r0[i], colhalf * 64 + i);
-          odd.push(r0[i + 1], colhalf * 64 + i + 1);
+          even.push(r0[i], i, keymask);
+          odd.push(r0[i + 1], i + 1, keymask);
         }
 #pragma unroll
         for (int i = 0; i < 32; i += 2) {
-          even.push(r1[i], colhalf * 64 + 32 + i);
-          odd.push(r1[i + 1], colhalf * 64 + 32 + i + 1);
+          even.push(r1[i], 32 + i, keymask);
+          odd.push(r1[i + 1], 32 + i + 1, keymask);
         }
         if (fminf(even.best, odd.best) < before) best_tile = tn;
         buf ^= 1;
       }
       even.merge(odd);
-      // the two column-halves of a row meet in shared memory; colhalf 0 decides the point
+      // the two column-halves of a row meet in shared memory (double-buffered by tile parity, so one
+      // barrier per tile orders write -> read, and the next write lands in the other buffer);
+      // colhalf 0 decides the point
       const int pair_bar = 1 + half * 4 + quarter;
-      if (colhalf == 1) xchg[row] = make_float4(even.best, even.second, __int_as_float(best_tile), 0.f);
+      float4 *const xb = xchg + (tile_parity ? kTileM : 0);
+      tile_parity ^= 1;
+      if (colhalf == 1) xb[row] = make_float4(even.best, even.second, __int_as_float(best_tile), 0.f);
       asm volatile("bar.sync %0, %1;" ::"r"(pair_bar), "r"(64) : "memory");
       if (colhalf == 0) {
-        const float4 o = xchg[row];
-        if (o.x < even.best) best_tile = __float_as_int(o.z);
+        const float4 o = xb[row];
+        int win_half = 0;  // which 64-column half of the centroid tile holds the winner
+        if (o.x < even.best) { best_tile = __float_as_int(o.z); win_half = 64; }
         Top2 other;
         other.best = o.x; other.second = o.y;
         even.merge(other);
         const long long p = tm * kTileM + row;
-        int decided = -1;  // cluster of a point decided on the tensor cores, else -1
         if (p < a.n) {
-          const int bidx = best_tile * kTileN + (int)(__float_as_uint(even.best) & 0x7Fu);
+          const int bidx = best_tile * kTileN + win_half + (int)(__float_as_uint(even.best) & 0x3Fu);
           const float xnorm = sqrtf(xn);
           const float reach = xnorm + cmax;
           // 2^-7 |x||c| (TF32 operands, both sides of the margin) + (d 2^-22 + 2^-14)(|x|+|c|)^2
-          // (FP32 accumulation, the scan's own rounding, the 7 index bits of the keys)
+          // (FP32 accumulation, the scan's own rounding, the 6 index bits of the keys)
           const float thr = 0.0078125f * xnorm * cmax + ((float)a.d * 2.3841858e-07f + 6.1035156e-05f) * reach * reach;
-          if (a.assign) a.assign[p] = bidx;
+          a.assign[p] = bidx;
           if (even.second - even.best > thr) {
-            decided = bidx;
+            if (!a.debug) atomicAdd(a.lcounts + bidx, 1u);  // decided on the tensor cores
           } else {  // inside the rounding bound (or NaN / inf): the exact scan decides
-            const unsigned int slot = atomicAdd(a.flag_count, 1u);
-            a.flag_list[slot] = (int32_t)p;  // p < 2^31 per launch (the host chunks larger inputs)
-          }
-        }
-        xchg[row].w = __int_as_float(decided);
-      }
-      asm volatile("bar.sync %0, %1;" ::"r"(pair_bar), "r"(64) : "memory");
-      // K4 for the decided points: both warps of the pair take 16 rows each; a row is added by
-      // the whole warp, lane j adding coordinates j, j+32, ... (coalesced FP64 REDs; the row was
-      // TMA-loaded microseconds ago and is still in L2)
-      {
-        const int row0 = half * 128 + quarter * 32 + colhalf * 16;
-        for (int i = 0; i < 16; ++i) {
-          const int c = __float_as_int(xchg[row0 + i].w);
-          if (c >= 0) {
-            const float *x = a.pts + (tm * kTileM + row0 + i) * a.d;
-            double *dst = a.sums + (size_t)c * a.d;
-            for (int j = lane; j < a.d; j += 32) atomicAdd(dst + j, (double)__ldg(x + j));
-            if (lane == 0) atomicAdd(a.counts + c, 1ull);
+            if (!a.debug) {
+              const unsigned int slot = atomicAdd(a.flag_count, 1u);
+              a.flag_list[slot] = (int32_t)p;
+            }  // p < 2^31 per launch (the host chunks larger inputs)
           }
         }
       }
-      asm volatile("bar.sync %0, %1;" ::"r"(pair_bar), "r"(64) : "memory");  // xchg reusable
     }
   }
   __syncthreads();
-  if (warp == 2) {
+  if (warp == kAllocWarp) {
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols));
   }
 }
 
-// ---- K3: exact re-check of the flagged points, one warp per point; it also adds them to the
-// partial sums (K4 for these points) --------------------------------------------------------------
+// ---- K3: exact re-check of the flagged points, one warp per point ---------------------------------
 __global__ void recheck_kernel(const float *__restrict__ pts, int d, const float *__restrict__ cent, int k,
                                const int32_t *__restrict__ flag_list, const unsigned int *__restrict__ flag_count,
-                               int32_t *__restrict__ assign, double *__restrict__ sums,
-                               unsigned long long *__restrict__ counts) {
+                               int32_t *__restrict__ assign, unsigned int *__restrict__ lcounts) {
   const unsigned int nflag = *flag_count;
   const int lane = threadIdx.x % 32;
   const unsigned int warps = (gridDim.x * blockDim.x) / 32;
@@ -438,10 +458,161 @@ __global__ void recheck_kernel(const float *__restrict__ pts, int d, const float
     }
     const int c = (best < INFINITY) ? arg : 0;  // nothing beat +inf: the scan keeps index 0
     if (lane == 0) {
-      if (assign) assign[p] = c;
-      atomicAdd(&counts[c], 1ull);
+      assign[p] = c;
+      atomicAdd(&lcounts[c], 1u);
     }
-    for (int j = lane; j < d; j += 32) atomicAdd(&sums[(size_t)c * d + j], (double)x[j]);
+  }
+}
+
+// ---- K4: per-cluster sums as a segmented reduction ------------------------------------------------
+constexpr int kRedChunk = 1024;  // point indices per work item of gather_reduce_kernel
+
+// One CTA.  meta = [lcounts k][offsets k+1][cursor k][items k+1]: offsets = exclusive scan of the
+// launch's counts, items = exclusive scan of ceil(count / kRedChunk); the counts join the
+// cumulative partials and the cursors start at 0.
+__global__ void __launch_bounds__(1024) cluster_offsets_kernel(unsigned int *__restrict__ meta, int k,
+                                                               unsigned long long *__restrict__ counts) {
+  __shared__ unsigned int warp_a[32], warp_b[32];
+  __shared__ unsigned int carry_a, carry_b;
+  unsigned int *lcounts = meta, *offsets = meta + k, *cursor = meta + 2 * k + 1, *items = meta + 3 * k + 1;
+  if (threadIdx.x == 0) carry_a = carry_b = 0;
+  __syncthreads();
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int first = 0; first < k; first += 1024) {
+    const int i = first + threadIdx.x;
+    const unsigned int cnt = i < k ? lcounts[i] : 0u;
+    const unsigned int itm = (cnt + kRedChunk - 1) / kRedChunk;
+    unsigned int ia = cnt, ib = itm;
+    for (int o = 1; o < 32; o <<= 1) {
+      const unsigned int ta = __shfl_up_sync(0xffffffffu, ia, o), tb = __shfl_up_sync(0xffffffffu, ib, o);
+      if (lane >= o) { ia += ta; ib += tb; }
+    }
+    if (lane == 31) { warp_a[warp] = ia; warp_b[warp] = ib; }
+    __syncthreads();
+    if (warp == 0) {
+      const unsigned int wa = warp_a[lane], wb = warp_b[lane];
+      unsigned int sa = wa, sb = wb;
+      for (int o = 1; o < 32; o <<= 1) {
+        const unsigned int ta = __shfl_up_sync(0xffffffffu, sa, o), tb = __shfl_up_sync(0xffffffffu, sb, o);
+        if (lane >= o) { sa += ta; sb += tb; }
+      }
+      warp_a[lane] = sa - wa;
+      warp_b[lane] = sb - wb;
+    }
+    __syncthreads();
+    const unsigned int ea = carry_a + warp_a[warp] + ia - cnt, eb = carry_b + warp_b[warp] + ib - itm;
+    if (i < k) {
+      offsets[i] = ea;
+      items[i] = eb;
+      cursor[i] = 0;
+      if (cnt) counts[i] += cnt;  // one writer per cluster; earlier launches are ordered by the stream
+    }
+    __syncthreads();
+    if (threadIdx.x == 1023) { carry_a = ea + cnt; carry_b = eb + itm; }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) { offsets[k] = carry_a; items[k] = carry_b; }
+}
+
+// order[offsets[c] .. offsets[c+1]) <- the points assigned to c (in no particular order).
+// A CTA takes kScatterChunk consecutive points at a time: a shared-memory histogram of the chunk,
+// ONE global atomic per cluster present to reserve its run of slots (a global atomic per point on k
+// hot addresses ran at 13 G/s: 3 ms for 40 M points), then the ranks inside the run from shared
+// atomics.  k <= kScatterMaxK; larger tables take scatter_order_direct_kernel.
+constexpr int kScatterChunk = 16384;
+constexpr int kScatterMaxK = 8192;
+__global__ void __launch_bounds__(512) scatter_order_kernel(const int32_t *__restrict__ assign, long long n, int k,
+                                                            unsigned int *__restrict__ meta,
+                                                            int32_t *__restrict__ order) {
+  extern __shared__ unsigned int sh[];  // [k] counts -> ranks, [k] global base of the run
+  unsigned int *cnt = sh, *base = sh + k;
+  const unsigned int *offsets = meta + k;
+  unsigned int *cursor = meta + 2 * k + 1;
+  const long long chunks = (n + kScatterChunk - 1) / kScatterChunk;
+  for (long long ch = blockIdx.x; ch < chunks; ch += gridDim.x) {
+    const long long p0 = ch * kScatterChunk;
+    const int m = (int)min((long long)kScatterChunk, n - p0);
+    for (int c = threadIdx.x; c < k; c += blockDim.x) cnt[c] = 0;
+    __syncthreads();
+    for (int i = threadIdx.x; i < m; i += blockDim.x) atomicAdd(&cnt[assign[p0 + i]], 1u);
+    __syncthreads();
+    for (int c = threadIdx.x; c < k; c += blockDim.x) {
+      const unsigned int have = cnt[c];
+      base[c] = have ? offsets[c] + atomicAdd(&cursor[c], have) : 0u;
+      cnt[c] = 0;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < m; i += blockDim.x) {
+      const int c = assign[p0 + i];
+      order[base[c] + atomicAdd(&cnt[c], 1u)] = (int32_t)(p0 + i);
+    }
+    __syncthreads();
+  }
+}
+__global__ void scatter_order_direct_kernel(const int32_t *__restrict__ assign, long long n, int k,
+                                            unsigned int *__restrict__ meta, int32_t *__restrict__ order) {
+  const unsigned int *offsets = meta + k;
+  unsigned int *cursor = meta + 2 * k + 1;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < n; p += stride) {
+    const int c = assign[p];
+    order[offsets[c] + atomicAdd(&cursor[c], 1u)] = (int32_t)p;
+  }
+}
+
+// One work item = up to kRedChunk points of one cluster: 8 warps gather their rows (lane j holds
+// coordinates j, j+32, ...: every row read is a coalesced 128-byte line per 32 coordinates), sum
+// in FP64 registers, meet in shared memory, and one thread per coordinate adds the item's sum.
+template <int D32>
+__global__ void __launch_bounds__(256) gather_reduce_kernel(const float *__restrict__ pts, int k,
+                                                            const unsigned int *__restrict__ meta,
+                                                            const int32_t *__restrict__ order,
+                                                            double *__restrict__ sums) {
+  constexpr int d = D32 * 32;
+  __shared__ double red[8][d];
+  const unsigned int *offsets = meta + k, *items = meta + 3 * k + 1;
+  const unsigned int total = items[k];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (unsigned int item = blockIdx.x; item < total; item += gridDim.x) {
+    int lo = 0, hi = k;  // largest c with items[c] <= item
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (items[mid] <= item) lo = mid; else hi = mid;
+    }
+    const int c = lo;
+    const unsigned int begin = offsets[c] + (item - items[c]) * kRedChunk;
+    const unsigned int end = min(offsets[c + 1], begin + kRedChunk);
+    double acc[D32];
+#pragma unroll
+    for (int m = 0; m < D32; ++m) acc[m] = 0.0;
+    unsigned int i = begin + warp;
+    for (; i + 24 < end; i += 32) {  // four rows in flight per warp
+      const float *r0 = pts + (size_t)order[i] * d, *r1 = pts + (size_t)order[i + 8] * d;
+      const float *r2 = pts + (size_t)order[i + 16] * d, *r3 = pts + (size_t)order[i + 24] * d;
+      float v[4][D32];
+#pragma unroll
+      for (int m = 0; m < D32; ++m) {
+        v[0][m] = __ldg(r0 + lane + 32 * m); v[1][m] = __ldg(r1 + lane + 32 * m);
+        v[2][m] = __ldg(r2 + lane + 32 * m); v[3][m] = __ldg(r3 + lane + 32 * m);
+      }
+#pragma unroll
+      for (int m = 0; m < D32; ++m) acc[m] += ((double)v[0][m] + (double)v[1][m]) + ((double)v[2][m] + (double)v[3][m]);
+    }
+    for (; i < end; i += 8) {
+      const float *r = pts + (size_t)order[i] * d;
+#pragma unroll
+      for (int m = 0; m < D32; ++m) acc[m] += (double)__ldg(r + lane + 32 * m);
+    }
+#pragma unroll
+    for (int m = 0; m < D32; ++m) red[warp][lane + 32 * m] = acc[m];
+    __syncthreads();
+    if (threadIdx.x < d) {
+      double t = 0.0;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) t += red[w][threadIdx.x];
+      atomicAdd(&sums[(size_t)c * d + threadIdx.x], t);
+    }
+    __syncthreads();
   }
 }
 
@@ -476,7 +647,7 @@ bool make_map(CUtensorMap *map, const float *base, uint64_t rows, uint64_t cols)
 
 size_t tensor_smem_bytes(int d, int stages) {
   const int kblocks = d / kBlockK;
-  return (size_t)2 * kblocks * kABytes + kABytes + (size_t)stages * kBBytes + 512 + kTileM * 16 + 1024;
+  return (size_t)2 * kblocks * kABytes + kABytes + (size_t)stages * kBBytes + 512 + 2 * kTileM * 16 + 1024;
 }
 int tensor_stages(int d, size_t smem_optin) {
   int stages = kMaxStages;
@@ -503,14 +674,17 @@ cudaError_t launch_tensor_prep(const float *d_cent, int k, int d, float *d_caug,
   return cudaGetLastError();
 }
 
-// scores + assignment + accumulation (K2), then the exact re-check of the flagged points (K3)
+size_t tensor_meta_words(int k) { return (size_t)4 * k + 2; }
+
+// scores + assignment (K2), the exact re-check of the flagged points (K3), then the per-cluster sums
+// as a segmented reduction (K4): 5 launches
 cudaError_t launch_tensor_map(const float *d_pts, int64_t n, int d, const float *d_cent, int k, const float *d_caug,
                               const unsigned int *d_cmax_bits, int32_t *d_assign, int32_t *d_flag_list,
-                              unsigned int *d_flag_count, double *d_sums, unsigned long long *d_counts, int sm_count,
-                              size_t smem_optin, cudaStream_t s) {
+                              unsigned int *d_flag_count, unsigned int *d_meta, int32_t *d_order, double *d_sums,
+                              unsigned long long *d_counts, int sm_count, size_t smem_optin, cudaStream_t s) {
   if (n <= 0) return cudaSuccess;
   if (n > 0x7FFFFFFFll) return cudaErrorInvalidValue;
-  if ((reinterpret_cast<uintptr_t>(d_pts) & 15) != 0) return cudaErrorInvalidValue;
+  if ((reinterpret_cast<uintptr_t>(d_pts) & 15) != 0 || !d_assign) return cudaErrorInvalidValue;
   CUtensorMap map_x, map_c;
   const int k_pad = tensor_k_pad(k);
   if (!make_map(&map_x, d_pts, (uint64_t)n, (uint64_t)d) ||
@@ -518,17 +692,42 @@ cudaError_t launch_tensor_map(const float *d_pts, int64_t n, int d, const float 
     return cudaErrorInvalidValue;
   cudaError_t e = cudaMemsetAsync(d_flag_count, 0, 4, s);
   if (e != cudaSuccess) return e;
+  e = cudaMemsetAsync(d_meta, 0, (size_t)k * 4, s);  // the launch's per-cluster counts
+  if (e != cudaSuccess) return e;
   const int stages = tensor_stages(d, smem_optin);
   const size_t smem = tensor_smem_bytes(d, stages);  // includes 1 KiB of slack to align the base
   e = cudaFuncSetAttribute(tensor_assign_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  TensorArgs a{(long long)n, k, k_pad, d, stages, d_cmax_bits, d_pts, d_sums, d_counts, d_assign, d_flag_list, d_flag_count};
+  TensorArgs a{(long long)n, k, k_pad, d, stages, ~0x3Fu, getenv("HGM_TENSOR_DEBUG") ? atoi(getenv("HGM_TENSOR_DEBUG")) : 0, d_cmax_bits, d_pts, d_meta, d_assign, d_flag_list, d_flag_count};
   const long long tiles = (n + kTileM - 1) / kTileM;
   const int grid = (int)(tiles < sm_count ? tiles : sm_count);
   tensor_assign_kernel<<<grid, kThreads, smem, s>>>(map_x, map_c, a);
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
-  recheck_kernel<<<sm_count * 4, 256, 0, s>>>(d_pts, d, d_cent, k, d_flag_list, d_flag_count, d_assign, d_sums,
-                                              d_counts);
+  if (a.debug) return cudaSuccess;  // experiments time K2 alone; its output is meaningless then
+  recheck_kernel<<<sm_count * 4, 256, 0, s>>>(d_pts, d, d_cent, k, d_flag_list, d_flag_count, d_assign, d_meta);
+  if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  cluster_offsets_kernel<<<1, 1024, 0, s>>>(d_meta, k, d_counts);
+  if (k <= kScatterMaxK) {
+    long long sblocks = (n + kScatterChunk - 1) / kScatterChunk;
+    if (sblocks > (long long)sm_count * 2) sblocks = (long long)sm_count * 2;
+    const size_t sbytes = (size_t)2 * k * sizeof(unsigned int);
+    if (sbytes > 48 * 1024) {
+      e = cudaFuncSetAttribute(scatter_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sbytes);
+      if (e != cudaSuccess) return e;
+    }
+    scatter_order_kernel<<<(int)sblocks, 512, sbytes, s>>>(d_assign, (long long)n, k, d_meta, d_order);
+  } else {
+    long long sblocks = (n + 255) / 256;
+    if (sblocks > (long long)sm_count * 16) sblocks = (long long)sm_count * 16;
+    scatter_order_direct_kernel<<<(int)sblocks, 256, 0, s>>>(d_assign, (long long)n, k, d_meta, d_order);
+  }
+  const int rgrid = sm_count * 8;
+  switch (d / 32) {
+    case 1: gather_reduce_kernel<1><<<rgrid, 256, 0, s>>>(d_pts, k, d_meta, d_order, d_sums); break;
+    case 2: gather_reduce_kernel<2><<<rgrid, 256, 0, s>>>(d_pts, k, d_meta, d_order, d_sums); break;
+    case 3: gather_reduce_kernel<3><<<rgrid, 256, 0, s>>>(d_pts, k, d_meta, d_order, d_sums); break;
+    default: gather_reduce_kernel<4><<<rgrid, 256, 0, s>>>(d_pts, k, d_meta, d_order, d_sums); break;
+  }
   return cudaGetLastError();
 }
 

@@ -114,7 +114,8 @@ def test_unindexable_centroids_fall_to_exact_scan(slot, oracle):
 
 
 @pytest.mark.parametrize("d,k,n", [(1, 5, 4001), (3, 17, 5003), (4, 64, 9001), (8, 33, 7001), (9, 12, 3001),
-                                   (16, 50, 6007), (64, 100, 4099), (128, 257, 2053), (300, 9, 777)])
+                                   (16, 50, 6007), (64, 100, 4099), (128, 257, 2053), (300, 9, 777),
+                                   (32, 8200, 1501)])
 def test_general_dimensions_exact_scan(slot, oracle, d, k, n):
     pts, cent = cases.general_d(n, d, k, seed=d * 1000 + k)
     tensor = d % 32 == 0 and 32 <= d <= 128 and k >= 128 and k * d >= 8192  # hgm_api.cu:pick_kernel
