@@ -195,6 +195,7 @@ struct TensorArgs {
   long long n;
   int k, k_pad, d, stages;
   uint32_t keymask;             // ~0x3F (see Top2::push)
+  long long *trace;             // experiments only (HGM_TENSOR_TRACE): [role][512][2] event log of CTA 0
   int debug;                    // experiments only (HGM_TENSOR_DEBUG): 1 = no MMA issued, 2 = no TMEM loads, 3 = neither TMEM loads nor B tiles (stale operands)
   const unsigned int *cmax_bits;
   const float *pts;
@@ -433,6 +434,319 @@ __global__ void __launch_bounds__(kThreads, 1)
   }
 }
 
+// ---- K2, pair form: two CTAs of a cluster drive ONE tcgen05.mma.cta_group::2 ------------------------
+// Measured on the single-CTA kernel above (HGM_TENSOR_DEBUG experiments, profiles/r01_tensor_summary.md):
+// with both operands in shared memory a 128x128x8 TF32 MMA takes ~120 cycles instead of 64 -- the
+// 8 KiB of operands per instruction are all one SM's shared memory can feed.  In pair form a
+// 256x256x8 MMA reads the same 8 KiB per SM (its own 128 rows of X and its own 128 of the 256
+// centroid rows; the other halves come from the peer's shared memory) for twice the work.
+//   per CTA: 128 points resident (kblocks x 16 KiB, double-buffered), B stages of 128 centroid rows, TMEM = 2 buffers x 256
+//   columns; warp 0 loads (both CTAs, signalling the leader's barriers), warp 1 of the LEADER issues the
+//   MMAs and multicasts its commits to both CTAs, the 16 epilogue warps of each CTA scan 32 rows x 64 of
+//   the 256 columns each and free the accumulator on the leader's barrier.
+constexpr int kPairN = 256;
+constexpr int kPairRows = 128;  // points per CTA and tile
+constexpr uint32_t kIdescPair = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kPairN >> 3) << 17) | ((256u >> 4) << 24);
+constexpr uint32_t kLeaderMask = 0xFEFFFFFFu;  // shared-window addresses carry the CTA's cluster rank in bit 24
+
+__device__ __forceinline__ uint32_t cluster_rank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// TMA load into THIS CTA's shared memory whose bytes are counted on the LEADER's mbarrier
+__device__ __forceinline__ void tma_load_2d_pair(void *dst, const CUtensorMap *map, int c0, int c1, uint64_t *bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::
+          "r"(smem_u32(dst)),
+      "l"(map), "r"(smem_u32(bar) & kLeaderMask), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void umma_tf32_pair(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t}" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(kIdescPair), "r"(accumulate)
+      : "memory");
+}
+// arrive on the barrier at this shared-memory offset in BOTH CTAs once the MMAs issued so far have retired
+__device__ __forceinline__ void umma_commit_pair(uint64_t *bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+          smem_u32(bar)),
+      "h"((uint16_t)3)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_leader(uint64_t *bar) {
+  // no .release.cluster: nothing in memory is handed over (the scores left TMEM through tcgen05.ld +
+  // wait::ld), and that qualifier costs a MEMBAR.GPU + ERRBAR per arrive -- a third of all stall samples
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(smem_u32(bar) & kLeaderMask) : "memory");
+}
+
+// event log for the pipeline experiments: role 0 = TMA, 1 = MMA, 2 = first epilogue warp; CTA 0 only
+struct Trace {
+  long long *base;
+  int n;
+  __device__ __forceinline__ void operator()(int code, int x) {
+    if (base && n < 512) {
+      base[2 * n] = ((long long)code << 32) | (unsigned)x;
+      base[2 * n + 1] = clock64();
+      ++n;
+    }
+  }
+};
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+    tensor_assign_pair_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_c,
+                              const TensorArgs a) {
+  extern __shared__ unsigned char smem_raw[];
+  unsigned char *smem = reinterpret_cast<unsigned char *>(
+      (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int kblocks = a.d / kBlockK;
+  const int ntiles_n = a.k_pad / kPairN;
+  unsigned char *a_res = smem;                                   // [2][kblocks] x 16 KiB: my 128 points, double-buffered
+  const size_t a_bytes = (size_t)kblocks * kABytes;              // (the next tile's rows land while this one is scored)
+  unsigned char *a_aug = a_res + 2 * a_bytes;                    // the constant |c|^2 tile
+  const int kStages = a.stages;
+  unsigned char *b_stage = a_aug + kABytes;                  // stages x 16 KiB: my 128 of the tile's 256 centroid rows
+  uint64_t *bars = reinterpret_cast<uint64_t *>(b_stage + (size_t)kStages * kBBytes);
+  uint64_t *full = bars, *empty = bars + kMaxStages;
+  uint64_t *a_full = bars + 2 * kMaxStages, *a_empty = a_full + 2;
+  uint64_t *t_full = a_empty + 2, *t_empty = t_full + 2;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(t_empty + 2);
+  float4 *const xchg = reinterpret_cast<float4 *>(tmem_slot + 4);  // [2 parities][3 column groups][128 rows]
+
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const uint32_t rank = cluster_rank();
+  const bool leader = rank == 0;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&a_full[b], 1);
+      mbar_init(&a_empty[b], 1 + kEpiWarps);
+      mbar_init(&t_full[b], 1);
+      mbar_init(&t_empty[b], 2 * kEpiWarps);
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  for (int i = threadIdx.x; i < kABytes / 16; i += kThreads) {
+    const int r = i / 8, chunk = i % 8;
+    const float4 val = chunk == (r % 8) ? make_float4(1.f, 1.f, 1.f, 0.f) : make_float4(0.f, 0.f, 0.f, 0.f);
+    reinterpret_cast<float4 *>(a_aug)[i] = val;
+  }
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+  if (warp == kAllocWarp) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"(kTmemCols));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::);
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  cluster_sync_all();  // the peer's barriers are initialised before anything arrives on them
+  asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+  const uint32_t tmem_base = *tmem_slot;
+
+  const long long tiles = (a.n + 2 * kPairRows - 1) / (2 * kPairRows);
+  const long long pair0 = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+
+  if (warp == kTmaWarp) {
+    // ===== TMA producer: in BOTH CTAs; every byte is counted on the leader's barriers =====
+    uint32_t stage = 0, phase = 0, a_phase[2] = {0, 0};
+    int ab = 0;
+    Trace tr{(a.trace && blockIdx.x == 0 && lane == 0) ? a.trace : nullptr, 0};
+    for (long long tm = pair0; tm < tiles; tm += npairs) {
+      tr(1, (int)tm);
+      mbar_wait(&a_empty[ab], a_phase[ab] ^ 1);
+      tr(2, (int)tm);
+      if (elect_one()) {
+        if (leader) mbar_expect_tx(&a_full[ab], 2 * kblocks * kABytes);
+        for (int kb = 0; kb < kblocks; ++kb)
+          tma_load_2d_pair(a_res + ab * a_bytes + (size_t)kb * kABytes, &map_x, kb * kBlockK,
+                           (int)(tm * 2 * kPairRows + rank * kPairRows), &a_full[ab]);
+      }
+      __syncwarp();
+      a_phase[ab] ^= 1;
+      ab ^= 1;
+      for (int tn = 0; tn < ntiles_n; ++tn)
+        for (int kb = 0; kb <= kblocks; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          tr(3, tn * 16 + kb);
+          if (elect_one()) {
+            if (leader) mbar_expect_tx(&full[stage], 2 * kBBytes);
+            tma_load_2d_pair(b_stage + (size_t)stage * kBBytes, &map_c, kb * kBlockK,
+                             tn * kPairN + (int)rank * 128, &full[stage]);
+          }
+          __syncwarp();
+          if (++stage == (uint32_t)kStages) { stage = 0; phase ^= 1; }
+        }
+    }
+  } else if (warp == kMmaWarp) {
+    // ===== MMA issuer: the leader CTA only; commits are multicast to both CTAs =====
+    if (leader) {
+      const uint64_t a_desc0 = umma_desc(a_res, 0), aug_desc = umma_desc(a_aug, 0), b_desc0 = umma_desc(b_stage, 0);
+      uint32_t stage = 0, phase = 0, a_phase[2] = {0, 0}, t_phase[2] = {0, 0};
+      int buf = 0, ab = 0;
+      Trace tr{(a.trace && blockIdx.x == 0 && lane == 0) ? a.trace + 1024 : nullptr, 0};
+      for (long long tm = pair0; tm < tiles; tm += npairs) {
+        tr(1, (int)tm);
+        mbar_wait(&a_full[ab], a_phase[ab]);
+        tr(2, (int)tm);
+        a_phase[ab] ^= 1;
+        const uint64_t a_desc_tile = a_desc0 + (uint64_t)(ab * (a_bytes >> 4));
+        for (int tn = 0; tn < ntiles_n; ++tn) {
+          mbar_wait(&t_empty[buf], t_phase[buf] ^ 1);
+          tr(3, tn);
+          asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+          const uint32_t tacc = tmem_base + (uint32_t)(buf * kPairN);
+          for (int kb = 0; kb < kblocks; ++kb) {
+            mbar_wait(&full[stage], phase);
+            tr(4, tn * 16 + kb);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint64_t bd = b_desc0 + (uint64_t)(stage * (kBBytes >> 4));
+            const uint64_t ad = a_desc_tile + (uint64_t)(kb * (kABytes >> 4));
+            if (elect_one()) {
+#pragma unroll
+              for (int ks = 0; ks < kBlockK / kUmmaK; ++ks)
+                if (a.debug != 1) umma_tf32_pair(tacc, ad + 2 * ks, bd + 2 * ks, (kb | ks) != 0);
+              umma_commit_pair(&empty[stage]);
+            }
+            __syncwarp();
+            if (++stage == (uint32_t)kStages) { stage = 0; phase ^= 1; }
+          }
+          {
+            mbar_wait(&full[stage], phase);
+            asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+            const uint64_t bd = b_desc0 + (uint64_t)(stage * (kBBytes >> 4));
+            if (elect_one()) {
+              if (a.debug != 1) umma_tf32_pair(tacc, aug_desc, bd, 1);
+              umma_commit_pair(&empty[stage]);
+              umma_commit_pair(&t_full[buf]);
+            }
+            __syncwarp();
+            tr(5, tn);
+            if (++stage == (uint32_t)kStages) { stage = 0; phase ^= 1; }
+          }
+          t_phase[buf] ^= 1;
+          buf ^= 1;
+        }
+        if (elect_one()) umma_commit_pair(&a_empty[ab]);
+        __syncwarp();
+        ab ^= 1;
+      }
+    }
+  } else if (warp >= kFirstEpiWarp) {
+    // ===== epilogue: a thread owns one of my 128 points and 64 of each tile's 256 score columns =====
+    const int ew = warp - kFirstEpiWarp;
+    const int quarter = warp % 4;   // TMEM lanes 32*(warp % 4) .. +31
+    const int colgroup = ew / 4;    // columns [64*colgroup, +64)
+    const int row = quarter * 32 + lane;
+    const float cmax = __uint_as_float(*a.cmax_bits);
+    const uint32_t keymask = a.keymask;
+    uint32_t t_phase[2] = {0, 0};
+    int buf = 0, tile_parity = 0;  // tile_parity also names the A buffer of the tile
+    Trace tr{(a.trace && blockIdx.x == 0 && ew == 0 && lane == 0) ? a.trace + 2048 : nullptr, 0};
+    for (long long tm = pair0; tm < tiles; tm += npairs) {
+      tr(1, (int)tm);
+      Top2 even, odd;
+      int best_tile = 0;
+      float xn = 0.f;
+      for (int tn = 0; tn < ntiles_n; ++tn) {
+        tr(2, tn);
+        mbar_wait(&t_full[buf], t_phase[buf]);
+        tr(3, tn);
+        t_phase[buf] ^= 1;
+        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+        const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * kPairN + colgroup * 64);
+        uint32_t r0[32], r1[32];
+        if (a.debug == 2) {
+          for (int i = 0; i < 32; ++i) r0[i] = r1[i] = 0x7F000000u + (uint32_t)tn;
+        } else {
+          tmem_ld32_issue(taddr, r0);
+          tmem_ld32_issue(taddr + 32, r1);
+        }
+        const float before = fminf(even.best, odd.best);
+        if (tn == 0) {
+          // the first accumulator of a point tile exists, so the tile's rows have landed (only the
+          // leader's barrier saw the TMA): |x|^2 of my row from the swizzled tile, then let it go
+          if (colgroup == 0) {
+            for (int kb = 0; kb < kblocks; ++kb) {
+              const float4 *tile = reinterpret_cast<const float4 *>(a_res + tile_parity * a_bytes + (size_t)kb * kABytes);
+#pragma unroll
+              for (int ch = 0; ch < 8; ++ch) {
+                const float4 v = tile[row * 8 + (ch ^ (row % 8))];
+                xn += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+              }
+            }
+          }
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&a_empty[tile_parity]);
+        }
+        tmem_wait();
+        tr(4, tn);
+        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+        __syncwarp();
+        if (lane == 0) mbar_arrive_leader(&t_empty[buf]);  // the MMA issuer counts both CTAs' warps
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          even.push(r0[i], i, keymask);
+          odd.push(r0[i + 1], i + 1, keymask);
+        }
+#pragma unroll
+        for (int i = 0; i < 32; i += 2) {
+          even.push(r1[i], 32 + i, keymask);
+          odd.push(r1[i + 1], 32 + i + 1, keymask);
+        }
+        if (fminf(even.best, odd.best) < before) best_tile = tn;
+        buf ^= 1;
+      }
+      tr(5, (int)tm);
+      even.merge(odd);
+      // the four column groups of a row meet in shared memory (double-buffered by tile parity);
+      // group 0 decides the point
+      const int quad_bar = 1 + quarter;
+      float4 *const xb = xchg + (tile_parity ? 3 * kPairRows : 0);
+      tile_parity ^= 1;
+      if (colgroup != 0) xb[(colgroup - 1) * kPairRows + row] = make_float4(even.best, even.second, __int_as_float(best_tile), 0.f);
+      asm volatile("bar.sync %0, %1;" ::"r"(quad_bar), "r"(128) : "memory");
+      if (colgroup == 0) {
+        int win_group = 0;
+#pragma unroll
+        for (int g = 1; g < 4; ++g) {
+          const float4 o = xb[(g - 1) * kPairRows + row];
+          if (o.x < even.best) { best_tile = __float_as_int(o.z); win_group = g; }
+          Top2 other;
+          other.best = o.x; other.second = o.y;
+          even.merge(other);
+        }
+        const long long p = tm * 2 * kPairRows + (long long)rank * kPairRows + row;
+        if (p < a.n) {
+          const int bidx = best_tile * kPairN + win_group * 64 + (int)(__float_as_uint(even.best) & 0x3Fu);
+          const float xnorm = sqrtf(xn);
+          const float reach = xnorm + cmax;
+          const float thr = 0.0078125f * xnorm * cmax + ((float)a.d * 2.3841858e-07f + 6.1035156e-05f) * reach * reach;
+          a.assign[p] = bidx;
+          if (even.second - even.best > thr) {
+            if (!a.debug) atomicAdd(a.lcounts + bidx, 1u);
+          } else if (!a.debug) {
+            const unsigned int slot = atomicAdd(a.flag_count, 1u);
+            a.flag_list[slot] = (int32_t)p;
+          }
+        }
+      }
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+  __syncthreads();
+  cluster_sync_all();  // neither CTA frees tensor memory or exits while the other still uses it
+  if (warp == kAllocWarp) {
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "r"(kTmemCols));
+  }
+}
+
 // ---- K3: exact re-check of the flagged points, one warp per point ---------------------------------
 __global__ void recheck_kernel(const float *__restrict__ pts, int d, const float *__restrict__ cent, int k,
                                const int32_t *__restrict__ flag_list, const unsigned int *__restrict__ flag_count,
@@ -649,6 +963,10 @@ size_t tensor_smem_bytes(int d, int stages) {
   const int kblocks = d / kBlockK;
   return (size_t)2 * kblocks * kABytes + kABytes + (size_t)stages * kBBytes + 512 + 2 * kTileM * 16 + 1024;
 }
+size_t tensor_pair_smem_bytes(int d, int stages) {
+  const int kblocks = d / kBlockK;
+  return (size_t)2 * kblocks * kABytes + kABytes + (size_t)stages * kBBytes + 512 + 2 * 3 * kPairRows * 16 + 1024;
+}
 int tensor_stages(int d, size_t smem_optin) {
   int stages = kMaxStages;
   if (const char *v = getenv("HGM_TENSOR_STAGES")) stages = atoi(v);  // tuning knob
@@ -662,7 +980,7 @@ int tensor_stages(int d, size_t smem_optin) {
 bool tensor_shape_ok(int k, int d, size_t smem_optin) {
   return d % kBlockK == 0 && d >= kBlockK && d <= 128 && k >= 128 && tensor_smem_bytes(d, 2) <= smem_optin;
 }
-int tensor_k_pad(int k) { return (k + kTileN - 1) / kTileN * kTileN; }
+int tensor_k_pad(int k) { return (k + kPairN - 1) / kPairN * kPairN; }  // whole tiles of either kernel form
 size_t tensor_caug_floats(int k, int d) { return (size_t)tensor_k_pad(k) * (d + kBlockK); }
 
 cudaError_t launch_tensor_prep(const float *d_cent, int k, int d, float *d_caug, unsigned int *d_cmax_bits,
@@ -694,14 +1012,51 @@ cudaError_t launch_tensor_map(const float *d_pts, int64_t n, int d, const float 
   if (e != cudaSuccess) return e;
   e = cudaMemsetAsync(d_meta, 0, (size_t)k * 4, s);  // the launch's per-cluster counts
   if (e != cudaSuccess) return e;
-  const int stages = tensor_stages(d, smem_optin);
-  const size_t smem = tensor_smem_bytes(d, stages);  // includes 1 KiB of slack to align the base
-  e = cudaFuncSetAttribute(tensor_assign_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  // Which form: the pair kernel wins where a point tile carries enough MMA work to hide its fixed cost
+  // (d = 128, k = 4096: 14.4 vs 15.9 ms for 8 M points), the single-CTA kernel where tiles are short
+  // (d = 64, k = 1024: 14.9 vs 17.2 ms for 40 M).  HGM_TENSOR_FORM=single|pair overrides (comparison runs).
+  const char *form = getenv("HGM_TENSOR_FORM");
+  const bool pair = sm_count >= 2 && (form ? form[0] == 'p' : d >= 96);
+  int stages = tensor_stages(d, smem_optin);
+  if (pair) {
+    stages = kMaxStages;
+    while (stages > 2 && tensor_pair_smem_bytes(d, stages) > smem_optin) --stages;
+  }
+  const size_t smem = pair ? tensor_pair_smem_bytes(d, stages) : tensor_smem_bytes(d, stages);  // incl. 1 KiB to align the base
+  e = pair ? cudaFuncSetAttribute(tensor_assign_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
+           : cudaFuncSetAttribute(tensor_assign_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  TensorArgs a{(long long)n, k, k_pad, d, stages, ~0x3Fu, getenv("HGM_TENSOR_DEBUG") ? atoi(getenv("HGM_TENSOR_DEBUG")) : 0, d_cmax_bits, d_pts, d_meta, d_assign, d_flag_list, d_flag_count};
-  const long long tiles = (n + kTileM - 1) / kTileM;
-  const int grid = (int)(tiles < sm_count ? tiles : sm_count);
-  tensor_assign_kernel<<<grid, kThreads, smem, s>>>(map_x, map_c, a);
+  TensorArgs a{(long long)n, k, k_pad, d, stages, ~0x3Fu, nullptr, getenv("HGM_TENSOR_DEBUG") ? atoi(getenv("HGM_TENSOR_DEBUG")) : 0, d_cmax_bits, d_pts, d_meta, d_assign, d_flag_list, d_flag_count};
+  const long long tiles = (n + kTileM - 1) / kTileM;  // 256 points: one CTA's tile, or one pair's
+  if (pair) {
+    const long long pairs = tiles < sm_count / 2 ? tiles : sm_count / 2;
+    const char *trace_path = getenv("HGM_TENSOR_TRACE");  // experiments: event log of CTA 0, written after a sync
+    if (trace_path) {
+      long long *d_trace = nullptr;
+      if (cudaMalloc(&d_trace, 3 * 1024 * 8) == cudaSuccess) {
+        cudaMemsetAsync(d_trace, 0, 3 * 1024 * 8, s);
+        a.trace = d_trace;
+        tensor_assign_pair_kernel<<<(int)(2 * pairs), kThreads, smem, s>>>(map_x, map_c, a);
+        cudaStreamSynchronize(s);
+        static long long h_trace[3 * 1024];
+        cudaMemcpy(h_trace, d_trace, sizeof h_trace, cudaMemcpyDeviceToHost);
+        cudaFree(d_trace);
+        if (FILE *f = fopen(trace_path, "w")) {
+          for (int role = 0; role < 3; ++role)
+            for (int i = 0; i < 512 && h_trace[role * 1024 + 2 * i + 1]; ++i)
+              fprintf(f, "%d %lld %lld %lld\n", role, h_trace[role * 1024 + 2 * i] >> 32,
+                      h_trace[role * 1024 + 2 * i] & 0xffffffffll, h_trace[role * 1024 + 2 * i + 1]);
+          fclose(f);
+        }
+        a.trace = nullptr;
+      }
+    } else {
+      tensor_assign_pair_kernel<<<(int)(2 * pairs), kThreads, smem, s>>>(map_x, map_c, a);
+    }
+  } else {
+    const int grid = (int)(tiles < sm_count ? tiles : sm_count);
+    tensor_assign_kernel<<<grid, kThreads, smem, s>>>(map_x, map_c, a);
+  }
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
   if (a.debug) return cudaSuccess;  // experiments time K2 alone; its output is meaningless then
   recheck_kernel<<<sm_count * 4, 256, 0, s>>>(d_pts, d, d_cent, k, d_flag_list, d_flag_count, d_assign, d_meta);

@@ -247,17 +247,22 @@ def test_idempotent_and_centroid_update_roundtrip(slot, oracle):
 
 @pytest.mark.parametrize("d,k,n", [(32, 128, 5000), (64, 1024, 20011), (128, 512, 6001), (96, 300, 4097),
                                    (64, 129, 255), (64, 256, 256), (64, 256, 1)])
-def test_tensor_path_matches_oracle(slot, oracle, d, k, n):
+@pytest.mark.parametrize("form", ["single", "pair"])
+def test_tensor_path_matches_oracle(slot, oracle, monkeypatch, form, d, k, n):
     """BASELINE config 4/5 shapes at test size: assignments bit-exact through the TF32 GEMM +
-    FP32 re-check, counts exact, sums within tolerance."""
+    FP32 re-check, counts exact, sums within tolerance -- in both forms of K2 (one CTA per tile,
+    and the cta_group::2 pair; the library picks by shape, HGM_TENSOR_FORM forces one)."""
+    monkeypatch.setenv("HGM_TENSOR_FORM", form)
     pts, cent = cases.general_d(n, d, k, seed=d + k)
     run_case(slot, oracle, pts, cent, capi.KERNEL_TENSOR)
 
 
-def test_tensor_path_decides_almost_everything_on_the_tensor_cores(slot, oracle):
+@pytest.mark.parametrize("form", ["single", "pair"])
+def test_tensor_path_decides_almost_everything_on_the_tensor_cores(slot, oracle, monkeypatch, form):
     """If the GEMM scores were wrong every point would be flagged and the exact re-check would
     hide it: on well-separated data the re-check must stay rare, on duplicated centroids it
     must take (at least) the points of the duplicated clusters."""
+    monkeypatch.setenv("HGM_TENSOR_FORM", form)
     pts, cent = cases.general_d(50000, 64, 1024, seed=77)
     slot.set_kernel(capi.KERNEL_TENSOR)
     slot.set_centroids(cent)
