@@ -48,8 +48,9 @@ def parse_args():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--points", type=int, default=200_000_000, help="points per GPU (configs[1])")
-    ap.add_argument("--k", type=int, default=128)
-    ap.add_argument("--d", type=int, default=2)
+    ap.add_argument("--k", "--clusters", dest="k", type=int, default=128)
+    ap.add_argument("--d", "--dims", dest="d", type=int, default=2,
+                    help="(under torchrun spell it --dims: its own parser takes a bare --d as an abbreviation)")
     ap.add_argument("--cpu-points", type=int, default=1 << 19, help="points per CPU process in the baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
