@@ -11,6 +11,7 @@
 #include <stdlib.h>
 
 #include <algorithm>
+#include <string>
 #include <unordered_map>
 #include <vector>
 
@@ -884,6 +885,248 @@ static int cache_store_text(hgm_ctx *c, int64_t split_id, SplitSource &src) {
   return cleanup(HGM_OK);
 }
 
+// ---- SequenceFile splits: header and sync search on the host, record walk on the device ------
+
+struct SeqHeader {
+  int64_t header_end = 0;  // position of the first record
+  SeqSync sync{};
+};
+
+// WritableUtils.readVInt (same coding as c++/utils/impl/SerialUtils.cc:217-244)
+static bool seq_read_vint(const unsigned char *&p, const unsigned char *end, int64_t *out) {
+  if (p >= end) return false;
+  const int8_t first = (int8_t)*p++;
+  if (first >= -112) { *out = first; return true; }
+  const bool negative = first < -120;
+  const int len = negative ? -(first + 120) : -(first + 112);
+  if (p + len > end) return false;
+  int64_t v = 0;
+  for (int i = 0; i < len; ++i) v = (v << 8) | *p++;
+  *out = negative ? ~v : v;
+  return true;
+}
+static bool seq_read_text(const unsigned char *&p, const unsigned char *end, std::string *out) {
+  int64_t len = 0;
+  if (!seq_read_vint(p, end, &len) || len < 0 || p + len > end) return false;
+  if (out) out->assign(reinterpret_cast<const char *>(p), (size_t)len);
+  p += len;
+  return true;
+}
+
+// SequenceFile.Reader.init (core/org/apache/hadoop/io/SequenceFile.java:1506-1571): version 6,
+// Text class names, the two compression flags, metadata, 16 sync bytes.
+static int seq_read_header(hgm_ctx *c, FILE *f, SeqHeader *h) {
+  std::vector<unsigned char> buf(64 * 1024);
+  fseeko(f, 0, SEEK_SET);
+  const size_t got = fread(buf.data(), 1, buf.size(), f);
+  const unsigned char *p = buf.data(), *end = p + got;
+  if (got < 4 || p[0] != 'S' || p[1] != 'E' || p[2] != 'Q') return fail(c, HGM_EFORMAT, "not a SequenceFile");
+  if (p[3] != 6) return fail(c, HGM_EFORMAT, "SequenceFile version %d is not supported (6 is)", (int)p[3]);
+  p += 4;
+  std::string key_class, val_class;
+  if (!seq_read_text(p, end, &key_class) || !seq_read_text(p, end, &val_class))
+    return fail(c, HGM_EFORMAT, "SequenceFile header is truncated");
+  if (val_class != "org.apache.hadoop.io.BytesWritable")
+    return fail(c, HGM_EFORMAT, "SequenceFile values are %s; rows must be BytesWritable", val_class.c_str());
+  if (p + 2 > end) return fail(c, HGM_EFORMAT, "SequenceFile header is truncated");
+  if (p[0] != 0 || p[1] != 0) return fail(c, HGM_EFORMAT, "compressed SequenceFiles are not supported");
+  p += 2;
+  if (p + 4 > end) return fail(c, HGM_EFORMAT, "SequenceFile header is truncated");
+  const int64_t meta = ((int64_t)p[0] << 24) | (p[1] << 16) | (p[2] << 8) | p[3];
+  p += 4;
+  for (int64_t i = 0; i < 2 * meta; ++i)
+    if (!seq_read_text(p, end, nullptr)) return fail(c, HGM_EFORMAT, "SequenceFile metadata is truncated or over 64 KiB");
+  if (p + 16 > end) return fail(c, HGM_EFORMAT, "SequenceFile header is truncated");
+  memcpy(h->sync.marker, p, 16);
+  h->header_end = (int64_t)(p + 16 - buf.data());
+  return HGM_OK;
+}
+
+// SequenceFile.Reader.sync(position) (SequenceFile.java:2221-2246): the first sync entry whose
+// escape starts at or after position, the end of the file if there is none.
+static int64_t seq_sync_at_or_after(FILE *f, int64_t size, const SeqHeader &h, int64_t position) {
+  if (position + 20 >= size) return size;
+  std::vector<unsigned char> buf(256 * 1024 + 16);
+  int64_t at = position + 4;  // where a marker may start
+  size_t keep = 0;
+  fseeko(f, (off_t)at, SEEK_SET);
+  for (;;) {
+    const size_t got = fread(buf.data() + keep, 1, buf.size() - keep, f);
+    const size_t have = keep + got;
+    if (have < 16) return size;
+    for (size_t i = 0; i + 16 <= have; ++i)
+      if (buf[i] == h.sync.marker[0] && memcmp(buf.data() + i, h.sync.marker, 16) == 0) return at + (int64_t)i - 4;
+    if (got == 0) return size;
+    keep = 15;  // a marker may straddle the buffers
+    memmove(buf.data(), buf.data() + have - keep, keep);
+    at += (int64_t)(have - keep);
+  }
+}
+
+// Byte range of the records SequenceFileRecordReader delivers for FileSplit(off, len)
+// (mapred/org/apache/hadoop/mapred/SequenceFileRecordReader.java:40-52, 71-84): from the first sync
+// entry at or after off (the header's end for the split that contains it) up to the first sync
+// entry at or after off + len.
+static int seq_split_bounds(hgm_ctx *c, FILE *f, int64_t off, int64_t len, SeqHeader *h, int64_t *start, int64_t *stop) {
+  const int rc = seq_read_header(c, f, h);
+  if (rc != HGM_OK) return rc;
+  fseeko(f, 0, SEEK_END);
+  const int64_t size = (int64_t)ftello(f);
+  int64_t end = len < 0 ? size : off + len;
+  if (end > size) end = size;
+  *start = off > h->header_end ? seq_sync_at_or_after(f, size, *h, off) : h->header_end;
+  *stop = end > h->header_end ? seq_sync_at_or_after(f, size, *h, end) : h->header_end;
+  if (*start >= end) *stop = *start;  // "more = start < end"
+  if (*stop < *start) *stop = *start;
+  return HGM_OK;
+}
+
+// Stage the byte range, walk it on the device, leave the rows in *d_rows (an arena slot when block_out is
+// given, else a cudaMalloc the caller frees).  *n_floats <- floats decoded.
+static int decode_seq(hgm_ctx *c, FILE *f, int64_t start, int64_t stop, const SeqHeader &h, bool big_endian,
+                      float **d_rows, int64_t *n_floats, int *block_out) {
+  const size_t nbytes = (size_t)(stop - start);
+  *d_rows = nullptr;
+  *n_floats = 0;
+  if (nbytes >= (size_t(1) << 33)) return fail(c, HGM_EINVAL, "a SequenceFile split must be smaller than 8 GiB");
+  int rc = ensure_pipeline(c, false, 1, true);
+  if (rc != HGM_OK) return rc;
+  CU(c, cudaStreamSynchronize(c->stream));
+  unsigned char *d_bytes = nullptr;
+  unsigned int *d_blocks = nullptr, *d_seg = nullptr;
+  long long *d_pos = nullptr;
+  TextStats *d_stats = nullptr;
+  TextStats st = {0ull, ~0ull};
+  int block = -1;
+  auto cleanup = [&](int code) {
+    cudaFree(d_bytes); cudaFree(d_blocks); cudaFree(d_seg); cudaFree(d_pos); cudaFree(d_stats);
+    if (code != HGM_OK && *d_rows) {
+      if (block >= 0) arena_release(c, block); else cudaFree(*d_rows);
+      *d_rows = nullptr;
+    }
+    return code;
+  };
+  auto no_room = [&](cudaError_t e) {
+    cudaGetLastError();
+    return cleanup(fail(c, HGM_ENOMEM, "SequenceFile split of %zu bytes does not fit the device: %s", nbytes,
+                        cudaGetErrorString(e)));
+  };
+  cudaError_t e = cudaMalloc(&d_bytes, nbytes + 32);
+  if (e == cudaSuccess) e = cudaMalloc(&d_blocks, (seq_block_count(nbytes) + 1) * sizeof(unsigned int));
+  if (e == cudaSuccess) e = cudaMalloc(&d_pos, (nbytes / 20 + 2) * sizeof(long long));
+  if (e == cudaSuccess) e = cudaMalloc(&d_stats, sizeof(TextStats));
+  if (e != cudaSuccess) return no_room(e);
+  if (fseeko(f, (off_t)start, SEEK_SET) != 0) return cleanup(fail(c, HGM_EIO, "cannot seek to %lld", (long long)start));
+  size_t off = 0;
+  int bi = 0;
+  while (off < nbytes) {
+    const size_t piece = std::min(kBounceBytes, nbytes - off);
+    if (cudaEventSynchronize(c->ev_bounce[bi]) != cudaSuccess) cudaGetLastError();
+    if (fread(c->h_bounce[bi], 1, piece, f) != piece)
+      return cleanup(fail(c, HGM_EIO, "short read from split file: %s", strerror(errno)));
+    e = cudaMemcpyAsync(d_bytes + off, c->h_bounce[bi], piece, cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) e = cudaEventRecord(c->ev_bounce[bi], c->stream);
+    if (e != cudaSuccess) return cleanup(fail(c, HGM_ECUDA, "split copy: %s", cudaGetErrorString(e)));
+    bi = (bi + 1) % kStages;
+    off += piece;
+  }
+  auto fetch = [&]() {
+    cudaError_t er = cudaMemcpyAsync(&st, d_stats, sizeof st, cudaMemcpyDeviceToHost, c->stream);
+    if (er == cudaSuccess) er = cudaStreamSynchronize(c->stream);
+    return er;
+  };
+  e = launch_seq_find_syncs(d_bytes, nbytes, h.sync, d_blocks, d_pos, d_stats, c->stream);
+  if (e == cudaSuccess) e = fetch();
+  if (e != cudaSuccess) return cleanup(fail(c, HGM_ECUDA, "SequenceFile sync search: %s", cudaGetErrorString(e)));
+  const long long n_sync = (long long)st.n_fields;
+  c->total_launches += 3;
+  e = cudaMalloc(&d_seg, (size_t)(n_sync + 2) * sizeof(unsigned int));
+  if (e != cudaSuccess) return no_room(e);
+  e = launch_seq_walk(d_bytes, nbytes, d_pos, n_sync, c->d, big_endian, d_seg, nullptr, 0, d_stats, 0, c->sm_count, c->stream);
+  if (e == cudaSuccess) e = fetch();
+  if (e != cudaSuccess) return cleanup(fail(c, HGM_ECUDA, "SequenceFile record walk: %s", cudaGetErrorString(e)));
+  c->total_launches += 2;
+  if (st.first_error != ~0ull) {
+    const long long pos = (long long)(st.first_error >> 4) + start;
+    return cleanup(fail(c, HGM_EFORMAT, (st.first_error & 15u) == HGM_TEXT_RAGGED
+                            ? "SequenceFile split: the record at byte %lld does not hold whole rows of d=%d float32"
+                            : "SequenceFile split: the record at byte %lld is malformed (d=%d)", pos, c->d));
+  }
+  const size_t floats = (size_t)st.n_fields;
+  if (block_out) {
+    *d_rows = static_cast<float *>(arena_alloc(c, floats * 4, &block, &e));
+    if (!*d_rows) return no_room(e);
+  } else {
+    e = cudaMalloc(d_rows, floats ? floats * 4 : 16);
+    if (e != cudaSuccess) { *d_rows = nullptr; return no_room(e); }
+  }
+  if (floats) {
+    e = launch_seq_walk(d_bytes, nbytes, d_pos, n_sync, c->d, big_endian, d_seg, *d_rows, floats, d_stats, 1, c->sm_count, c->stream);
+    if (e == cudaSuccess) e = fetch();
+    if (e != cudaSuccess) return cleanup(fail(c, HGM_ECUDA, "SequenceFile record copy: %s", cudaGetErrorString(e)));
+    c->total_launches += 1;
+    if (st.first_error != ~0ull) return cleanup(fail(c, HGM_ECUDA, "SequenceFile record copy ran out of room"));
+  }
+  *n_floats = (int64_t)floats;
+  if (block_out) *block_out = block;
+  return cleanup(HGM_OK);
+}
+
+static int map_seq_file(hgm_ctx *c, const char *path, int64_t offset, int64_t length, bool big_endian, double *sums,
+                        int64_t *counts, int32_t *assign, int64_t *n_points_out) {
+  if (!c->d_partials) return fail(c, HGM_EINVAL, "hgm_set_centroids has not been called");
+  if (!sums || !counts) return fail(c, HGM_EINVAL, "sums_kxd and counts_k are required");
+  if (assign) return fail(c, HGM_EINVAL, "assignments of a SequenceFile split are not returned (cache it instead)");
+  if (!path || offset < 0) return fail(c, HGM_EINVAL, "bad path or offset");
+  FILE *f = fopen(path, "rb");
+  if (!f) return fail(c, HGM_EIO, "cannot open %s: %s", path, strerror(errno));
+  SeqHeader h;
+  int64_t start = 0, stop = 0, n_floats = 0;
+  float *d_rows = nullptr;
+  int rc = seq_split_bounds(c, f, offset, length, &h, &start, &stop);
+  if (rc == HGM_OK) rc = decode_seq(c, f, start, stop, h, big_endian, &d_rows, &n_floats, nullptr);
+  fclose(f);
+  if (rc != HGM_OK) return rc;
+  const int64_t n = n_floats / c->d;
+  if (n_points_out) *n_points_out = n;
+  c->last_launches = 0;
+  cudaError_t e = cudaMemsetAsync(c->d_partials, 0, partial_bytes(c), c->stream);
+  if (e == cudaSuccess) e = cudaEventRecord(c->ev_t0, c->stream);
+  if (e == cudaSuccess) rc = map_points_async(c, d_rows, n, nullptr);
+  if (e == cudaSuccess && rc == HGM_OK) {
+    e = cudaEventRecord(c->ev_t1, c->stream);
+    c->timing_open = true;
+    if (e == cudaSuccess) e = cudaMemcpyAsync(sums, sums_ptr(c), (size_t)c->k * c->d * 8, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(counts, counts_ptr(c), (size_t)c->k * 8, cudaMemcpyDeviceToHost, c->stream);
+  }
+  const cudaError_t es = cudaStreamSynchronize(c->stream);
+  cudaFree(d_rows);
+  if (rc != HGM_OK) return rc;
+  if (e != cudaSuccess || es != cudaSuccess)
+    return fail(c, HGM_ECUDA, "SequenceFile map: %s", cudaGetErrorString(e != cudaSuccess ? e : es));
+  return HGM_OK;
+}
+
+static int cache_seq_file(hgm_ctx *c, int64_t split_id, const char *path, int64_t offset, int64_t length, bool big_endian) {
+  if (!c->d_partials) return fail(c, HGM_EINVAL, "hgm_set_centroids has not been called (d is unknown)");
+  if (split_id < 0) return fail(c, HGM_EINVAL, "split_id must be >= 0");
+  if (!path || offset < 0) return fail(c, HGM_EINVAL, "bad path or offset");
+  FILE *f = fopen(path, "rb");
+  if (!f) return fail(c, HGM_EIO, "cannot open %s: %s", path, strerror(errno));
+  SeqHeader h;
+  int64_t start = 0, stop = 0, n_floats = 0;
+  float *d_rows = nullptr;
+  int block = -1;
+  CU(c, cudaStreamSynchronize(c->stream));
+  cache_erase(c, split_id);
+  int rc = seq_split_bounds(c, f, offset, length, &h, &start, &stop);
+  if (rc == HGM_OK) rc = decode_seq(c, f, start, stop, h, big_endian, &d_rows, &n_floats, &block);
+  fclose(f);
+  if (rc != HGM_OK) return rc;
+  c->cache[split_id] = hgm_ctx::CachedSplit{d_rows, n_floats / c->d, (size_t)n_floats * 4, block};
+  return HGM_OK;
+}
+
 // Opens path and frames the split: exact bytes for binary rows, LineRecordReader's rule for text.
 static int open_split_file(hgm_ctx *c, const char *path, int64_t offset, int64_t length, int32_t fmt, SplitSource *src) {
   if (!path || offset < 0) return fail(c, HGM_EINVAL, "bad path or offset");
@@ -918,12 +1161,16 @@ int hgm_map_split(hgm_ctx *c, const void *host_bytes, size_t nbytes, int32_t fmt
   src.nbytes = nbytes;
   src.pinned = nbytes > 0 && is_pinned(host_bytes);
   if (fmt == HGM_FMT_TEXT) return map_text_stream(c, src, sums, counts, assign, n_points_out);
+  if (fmt == HGM_FMT_SEQ_F32BE || fmt == HGM_FMT_SEQ_F32LE)
+    return fail(c, HGM_EFORMAT, "SequenceFile splits are read from the file (its header holds the sync marker): use hgm_map_file");
   return map_stream(c, src, fmt, sums, counts, assign, n_points_out);
 }
 
 int hgm_map_file(hgm_ctx *c, const char *path, int64_t offset, int64_t length, int32_t fmt,
                  double *sums, int64_t *counts, int32_t *assign, int64_t *n_points_out) {
   NEED_CTX(c);
+  if (fmt == HGM_FMT_SEQ_F32BE || fmt == HGM_FMT_SEQ_F32LE)
+    return map_seq_file(c, path, offset, length, fmt == HGM_FMT_SEQ_F32BE, sums, counts, assign, n_points_out);
   SplitSource src;
   int rc = open_split_file(c, path, offset, length, fmt, &src);
   if (rc != HGM_OK) return rc;
@@ -997,11 +1244,15 @@ int hgm_cache_put(hgm_ctx *c, int64_t split_id, const void *host_bytes, size_t n
   src.mem = static_cast<const unsigned char *>(host_bytes);
   src.nbytes = nbytes;
   if (fmt == HGM_FMT_TEXT) return cache_store_text(c, split_id, src);
+  if (fmt == HGM_FMT_SEQ_F32BE || fmt == HGM_FMT_SEQ_F32LE)
+    return fail(c, HGM_EFORMAT, "SequenceFile splits are read from the file (its header holds the sync marker): use hgm_cache_put_file");
   return cache_store(c, split_id, src, fmt);
 }
 
 int hgm_cache_put_file(hgm_ctx *c, int64_t split_id, const char *path, int64_t offset, int64_t length, int32_t fmt) {
   NEED_CTX(c);
+  if (fmt == HGM_FMT_SEQ_F32BE || fmt == HGM_FMT_SEQ_F32LE)
+    return cache_seq_file(c, split_id, path, offset, length, fmt == HGM_FMT_SEQ_F32BE);
   SplitSource src;
   int rc = open_split_file(c, path, offset, length, fmt, &src);
   if (rc != HGM_OK) return rc;

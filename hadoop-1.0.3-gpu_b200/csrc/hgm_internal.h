@@ -74,6 +74,15 @@ size_t text_block_count(size_t nbytes);
 cudaError_t launch_text_decode(const unsigned char *d_text, size_t nbytes, int d, float *d_out, size_t out_cap,
                                unsigned int *d_block_counts, TextStats *d_stats, cudaStream_t s);
 
+// SequenceFile decode (kernels_seq.cu)
+struct SeqSync { unsigned char marker[16]; };
+size_t seq_block_count(size_t nbytes);
+cudaError_t launch_seq_find_syncs(const unsigned char *d_bytes, size_t nbytes, const SeqSync &sync, unsigned int *d_blocks,
+                                  long long *d_positions, TextStats *d_stats, cudaStream_t s);
+cudaError_t launch_seq_walk(const unsigned char *d_bytes, size_t nbytes, const long long *d_positions, long long n_sync,
+                            int d, int big_endian, unsigned int *d_seg, float *d_out, size_t out_cap, TextStats *d_stats,
+                            int pass, int sm_count, cudaStream_t s);
+
 cudaError_t launch_bswap32(uint32_t *d_words, int64_t n_words, cudaStream_t s);
 
 cudaError_t launch_synth_points(uint64_t seed, int64_t first, int64_t n, int d, int k,

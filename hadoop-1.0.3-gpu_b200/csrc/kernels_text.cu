@@ -175,6 +175,12 @@ __global__ void __launch_bounds__(kTextThreads) text_parse_kernel(const unsigned
 
 }  // namespace
 
+// in place: values[i] <- sum of values[0..i), stats->n_fields <- total (also used by kernels_seq.cu)
+cudaError_t launch_u32_scan(unsigned int *d_values, long long n, TextStats *d_stats, cudaStream_t s) {
+  text_scan_kernel<<<1, 1024, 0, s>>>(d_values, n, d_stats);
+  return cudaGetLastError();
+}
+
 size_t text_block_count(size_t nbytes) { return (nbytes + kTextBlockBytes - 1) / kTextBlockBytes; }
 
 cudaError_t launch_text_decode(const unsigned char *d_text, size_t nbytes, int d, float *d_out, size_t out_cap,

@@ -24,7 +24,8 @@
 //       NLineInputFormat config, conf/mapred-site.xml:13-22);
 //   C++ reader (=false): the FileSplit (mapred/FileSplit.java:81-85) is handed to
 //       hgm_map_file and read straight into pinned memory -- no per-record traffic at all
-//       (text: framed like LineRecordReader, mapred/LineRecordReader.java:79-95).
+//       (text: framed like LineRecordReader, mapred/LineRecordReader.java:79-95; sequencefile: like
+//       SequenceFileRecordReader, records walked on the device between sync entries).
 // There is no CPU fallback: any hgm_* failure throws HadoopUtils::Error and the task fails.
 #include <stdint.h>
 #include <stdio.h>
@@ -101,8 +102,10 @@ std::string stripScheme(const std::string &uri) {  // "file:/x" -> "/x"
 static int formatCode(const std::string &f) {
   if (f == "binary") return HGM_FMT_F32LE;
   if (f == "binary-be") return HGM_FMT_F32BE;
-  HADOOP_ASSERT(f == "text", "record format " + f + " is not one of binary, binary-be, text");
-  return HGM_FMT_TEXT;
+  if (f == "text") return HGM_FMT_TEXT;
+  if (f == "sequencefile") return HGM_FMT_SEQ_F32BE;     // BytesWritable rows as DataOutput.writeFloat wrote them
+  HADOOP_ASSERT(f == "sequencefile-le", "record format " + f + " is not one of binary, binary-be, text, sequencefile, sequencefile-le");
+  return HGM_FMT_SEQ_F32LE;
 }
 
 class KMeansGpuMap : public HadoopPipes::Mapper {
@@ -165,6 +168,10 @@ class KMeansGpuMap : public HadoopPipes::Mapper {
     }
     if (conf->hasKey("hadoop.pipes.java.recordreader") && !conf->getBoolean("hadoop.pipes.java.recordreader"))
       format_ = SPLIT;
+    // a SequenceFile is decoded from the file (the sync marker is in its header); piped through Java's
+    // SequenceFileRecordReader its BytesWritable values arrive as plain bytes: that is "binary-be"
+    HADOOP_ASSERT(format_ != BINARY || (fmt_code_ != HGM_FMT_SEQ_F32BE && fmt_code_ != HGM_FMT_SEQ_F32LE),
+                  "sequencefile input needs hadoop.pipes.java.recordreader=false or kmeans.input.format=path");
     if (conf->hasKey("kmeans.gpu.device")) g_device = conf->getInt("kmeans.gpu.device");
 
     const std::string &cpath = conf->get("kmeans.centroids");

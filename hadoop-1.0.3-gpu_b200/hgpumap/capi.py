@@ -17,7 +17,7 @@ import os
 
 import numpy as np
 
-FMT_F32LE, FMT_F32BE, FMT_TEXT = 0, 1, 2
+FMT_F32LE, FMT_F32BE, FMT_TEXT, FMT_SEQ_F32BE, FMT_SEQ_F32LE = 0, 1, 2, 3, 4
 KERNEL_AUTO, KERNEL_EXACT, KERNEL_GRID2D, KERNEL_TENSOR = 0, 1, 2, 3
 
 _PKG_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))

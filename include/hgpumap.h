@@ -55,6 +55,15 @@ typedef struct hgm_ctx hgm_ctx;
                         /* LineRecordReader.java:79-95,137-157): the first line belongs to  */
                         /* the previous split unless offset == 0, the last one is read to   */
                         /* its end.  Assignments are not returned for text (pass NULL).     */
+#define HGM_FMT_SEQ_F32BE 3 /* an uncompressed version-6 SequenceFile (core/org/apache/hadoop/io/  */
+#define HGM_FMT_SEQ_F32LE 4 /* SequenceFile.java) whose values are BytesWritable holding whole rows  */
+                            /* of d float32, big-endian (DataOutput.writeFloat) or little-endian;    */
+                            /* keys are skipped.  File entry points only (hgm_map_file,              */
+                            /* hgm_cache_put_file): (offset, length) is framed the way               */
+                            /* SequenceFileRecordReader does (mapred/SequenceFileRecordReader.java:  */
+                            /* 40-52, 71-84): from the first sync entry at or after offset to the    */
+                            /* first one at or after offset+length; records are walked on the device */
+                            /* in parallel between sync entries.  Compressed files: HGM_EFORMAT.     */
 
 /* Kernel families (hgm_set_kernel); AUTO picks by shape. */
 #define HGM_KERNEL_AUTO 0

@@ -210,6 +210,119 @@ int64_t hgo_text_split_decode(const char *file, int64_t size, int64_t off, int64
   return total;
 }
 
+/* ---- section 8(f)3: SequenceFile framing -------------------------------------
+ * An uncompressed version-6 SequenceFile of BytesWritable values held in memory,
+ * read the way SequenceFileRecordReader reads FileSplit(off, len)
+ * (mapred/org/apache/hadoop/mapred/SequenceFileRecordReader.java:40-52 constructor,
+ * :71-84 next) on top of SequenceFile.Reader (core/org/apache/hadoop/io/
+ * SequenceFile.java: init :1506-1571, readRecordLength :1949-1969, sync :2221-2246).
+ * No SequenceFile fixture exists in the reference tree, so this restatement is
+ * pinned by the source only; tests/seqfile.py writes files the way
+ * SequenceFile.Writer does (:985-990 sync, :1025-1030 checkAndWriteSync, append). */
+
+static int64_t hgo_be32(const unsigned char *p) {
+  return (int32_t)(((uint32_t)p[0] << 24) | ((uint32_t)p[1] << 16) | ((uint32_t)p[2] << 8) | p[3]);
+}
+
+/* Text.readString: vint length + bytes. Returns bytes consumed or -1. */
+static int64_t hgo_skip_text(const unsigned char *p, int64_t avail, char *copy, int64_t copy_cap) {
+  int64_t len = 0;
+  int32_t used = hgo_vint_decode(p, avail, &len);
+  if (used <= 0 || len < 0 || used + len > avail) return -1;
+  if (copy) {
+    int64_t m = len < copy_cap - 1 ? len : copy_cap - 1;
+    memcpy(copy, p + used, (size_t)m);
+    copy[m] = 0;
+  }
+  return used + len;
+}
+
+/* Parses the header; returns its length (position of the first record) or -1 if the
+ * file is not an uncompressed v6 SequenceFile of BytesWritable values. sync16 <- marker. */
+int64_t hgo_seq_header(const unsigned char *file, int64_t size, unsigned char *sync16) {
+  char cls[128];
+  int64_t pos = 4, n;
+  if (size < 4 || file[0] != 'S' || file[1] != 'E' || file[2] != 'Q' || file[3] != 6) return -1;
+  if ((n = hgo_skip_text(file + pos, size - pos, NULL, 0)) < 0) return -1;       /* key class */
+  pos += n;
+  if ((n = hgo_skip_text(file + pos, size - pos, cls, sizeof cls)) < 0) return -1; /* value class */
+  pos += n;
+  if (strcmp(cls, "org.apache.hadoop.io.BytesWritable") != 0) return -1;
+  if (pos + 2 > size || file[pos] != 0 || file[pos + 1] != 0) return -1;          /* compressed / block-compressed */
+  pos += 2;
+  if (pos + 4 > size) return -1;
+  int64_t meta = hgo_be32(file + pos);
+  pos += 4;
+  for (int64_t i = 0; i < 2 * meta; ++i) {
+    if ((n = hgo_skip_text(file + pos, size - pos, NULL, 0)) < 0) return -1;
+    pos += n;
+  }
+  if (pos + 16 > size) return -1;
+  memcpy(sync16, file + pos, 16);
+  return pos + 16;
+}
+
+/* SequenceFile.Reader.sync(position): the position of the first sync entry (escape + marker)
+ * that starts at or after position; the end of the file if there is none. */
+static int64_t hgo_seq_sync(const unsigned char *file, int64_t size, const unsigned char *sync16, int64_t position) {
+  if (position + 20 >= size) return size;
+  for (int64_t h = position + 4; h + 16 <= size; ++h)
+    if (memcmp(file + h, sync16, 16) == 0) return h - 4;
+  return size;
+}
+
+/* Decodes the BytesWritable values of FileSplit(off, len) as rows of d float32 (big-endian
+ * if be != 0). Returns the number of floats, -1 - (record index) on a malformed record,
+ * INT64_MIN if the header is not acceptable or out is too small. */
+int64_t hgo_seq_split_decode(const unsigned char *file, int64_t size, int64_t off, int64_t len, int32_t d,
+                             int32_t be, float *out, int64_t cap, int64_t *n_records) {
+  unsigned char sync16[16];
+  int64_t pos = hgo_seq_header(file, size, sync16);
+  int64_t end = off + len, total = 0, rec = 0;
+  if (pos < 0) return INT64_MIN;
+  if (off > pos) pos = hgo_seq_sync(file, size, sync16, off);
+  int more = pos < end;
+  while (more) {
+    int64_t before = pos;
+    int sync_seen = 0;
+    if (pos >= size) break;                       /* readRecordLength: -1 at end of file */
+    if (pos + 4 > size) return -1 - rec;
+    int64_t length = hgo_be32(file + pos);
+    pos += 4;
+    if (length == -1) {
+      if (pos + 16 > size || memcmp(file + pos, sync16, 16) != 0) return -1 - rec; /* "File is corrupt!" */
+      pos += 16;
+      sync_seen = 1;
+      if (pos >= size) break;
+      if (pos + 4 > size) return -1 - rec;
+      length = hgo_be32(file + pos);
+      pos += 4;
+    }
+    if (before >= end && sync_seen) break;        /* the record belongs to the next split */
+    if (pos + 4 > size) return -1 - rec;
+    int64_t key_len = hgo_be32(file + pos);
+    pos += 4;
+    if (length < 0 || key_len < 0 || key_len > length || pos + length > size) return -1 - rec;
+    const unsigned char *val = file + pos + key_len;
+    int64_t val_len = length - key_len;
+    pos += length;
+    if (val_len < 4) return -1 - rec;
+    int64_t bytes = hgo_be32(val);
+    if (bytes != val_len - 4 || bytes % (4 * (int64_t)d) != 0) return -1 - rec;
+    if (total + bytes / 4 > cap) return INT64_MIN;
+    for (int64_t i = 0; i < bytes / 4; ++i) {
+      const unsigned char *q = val + 4 + 4 * i;
+      uint32_t u = be ? (((uint32_t)q[0] << 24) | ((uint32_t)q[1] << 16) | ((uint32_t)q[2] << 8) | q[3])
+                      : (((uint32_t)q[3] << 24) | ((uint32_t)q[2] << 16) | ((uint32_t)q[1] << 8) | q[0]);
+      memcpy(&out[total + i], &u, 4);
+    }
+    total += bytes / 4;
+    ++rec;
+  }
+  if (n_records) *n_records = rec;
+  return total;
+}
+
 /* XDR float as on the wire (progress messages): 4 bytes, big-endian */
 void hgo_xdr_float(float f, uint8_t out[4]) {
   uint32_t bits;

@@ -130,6 +130,19 @@ class Oracle:
             raise ValueError("record %d is malformed or ragged" % (-1 - n))
         return out[:n].reshape(-1, d).copy(), nrec.value
 
+    def seq_split_decode(self, file_bytes, off, length, d, big_endian=True):
+        """SequenceFileRecordReader + BytesWritable rows of FileSplit(off, length): (rows [n][d], records)."""
+        cap = len(file_bytes) // 4 + 8
+        out = np.empty(cap, np.float32)
+        nrec = C.c_int64(0)
+        self.lib.hgo_seq_split_decode.restype = C.c_int64
+        n = self.lib.hgo_seq_split_decode(file_bytes, C.c_int64(len(file_bytes)), C.c_int64(off), C.c_int64(length),
+                                          C.c_int32(d), C.c_int32(1 if big_endian else 0), self._p(out), C.c_int64(cap),
+                                          C.byref(nrec))
+        if n < 0:
+            raise ValueError("record %d is malformed, or the header is not acceptable" % (-1 - n))
+        return out[:n].reshape(-1, d).copy(), nrec.value
+
     def synth_centres(self, seed, k, d):
         out = np.empty((k, d), np.float32)
         self.lib.hgo_synth_centres(seed, k, d, self._p(out))

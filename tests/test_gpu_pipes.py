@@ -209,3 +209,34 @@ def test_gpubin_malformed_text_fails_the_task(tmp_path):
     proc, out, _ = ph.run_child(GPU_BIN, dl.close(), args=("0",))
     up = wire.parse_uplink(out)
     assert not up.done and b"whole number" in proc.stderr
+
+
+def test_gpubin_sequencefile_filesplits(oracle, tmp_path):
+    """C++ reader route over a SequenceFile<LongWritable, BytesWritable>: splits cut anywhere, records
+    owned by sync entries (SequenceFileRecordReader.java:40-52, 71-84)."""
+    import seqfile
+
+    pts, cent = cases.blobs(30000, 2, 64, seed=43)
+    cpath = str(tmp_path / "cent.bin")
+    cent.astype("<f4").tofile(cpath)
+    data = seqfile.write(pts, 4, big_endian=True)
+    path = str(tmp_path / "points.seq")
+    open(path, "wb").write(data)
+    conf = gpu_conf(cpath, 64, 2, "sequencefile")
+    conf["hadoop.pipes.java.recordreader"] = "false"
+    cuts = [0, len(data) // 3 + 11, len(data)]
+    total_counts = np.zeros(64, np.int64)
+    total_sums = np.zeros((64, 2))
+    for a, b in zip(cuts, cuts[1:]):
+        dl = (wire.Downlink().authenticate().start().set_job_conf(conf).set_input_types("k", "v")
+              .run_map(wire.file_split("file:" + path, a, b - a), 1, False))
+        proc, out, _ = ph.run_child(GPU_BIN, dl, args=("0",))
+        up = wire.parse_uplink(out)
+        assert up.done, proc.stderr
+        c, s = wire.kmeans_partials([(k, v) for _, k, v in up.partitioned], 64, 2)
+        rows, _ = oracle.seq_split_decode(data, a, b - a, 2)
+        assert c.sum() == len(rows)
+        total_counts += c
+        total_sums += s
+    o = oracle.map_combine(pts, cent)
+    check_partials(total_sums, total_counts, o[0], o[1], o[2])
