@@ -251,6 +251,24 @@ __device__ __forceinline__ int resolve_exact(float x, float y, uint32_t entry, u
 
 constexpr uint16_t kNoIndex = 0xFFFF;  // lidx value: this entry's assignment is already written
 
+// Threads per cluster in the column-sum phase, and the row stride of the striped buffer that goes
+// with it.  A warp's LDS.64 is served in two half-warp phases of 128 bytes; the 16 lanes of a phase
+// read (16 / tpc) neighbouring clusters from tpc consecutive rows, so consecutive rows must start
+// (16 / tpc) slots further along the 16-slot bank row: stride = that (mod 16).  With stride = k
+// (a multiple of 16 at k = 128) the rows of a phase landed on the same banks: the column reads,
+// a quarter of all shared-memory wavefronts, ran at 3.7 wavefronts per instruction instead of 2.
+__host__ __device__ inline int column_threads(int k, int group_threads) {
+  int tpc = 1;
+  while (tpc < 32 && tpc * 2 * k <= group_threads) tpc *= 2;
+  return tpc;
+}
+__host__ __device__ inline int row_stride(int k, int tpc) {
+  const int off = tpc >= 32 ? 1 : (tpc > 1 ? 16 / tpc : 0);
+  int rs = (k / 16) * 16 + off;
+  if (rs < k) rs += 16;
+  return rs;
+}
+
 template <class S, bool kVec4, bool kAssign, bool kT8>
 __global__ void __launch_bounds__(S::kThreads, 1)
     grid2d_map_kernel(const float *__restrict__ pts, long long n, const float *__restrict__ cent,
@@ -265,7 +283,8 @@ __global__ void __launch_bounds__(S::kThreads, 1)
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int group = threadIdx.x / kGT;
   const int t = threadIdx.x % kGT;  // thread within the group
-  const int qoff = rcap * k;                      // queue 0 starts here, queue 1 at qoff + qcap
+  const int rs = row_stride(k, column_threads(k, kGT));  // slots per row of the striped buffer (>= k)
+  const int qoff = rcap * rs;                     // queue 0 starts here, queue 1 at qoff + qcap
   const int tend = slots - qoff - 2 * qcap;       // capacity of the overflow region (slots-1 downwards)
 
   // carve shared memory (pointers computed, not looked up: no local-memory struct)
@@ -311,8 +330,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
 
   // threads per cluster in the column-sum phase (power of two, <= 32); when every cluster has
   // its own fixed lanes (one pass) their partials stay in registers across tiles
-  int tpc = 1;
-  while (tpc < 32 && tpc * 2 * k <= kGT) tpc *= 2;
+  const int tpc = column_threads(k, kGT);
   const int owners = kGT / tpc;  // clusters covered per pass
   const int sub = t & (tpc - 1);
   const bool one_pass = k <= owners;
@@ -386,7 +404,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
   // overflow region of parity `par`; returns false if even that is full
   auto place = [&](float x, float y, int c, int par, uint16_t li) -> bool {
     const int r = atomicAdd(&hist[c], 1);
-    int pos = r * k + c;
+    int pos = r * rs + c;
     if (r >= rcap) {
       const int r2 = atomicAdd(&hist[k + 2 + par], 1);
       if (r2 >= tend) return false;
@@ -437,7 +455,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
         const int r = atomicAdd(resolved ? &hist[e] : my_qcount, 1);
         const int local = 2 * ((i >> 1) * kGT + t) + (i & 1);
         if (kAssign && resolved) assign[base + local] = (int)e;
-        int pos = resolved ? r * k + (int)e : my_q + r;
+        int pos = resolved ? r * rs + (int)e : my_q + r;
         bool ok = true;
         if (__any_sync(0xFFFFFFFFu, r >= (resolved ? rcap : qcap))) {  // rare: a bin outgrew its room
           if (r >= (resolved ? rcap : qcap)) {
@@ -501,8 +519,8 @@ __global__ void __launch_bounds__(S::kThreads, 1)
         const bool on = my_c < k;
         const int h = on ? hist[my_c] : 0;
         const int m = min(h, rcap);
-        const int step = tpc * k;
-        const float2 *p = sorted + my_c + sub * k;
+        const int step = tpc * rs;
+        const float2 *p = sorted + my_c + sub * rs;
         int r = sub;
         for (; r + tpc < m; r += 2 * tpc, p += 2 * step) {  // two rows per trip
           const float2 v0 = p[0];
@@ -525,7 +543,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
           double ax = 0.0, ay = 0.0;
           const float2 *col = sorted + c;
           for (int r = sub; r < m; r += tpc) {
-            const float2 v = col[r * k];
+            const float2 v = col[r * rs];
             ax += (double)v.x;
             ay += (double)v.y;
           }
@@ -692,7 +710,7 @@ Plan make_plan(int G, int k, bool with_assign, size_t smem_optin) {
   if ((long long)slots < S::kTile) return p;  // the packed path needs a whole tile
   // queues: 3/16 of a tile each (the benchmark queues ~5 %); overflow region: >= 1/4 tile
   const int qcap = S::kTile * 3 / 16;
-  int rcap = ((int)slots - 2 * qcap - S::kTile / 4) / k;
+  int rcap = ((int)slots - 2 * qcap - S::kTile / 4) / row_stride(k, column_threads(k, S::kGroupThreads));
   if (rcap < 1) rcap = 0;  // no striped rows: every tile takes the packed path
   if (rcap > 1023) rcap = 1023;
   p.slots = (int)slots;
