@@ -58,6 +58,19 @@ def parse_args():
     return ap.parse_args()
 
 
+def ncu_traffic(kernel_family, d, k, n):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture of exactly
+    this workload (profiles/ncu_traffic.json), else None."""
+    from hgpumap import capi
+
+    fam = {capi.KERNEL_GRID2D: "grid2d_map_kernel", capi.KERNEL_TENSOR: "tensor_assign_kernel"}.get(kernel_family)
+    try:
+        table = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        return table[f"{fam}:d={d}:k={k}:points={n}"]["bytes"]
+    except (OSError, KeyError, ValueError):
+        return None
+
+
 def workload_name(args):
     return (f"K-means 1 iteration, {args.points:,} 2-D points per GPU, k={args.k}, single B200 GPU map slot"
             if args.d == 2 else f"K-means 1 iteration, {args.points:,} points per GPU, d={args.d}, k={args.k}")
@@ -401,6 +414,7 @@ def run_ours(args):
     if rank == 0:
         peak, peak_src = hbm_peak()
         achieved = n * d * 4 / (kernel_ms * 1e-3) / 1e9
+        traffic = ncu_traffic(kernel_family, d, k, n)
         fam = {capi.KERNEL_GRID2D: "grid2d_map_kernel", capi.KERNEL_EXACT: "exact_map_kernel",
                capi.KERNEL_TENSOR: "tensor_assign_kernel"}.get(kernel_family, "?")
         if kernel_family == capi.KERNEL_TENSOR:
@@ -410,13 +424,13 @@ def run_ours(args):
             tf32 = tf32_peak_tflops(torch, dev)
             achieved_tf = 2.0 * d * k * n / (kernel_ms * 1e-3) / 1e12
             roofline = {"bound": "tensor", "achieved": achieved_tf, "peak": tf32, "unit": "TFLOP/s",
-                        "frac": achieved_tf / tf32, "traffic": None, "kernel": fam, "kernel_ms": kernel_ms,
+                        "frac": achieved_tf / tf32, "traffic": traffic, "kernel": fam, "kernel_ms": kernel_ms,
                         "peak_source": "measured in this run: cuBLAS TF32 8192^3, best of 5 (the path runs "
                                        "tcgen05 kind::tf32; MEASURED_PEAKS.json holds only the bf16 rate)",
                         "algorithmic_flops_per_point": 2 * d * k, "rechecked_points_last_step": slot.last_rechecks()}
         else:
             roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                        "traffic": None, "kernel": fam, "kernel_ms": kernel_ms, "peak_source": peak_src,
+                        "traffic": traffic, "kernel": fam, "kernel_ms": kernel_ms, "peak_source": peak_src,
                         "algorithmic_bytes_per_point": 4 * d}
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
