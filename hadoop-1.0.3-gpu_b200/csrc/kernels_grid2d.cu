@@ -448,11 +448,22 @@ __global__ void __launch_bounds__(S::kThreads, 1)
     bool lost = false;
     int *const my_qcount = &hist[k + par];
     if (live == kTile) {  // full tile: straight-line code, no bounds checks
+      // Three passes over the thread's points, not one loop: the table is a byte array, so the
+      // compiler must keep every later table load behind every earlier store to the sort buffer, and a
+      // single loop became one serial chain LDS -> ATOMS -> STS per point, 8 times in a row (seen in
+      // SASS: the same three registers reused).  Split, the 8 loads, then the 8 atomics, then the 8
+      // stores each go out back to back and their latencies overlap.
+      uint32_t ent[kPPT];
+      int rank[kPPT];
+#pragma unroll
+      for (int i = 0; i < kPPT; ++i) ent[i] = table_s[cell_of(xs[i], ys[i], g)];
+#pragma unroll
+      for (int i = 0; i < kPPT; ++i) rank[i] = atomicAdd(ent[i] < kMulti ? &hist[ent[i]] : my_qcount, 1);
 #pragma unroll
       for (int i = 0; i < kPPT; ++i) {
-        const uint32_t e = table_s[cell_of(xs[i], ys[i], g)];
+        const uint32_t e = ent[i];
         const bool resolved = e < kMulti;
-        const int r = atomicAdd(resolved ? &hist[e] : my_qcount, 1);
+        const int r = rank[i];
         const int local = 2 * ((i >> 1) * kGT + t) + (i & 1);
         if (kAssign && resolved) assign[base + local] = (int)e;
         int pos = resolved ? r * rs + (int)e : my_q + r;
@@ -679,6 +690,8 @@ using ShapeA = Shape<2, 512, false>;  // 1024 threads, two groups, L2 prefetch
 using ShapeB = Shape<2, 512, true>;   // 1024 threads, register prefetch
 using ShapeC = Shape<4, 256, false>;  // 1024 threads, four groups, L2 prefetch
 using ShapeD = Shape<3, 256, true>;   // 768 threads, register prefetch
+using ShapeE = Shape<8, 128, false>;  // 1024 threads, eight groups of four warps: shorter barriers, smaller tiles
+using ShapeF = Shape<6, 128, false>;  // 768 threads, six groups
 
 // HGM_GRID2D_VARIANT forces a shape (tuning knob); otherwise the shape is picked per job.
 int forced_variant() {
@@ -760,8 +773,10 @@ bool shape_fits(int G, int k, size_t smem_optin) {
 
 }  // namespace
 
-// Pick the table size and kernel shape for k clusters: four groups of 256 threads (the
-// measured best at k = 128) while the table can stay at 160+ cells per side, otherwise two
+// Pick the table size and kernel shape for k clusters: six groups of 128 threads at k <= 128
+// (measured best at k = 128: 0.765 ms against 0.84 for four groups of 256 -- a third of all warp time
+// was spent waiting at the two group barriers of a tile, and four warps meet faster than eight),
+// four groups of 256 above that while the table can stay at 160+ cells per side, otherwise two
 // groups of 512, whose per-group arrays cost half as much shared memory.
 bool grid2d_plan(int k, size_t smem_optin, int *G_out, int *shape_out) {
   const int forced = forced_variant();
@@ -770,13 +785,16 @@ bool grid2d_plan(int k, size_t smem_optin, int *G_out, int *shape_out) {
       case 0: return shape_fits<ShapeA>(G, k, smem_optin);
       case 1: return shape_fits<ShapeB>(G, k, smem_optin);
       case 3: return shape_fits<ShapeD>(G, k, smem_optin);
+      case 4: return shape_fits<ShapeE>(G, k, smem_optin);
+      case 5: return shape_fits<ShapeF>(G, k, smem_optin);
       default: return shape_fits<ShapeC>(G, k, smem_optin);
     }
   };
-  const int order[2] = {2, 0};
-  for (int pass = 0; pass < 2; ++pass) {
+  // six groups of 128 need one owner lane per cluster to keep the partials in registers: k <= 128 only
+  const int order[3] = {k <= 128 ? 5 : 2, 2, 0};
+  for (int pass = 0; pass < 3; ++pass) {
     const int shape = forced >= 0 ? forced : order[pass];
-    const int gmin = (forced >= 0 || pass == 1) ? 64 : 160;
+    const int gmin = (forced >= 0 || pass == 2) ? 64 : 160;
     for (int G = 256; G >= gmin; G -= 32)
       if (fits(shape, G)) { *G_out = G; *shape_out = shape; return true; }
     if (forced >= 0) break;
@@ -803,6 +821,8 @@ cudaError_t launch_grid2d_map(const float *d_pts, int64_t n, const float *d_cent
     case 0: return launch_shape<ShapeA>(HGM_ARGS);
     case 1: return launch_shape<ShapeB>(HGM_ARGS);
     case 3: return launch_shape<ShapeD>(HGM_ARGS);
+    case 4: return launch_shape<ShapeE>(HGM_ARGS);
+    case 5: return launch_shape<ShapeF>(HGM_ARGS);
     default: return launch_shape<ShapeC>(HGM_ARGS);
   }
 #undef HGM_ARGS
