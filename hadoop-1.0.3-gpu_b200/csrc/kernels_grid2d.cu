@@ -37,17 +37,17 @@ namespace hgm {
 namespace {
 
 constexpr int kMaxK = 1024;
-constexpr int kPPT = 8;  // points per thread per tile
 
 // Shape of the map kernel: kGroups independent thread groups of kGroupThreads per CTA, each
 // working on tiles of kGroupThreads * kPPT points; kRegPrefetch keeps the next tile's loads
 // in registers, otherwise the next tile is pulled into L2 with prefetch instructions.
-template <int kGroupsT, int kGroupThreadsT, bool kRegPrefetchT>
+template <int kGroupsT, int kGroupThreadsT, bool kRegPrefetchT, int kPPTT = 8>
 struct Shape {
+  static constexpr int kPPT = kPPTT;  // points per thread per tile (even)
   static constexpr int kGroups = kGroupsT;
   static constexpr int kGroupThreads = kGroupThreadsT;
   static constexpr int kThreads = kGroupsT * kGroupThreadsT;
-  static constexpr int kTile = kGroupThreadsT * kPPT;
+  static constexpr int kTile = kGroupThreadsT * kPPTT;
   static constexpr bool kRegPrefetch = kRegPrefetchT;
 };
 
@@ -63,6 +63,9 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
                "r"(bytes)
                : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
 }
 __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
   asm volatile(
@@ -278,6 +281,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
                       int32_t *__restrict__ assign) {
   constexpr int kGT = S::kGroupThreads;
   constexpr int kTile = S::kTile;
+  constexpr int kPPT = S::kPPT;
   using entry_t = typename std::conditional<kT8, uint8_t, uint16_t>::type;
   constexpr uint32_t kMulti = kT8 ? (uint32_t)kTable8Multi : (uint32_t)kCellMulti;
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -301,6 +305,10 @@ __global__ void __launch_bounds__(S::kThreads, 1)
   int *const late = reinterpret_cast<int *>(reinterpret_cast<unsigned char *>(offs) + align16((size_t)(k + 1) * 4));
   int *const flag = reinterpret_cast<int *>(reinterpret_cast<unsigned char *>(late) + align16((size_t)k * 4));
   uint16_t *const lidx = reinterpret_cast<uint16_t *>(reinterpret_cast<unsigned char *>(flag) + 16);
+  // "the sort buffer is free again": one arrival per warp at the end of a tile, waited for just before
+  // the next tile's first write to the buffer -- the global loads, the cell arithmetic and the table
+  // lookups of the next tile run in the shadow of the slowest warp's column sums
+  uint64_t *const free_bar = reinterpret_cast<uint64_t *>(flag + 2);
 
   // stage the cell table and the centroids with TMA bulk copies (SASS: UBLKCP)
   const unsigned char *table_src = kT8 ? reinterpret_cast<const unsigned char *>(table + (size_t)g.G * g.G)
@@ -308,6 +316,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
   const uint32_t table_bytes = (uint32_t)table_bytes_al;
   const uint32_t cent_bytes = (uint32_t)align16((size_t)k * 8);
   if (threadIdx.x == 0) mbar_init(bar, 1);
+  if (t == 0) mbar_init(free_bar, kGT / 32);
   __syncthreads();
   if (threadIdx.x == 0) {
     mbar_expect_tx(bar, table_bytes + cent_bytes);
@@ -424,7 +433,13 @@ __global__ void __launch_bounds__(S::kThreads, 1)
   int par = 0;
   long long prev_base = 0;
   bool pending = false;  // the previous tile left points in its queue
-  for (long long tile = tile0; tile < ntiles || pending; tile += tile_stride, par ^= 1) {
+  uint32_t tiles_done = 0;  // tiles this group has finished = arrivals phases completed or pending on free_bar
+  for (long long tile = tile0; tile < ntiles || pending; tile += tile_stride, par ^= 1, ++tiles_done) {
+    bool buffer_free = tiles_done == 0;
+    auto wait_free = [&]() {
+      if (!buffer_free) mbar_wait(free_bar, (tiles_done - 1) & 1);
+      buffer_free = true;
+    };
     const bool has_tile = tile < ntiles;
     const long long base = tile * kTile;  // first point of the tile (even)
     const int live = has_tile ? (int)min((long long)kTile, n - base) : 0;
@@ -457,6 +472,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
       int rank[kPPT];
 #pragma unroll
       for (int i = 0; i < kPPT; ++i) ent[i] = table_s[cell_of(xs[i], ys[i], g)];
+      wait_free();
 #pragma unroll
       for (int i = 0; i < kPPT; ++i) rank[i] = atomicAdd(ent[i] < kMulti ? &hist[ent[i]] : my_qcount, 1);
 #pragma unroll
@@ -482,6 +498,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
         }
       }
     } else if (live > 0) {
+      wait_free();
 #pragma unroll
       for (int i = 0; i < kPPT; ++i) {
         const int local = 2 * ((i >> 1) * kGT + t) + (i & 1);  // index within the tile
@@ -509,6 +526,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
       }
     }
     // ---- phase 1b: drain the previous tile's queue into this tile's striped array ------------
+    wait_free();
     if (pending) {
       const int nq = min(hist[k + (par ^ 1)], qcap);
       for (int u = t; u < nq; u += kGT) {
@@ -661,8 +679,10 @@ __global__ void __launch_bounds__(S::kThreads, 1)
       if (t == 0) *flag = 0;
       pending = false;
     }
-    group_sync(group, kGT);  // sort buffer, counters and flag are free for the next tile
+    __syncwarp();  // sort buffer, counters and flag are free for the next tile once every warp has said so
+    if ((t & 31) == 0) mbar_arrive(free_bar);
   }
+  if (tiles_done) mbar_wait(free_bar, (tiles_done - 1) & 1);  // everybody's late points are in
 
   // ---- partials -> global: registers first (one_pass), then the group's shared partials ----
   if (one_pass) {
