@@ -41,6 +41,7 @@
 #include "hadoop/StringUtils.hh"
 #include "hadoop/TemplateFactory.hh"
 #include "hgpumap.h"
+#include "../worker/worker_client.hh"
 
 static int g_device = 0;
 
@@ -110,7 +111,10 @@ static int formatCode(const std::string &f) {
 
 class KMeansGpuMap : public HadoopPipes::Mapper {
   HadoopPipes::MapContext *ctx_;
-  hgm_ctx *gpu_ = nullptr;
+  hgm_ctx *gpu_ = nullptr;             // own CUDA context ...
+  hgmw::Client *worker_ = nullptr;     // ... or the slot's persistent worker (kmeans.gpu.worker.socket)
+  bool worker_cache_ = false;          // kmeans.gpu.worker.cache: keep file splits in the worker's HBM cache
+  HadoopPipes::TaskContext::Counter *cacheHits_ = nullptr;
   int k_, d_;
   enum { BINARY, PATH, SPLIT } format_ = BINARY;
   int fmt_code_ = HGM_FMT_F32LE;
@@ -125,10 +129,15 @@ class KMeansGpuMap : public HadoopPipes::Mapper {
     for (size_t i = 0; i < sums_.size(); ++i) sums_[i] += part_sums_[i];
     for (size_t i = 0; i < counts_.size(); ++i) counts_[i] += part_counts_[i];
   }
-  void account(int64_t n) {
+  void account(int64_t n, const hgmw::MapReply *from_worker = nullptr) {
     float ms = 0;
     int32_t launches = 0;
-    hgm_last_map_ms(gpu_, &ms, &launches);
+    if (from_worker) {
+      ms = from_worker->map_ms;
+      if (from_worker->cache_hit) ctx_->incrementCounter(cacheHits_, 1);
+    } else {
+      hgm_last_map_ms(gpu_, &ms, &launches);
+    }
     points_ += n;
     ctx_->incrementCounter(pointsIn_, (uint64_t)n);
     ctx_->incrementCounter(gpuMicros_, (uint64_t)(ms * 1000.0f));
@@ -137,6 +146,18 @@ class KMeansGpuMap : public HadoopPipes::Mapper {
   void flush() {
     if (batch_used_ == 0) return;
     int64_t n = 0;
+    if (worker_) {
+      hgmw::MapReply info;
+      try {
+        n = worker_->map_bytes(batch_, batch_used_, fmt_code_, part_sums_.data(), part_counts_.data(), &info);
+      } catch (const std::exception &e) {
+        throw HadoopUtils::Error(e.what());
+      }
+      fold();
+      account(n, &info);
+      batch_used_ = 0;
+      return;
+    }
     check(gpu_, hgm_map_split(gpu_, batch_, batch_used_, fmt_code_, part_sums_.data(), part_counts_.data(), nullptr, &n),
           "hgm_map_split");
     fold();
@@ -145,6 +166,17 @@ class KMeansGpuMap : public HadoopPipes::Mapper {
   }
   void mapFile(const std::string &path, int64_t off, int64_t len) {
     int64_t n = 0;
+    if (worker_) {
+      hgmw::MapReply info;
+      try {
+        n = worker_->map_file(path, off, len, fmt_code_, worker_cache_, part_sums_.data(), part_counts_.data(), &info);
+      } catch (const std::exception &e) {
+        throw HadoopUtils::Error(e.what());
+      }
+      fold();
+      account(n, &info);
+      return;
+    }
     check(gpu_, hgm_map_file(gpu_, path.c_str(), off, len, fmt_code_, part_sums_.data(), part_counts_.data(), nullptr, &n),
           "hgm_map_file");
     fold();
@@ -182,8 +214,23 @@ class KMeansGpuMap : public HadoopPipes::Mapper {
     fclose(f);
     HADOOP_ASSERT(got == cent.size(), "centroid file " + cpath + " is shorter than k*d floats");
 
-    check(nullptr, hgm_open(g_device, &gpu_), "hgm_open");
-    check(gpu_, hgm_set_centroids(gpu_, cent.data(), k_, d_), "hgm_set_centroids");
+    if (conf->hasKey("kmeans.gpu.worker.socket")) {
+      // the slot's persistent worker owns the CUDA context (csrc/worker/): no ~1 s of context creation
+      // per task, and file splits can stay in its HBM cache from one iteration's job to the next
+      std::string sock = conf->get("kmeans.gpu.worker.socket");
+      const size_t at = sock.find("%d");
+      if (at != std::string::npos) sock.replace(at, 2, HadoopUtils::toString(g_device));
+      worker_cache_ = conf->hasKey("kmeans.gpu.worker.cache") && conf->getBoolean("kmeans.gpu.worker.cache");
+      try {
+        worker_ = new hgmw::Client(sock);
+        worker_->set_centroids(cent.data(), k_, d_);
+      } catch (const std::exception &e) {
+        throw HadoopUtils::Error(e.what());  // no worker, no task: the scheduler re-queues the split
+      }
+    } else {
+      check(nullptr, hgm_open(g_device, &gpu_), "hgm_open");
+      check(gpu_, hgm_set_centroids(gpu_, cent.data(), k_, d_), "hgm_set_centroids");
+    }
     sums_.assign((size_t)k_ * d_, 0.0);
     part_sums_.assign((size_t)k_ * d_, 0.0);
     counts_.assign(k_, 0);
@@ -191,10 +238,16 @@ class KMeansGpuMap : public HadoopPipes::Mapper {
     if (format_ == BINARY) {
       const size_t row = 4 * (size_t)d_;
       batch_cap_ = fmt_code_ == HGM_FMT_TEXT ? (size_t(64) << 20) : std::max<size_t>(row, ((size_t(64) << 20) / row) * row);
-      void *p = nullptr;
-      check(gpu_, hgm_host_alloc(gpu_, batch_cap_, &p), "hgm_host_alloc");
-      batch_ = static_cast<unsigned char *>(p);
+      if (worker_) {  // the batch crosses a socket, not PCIe: ordinary memory
+        batch_ = static_cast<unsigned char *>(malloc(batch_cap_));
+        HADOOP_ASSERT(batch_ != NULL, "cannot allocate the record batch");
+      } else {
+        void *p = nullptr;
+        check(gpu_, hgm_host_alloc(gpu_, batch_cap_, &p), "hgm_host_alloc");
+        batch_ = static_cast<unsigned char *>(p);
+      }
     }
+    cacheHits_ = context.getCounter(KMEANS, "GPU_CACHE_HITS");
     pointsIn_ = context.getCounter(KMEANS, "POINTS");
     gpuMicros_ = context.getCounter(KMEANS, "GPU_MAP_MICROS");
     batches_ = context.getCounter(KMEANS, "GPU_BATCHES");
@@ -204,6 +257,9 @@ class KMeansGpuMap : public HadoopPipes::Mapper {
     if (gpu_) {
       if (batch_) hgm_host_free(gpu_, batch_);
       hgm_close(gpu_);
+    } else if (worker_) {
+      free(batch_);
+      delete worker_;
     }
   }
 

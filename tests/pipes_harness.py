@@ -79,12 +79,14 @@ def wordcount_downlink(num_reduces: int) -> wire.Downlink:
     return d.close()
 
 
-def kmeans_downlink(points, centroid_path, k, d, fmt="binary", num_reduces=1, per_record=1, io_sort_mb=100):
+def kmeans_downlink(points, centroid_path, k, d, fmt="binary", num_reduces=1, per_record=1, io_sort_mb=100,
+                    extra_conf=None):
     """Downlink for a K-means map task with piped input.  `per_record` points per MAP_ITEM."""
     import numpy as np
 
     conf = {"kmeans.k": str(k), "kmeans.d": str(d), "kmeans.centroids": centroid_path,
             "kmeans.input.format": fmt, "io.sort.mb": str(io_sort_mb)}
+    conf.update(extra_conf or {})
     dl = (wire.Downlink().authenticate().start().set_job_conf(conf)
           .set_input_types("org.apache.hadoop.io.LongWritable", "org.apache.hadoop.io.BytesWritable")
           .run_map(b"ignored-split", num_reduces, True))

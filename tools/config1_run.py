@@ -6,6 +6,7 @@ replay), on
   cpu      the reference's own Pipes runtime + the CPU K-means program (oracle/_ref/kmeans-pipes-cpu)
   gpu      this repository's -gpubin on this repository's Pipes runtime
   gpu-ref  the same -gpubin linked against the reference's libhadooppipes (oracle/_ref/kmeans-pipes-gpu-refrt)
+  gpu-worker  the -gpubin handing its batches to the slot's persistent worker (hgm-worker), which owns the CUDA context
 
 for two record shapes: one point per MAP_ITEM (what TextInputFormat-style feeding costs) and 1024
 points per MAP_ITEM.  Wall time covers process start, CUDA context creation, protocol replay and
@@ -49,11 +50,22 @@ def main():
         "gpu": os.path.join(ROOT, "hadoop-1.0.3-gpu_b200", "kmeans-pipes-gpu"),
         "gpu-ref": os.path.join(ROOT, "oracle", "_ref", "kmeans-pipes-gpu-refrt"),
     }
+    import subprocess
+
+    sock = os.path.join(tmp, "gpu0.sock")
+    worker = subprocess.Popen([os.path.join(ROOT, "hadoop-1.0.3-gpu_b200", "hgm-worker"), "--device", "0", "--socket", sock],
+                              stderr=subprocess.DEVNULL)
+    for _ in range(600):
+        if os.path.exists(sock):
+            break
+        time.sleep(0.05)
+    bins["gpu-worker"] = bins["gpu"]
     results = []
     reference = None
     for per_record in (1, 1024):
-        dl = ph.kmeans_downlink(pts, cpath, k, d, "binary", 1, per_record)
         for name, binary in bins.items():
+            dl = ph.kmeans_downlink(pts, cpath, k, d, "binary", 1, per_record,
+                                    extra_conf={"kmeans.gpu.worker.socket": sock} if name == "gpu-worker" else None)
             if not os.path.exists(binary):
                 continue
             best = None
@@ -82,6 +94,7 @@ def main():
                     best = rec
             results.append(best)
             print(json.dumps(best))
+    worker.terminate()
     summary = {"workload": f"config 1: {n:,} 2-D points, k={k}, one map task through the Pipes protocol",
                "same_counts_everywhere": True, "runs": results}
     if args.out:
