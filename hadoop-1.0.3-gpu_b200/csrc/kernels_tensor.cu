@@ -45,6 +45,7 @@ constexpr int kEpiWarps = 16;                    // two per (accumulator half, T
 constexpr int kThreads = (4 + kEpiWarps) * 32;   // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 spare, 4..19 epilogue
 // (putting the single-lane roles ABOVE the epilogue warps, where the issue arbiter favours them, measured 3 % slower)
 constexpr int kTmaWarp = 0, kMmaWarp = 1, kAllocWarp = 2, kFirstEpiWarp = 4;
+constexpr int kDeciderWarps = 2;  // warps 2 and 3 of the single-CTA form: row norms + per-point decisions
 constexpr uint32_t kTmemCols = 512;              // 2 buffers x 2 halves x 128 columns
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) {
@@ -222,15 +223,21 @@ __global__ void __launch_bounds__(kThreads, 1)
   uint64_t *full = bars, *empty = bars + kMaxStages;
   uint64_t *a_full = bars + 2 * kMaxStages, *a_empty = a_full + 1;
   uint64_t *t_full = a_empty + 1, *t_empty = t_full + 2;
-  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(t_empty + 2);
+  uint64_t *dec_full = t_empty + 2, *dec_empty = dec_full + 2;  // epilogue -> decider warps, per tile parity
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(dec_empty + 2);
 
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
     mbar_init(a_full, 1);
-    mbar_init(a_empty, 1 + kEpiWarps);
-    for (int b = 0; b < 2; ++b) { mbar_init(&t_full[b], 1); mbar_init(&t_empty[b], kEpiWarps); }
+    mbar_init(a_empty, 1 + kDeciderWarps);
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&t_full[b], 1);
+      mbar_init(&t_empty[b], kEpiWarps);
+      mbar_init(&dec_full[b], kEpiWarps);
+      mbar_init(&dec_empty[b], kDeciderWarps);
+    }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   // the |c|^2 K-block of the x side: every row = [1, 1, 1, 0, ...]; 16-byte chunk 0 of row r sits at
@@ -334,34 +341,18 @@ __global__ void __launch_bounds__(kThreads, 1)
     }
   } else if (warp >= kFirstEpiWarp) {
     // ===== epilogue: a thread owns one point (TMEM lane) and half of each tile's score columns =====
+    // Nothing but the scan: the row norms, the merge of the two column halves and the per-point decision
+    // belong to the decider warps below, so that the TMEM buffers are never held up by them.
     const int ew = warp - kFirstEpiWarp;
     const int quarter = warp % 4;      // a warp may only touch TMEM lanes 32*(warp % 4) .. +31
     const int half = ew / 8;           // which 128-row accumulator
     const int colhalf = (ew / 4) % 2;  // columns [64*colhalf, +64) of every centroid tile
     const int row = half * 128 + quarter * 32 + lane;  // row within the CTA tile
-    const float cmax = __uint_as_float(*a.cmax_bits);
     const uint32_t keymask = a.keymask;
-    float4 *const xchg = reinterpret_cast<float4 *>(tmem_slot + 4);  // [2][256 rows] partner results
-    uint32_t a_phase = 0, t_phase[2] = {0, 0};
-    int buf = 0, tile_parity = 0;
+    float4 *const xchg = reinterpret_cast<float4 *>(tmem_slot + 4);  // [2 parities][2 column halves][256 rows]
+    uint32_t t_phase[2] = {0, 0}, d_phase[2] = {0, 0};
+    int buf = 0, par = 0;
     for (long long tm = blockIdx.x; tm < tiles_m; tm += gridDim.x) {
-      // |x|^2 of my row from the swizzled A tile
-      mbar_wait(a_full, a_phase);
-      a_phase ^= 1;
-      float xn = 0.f;
-      if (colhalf == 0) {
-        const int r = row % 128;
-        for (int kb = 0; kb < kblocks; ++kb) {
-          const float4 *tile = reinterpret_cast<const float4 *>(a_res + ((size_t)half * kblocks + kb) * kABytes);
-#pragma unroll
-          for (int ch = 0; ch < 8; ++ch) {
-            const float4 v = tile[r * 8 + (ch ^ (r % 8))];
-            xn += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
-          }
-        }
-      }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(a_empty);
       Top2 even, odd;          // two independent chains for instruction-level parallelism
       int best_tile = 0;
       for (int tn = 0; tn < ntiles_n; ++tn) {
@@ -392,40 +383,71 @@ __global__ void __launch_bounds__(kThreads, 1)
         buf ^= 1;
       }
       even.merge(odd);
-      // the two column-halves of a row meet in shared memory (double-buffered by tile parity, so one
-      // barrier per tile orders write -> read, and the next write lands in the other buffer);
-      // colhalf 0 decides the point
-      const int pair_bar = 1 + half * 4 + quarter;
-      float4 *const xb = xchg + (tile_parity ? kTileM : 0);
-      tile_parity ^= 1;
-      if (colhalf == 1) xb[row] = make_float4(even.best, even.second, __int_as_float(best_tile), 0.f);
-      asm volatile("bar.sync %0, %1;" ::"r"(pair_bar), "r"(64) : "memory");
-      if (colhalf == 0) {
-        const float4 o = xb[row];
-        int win_half = 0;  // which 64-column half of the centroid tile holds the winner
-        if (o.x < even.best) { best_tile = __float_as_int(o.z); win_half = 64; }
-        Top2 other;
-        other.best = o.x; other.second = o.y;
-        even.merge(other);
+      mbar_wait(&dec_empty[par], d_phase[par] ^ 1);  // the deciders are done with this parity's slots (two tiles ago)
+      d_phase[par] ^= 1;
+      xchg[(par * 2 + colhalf) * kTileM + row] = make_float4(even.best, even.second, __int_as_float(best_tile), 0.f);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&dec_full[par]);
+      par ^= 1;
+    }
+  } else if (warp == kAllocWarp || warp == kAllocWarp + 1) {
+    // ===== deciders: |x|^2 of the tile's rows, then per point the merge of its two column halves,
+    // the margin test and the bookkeeping -- off the scan's critical path, one tile behind it =====
+    const int dw = warp - kAllocWarp;
+    const float cmax = __uint_as_float(*a.cmax_bits);
+    const float4 *const xchg = reinterpret_cast<const float4 *>(tmem_slot + 4);
+    uint32_t a_phase = 0, d_phase[2] = {0, 0};
+    int par = 0;
+    for (long long tm = blockIdx.x; tm < tiles_m; tm += gridDim.x) {
+      mbar_wait_backoff(a_full, a_phase, 100);
+      a_phase ^= 1;
+      float xn[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {  // my rows: dw * 128 + lane + 32 j
+        const int r = lane + 32 * j;
+        float acc = 0.f;
+        for (int kb = 0; kb < kblocks; ++kb) {
+          const float4 *tile = reinterpret_cast<const float4 *>(a_res + ((size_t)dw * kblocks + kb) * kABytes);
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) {
+            const float4 v = tile[r * 8 + (ch ^ (r % 8))];
+            acc += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+          }
+        }
+        xn[j] = acc;
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(a_empty);  // the point tile may be replaced once the MMAs are through with it as well
+      mbar_wait_backoff(&dec_full[par], d_phase[par], 100);
+      d_phase[par] ^= 1;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int row = dw * 128 + lane + 32 * j;
+        const float4 o0 = xchg[(par * 2 + 0) * kTileM + row], o1 = xchg[(par * 2 + 1) * kTileM + row];
+        const bool second_half = o1.x < o0.x;  // a tie keeps the lower column, as the scan would
+        const float best = second_half ? o1.x : o0.x;
+        const float second = fminf(fminf(o0.y, o1.y), fmaxf(o0.x, o1.x));
+        const int best_tile = __float_as_int(second_half ? o1.z : o0.z);
         const long long p = tm * kTileM + row;
         if (p < a.n) {
-          const int bidx = best_tile * kTileN + win_half + (int)(__float_as_uint(even.best) & 0x3Fu);
-          const float xnorm = sqrtf(xn);
+          const int bidx = best_tile * kTileN + (second_half ? 64 : 0) + (int)(__float_as_uint(best) & 0x3Fu);
+          const float xnorm = sqrtf(xn[j]);
           const float reach = xnorm + cmax;
           // 2^-7 |x||c| (TF32 operands, both sides of the margin) + (d 2^-22 + 2^-14)(|x|+|c|)^2
           // (FP32 accumulation, the scan's own rounding, the 6 index bits of the keys)
           const float thr = 0.0078125f * xnorm * cmax + ((float)a.d * 2.3841858e-07f + 6.1035156e-05f) * reach * reach;
           a.assign[p] = bidx;
-          if (even.second - even.best > thr) {
+          if (second - best > thr) {
             if (!a.debug) atomicAdd(a.lcounts + bidx, 1u);  // decided on the tensor cores
-          } else {  // inside the rounding bound (or NaN / inf): the exact scan decides
-            if (!a.debug) {
-              const unsigned int slot = atomicAdd(a.flag_count, 1u);
-              a.flag_list[slot] = (int32_t)p;
-            }  // p < 2^31 per launch (the host chunks larger inputs)
+          } else if (!a.debug) {  // inside the rounding bound (or NaN / inf): the exact scan decides
+            const unsigned int slot = atomicAdd(a.flag_count, 1u);
+            a.flag_list[slot] = (int32_t)p;  // p < 2^31 per launch (the host chunks larger inputs)
           }
         }
       }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&dec_empty[par]);
+      par ^= 1;
     }
   }
   __syncthreads();
@@ -961,7 +983,7 @@ bool make_map(CUtensorMap *map, const float *base, uint64_t rows, uint64_t cols)
 
 size_t tensor_smem_bytes(int d, int stages) {
   const int kblocks = d / kBlockK;
-  return (size_t)2 * kblocks * kABytes + kABytes + (size_t)stages * kBBytes + 512 + 2 * kTileM * 16 + 1024;
+  return (size_t)2 * kblocks * kABytes + kABytes + (size_t)stages * kBBytes + 512 + 4 * kTileM * 16 + 1024;
 }
 size_t tensor_pair_smem_bytes(int d, int stages) {
   const int kblocks = d / kBlockK;
