@@ -538,8 +538,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
   uint64_t *full = bars, *empty = bars + kMaxStages;
   uint64_t *a_full = bars + 2 * kMaxStages, *a_empty = a_full + 2;
   uint64_t *t_full = a_empty + 2, *t_empty = t_full + 2;
-  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(t_empty + 2);
-  float4 *const xchg = reinterpret_cast<float4 *>(tmem_slot + 4);  // [2 parities][3 column groups][128 rows]
+  uint64_t *dec_full = t_empty + 2, *dec_empty = dec_full + 2;  // epilogue -> decider warps, per tile parity (local to each CTA)
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(dec_empty + 2);
+  float4 *const xchg = reinterpret_cast<float4 *>(tmem_slot + 4);  // [2 parities][4 column groups][128 rows]
 
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
   const uint32_t rank = cluster_rank();
@@ -549,9 +550,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
     for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
     for (int b = 0; b < 2; ++b) {
       mbar_init(&a_full[b], 1);
-      mbar_init(&a_empty[b], 1 + kEpiWarps);
+      mbar_init(&a_empty[b], 1 + kDeciderWarps);
       mbar_init(&t_full[b], 1);
       mbar_init(&t_empty[b], 2 * kEpiWarps);
+      mbar_init(&dec_full[b], kEpiWarps);
+      mbar_init(&dec_empty[b], kDeciderWarps);
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -661,21 +664,20 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
       }
     }
   } else if (warp >= kFirstEpiWarp) {
-    // ===== epilogue: a thread owns one of my 128 points and 64 of each tile's 256 score columns =====
+    // ===== epilogue: a thread owns one of my 128 points and 64 of each tile's 256 score columns; nothing
+    // but the scan (norms, merge of the four column groups and decisions: the decider warps below) =====
     const int ew = warp - kFirstEpiWarp;
     const int quarter = warp % 4;   // TMEM lanes 32*(warp % 4) .. +31
     const int colgroup = ew / 4;    // columns [64*colgroup, +64)
     const int row = quarter * 32 + lane;
-    const float cmax = __uint_as_float(*a.cmax_bits);
     const uint32_t keymask = a.keymask;
-    uint32_t t_phase[2] = {0, 0};
-    int buf = 0, tile_parity = 0;  // tile_parity also names the A buffer of the tile
+    uint32_t t_phase[2] = {0, 0}, d_phase[2] = {0, 0};
+    int buf = 0, par = 0;
     Trace tr{(a.trace && blockIdx.x == 0 && ew == 0 && lane == 0) ? a.trace + 2048 : nullptr, 0};
     for (long long tm = pair0; tm < tiles; tm += npairs) {
       tr(1, (int)tm);
       Top2 even, odd;
       int best_tile = 0;
-      float xn = 0.f;
       for (int tn = 0; tn < ntiles_n; ++tn) {
         tr(2, tn);
         mbar_wait(&t_full[buf], t_phase[buf]);
@@ -691,22 +693,6 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
           tmem_ld32_issue(taddr + 32, r1);
         }
         const float before = fminf(even.best, odd.best);
-        if (tn == 0) {
-          // the first accumulator of a point tile exists, so the tile's rows have landed (only the
-          // leader's barrier saw the TMA): |x|^2 of my row from the swizzled tile, then let it go
-          if (colgroup == 0) {
-            for (int kb = 0; kb < kblocks; ++kb) {
-              const float4 *tile = reinterpret_cast<const float4 *>(a_res + tile_parity * a_bytes + (size_t)kb * kABytes);
-#pragma unroll
-              for (int ch = 0; ch < 8; ++ch) {
-                const float4 v = tile[row * 8 + (ch ^ (row % 8))];
-                xn += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
-              }
-            }
-          }
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&a_empty[tile_parity]);
-        }
         tmem_wait();
         tr(4, tn);
         asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -727,31 +713,60 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
       }
       tr(5, (int)tm);
       even.merge(odd);
-      // the four column groups of a row meet in shared memory (double-buffered by tile parity);
-      // group 0 decides the point
-      const int quad_bar = 1 + quarter;
-      float4 *const xb = xchg + (tile_parity ? 3 * kPairRows : 0);
-      tile_parity ^= 1;
-      if (colgroup != 0) xb[(colgroup - 1) * kPairRows + row] = make_float4(even.best, even.second, __int_as_float(best_tile), 0.f);
-      asm volatile("bar.sync %0, %1;" ::"r"(quad_bar), "r"(128) : "memory");
-      if (colgroup == 0) {
-        int win_group = 0;
+      mbar_wait(&dec_empty[par], d_phase[par] ^ 1);  // the deciders are done with this parity's slots (two tiles ago)
+      d_phase[par] ^= 1;
+      xchg[(par * 4 + colgroup) * kPairRows + row] = make_float4(even.best, even.second, __int_as_float(best_tile), 0.f);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&dec_full[par]);
+      par ^= 1;
+    }
+  } else if (warp == kAllocWarp || warp == kAllocWarp + 1) {
+    // ===== deciders (both CTAs): when a tile's scan is complete -- its MMAs have retired, so its rows are
+    // certainly in shared memory even in the CTA whose TMA was counted on the leader's barrier -- the row
+    // norms, then per point the merge of the four column groups, the margin test and the bookkeeping =====
+    const int dw = warp - kAllocWarp;
+    const float cmax = __uint_as_float(*a.cmax_bits);
+    uint32_t d_phase[2] = {0, 0};
+    int par = 0;  // also the A buffer of the tile
+    for (long long tm = pair0; tm < tiles; tm += npairs) {
+      mbar_wait_backoff(&dec_full[par], d_phase[par], 100);
+      d_phase[par] ^= 1;
+      float xn[2];
 #pragma unroll
-        for (int g = 1; g < 4; ++g) {
-          const float4 o = xb[(g - 1) * kPairRows + row];
-          if (o.x < even.best) { best_tile = __float_as_int(o.z); win_group = g; }
-          Top2 other;
-          other.best = o.x; other.second = o.y;
-          even.merge(other);
+      for (int j = 0; j < 2; ++j) {  // my rows: dw * 64 + lane + 32 j
+        const int r = dw * 64 + lane + 32 * j;
+        float acc = 0.f;
+        for (int kb = 0; kb < kblocks; ++kb) {
+          const float4 *tile = reinterpret_cast<const float4 *>(a_res + par * a_bytes + (size_t)kb * kABytes);
+#pragma unroll
+          for (int ch = 0; ch < 8; ++ch) {
+            const float4 v = tile[r * 8 + (ch ^ (r % 8))];
+            acc += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+          }
+        }
+        xn[j] = acc;
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&a_empty[par]);  // this buffer of rows may be reloaded (the MMAs committed theirs already)
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int row = dw * 64 + lane + 32 * j;
+        float best = INFINITY, second = INFINITY;
+        int best_tile = 0, win_group = 0;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          const float4 o = xchg[(par * 4 + g) * kPairRows + row];
+          second = fminf(fminf(second, o.y), fmaxf(best, o.x));
+          if (o.x < best) { best = o.x; best_tile = __float_as_int(o.z); win_group = g; }  // a tie keeps the lower columns
         }
         const long long p = tm * 2 * kPairRows + (long long)rank * kPairRows + row;
         if (p < a.n) {
-          const int bidx = best_tile * kPairN + win_group * 64 + (int)(__float_as_uint(even.best) & 0x3Fu);
-          const float xnorm = sqrtf(xn);
+          const int bidx = best_tile * kPairN + win_group * 64 + (int)(__float_as_uint(best) & 0x3Fu);
+          const float xnorm = sqrtf(xn[j]);
           const float reach = xnorm + cmax;
           const float thr = 0.0078125f * xnorm * cmax + ((float)a.d * 2.3841858e-07f + 6.1035156e-05f) * reach * reach;
           a.assign[p] = bidx;
-          if (even.second - even.best > thr) {
+          if (second - best > thr) {
             if (!a.debug) atomicAdd(a.lcounts + bidx, 1u);
           } else if (!a.debug) {
             const unsigned int slot = atomicAdd(a.flag_count, 1u);
@@ -759,6 +774,9 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
           }
         }
       }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&dec_empty[par]);
+      par ^= 1;
     }
   }
   asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
@@ -987,7 +1005,7 @@ size_t tensor_smem_bytes(int d, int stages) {
 }
 size_t tensor_pair_smem_bytes(int d, int stages) {
   const int kblocks = d / kBlockK;
-  return (size_t)2 * kblocks * kABytes + kABytes + (size_t)stages * kBBytes + 512 + 2 * 3 * kPairRows * 16 + 1024;
+  return (size_t)2 * kblocks * kABytes + kABytes + (size_t)stages * kBBytes + 512 + 2 * 4 * kPairRows * 16 + 1024;
 }
 int tensor_stages(int d, size_t smem_optin) {
   int stages = kMaxStages;
@@ -1034,11 +1052,12 @@ cudaError_t launch_tensor_map(const float *d_pts, int64_t n, int d, const float 
   if (e != cudaSuccess) return e;
   e = cudaMemsetAsync(d_meta, 0, (size_t)k * 4, s);  // the launch's per-cluster counts
   if (e != cudaSuccess) return e;
-  // Which form: the pair kernel wins where a point tile carries enough MMA work to hide its fixed cost
-  // (d = 128, k = 4096: 14.4 vs 15.9 ms for 8 M points), the single-CTA kernel where tiles are short
-  // (d = 64, k = 1024: 14.9 vs 17.2 ms for 40 M).  HGM_TENSOR_FORM=single|pair overrides (comparison runs).
+  // Which form: with the per-point decisions off the scan's critical path the pair kernel wins at both
+  // benchmark shapes (A/B on one box: d = 64, k = 1024: 14.9 vs 15.3 ms for 40 M points; d = 128, k = 4096:
+  // 14.3 vs 16.7 ms for 8 M); the single-CTA kernel keeps d = 32, where a point tile is one K-block.
+  // HGM_TENSOR_FORM=single|pair overrides (comparison runs).
   const char *form = getenv("HGM_TENSOR_FORM");
-  const bool pair = sm_count >= 2 && (form ? form[0] == 'p' : d >= 96);
+  const bool pair = sm_count >= 2 && (form ? form[0] == 'p' : d >= 64);
   int stages = tensor_stages(d, smem_optin);
   if (pair) {
     stages = kMaxStages;
