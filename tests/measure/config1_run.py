@@ -14,7 +14,7 @@ the uplink.  Programs on the reference runtime never finish in under 5 s: its pi
 before it can be joined (HadoopPipes.cc:1049) -- an artefact of running without a live parent that
 overlaps the work, so for those wall = max(5 s, work) and the program's own map time is the figure to read.
 
-    python tools/config1_run.py [--out profiles/rNN_config1_run.json]
+    python tests/measure/config1_run.py [--out profiles/rNN_config1_run.json]
 """
 import argparse
 import json
@@ -22,7 +22,7 @@ import os
 import sys
 import time
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path[:0] = [os.path.join(ROOT, "hadoop-1.0.3-gpu_b200"), os.path.join(ROOT, "tests")]
 
 import numpy as np  # noqa: E402

@@ -7,7 +7,7 @@
 Times include the host->device copy from pageable memory (the bytes come from a file or a Python
 buffer) and the decode kernels; the map itself is separate (hgm_cache_map).
 
-    python tools/format_decode_bench.py [--points 4000000] [--out profiles/rNN_format_decode.json]
+    python tests/measure/format_decode_bench.py [--points 4000000] [--out profiles/rNN_format_decode.json]
 """
 import argparse
 import json
@@ -15,7 +15,7 @@ import os
 import sys
 import time
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path[:0] = [os.path.join(ROOT, "hadoop-1.0.3-gpu_b200"), os.path.join(ROOT, "tests")]
 
 import numpy as np  # noqa: E402
