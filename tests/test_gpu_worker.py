@@ -139,3 +139,39 @@ def test_worker_errors_reach_the_task(worker, tmp_path):
     child, out, _ = ph.run_child(GPU_BIN, dl.close(), args=("0",))
     assert not wire.parse_uplink(out).done and b"GPU worker: text split" in child.stderr
     assert proc.poll() is None  # the worker survives a failed task
+
+
+@pytest.mark.parametrize("fmt", ["text", "sequencefile"])
+def test_text_and_sequencefile_splits_through_the_worker(worker, oracle, tmp_path, fmt):
+    import seqfile
+
+    sock, _ = worker
+    pts, cent = cases.blobs(20000, 2, 64, seed=107)
+    cpath = str(tmp_path / "cent.bin")
+    cent.astype("<f4").tofile(cpath)
+    if fmt == "text":
+        data = "".join("%.9g %.9g\n" % (x, y) for x, y in pts).encode()
+        decode = lambda a, n: oracle.text_split_decode(data, a, n, 2)[0]  # noqa: E731
+    else:
+        data = seqfile.write(pts, 8, big_endian=True)
+        decode = lambda a, n: oracle.seq_split_decode(data, a, n, 2, True)[0]  # noqa: E731
+    path = str(tmp_path / ("points." + fmt))
+    open(path, "wb").write(data)
+    conf = conf_for(cpath, 64, 2, sock, fmt=fmt, cache=True)
+    conf["hadoop.pipes.java.recordreader"] = "false"
+    cut = len(data) // 2 + 5
+    for run in range(2):
+        total = 0
+        for a, n in ((0, cut), (cut, len(data) - cut)):
+            dl = (wire.Downlink().authenticate().start().set_job_conf(conf).set_input_types("k", "v")
+                  .run_map(wire.file_split("file:" + path, a, n), 1, False))
+            proc, out, _ = ph.run_child(GPU_BIN, dl, args=("0",))
+            up = wire.parse_uplink(out)
+            assert up.done, proc.stderr
+            c, s = wire.kmeans_partials([(k, v) for _, k, v in up.partitioned], 64, 2)
+            rows = decode(a, n)
+            o = oracle.map_combine(rows, cent)
+            check_partials(s, c, o[0], o[1], o[2])
+            assert up.counter("KMEANS", "GPU_CACHE_HITS") == run
+            total += int(c.sum())
+        assert total == len(pts)
