@@ -8,8 +8,8 @@
 // specialised kernels do not take, and it is the re-check kernel behind them.
 //
 // The per-(point, centroid) sum must run over j sequentially to round like the scan does,
-// so the parallel axes are points (threads) and nothing else; centroids stream through
-// shared memory in chunks and are read as warp-wide broadcasts.
+// so the parallel axes are points (threads) and, in registers, 8 centroids per thread at a time;
+// centroids stream through shared memory in transposed chunks and are read as warp-wide broadcasts.
 #include "hgm_internal.h"
 
 namespace hgm {
@@ -29,8 +29,9 @@ __global__ void __launch_bounds__(kThreads)
   // layout: [acc doubles k*d][cnt u64 k] (if smem_acc) | centroid chunk kc*d | xT d*kThreads (D==0)
   double *acc_s = reinterpret_cast<double *>(raw);
   unsigned long long *cnt_s = reinterpret_cast<unsigned long long *>(acc_s + (smem_acc ? (size_t)k * d : 0));
-  float *cent_s = reinterpret_cast<float *>(cnt_s + (smem_acc ? k : 0));
-  float *xT = cent_s + (size_t)kc * d;
+  float *cent_s = reinterpret_cast<float *>(  // 16-byte aligned: read as float4
+      (reinterpret_cast<uintptr_t>(cnt_s + (smem_acc ? k : 0)) + 15) & ~uintptr_t(15));
+  float *xT = cent_s + (size_t)((kc + 7) & ~7) * d;
   const int t = threadIdx.x;
 
   if (smem_acc) {
@@ -59,20 +60,46 @@ __global__ void __launch_bounds__(kThreads)
     }
     float best = INFINITY;
     int arg = 0;
+    // d > 8: centroids stream through shared memory in chunks stored TRANSPOSED (cT[j][c], c padded to 8): a
+    // thread scores 8 centroids at a time -- per coordinate one x (one LDS) and two
+    // broadcast LDS.128 feed 24 FP32 instructions, instead of one LDS per 3 as a row-major chunk costs.
+    // Every centroid keeps its own accumulator and sees j = 0..d-1 in order, so the rounding is the
+    // scan's; the 8 results are then compared in ascending index with strict '<'.
+    const int kcp = (kc + 7) & ~7;
     for (int c0 = 0; c0 < k; c0 += kc) {
       const int m = min(kc, k - c0);
       __syncthreads();  // previous chunk fully consumed (and xT staged)
-      for (int i = t; i < m * d; i += kThreads) cent_s[i] = cent[(size_t)c0 * d + i];
-      __syncthreads();
-      for (int c = 0; c < m; ++c) {
-        float a = 0.0f;
-        if (D > 0) {
+      if constexpr (D > 0) {
+        // d <= 8: the point sits in registers and the scan is bound by FP32 issue (3 unfused
+        // instructions per coordinate): row-major chunk, one centroid at a time (measured faster here)
+        for (int i = t; i < m * d; i += kThreads) cent_s[i] = cent[(size_t)c0 * d + i];
+        __syncthreads();
+        for (int c = 0; c < m; ++c) {
+          float a = 0.0f;
 #pragma unroll
           for (int j = 0; j < D; ++j) a = __fadd_rn(a, sqdiff(xr[j], cent_s[c * D + j]));
-        } else {
-          for (int j = 0; j < d; ++j) a = __fadd_rn(a, sqdiff(xT[j * kThreads + t], cent_s[c * d + j]));
+          if (a < best) { best = a; arg = c0 + c; }
         }
-        if (a < best) { best = a; arg = c0 + c; }
+      } else {
+      for (int i = t; i < m * d; i += kThreads) cent_s[(i % d) * kcp + (i / d)] = cent[(size_t)c0 * d + i];
+      __syncthreads();
+      for (int c = 0; c < m; c += 8) {
+        float a[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) a[i] = 0.0f;
+        for (int j = 0; j < d; ++j) {
+          const float x = xT[j * kThreads + t];
+          const float4 u = *reinterpret_cast<const float4 *>(cent_s + j * kcp + c);
+          const float4 v = *reinterpret_cast<const float4 *>(cent_s + j * kcp + c + 4);
+          a[0] = __fadd_rn(a[0], sqdiff(x, u.x)); a[1] = __fadd_rn(a[1], sqdiff(x, u.y));
+          a[2] = __fadd_rn(a[2], sqdiff(x, u.z)); a[3] = __fadd_rn(a[3], sqdiff(x, u.w));
+          a[4] = __fadd_rn(a[4], sqdiff(x, v.x)); a[5] = __fadd_rn(a[5], sqdiff(x, v.y));
+          a[6] = __fadd_rn(a[6], sqdiff(x, v.z)); a[7] = __fadd_rn(a[7], sqdiff(x, v.w));
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+          if (c + i < m && a[i] < best) { best = a[i]; arg = c0 + c + i; }
+      }
       }
     }
     if (live) {
@@ -111,16 +138,16 @@ cudaError_t launch_exact_map(const float *d_pts, int64_t n, int d, const float *
                              int sm_count, size_t smem_optin, cudaStream_t s) {
   if (n <= 0) return cudaSuccess;
   const int smem_acc = ((long long)k * d <= kSmemAccLimit) ? 1 : 0;
-  const size_t acc_bytes = smem_acc ? ((size_t)k * d * 8 + (size_t)k * 8) : 0;
+  const size_t acc_bytes = smem_acc ? (((size_t)k * d * 8 + (size_t)k * 8 + 15) & ~size_t(15)) : 0;
   const bool reg_path = d <= 8;
   const size_t xt_bytes = reg_path ? 0 : (size_t)d * kThreads * 4;
   if (acc_bytes + xt_bytes + (size_t)d * 4 > smem_optin) return cudaErrorInvalidValue;
   size_t room = smem_optin - acc_bytes - xt_bytes;
   if (room > 64 * 1024) room = 64 * 1024;  // keep a few CTAs per SM
-  int kc = (int)(room / ((size_t)d * 4));
+  int kc = (int)(room / ((size_t)d * 4)) & ~7;  // the chunk is stored transposed, 8 centroids per step
+  if (kc < 8) return cudaErrorInvalidValue;
   if (kc > k) kc = k;
-  if (kc < 1) return cudaErrorInvalidValue;
-  const size_t smem = acc_bytes + (size_t)kc * d * 4 + xt_bytes;
+  const size_t smem = acc_bytes + (size_t)((kc + 7) & ~7) * d * 4 + xt_bytes;
 
   void (*kern)(const float *, long long, int, const float *, int, int, int, double *,
                unsigned long long *, int32_t *) = nullptr;
