@@ -224,7 +224,7 @@ int pick_kernel(hgm_ctx *c) {
   if (c->forced == HGM_KERNEL_TENSOR) return c->tensor_ok ? HGM_KERNEL_TENSOR : -1;
   if (c->grid_ok) return HGM_KERNEL_GRID2D;
   // the GEMM-shaped path pays off once a point meets a few thousand centroid coordinates
-  if (c->tensor_ok && (long long)c->k * c->d >= 8192) return HGM_KERNEL_TENSOR;
+  if (c->tensor_ok && (long long)c->k * c->d >= 2048) return HGM_KERNEL_TENSOR;  // below: the scan is cheaper than a padded tile
   return HGM_KERNEL_EXACT;
 }
 

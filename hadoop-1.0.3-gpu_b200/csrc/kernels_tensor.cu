@@ -1,4 +1,4 @@
-// kernels_tensor.cu -- K2/K3/K4: the GEMM-shaped map task (d = 32..128, k >= 128) on tcgen05.
+// kernels_tensor.cu -- K2/K3/K4: the GEMM-shaped map task (d = 32, 64, 96, 128; k*d >= 2048) on tcgen05.
 //
 // Fills the same two slots as the other kernels -- Mapper::map (c++/pipes/api/hadoop/Pipes.hh:
 // 158-161) and the combiner Reducer::reduce (Pipes.hh:166-169) -- for the shapes where the
@@ -1018,7 +1018,9 @@ int tensor_stages(int d, size_t smem_optin) {
 }  // namespace
 
 bool tensor_shape_ok(int k, int d, size_t smem_optin) {
-  return d % kBlockK == 0 && d >= kBlockK && d <= 128 && k >= 128 && tensor_smem_bytes(d, 2) <= smem_optin;
+  // k only has to fill a few columns of one centroid tile: even padded to 256 the GEMM form beats the
+  // exact scan (bound by three unfused FP32 instructions per coordinate) from k*d of a few thousand on
+  return d % kBlockK == 0 && d >= kBlockK && d <= 128 && k >= 8 && tensor_smem_bytes(d, 2) <= smem_optin;
 }
 int tensor_k_pad(int k) { return (k + kPairN - 1) / kPairN * kPairN; }  // whole tiles of either kernel form
 size_t tensor_caug_floats(int k, int d) { return (size_t)tensor_k_pad(k) * (d + kBlockK); }
