@@ -1,4 +1,4 @@
-// kernels_tensor.cu -- K2/K3/K4: the GEMM-shaped map task (d = 32, 64, 96, 128; k*d >= 2048) on tcgen05.
+// kernels_tensor.cu -- K2/K3/K4: the GEMM-shaped map task (d = 8..128 in steps of 4; k*d >= 2048) on tcgen05.
 //
 // Fills the same two slots as the other kernels -- Mapper::map (c++/pipes/api/hadoop/Pipes.hh:
 // 158-161) and the combiner Reducer::reduce (Pipes.hh:166-169) -- for the shapes where the
@@ -170,10 +170,11 @@ __global__ void tensor_prep_kernel(const float *__restrict__ cent, int k, int k_
                                    unsigned int *__restrict__ cmax_bits) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
   if (c >= k_pad) return;
-  float *row = caug + (size_t)c * (d + kBlockK);
+  const int dp = (d + kBlockK - 1) / kBlockK * kBlockK;  // coordinates padded with zeros to whole K-blocks
+  float *row = caug + (size_t)c * (dp + kBlockK);
   if (c >= k) {  // padding rows: a score no real centroid can undercut
-    for (int j = 0; j < d + kBlockK; ++j) row[j] = 0.f;
-    row[d] = 3.0e38f;
+    for (int j = 0; j < dp + kBlockK; ++j) row[j] = 0.f;
+    row[dp] = 3.0e38f;
     return;
   }
   double n = 0.0;
@@ -186,8 +187,9 @@ __global__ void tensor_prep_kernel(const float *__restrict__ cent, int k, int k_
   const double r1 = n - (double)hi;
   const float mid = tf32_rn((float)r1);
   const float lo = tf32_rn((float)(r1 - (double)mid));
-  row[d] = hi; row[d + 1] = mid; row[d + 2] = lo;
-  for (int j = 3; j < kBlockK; ++j) row[d + j] = 0.f;
+  for (int j = d; j < dp; ++j) row[j] = 0.f;
+  row[dp] = hi; row[dp + 1] = mid; row[dp + 2] = lo;
+  for (int j = 3; j < kBlockK; ++j) row[dp + j] = 0.f;
   atomicMax(cmax_bits, __float_as_uint((float)sqrt(n)));  // non-negative floats order like their bits
 }
 
@@ -213,7 +215,7 @@ __global__ void __launch_bounds__(kThreads, 1)
   // the 128-byte swizzle needs tiles on 1024-byte boundaries; the launch adds 1 KiB of slack
   unsigned char *smem = reinterpret_cast<unsigned char *>(
       (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  const int kblocks = a.d / kBlockK;           // real K-blocks; one more carries |c|^2
+  const int kblocks = (a.d + kBlockK - 1) / kBlockK;  // real K-blocks (the last one zero-filled by TMA past d); one more carries |c|^2
   const int ntiles_n = a.k_pad / kTileN;
   unsigned char *a_res = smem;                                  // [2 halves][kblocks] x 16 KiB
   unsigned char *a_aug = a_res + (size_t)2 * kblocks * kABytes; // 16 KiB constant tile
@@ -527,7 +529,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
   extern __shared__ unsigned char smem_raw[];
   unsigned char *smem = reinterpret_cast<unsigned char *>(
       (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  const int kblocks = a.d / kBlockK;
+  const int kblocks = (a.d + kBlockK - 1) / kBlockK;
   const int ntiles_n = a.k_pad / kPairN;
   unsigned char *a_res = smem;                                   // [2][kblocks] x 16 KiB: my 128 points, double-buffered
   const size_t a_bytes = (size_t)kblocks * kABytes;              // (the next tile's rows land while this one is scored)
@@ -921,9 +923,9 @@ template <int D32>
 __global__ void __launch_bounds__(256) gather_reduce_kernel(const float *__restrict__ pts, int k,
                                                             const unsigned int *__restrict__ meta,
                                                             const int32_t *__restrict__ order,
-                                                            double *__restrict__ sums) {
-  constexpr int d = D32 * 32;
-  __shared__ double red[8][d];
+                                                            double *__restrict__ sums, int d, int pitch) {
+  // d = columns of this launch (<= 128; wider rows are summed in column blocks), pitch = floats per row
+  __shared__ double red[8][D32 * 32];  // D32 = ceil(d / 32): lane j holds coordinates j, j+32, ... below d
   const unsigned int *offsets = meta + k, *items = meta + 3 * k + 1;
   const unsigned int total = items[k];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -941,21 +943,22 @@ __global__ void __launch_bounds__(256) gather_reduce_kernel(const float *__restr
     for (int m = 0; m < D32; ++m) acc[m] = 0.0;
     unsigned int i = begin + warp;
     for (; i + 24 < end; i += 32) {  // four rows in flight per warp
-      const float *r0 = pts + (size_t)order[i] * d, *r1 = pts + (size_t)order[i + 8] * d;
-      const float *r2 = pts + (size_t)order[i + 16] * d, *r3 = pts + (size_t)order[i + 24] * d;
+      const float *r0 = pts + (size_t)order[i] * pitch, *r1 = pts + (size_t)order[i + 8] * pitch;
+      const float *r2 = pts + (size_t)order[i + 16] * pitch, *r3 = pts + (size_t)order[i + 24] * pitch;
       float v[4][D32];
 #pragma unroll
       for (int m = 0; m < D32; ++m) {
-        v[0][m] = __ldg(r0 + lane + 32 * m); v[1][m] = __ldg(r1 + lane + 32 * m);
-        v[2][m] = __ldg(r2 + lane + 32 * m); v[3][m] = __ldg(r3 + lane + 32 * m);
+        const bool on = lane + 32 * m < d;
+        v[0][m] = on ? __ldg(r0 + lane + 32 * m) : 0.f; v[1][m] = on ? __ldg(r1 + lane + 32 * m) : 0.f;
+        v[2][m] = on ? __ldg(r2 + lane + 32 * m) : 0.f; v[3][m] = on ? __ldg(r3 + lane + 32 * m) : 0.f;
       }
 #pragma unroll
       for (int m = 0; m < D32; ++m) acc[m] += ((double)v[0][m] + (double)v[1][m]) + ((double)v[2][m] + (double)v[3][m]);
     }
     for (; i < end; i += 8) {
-      const float *r = pts + (size_t)order[i] * d;
+      const float *r = pts + (size_t)order[i] * pitch;
 #pragma unroll
-      for (int m = 0; m < D32; ++m) acc[m] += (double)__ldg(r + lane + 32 * m);
+      for (int m = 0; m < D32; ++m) acc[m] += lane + 32 * m < d ? (double)__ldg(r + lane + 32 * m) : 0.0;
     }
 #pragma unroll
     for (int m = 0; m < D32; ++m) red[warp][lane + 32 * m] = acc[m];
@@ -964,7 +967,7 @@ __global__ void __launch_bounds__(256) gather_reduce_kernel(const float *__restr
       double t = 0.0;
 #pragma unroll
       for (int w = 0; w < 8; ++w) t += red[w][threadIdx.x];
-      atomicAdd(&sums[(size_t)c * d + threadIdx.x], t);
+      atomicAdd(&sums[(size_t)c * pitch + threadIdx.x], t);
     }
     __syncthreads();
   }
@@ -1000,11 +1003,11 @@ bool make_map(CUtensorMap *map, const float *base, uint64_t rows, uint64_t cols)
 }
 
 size_t tensor_smem_bytes(int d, int stages) {
-  const int kblocks = d / kBlockK;
+  const int kblocks = (d + kBlockK - 1) / kBlockK;
   return (size_t)2 * kblocks * kABytes + kABytes + (size_t)stages * kBBytes + 512 + 4 * kTileM * 16 + 1024;
 }
 size_t tensor_pair_smem_bytes(int d, int stages) {
-  const int kblocks = d / kBlockK;
+  const int kblocks = (d + kBlockK - 1) / kBlockK;
   return (size_t)2 * kblocks * kABytes + kABytes + (size_t)stages * kBBytes + 512 + 2 * 4 * kPairRows * 16 + 1024;
 }
 int tensor_stages(int d, size_t smem_optin) {
@@ -1018,12 +1021,13 @@ int tensor_stages(int d, size_t smem_optin) {
 }  // namespace
 
 bool tensor_shape_ok(int k, int d, size_t smem_optin) {
-  // k only has to fill a few columns of one centroid tile: even padded to 256 the GEMM form beats the
-  // exact scan (bound by three unfused FP32 instructions per coordinate) from k*d of a few thousand on
-  return d % kBlockK == 0 && d >= kBlockK && d <= 128 && k >= 8 && tensor_smem_bytes(d, 2) <= smem_optin;
+  // k only has to fill a few columns of one centroid tile, and d only part of its last K-block (TMA zero-fills
+  // the columns past d; rows must be 16-byte multiples for it): even padded, the GEMM form beats the exact scan
+  // (bound by three unfused FP32 instructions per coordinate) from k*d of a few thousand on
+  return d % 4 == 0 && d >= 8 && d <= 128 && k >= 8 && tensor_smem_bytes(d, 2) <= smem_optin;
 }
 int tensor_k_pad(int k) { return (k + kPairN - 1) / kPairN * kPairN; }  // whole tiles of either kernel form
-size_t tensor_caug_floats(int k, int d) { return (size_t)tensor_k_pad(k) * (d + kBlockK); }
+size_t tensor_caug_floats(int k, int d) { return (size_t)tensor_k_pad(k) * ((d + kBlockK - 1) / kBlockK * kBlockK + kBlockK); }
 
 cudaError_t launch_tensor_prep(const float *d_cent, int k, int d, float *d_caug, unsigned int *d_cmax_bits,
                                cudaStream_t s) {
@@ -1031,6 +1035,40 @@ cudaError_t launch_tensor_prep(const float *d_cent, int k, int d, float *d_caug,
   if (e != cudaSuccess) return e;
   const int k_pad = tensor_k_pad(k);
   tensor_prep_kernel<<<(k_pad + 127) / 128, 128, 0, s>>>(d_cent, k, k_pad, d, d_caug, d_cmax_bits);
+  return cudaGetLastError();
+}
+
+// K4 for any kernel that has left assign[n] and the per-cluster counts of this launch in d_meta[0..k):
+// offsets -> order -> gather-reduce (rows wider than 128 floats in column blocks).  3+ launches.
+cudaError_t launch_segmented_sums(const float *d_pts, int64_t n, int d, int k, const int32_t *d_assign,
+                                  unsigned int *d_meta, int32_t *d_order, double *d_sums,
+                                  unsigned long long *d_counts, int sm_count, cudaStream_t s) {
+  cudaError_t e;
+  cluster_offsets_kernel<<<1, 1024, 0, s>>>(d_meta, k, d_counts);
+  if (k <= kScatterMaxK) {
+    long long sblocks = (n + kScatterChunk - 1) / kScatterChunk;
+    if (sblocks > (long long)sm_count * 2) sblocks = (long long)sm_count * 2;
+    const size_t sbytes = (size_t)2 * k * sizeof(unsigned int);
+    if (sbytes > 48 * 1024) {
+      e = cudaFuncSetAttribute(scatter_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sbytes);
+      if (e != cudaSuccess) return e;
+    }
+    scatter_order_kernel<<<(int)sblocks, 512, sbytes, s>>>(d_assign, (long long)n, k, d_meta, d_order);
+  } else {
+    long long sblocks = (n + 255) / 256;
+    if (sblocks > (long long)sm_count * 16) sblocks = (long long)sm_count * 16;
+    scatter_order_direct_kernel<<<(int)sblocks, 256, 0, s>>>(d_assign, (long long)n, k, d_meta, d_order);
+  }
+  const int rgrid = sm_count * 8;
+  for (int col = 0; col < d; col += 128) {
+    const int w = d - col < 128 ? d - col : 128;
+    switch ((w + 31) / 32) {
+      case 1: gather_reduce_kernel<1><<<rgrid, 256, 0, s>>>(d_pts + col, k, d_meta, d_order, d_sums + col, w, d); break;
+      case 2: gather_reduce_kernel<2><<<rgrid, 256, 0, s>>>(d_pts + col, k, d_meta, d_order, d_sums + col, w, d); break;
+      case 3: gather_reduce_kernel<3><<<rgrid, 256, 0, s>>>(d_pts + col, k, d_meta, d_order, d_sums + col, w, d); break;
+      default: gather_reduce_kernel<4><<<rgrid, 256, 0, s>>>(d_pts + col, k, d_meta, d_order, d_sums + col, w, d); break;
+    }
+  }
   return cudaGetLastError();
 }
 
@@ -1048,7 +1086,7 @@ cudaError_t launch_tensor_map(const float *d_pts, int64_t n, int d, const float 
   CUtensorMap map_x, map_c;
   const int k_pad = tensor_k_pad(k);
   if (!make_map(&map_x, d_pts, (uint64_t)n, (uint64_t)d) ||
-      !make_map(&map_c, d_caug, (uint64_t)k_pad, (uint64_t)(d + kBlockK)))
+      !make_map(&map_c, d_caug, (uint64_t)k_pad, (uint64_t)((d + kBlockK - 1) / kBlockK * kBlockK + kBlockK)))
     return cudaErrorInvalidValue;
   cudaError_t e = cudaMemsetAsync(d_flag_count, 0, 4, s);
   if (e != cudaSuccess) return e;
@@ -1056,10 +1094,10 @@ cudaError_t launch_tensor_map(const float *d_pts, int64_t n, int d, const float 
   if (e != cudaSuccess) return e;
   // Which form: with the per-point decisions off the scan's critical path the pair kernel wins at both
   // benchmark shapes (A/B on one box: d = 64, k = 1024: 14.9 vs 15.3 ms for 40 M points; d = 128, k = 4096:
-  // 14.3 vs 16.7 ms for 8 M); the single-CTA kernel keeps d = 32, where a point tile is one K-block.
+  // 14.3 vs 16.7 ms for 8 M); the single-CTA kernel keeps d <= 32, where a point tile is one K-block.
   // HGM_TENSOR_FORM=single|pair overrides (comparison runs).
   const char *form = getenv("HGM_TENSOR_FORM");
-  const bool pair = sm_count >= 2 && (form ? form[0] == 'p' : d >= 64);
+  const bool pair = sm_count >= 2 && (form ? form[0] == 'p' : d > 32);
   int stages = tensor_stages(d, smem_optin);
   if (pair) {
     stages = kMaxStages;
@@ -1104,29 +1142,7 @@ cudaError_t launch_tensor_map(const float *d_pts, int64_t n, int d, const float 
   if (a.debug) return cudaSuccess;  // experiments time K2 alone; its output is meaningless then
   recheck_kernel<<<sm_count * 4, 256, 0, s>>>(d_pts, d, d_cent, k, d_flag_list, d_flag_count, d_assign, d_meta);
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
-  cluster_offsets_kernel<<<1, 1024, 0, s>>>(d_meta, k, d_counts);
-  if (k <= kScatterMaxK) {
-    long long sblocks = (n + kScatterChunk - 1) / kScatterChunk;
-    if (sblocks > (long long)sm_count * 2) sblocks = (long long)sm_count * 2;
-    const size_t sbytes = (size_t)2 * k * sizeof(unsigned int);
-    if (sbytes > 48 * 1024) {
-      e = cudaFuncSetAttribute(scatter_order_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sbytes);
-      if (e != cudaSuccess) return e;
-    }
-    scatter_order_kernel<<<(int)sblocks, 512, sbytes, s>>>(d_assign, (long long)n, k, d_meta, d_order);
-  } else {
-    long long sblocks = (n + 255) / 256;
-    if (sblocks > (long long)sm_count * 16) sblocks = (long long)sm_count * 16;
-    scatter_order_direct_kernel<<<(int)sblocks, 256, 0, s>>>(d_assign, (long long)n, k, d_meta, d_order);
-  }
-  const int rgrid = sm_count * 8;
-  switch (d / 32) {
-    case 1: gather_reduce_kernel<1><<<rgrid, 256, 0, s>>>(d_pts, k, d_meta, d_order, d_sums); break;
-    case 2: gather_reduce_kernel<2><<<rgrid, 256, 0, s>>>(d_pts, k, d_meta, d_order, d_sums); break;
-    case 3: gather_reduce_kernel<3><<<rgrid, 256, 0, s>>>(d_pts, k, d_meta, d_order, d_sums); break;
-    default: gather_reduce_kernel<4><<<rgrid, 256, 0, s>>>(d_pts, k, d_meta, d_order, d_sums); break;
-  }
-  return cudaGetLastError();
+  return launch_segmented_sums(d_pts, n, d, k, d_assign, d_meta, d_order, d_sums, d_counts, sm_count, s);
 }
 
 }  // namespace hgm

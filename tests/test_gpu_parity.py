@@ -118,7 +118,7 @@ def test_unindexable_centroids_fall_to_exact_scan(slot, oracle):
                                    (32, 8200, 1501)])
 def test_general_dimensions_exact_scan(slot, oracle, d, k, n):
     pts, cent = cases.general_d(n, d, k, seed=d * 1000 + k)
-    tensor = d % 32 == 0 and 32 <= d <= 128 and k >= 8 and k * d >= 2048  # hgm_api.cu:pick_kernel
+    tensor = d % 4 == 0 and 8 <= d <= 128 and k >= 8 and k * d >= 2048  # hgm_api.cu:pick_kernel
     run_case(slot, oracle, pts, cent, capi.KERNEL_AUTO, want_kernel=capi.KERNEL_TENSOR if tensor else capi.KERNEL_EXACT)
     if tensor:
         run_case(slot, oracle, pts, cent, capi.KERNEL_EXACT)
@@ -247,7 +247,8 @@ def test_idempotent_and_centroid_update_roundtrip(slot, oracle):
 
 @pytest.mark.parametrize("d,k,n", [(32, 128, 5000), (64, 1024, 20011), (128, 512, 6001), (96, 300, 4097),
                                    (64, 129, 255), (64, 256, 256), (64, 256, 1), (64, 100, 3001), (32, 9, 2000),
-                                   (128, 8, 1000)])
+                                   (128, 8, 1000), (16, 200, 3000), (48, 64, 3001), (100, 300, 2500),
+                                   (8, 1024, 4000), (20, 128, 2999), (124, 40, 1000), (36, 70, 777)])
 @pytest.mark.parametrize("form", ["single", "pair"])
 def test_tensor_path_matches_oracle(slot, oracle, monkeypatch, form, d, k, n):
     """BASELINE config 4/5 shapes at test size: assignments bit-exact through the TF32 GEMM +
