@@ -118,7 +118,7 @@ def test_unindexable_centroids_fall_to_exact_scan(slot, oracle):
                                    (32, 8200, 1501)])
 def test_general_dimensions_exact_scan(slot, oracle, d, k, n):
     pts, cent = cases.general_d(n, d, k, seed=d * 1000 + k)
-    tensor = d % 4 == 0 and 8 <= d <= 128 and k >= 8 and k * d >= 2048  # hgm_api.cu:pick_kernel
+    tensor = d % 4 == 0 and 8 <= d <= 128 and k >= 8 and k * d >= (256 if d > 8 else 2048)  # hgm_api.cu:pick_kernel
     run_case(slot, oracle, pts, cent, capi.KERNEL_AUTO, want_kernel=capi.KERNEL_TENSOR if tensor else capi.KERNEL_EXACT)
     if tensor:
         run_case(slot, oracle, pts, cent, capi.KERNEL_EXACT)
@@ -286,7 +286,7 @@ def test_tensor_path_is_the_default_for_gemm_shapes(slot, oracle):
     run_case(slot, oracle, pts, cent, capi.KERNEL_AUTO, want_kernel=capi.KERNEL_TENSOR)
     pts, cent = cases.general_d(3000, 64, 100, seed=4)  # a quarter-filled centroid tile still beats the scan
     run_case(slot, oracle, pts, cent, capi.KERNEL_AUTO, want_kernel=capi.KERNEL_TENSOR)
-    pts, cent = cases.general_d(3000, 64, 20, seed=5)   # k*d < 2048: the scan is cheaper than a padded tile
+    pts, cent = cases.general_d(3000, 8, 100, seed=5)   # d = 8, k*d < 2048: the register scan is cheaper than a padded tile
     run_case(slot, oracle, pts, cent, capi.KERNEL_AUTO, want_kernel=capi.KERNEL_EXACT)
 
 
