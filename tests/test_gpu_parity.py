@@ -312,3 +312,17 @@ def test_tensor_path_near_ties_are_rechecked_exactly(slot, oracle):
     run_case(slot, oracle, pts, cent, capi.KERNEL_TENSOR)
     a = oracle.assign(pts, cent)
     assert not np.isin(a, [17, 200]).any()
+
+
+@pytest.mark.parametrize("form", ["single", "pair"])
+def test_tensor_path_with_non_finite_centroids(slot, oracle, monkeypatch, form):
+    """A NaN or infinite centroid poisons every score bound: nothing may be decided on the tensor
+    cores then, and the exact re-check must reproduce the scan (NaN and +inf distances never win)."""
+    monkeypatch.setenv("HGM_TENSOR_FORM", form)
+    pts, cent = cases.general_d(1500, 64, 256, seed=12)
+    cent = cent.copy()
+    cent[3, 5] = np.nan
+    cent[100] = np.inf
+    cent[200, 0] = -np.inf
+    run_case(slot, oracle, pts, cent, capi.KERNEL_TENSOR)
+    assert slot.last_rechecks() == len(pts)
