@@ -237,10 +237,8 @@ int map_points_async(hgm_ctx *c, const float *d_pts, int64_t n, int32_t *d_assig
   if (kern < 0) return fail(c, HGM_EINVAL, "forced kernel %d does not fit k=%d d=%d", c->forced, c->k, c->d);
   cudaError_t e;
   int launches = 1;
-  if (kern == HGM_KERNEL_TENSOR) {
-    if (reinterpret_cast<uintptr_t>(d_pts) & 15)
-      return fail(c, HGM_EINVAL, "the tensor path needs 16-byte aligned points");
-    if (c->tscratch_rows < (size_t)n) {  // scratch: assignments, re-check list, cluster order
+  if (kern != HGM_KERNEL_GRID2D) {  // scratch of the scan + segmented-sum paths: assignments, re-check list, cluster order
+    if (c->tscratch_rows < (size_t)n) {
       CU(c, cudaStreamSynchronize(c->stream));
       cudaFree(c->d_tlist); cudaFree(c->d_tassign); cudaFree(c->d_torder);
       c->d_tlist = c->d_tassign = c->d_torder = nullptr;
@@ -251,6 +249,10 @@ int map_points_async(hgm_ctx *c, const float *d_pts, int64_t n, int32_t *d_assig
       c->tscratch_rows = (size_t)n;
     }
     if (!c->d_tmeta) CU(c, cudaMalloc(&c->d_tmeta, tensor_meta_words(c->k) * 4));
+  }
+  if (kern == HGM_KERNEL_TENSOR) {
+    if (reinterpret_cast<uintptr_t>(d_pts) & 15)
+      return fail(c, HGM_EINVAL, "the tensor path needs 16-byte aligned points");
     e = launch_tensor_map(d_pts, n, c->d, c->d_cent, c->k, c->d_caug, c->d_tflags, d_assign ? d_assign : c->d_tassign,
                           c->d_tlist, c->d_tflags + 1, c->d_tmeta, c->d_torder, sums_ptr(c), counts_ptr(c), c->sm_count,
                           c->smem_optin, c->stream);
@@ -259,8 +261,9 @@ int map_points_async(hgm_ctx *c, const float *d_pts, int64_t n, int32_t *d_assig
     e = launch_grid2d_map(d_pts, n, c->d_cent, c->k, c->grid, c->d_table, c->d_cand, sums_ptr(c),
                           counts_ptr(c), d_assign, c->sm_count, c->smem_optin, c->stream);
   } else {
-    e = launch_exact_map(d_pts, n, c->d, c->d_cent, c->k, sums_ptr(c), counts_ptr(c), d_assign,
-                         c->sm_count, c->smem_optin, c->stream);
+    e = launch_exact_map(d_pts, n, c->d, c->d_cent, c->k, d_assign ? d_assign : c->d_tassign, c->d_tmeta, c->d_torder,
+                         sums_ptr(c), counts_ptr(c), c->sm_count, c->smem_optin, c->stream);
+    launches = 4 + (c->d - 1) / 128;
   }
   if (e != cudaSuccess) return fail(c, HGM_ECUDA, "map kernel launch failed: %s", cudaGetErrorString(e));
   c->last_kernel = kern;

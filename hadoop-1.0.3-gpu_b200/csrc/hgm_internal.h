@@ -49,9 +49,14 @@ cudaError_t launch_grid2d_map(const float *d_pts, int64_t n, const float *d_cent
                               int sm_count, size_t smem_optin, cudaStream_t s);
 bool grid2d_plan(int k, size_t smem_optin, int *G_out, int *shape_out);
 
-cudaError_t launch_exact_map(const float *d_pts, int64_t n, int d, const float *d_cent, int k,
-                             double *d_sums, unsigned long long *d_counts, int32_t *d_assign,
+// scan (assign + per-launch counts in d_meta) followed by the segmented sums; d_assign must not be NULL
+cudaError_t launch_exact_map(const float *d_pts, int64_t n, int d, const float *d_cent, int k, int32_t *d_assign,
+                             unsigned int *d_meta, int32_t *d_order, double *d_sums, unsigned long long *d_counts,
                              int sm_count, size_t smem_optin, cudaStream_t s);
+// per-cluster FP64 sums from assign[n] + the launch's counts in d_meta[0..k) (kernels_tensor.cu)
+cudaError_t launch_segmented_sums(const float *d_pts, int64_t n, int d, int k, const int32_t *d_assign,
+                                  unsigned int *d_meta, int32_t *d_order, double *d_sums,
+                                  unsigned long long *d_counts, int sm_count, cudaStream_t s);
 
 // tcgen05 path (kernels_tensor.cu)
 bool tensor_shape_ok(int k, int d, size_t smem_optin);

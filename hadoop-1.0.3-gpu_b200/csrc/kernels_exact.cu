@@ -16,28 +16,28 @@ namespace hgm {
 namespace {
 
 constexpr int kThreads = 128;
-constexpr int kSmemAccLimit = 4096;  // use shared FP64 accumulators when k*d <= this
+constexpr int kSmemHistLimit = 8192;  // clusters counted in shared memory per CTA (else straight to global)
 
+// Scan only: assign[p] and the per-cluster counts of this launch.  The sums follow as a segmented
+// reduction (launch_segmented_sums, kernels_tensor.cu).  The first version added every point with d FP64
+// atomics -- CAS loops in shared memory, REDs in global: with few clusters they all collide (d=5, k=2:
+// 10 ms per 100 M points against 6.4 ms at k=64), with wide rows they dominate (d=300, k=9: 58 ms per 4 M).
 template <int D>
 __global__ void __launch_bounds__(kThreads)
     exact_map_kernel(const float *__restrict__ pts, long long n, int d_rt,
-                     const float *__restrict__ cent, int k, int kc, int smem_acc,
-                     double *__restrict__ g_sums, unsigned long long *__restrict__ g_counts,
-                     int32_t *__restrict__ assign) {
+                     const float *__restrict__ cent, int k, int kc, int smem_hist,
+                     unsigned int *__restrict__ lcounts, int32_t *__restrict__ assign) {
   const int d = D > 0 ? D : d_rt;
   extern __shared__ __align__(16) unsigned char raw[];
-  // layout: [acc doubles k*d][cnt u64 k] (if smem_acc) | centroid chunk kc*d | xT d*kThreads (D==0)
-  double *acc_s = reinterpret_cast<double *>(raw);
-  unsigned long long *cnt_s = reinterpret_cast<unsigned long long *>(acc_s + (smem_acc ? (size_t)k * d : 0));
+  // layout: [hist u32 k] (if smem_hist) | centroid chunk | xT d*kThreads (D==0)
+  unsigned int *hist_s = reinterpret_cast<unsigned int *>(raw);
   float *cent_s = reinterpret_cast<float *>(  // 16-byte aligned: read as float4
-      (reinterpret_cast<uintptr_t>(cnt_s + (smem_acc ? k : 0)) + 15) & ~uintptr_t(15));
+      (reinterpret_cast<uintptr_t>(hist_s + (smem_hist ? k : 0)) + 15) & ~uintptr_t(15));
   float *xT = cent_s + (size_t)((kc + 7) & ~7) * d;
   const int t = threadIdx.x;
 
-  if (smem_acc) {
-    for (int i = t; i < k * d; i += kThreads) acc_s[i] = 0.0;
-    for (int i = t; i < k; i += kThreads) cnt_s[i] = 0ull;
-  }
+  if (smem_hist)
+    for (int i = t; i < k; i += kThreads) hist_s[i] = 0u;
   __syncthreads();
 
   const long long ntiles = (n + kThreads - 1) / kThreads;
@@ -103,25 +103,15 @@ __global__ void __launch_bounds__(kThreads)
       }
     }
     if (live) {
-      if (assign) assign[p] = arg;
-      double *sums = smem_acc ? acc_s : g_sums;
-      unsigned long long *cnts = smem_acc ? cnt_s : g_counts;
-      atomicAdd(&cnts[arg], 1ull);
-      if (D > 0) {
-#pragma unroll
-        for (int j = 0; j < D; ++j) atomicAdd(&sums[(size_t)arg * D + j], (double)xr[j]);
-      } else {
-        for (int j = 0; j < d; ++j) atomicAdd(&sums[(size_t)arg * d + j], (double)xT[j * kThreads + t]);
-      }
+      assign[p] = arg;
+      atomicAdd(smem_hist ? &hist_s[arg] : &lcounts[arg], 1u);
     }
     __syncthreads();  // xT is rewritten by the next tile
   }
-  if (smem_acc) {
+  if (smem_hist) {
     __syncthreads();
-    for (int i = t; i < k * d; i += kThreads)
-      if (acc_s[i] != 0.0) atomicAdd(&g_sums[i], acc_s[i]);
     for (int i = t; i < k; i += kThreads)
-      if (cnt_s[i] != 0ull) atomicAdd(&g_counts[i], cnt_s[i]);
+      if (hist_s[i]) atomicAdd(&lcounts[i], hist_s[i]);
   }
 }
 
@@ -133,24 +123,24 @@ __global__ void bswap32_kernel(uint32_t *w, long long n) {
 
 }  // namespace
 
-cudaError_t launch_exact_map(const float *d_pts, int64_t n, int d, const float *d_cent, int k,
-                             double *d_sums, unsigned long long *d_counts, int32_t *d_assign,
+cudaError_t launch_exact_map(const float *d_pts, int64_t n, int d, const float *d_cent, int k, int32_t *d_assign,
+                             unsigned int *d_meta, int32_t *d_order, double *d_sums, unsigned long long *d_counts,
                              int sm_count, size_t smem_optin, cudaStream_t s) {
   if (n <= 0) return cudaSuccess;
-  const int smem_acc = ((long long)k * d <= kSmemAccLimit) ? 1 : 0;
-  const size_t acc_bytes = smem_acc ? (((size_t)k * d * 8 + (size_t)k * 8 + 15) & ~size_t(15)) : 0;
+  if (!d_assign || n > 0x7FFFFFFFll) return cudaErrorInvalidValue;
+  const int smem_hist = k <= kSmemHistLimit ? 1 : 0;
+  const size_t hist_bytes = smem_hist ? (((size_t)k * 4 + 15) & ~size_t(15)) : 0;
   const bool reg_path = d <= 8;
   const size_t xt_bytes = reg_path ? 0 : (size_t)d * kThreads * 4;
-  if (acc_bytes + xt_bytes + (size_t)d * 4 > smem_optin) return cudaErrorInvalidValue;
-  size_t room = smem_optin - acc_bytes - xt_bytes;
+  if (hist_bytes + xt_bytes + (size_t)d * 32 > smem_optin) return cudaErrorInvalidValue;
+  size_t room = smem_optin - hist_bytes - xt_bytes;
   if (room > 64 * 1024) room = 64 * 1024;  // keep a few CTAs per SM
   int kc = (int)(room / ((size_t)d * 4)) & ~7;  // the chunk is stored transposed, 8 centroids per step
   if (kc < 8) return cudaErrorInvalidValue;
   if (kc > k) kc = k;
-  const size_t smem = acc_bytes + (size_t)((kc + 7) & ~7) * d * 4 + xt_bytes;
+  const size_t smem = hist_bytes + (size_t)((kc + 7) & ~7) * d * 4 + xt_bytes;
 
-  void (*kern)(const float *, long long, int, const float *, int, int, int, double *,
-               unsigned long long *, int32_t *) = nullptr;
+  void (*kern)(const float *, long long, int, const float *, int, int, int, unsigned int *, int32_t *) = nullptr;
   switch (reg_path ? d : 0) {
     case 1: kern = exact_map_kernel<1>; break;
     case 2: kern = exact_map_kernel<2>; break;
@@ -164,15 +154,17 @@ cudaError_t launch_exact_map(const float *d_pts, int64_t n, int d, const float *
   }
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
+  e = cudaMemsetAsync(d_meta, 0, (size_t)k * 4, s);  // the launch's per-cluster counts
+  if (e != cudaSuccess) return e;
   const long long ntiles = (n + kThreads - 1) / kThreads;
   int per_sm = (int)(smem_optin / (smem + 1024));
   if (per_sm < 1) per_sm = 1;
   if (per_sm > 8) per_sm = 8;
   long long grid = (long long)sm_count * per_sm;
   if (grid > ntiles) grid = ntiles;
-  kern<<<(int)grid, kThreads, smem, s>>>(d_pts, (long long)n, d, d_cent, k, kc, smem_acc, d_sums,
-                                         d_counts, d_assign);
-  return cudaGetLastError();
+  kern<<<(int)grid, kThreads, smem, s>>>(d_pts, (long long)n, d, d_cent, k, kc, smem_hist, d_meta, d_assign);
+  if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  return launch_segmented_sums(d_pts, n, d, k, d_assign, d_meta, d_order, d_sums, d_counts, sm_count, s);
 }
 
 cudaError_t launch_bswap32(uint32_t *d_words, int64_t n_words, cudaStream_t s) {

@@ -1038,6 +1038,49 @@ cudaError_t launch_tensor_prep(const float *d_cent, int k, int d, float *d_caug,
   return cudaGetLastError();
 }
 
+// Rows of at most 16 floats: a warp load would carry one short row; here lane = (sub-row q, coordinate j)
+// so that 32 / d rows travel per load, and the sub-rows meet in shared memory at the end.
+__global__ void __launch_bounds__(256) gather_reduce_small_kernel(const float *__restrict__ pts, int k,
+                                                                  const unsigned int *__restrict__ meta,
+                                                                  const int32_t *__restrict__ order,
+                                                                  double *__restrict__ sums, int d) {
+  __shared__ double red[8][32];
+  const unsigned int *offsets = meta + k, *items = meta + 3 * k + 1;
+  const unsigned int total = items[k];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int rows = 32 / d;                   // rows per warp load
+  const int q = lane / d, j = lane - q * d;  // lanes with q >= rows idle
+  const bool on = q < rows;
+  for (unsigned int item = blockIdx.x; item < total; item += gridDim.x) {
+    int lo = 0, hi = k;
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (items[mid] <= item) lo = mid; else hi = mid;
+    }
+    const int c = lo;
+    const unsigned int begin = offsets[c] + (item - items[c]) * kRedChunk;
+    const unsigned int end = min(offsets[c + 1], begin + kRedChunk);
+    double acc = 0.0;
+    const unsigned int step = 8 * rows;
+    unsigned int i = begin + warp * rows + q;
+    for (; on && i + 3 * step < end; i += 4 * step) {  // four rows in flight per lane
+      const float v0 = __ldg(pts + (size_t)order[i] * d + j), v1 = __ldg(pts + (size_t)order[i + step] * d + j);
+      const float v2 = __ldg(pts + (size_t)order[i + 2 * step] * d + j), v3 = __ldg(pts + (size_t)order[i + 3 * step] * d + j);
+      acc += ((double)v0 + (double)v1) + ((double)v2 + (double)v3);
+    }
+    for (; on && i < end; i += step) acc += (double)__ldg(pts + (size_t)order[i] * d + j);
+    red[warp][lane] = on ? acc : 0.0;
+    __syncthreads();
+    if (threadIdx.x < d) {
+      double t = 0.0;
+      for (int w = 0; w < 8; ++w)
+        for (int r = 0; r < rows; ++r) t += red[w][r * d + threadIdx.x];
+      atomicAdd(&sums[(size_t)c * d + threadIdx.x], t);
+    }
+    __syncthreads();
+  }
+}
+
 // K4 for any kernel that has left assign[n] and the per-cluster counts of this launch in d_meta[0..k):
 // offsets -> order -> gather-reduce (rows wider than 128 floats in column blocks).  3+ launches.
 cudaError_t launch_segmented_sums(const float *d_pts, int64_t n, int d, int k, const int32_t *d_assign,
@@ -1060,6 +1103,10 @@ cudaError_t launch_segmented_sums(const float *d_pts, int64_t n, int d, int k, c
     scatter_order_direct_kernel<<<(int)sblocks, 256, 0, s>>>(d_assign, (long long)n, k, d_meta, d_order);
   }
   const int rgrid = sm_count * 8;
+  if (d <= 16) {
+    gather_reduce_small_kernel<<<rgrid, 256, 0, s>>>(d_pts, k, d_meta, d_order, d_sums, d);
+    return cudaGetLastError();
+  }
   for (int col = 0; col < d; col += 128) {
     const int w = d - col < 128 ? d - col : 128;
     switch ((w + 31) / 32) {
