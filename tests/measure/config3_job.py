@@ -1,0 +1,203 @@
+#!/usr/bin/env python
+"""BASELINE config 3 as a JOB, JVM-free: K-means iterations over file splits, every map task a real Pipes
+child driven through the protocol (command-file replay), placed on CPU and GPU map slots by the fork's
+own hybrid rule (JobQueueTaskScheduler.assignTasks restated in libhgsched.so, `hgs_assign`), one call
+per "heartbeat" = per task completion.  What the Java side would do and cannot do here (no JVM):
+
+  GPU slot i   `kmeans-pipes-gpu <i>` child per task, C++ record reader route (FileSplit), talking to the
+               slot's persistent worker (`hgm-worker`), file splits kept in its HBM cache
+  CPU slot     the CPU K-means Pipes program (oracle/_ref/kmeans-pipes-cpu-hgmrt: the reference's
+               example-style mapper+combiner on this repository's runtime, so that a task does not sit
+               out the reference runtime's 5 s ping join), `kmeans.input.format=path`
+  reduce       the partial records of all tasks are summed here and the centroids updated
+
+It lives under tests/measure/ because the CPU slots run a program of oracle/.  The scheduler's inputs
+(mean CPU / GPU task times) are the measured wall times of the tasks of this very job, as
+JobInProgress keeps them (mapred/JobInProgress.java:527-565).
+
+    python tests/measure/config3_job.py [--splits 24] [--split-mib 16] [--iterations 3]
+                                        [--cpu-slots 4] [--gpu-slots 1] [--optional 1] [--fixes 0]
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+from concurrent.futures import FIRST_COMPLETED, ThreadPoolExecutor, wait
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+PKG = os.path.join(ROOT, "hadoop-1.0.3-gpu_b200")
+sys.path[:0] = [PKG, os.path.join(ROOT, "tests")]
+
+import numpy as np  # noqa: E402
+
+from hgpumap import capi, sched, synth, wire  # noqa: E402
+
+GPU_BIN = os.path.join(PKG, "kmeans-pipes-gpu")
+CPU_BIN = os.path.join(ROOT, "oracle", "_ref", "kmeans-pipes-cpu-hgmrt")
+WORKER = os.path.join(PKG, "hgm-worker")
+
+
+def run_task(binary, downlink, args, tmp):
+    """One map task: child process + command file; returns (uplink bytes, wall seconds)."""
+    fd, cmd = tempfile.mkstemp(prefix="task_", dir=tmp)
+    os.close(fd)
+    downlink.write(cmd)
+    env = {"hadoop.pipes.command.file": cmd, "PATH": os.environ.get("PATH", "")}
+    for key in ("LD_LIBRARY_PATH", "CUDA_VISIBLE_DEVICES"):
+        if key in os.environ:
+            env[key] = os.environ[key]
+    t0 = time.perf_counter()
+    proc = subprocess.run([binary, *args], env=env, capture_output=True, timeout=3600)
+    wall = time.perf_counter() - t0
+    out = cmd + ".out"
+    data = open(out, "rb").read() if os.path.exists(out) else b""
+    for path in (cmd, out):
+        if os.path.exists(path):
+            os.remove(path)
+    up = wire.parse_uplink(data)
+    if not up.done:
+        raise RuntimeError(f"map task failed: {proc.stderr.decode()[-400:]}")
+    return up, wall
+
+
+def gpu_downlink(path, nbytes, cpath, k, d, sock):
+    conf = {"kmeans.k": str(k), "kmeans.d": str(d), "kmeans.centroids": cpath, "kmeans.input.format": "binary",
+            "hadoop.pipes.java.recordreader": "false", "kmeans.gpu.worker.socket": sock,
+            "kmeans.gpu.worker.cache": "true"}
+    return (wire.Downlink().authenticate().start().set_job_conf(conf).set_input_types("k", "v")
+            .run_map(wire.file_split("file:" + path, 0, nbytes), 1, False))
+
+
+def cpu_downlink(path, cpath, k, d):
+    conf = {"kmeans.k": str(k), "kmeans.d": str(d), "kmeans.centroids": cpath, "kmeans.input.format": "path",
+            "io.sort.mb": "100"}
+    dl = (wire.Downlink().authenticate().start().set_job_conf(conf)
+          .set_input_types("org.apache.hadoop.io.LongWritable", "org.apache.hadoop.io.Text").run_map(b"split", 1, True))
+    dl.map_item((0).to_bytes(8, "big"), path)
+    return dl.close()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--splits", type=int, default=24)
+    ap.add_argument("--split-mib", type=int, default=16)
+    ap.add_argument("--iterations", type=int, default=3)
+    ap.add_argument("--cpu-slots", type=int, default=4)
+    ap.add_argument("--gpu-slots", type=int, default=1)
+    ap.add_argument("--optional", type=int, default=1, help="mapred.jobtracker.map.optionalscheduling")
+    ap.add_argument("--fixes", type=int, default=0, help="HGS_FIX_* flags (4 = carry the acceleration factor over)")
+    ap.add_argument("--k", type=int, default=128)
+    ap.add_argument("--out", default="")
+    args = ap.parse_args()
+    k, d = args.k, 2
+    tmp = os.path.join(ROOT, "gpurun_out", "job_tmp")
+    os.makedirs(tmp, exist_ok=True)
+    centres = synth.centres(synth.SEED_POINTS, k, d)
+    cent = synth.perturb(synth.SEED_CENTROIDS, centres)
+    pts_per_split = args.split_mib * (1 << 20) // (4 * d)
+    files = []
+    for s in range(args.splits):
+        path = os.path.join(tmp, f"part-{s:05d}")
+        capi.synth_points_host(synth.SEED_POINTS, s * pts_per_split, pts_per_split, centres).tofile(path)
+        files.append(path)
+    n_points = args.splits * pts_per_split
+
+    workers, socks = [], []
+    for g in range(args.gpu_slots):
+        sock = os.path.join(tmp, f"gpu{g}.sock")
+        if os.path.exists(sock):
+            os.remove(sock)  # a stale socket of an earlier run would end the wait below too early
+        workers.append(subprocess.Popen([WORKER, "--device", str(g), "--socket", sock], stderr=subprocess.DEVNULL))
+        socks.append(sock)
+    for sock in socks:
+        for _ in range(1200):
+            if os.path.exists(sock):
+                break
+            time.sleep(0.05)
+
+    report = {"workload": f"{args.splits} splits x {args.split_mib} MiB = {n_points:,} 2-D points, k={k}, "
+                          f"{args.iterations} iterations; {args.gpu_slots} GPU + {args.cpu_slots} CPU map slots, "
+                          f"optional={args.optional}, fixes={args.fixes}", "iterations": []}
+    prior = 0.0
+    pool = ThreadPoolExecutor(max_workers=args.cpu_slots + args.gpu_slots)
+    t_job = time.perf_counter()
+    try:
+        for it in range(args.iterations):
+            cpath = os.path.join(tmp, f"centroids-{it}.bin")
+            cent.astype("<f4").tofile(cpath)
+            pending = list(range(args.splits))
+            running = {}  # future -> (kind, device, split)
+            cpu_times, gpu_times = [], []
+            sums = np.zeros((k, d))
+            counts = np.zeros(k, np.int64)
+            hits = skips = beats = 0
+            t_it = time.perf_counter()
+            while pending or running:
+                # one heartbeat: the tracker reports its slots, the rule answers with tasks to start
+                busy = 0
+                for kind, dev, _ in running.values():
+                    if kind == "gpu":
+                        busy |= 1 << dev
+                job = sched.Job(args.splits, args.splits - len(pending) - len(running), len(running),
+                                int(np.mean(cpu_times)) if cpu_times else 0, int(max(np.mean(gpu_times), 1)) if gpu_times else 0,
+                                1, prior)
+                tracker = sched.Tracker(args.cpu_slots, args.gpu_slots,
+                                        sum(1 for v in running.values() if v[0] == "cpu"),
+                                        sum(1 for v in running.values() if v[0] == "gpu"), busy)
+                dec = sched.assign([job], tracker, 1, bool(args.optional), args.fixes, want=len(pending))
+                beats += 1
+                skips += dec.cpu_pass_skipped
+                for i in range(dec.n_gpu):
+                    if not pending:
+                        break
+                    s, dev = pending.pop(0), dec.gpu_device[i]
+                    dl = gpu_downlink(files[s], os.path.getsize(files[s]), cpath, k, d, socks[dev])
+                    running[pool.submit(run_task, GPU_BIN, dl, (str(dev),), tmp)] = ("gpu", dev, s)
+                for _ in range(dec.n_cpu):
+                    if not pending:
+                        break
+                    s = pending.pop(0)
+                    running[pool.submit(run_task, CPU_BIN, cpu_downlink(files[s], cpath, k, d), (), tmp)] = ("cpu", -1, s)
+                if not running:
+                    raise RuntimeError("the scheduler assigned nothing although slots are free and maps are pending")
+                done, _ = wait(list(running), return_when=FIRST_COMPLETED)
+                for fut in done:
+                    kind, dev, s = running.pop(fut)
+                    up, wall = fut.result()
+                    (cpu_times if kind == "cpu" else gpu_times).append(wall * 1e3)
+                    c, sm = wire.kmeans_partials([(key, v) for _, key, v in up.partitioned], k, d)
+                    counts += c
+                    sums += sm
+                    if kind == "gpu":
+                        hits += up.counter("KMEANS", "GPU_CACHE_HITS")
+            assert counts.sum() == n_points, (counts.sum(), n_points)
+            dt = time.perf_counter() - t_it
+            if cpu_times and gpu_times:
+                prior = float(np.mean(cpu_times) / max(np.mean(gpu_times), 1e-3))
+            nz = counts > 0
+            cent = cent.copy()
+            cent[nz] = (sums[nz] / counts[nz, None]).astype(np.float32)
+            rec = {"iteration": it + 1, "wall_s": dt, "points_per_s": n_points / dt, "cpu_tasks": len(cpu_times),
+                   "gpu_tasks": len(gpu_times), "cpu_task_mean_ms": float(np.mean(cpu_times)) if cpu_times else None,
+                   "gpu_task_mean_ms": float(np.mean(gpu_times)) if gpu_times else None, "gpu_cache_hits": hits,
+                   "heartbeats": beats, "cpu_pass_skips": skips}
+            report["iterations"].append(rec)
+            print(json.dumps(rec))
+    finally:
+        pool.shutdown(wait=False)
+        for w in workers:
+            w.terminate()
+        for path in files:
+            os.remove(path)
+    report["job_wall_s"] = time.perf_counter() - t_job
+    print(json.dumps({"job_wall_s": report["job_wall_s"]}))
+    if args.out:
+        with open(args.out, "w") as f:
+            f.write(json.dumps(report, indent=1) + "\n")
+
+
+if __name__ == "__main__":
+    main()
