@@ -89,6 +89,9 @@ def main():
     ap.add_argument("--gpu-slots", type=int, default=1)
     ap.add_argument("--optional", type=int, default=1, help="mapred.jobtracker.map.optionalscheduling")
     ap.add_argument("--fixes", type=int, default=0, help="HGS_FIX_* flags (4 = carry the acceleration factor over)")
+    ap.add_argument("--affinity", type=int, default=0,
+                    help="1: hand a GPU slot a split its worker already holds in HBM when there is one (the device-level "
+                         "analogue of obtainNewNodeLocalMapTask; the reference picks splits without regard to devices)")
     ap.add_argument("--k", type=int, default=128)
     ap.add_argument("--out", default="")
     args = ap.parse_args()
@@ -120,8 +123,18 @@ def main():
 
     report = {"workload": f"{args.splits} splits x {args.split_mib} MiB = {n_points:,} 2-D points, k={k}, "
                           f"{args.iterations} iterations; {args.gpu_slots} GPU + {args.cpu_slots} CPU map slots, "
-                          f"optional={args.optional}, fixes={args.fixes}", "iterations": []}
+                          f"optional={args.optional}, fixes={args.fixes}, affinity={args.affinity}", "iterations": []}
     prior = 0.0
+    cached_on = {}  # split -> device whose worker holds it
+
+    def pick(dev, pending):
+        if args.affinity:
+            for want in (lambda s: cached_on.get(s) == dev, lambda s: s not in cached_on):
+                for i, s in enumerate(pending):
+                    if want(s):
+                        return pending.pop(i)
+        return pending.pop(0)
+
     pool = ThreadPoolExecutor(max_workers=args.cpu_slots + args.gpu_slots)
     t_job = time.perf_counter()
     try:
@@ -153,7 +166,9 @@ def main():
                 for i in range(dec.n_gpu):
                     if not pending:
                         break
-                    s, dev = pending.pop(0), dec.gpu_device[i]
+                    dev = dec.gpu_device[i]
+                    s = pick(dev, pending)
+                    cached_on[s] = dev
                     dl = gpu_downlink(files[s], os.path.getsize(files[s]), cpath, k, d, socks[dev])
                     running[pool.submit(run_task, GPU_BIN, dl, (str(dev),), tmp)] = ("gpu", dev, s)
                 for _ in range(dec.n_cpu):
