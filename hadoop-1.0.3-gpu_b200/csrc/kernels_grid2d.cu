@@ -37,6 +37,7 @@ namespace hgm {
 namespace {
 
 constexpr int kMaxK = 1024;
+constexpr uint16_t kCandEnd = 0xFFFF;  // pads a candidate list; a list of nothing else = scan all k
 
 // Shape of the map kernel: kGroups independent thread groups of kGroupThreads per CTA, each
 // working on tiles of kGroupThreads * kPPT points; kRegPrefetch keeps the next tile's loads
@@ -158,10 +159,14 @@ __global__ void __launch_bounds__(256) grid2d_build_kernel(const float *__restri
     entry = (uint16_t)c0;
   } else if (cnt <= kMaxCand) {
     entry = (uint16_t)(kCellMulti | cnt);
-    for (int i = 0; i < kMaxCand; ++i) cand[(size_t)cell * kMaxCand + i] = i < cnt ? list[i] : 0;
+    for (int i = 0; i < kMaxCand; ++i) cand[(size_t)cell * kMaxCand + i] = i < cnt ? list[i] : kCandEnd;
   } else {
     entry = kCellBrute;
   }
+  // a "scan everything" cell says so in its candidate list too: the map kernel resolves a queued
+  // point from the list alone: one global load instead of two dependent ones (16-bit entry, then list)
+  if (entry == kCellBrute)
+    for (int i = 0; i < kMaxCand; ++i) cand[(size_t)cell * kMaxCand + i] = kCandEnd;
   table[cell] = entry;
   table8[cell] = entry < kCellMulti ? (uint8_t)(entry < kTable8Multi ? entry : kTable8Multi) : kTable8Multi;
 }
@@ -244,6 +249,35 @@ __device__ __forceinline__ int resolve_exact(float x, float y, uint32_t entry, u
       const unsigned long long hi = ((unsigned long long)ids.w << 32) | ids.z;
       for (int i = 2; i < cnt; ++i) {
         const int c = (int)(((i < 4 ? lo : hi) >> (16 * (i & 3))) & 0xFFFF);
+        const float dd = dist2(x, y, cent_s[c]);
+        if (dd < best) { best = dd; arg = c; }
+      }
+    }
+  }
+  return arg;
+}
+
+// The same scan from the cell's candidate list alone (multi-candidate and scan-all cells only): the list
+// is kCandEnd-padded, a list of nothing but kCandEnd means every centroid.
+__device__ __forceinline__ int resolve_cand(float x, float y, uint4 ids, const float2 *cent_s, int k) {
+  float best = INFINITY;
+  int arg = 0;
+  if (ids.x == 0xFFFFFFFFu) {
+    for (int c = 0; c < k; ++c) {
+      const float dd = dist2(x, y, cent_s[c]);
+      if (dd < best) { best = dd; arg = c; }
+    }
+  } else {
+    const int c0 = ids.x & 0xFFFF, c1 = ids.x >> 16;
+    const float d0 = dist2(x, y, cent_s[c0]), d1 = dist2(x, y, cent_s[c1]);
+    if (d0 < best) { best = d0; arg = c0; }
+    if (d1 < best) { best = d1; arg = c1; }
+    if ((ids.y & 0xFFFF) != kCandEnd) {
+      const unsigned long long lo = ((unsigned long long)ids.y << 32) | ids.x;
+      const unsigned long long hi = ((unsigned long long)ids.w << 32) | ids.z;
+      for (int i = 2; i < kMaxCand; ++i) {
+        const int c = (int)(((i < 4 ? lo : hi) >> (16 * (i & 3))) & 0xFFFF);
+        if (c == kCandEnd) break;
         const float dd = dist2(x, y, cent_s[c]);
         if (dd < best) { best = dd; arg = c; }
       }
@@ -531,8 +565,10 @@ __global__ void __launch_bounds__(S::kThreads, 1)
       const int nq = min(hist[k + (par ^ 1)], qcap);
       for (int u = t; u < nq; u += kGT) {
         const float2 v = sorted[prev_q + u];
-        const uint32_t cell = cell_of(v.x, v.y, g);
-        const int c = resolve_exact(v.x, v.y, entry16(cell), cell, cent_s, k, cand);
+        // the candidate list alone decides (one global load; the 16-bit entry + list were two dependent
+        // ones, in front of the group barrier: 0.733 -> 0.693 ms per 200 M points)
+        const uint4 ids = __ldg(reinterpret_cast<const uint4 *>(cand + (size_t)cell_of(v.x, v.y, g) * kMaxCand));
+        const int c = resolve_cand(v.x, v.y, ids, cent_s, k);
         if (kAssign) assign[prev_base + lidx[prev_q + u]] = c;
         lost |= !place(v.x, v.y, c, par, kNoIndex);
       }
