@@ -38,6 +38,7 @@ namespace {
 
 constexpr int kMaxK = 1024;
 constexpr uint16_t kCandEnd = 0xFFFF;  // pads a candidate list; a list of nothing else = scan all k
+constexpr uint16_t kCandMore = 0x8000;  // set in a list's first id: the list holds more than two candidates
 
 // Shape of the map kernel: kGroups independent thread groups of kGroupThreads per CTA, each
 // working on tiles of kGroupThreads * kPPT points; kRegPrefetch keeps the next tile's loads
@@ -160,6 +161,7 @@ __global__ void __launch_bounds__(256) grid2d_build_kernel(const float *__restri
   } else if (cnt <= kMaxCand) {
     entry = (uint16_t)(kCellMulti | cnt);
     for (int i = 0; i < kMaxCand; ++i) cand[(size_t)cell * kMaxCand + i] = i < cnt ? list[i] : kCandEnd;
+    if (cnt > 2) cand[(size_t)cell * kMaxCand] = (uint16_t)(list[0] | kCandMore);  // first word = whole answer otherwise
   } else {
     entry = kCellBrute;
   }
@@ -240,7 +242,7 @@ __device__ __forceinline__ int resolve_exact(float x, float y, uint32_t entry, u
   } else {
     const int cnt = entry & 0x7FFF;
     const uint4 ids = __ldg(reinterpret_cast<const uint4 *>(cand + (size_t)cell * kMaxCand));
-    const int c0 = ids.x & 0xFFFF, c1 = ids.x >> 16;
+    const int c0 = ids.x & 0x7FFF, c1 = ids.x >> 16;  // bit 15 of the first id: kCandMore
     const float d0 = dist2(x, y, cent_s[c0]), d1 = dist2(x, y, cent_s[c1]);
     if (d0 < best) { best = d0; arg = c0; }
     if (d1 < best) { best = d1; arg = c1; }
@@ -257,22 +259,26 @@ __device__ __forceinline__ int resolve_exact(float x, float y, uint32_t entry, u
   return arg;
 }
 
-// The same scan from the cell's candidate list alone (multi-candidate and scan-all cells only): the list
-// is kCandEnd-padded, a list of nothing but kCandEnd means every centroid.
-__device__ __forceinline__ int resolve_cand(float x, float y, uint4 ids, const float2 *cent_s, int k) {
+// The same scan from the cell's candidate list alone (multi-candidate and scan-all cells only).  The
+// first 32-bit word of a list is the whole answer for a two-candidate cell (by far the common case):
+// two ids, kCandMore clear.  All ones = scan every centroid; kCandMore set = read the rest of the
+// kCandEnd-padded list.
+__device__ __forceinline__ int resolve_cand(float x, float y, uint32_t id01, const uint16_t *__restrict__ list,
+                                            const float2 *cent_s, int k) {
   float best = INFINITY;
   int arg = 0;
-  if (ids.x == 0xFFFFFFFFu) {
+  if (id01 == 0xFFFFFFFFu) {
     for (int c = 0; c < k; ++c) {
       const float dd = dist2(x, y, cent_s[c]);
       if (dd < best) { best = dd; arg = c; }
     }
   } else {
-    const int c0 = ids.x & 0xFFFF, c1 = ids.x >> 16;
+    const int c0 = id01 & 0x7FFF, c1 = id01 >> 16;
     const float d0 = dist2(x, y, cent_s[c0]), d1 = dist2(x, y, cent_s[c1]);
     if (d0 < best) { best = d0; arg = c0; }
     if (d1 < best) { best = d1; arg = c1; }
-    if ((ids.y & 0xFFFF) != kCandEnd) {
+    if (id01 & kCandMore) {
+      const uint4 ids = __ldg(reinterpret_cast<const uint4 *>(list));
       const unsigned long long lo = ((unsigned long long)ids.y << 32) | ids.x;
       const unsigned long long hi = ((unsigned long long)ids.w << 32) | ids.z;
       for (int i = 2; i < kMaxCand; ++i) {
@@ -495,6 +501,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
 
     // ---- phase 1a: cell -> (cluster | queue) -> rank -> slot --------------------------------
     bool lost = false;
+    uint32_t qid01 = 0;
     int *const my_qcount = &hist[k + par];
     if (live == kTile) {  // full tile: straight-line code, no bounds checks
       // Three passes over the thread's points, not one loop: the table is a byte array, so the
@@ -509,6 +516,13 @@ __global__ void __launch_bounds__(S::kThreads, 1)
       wait_free();
 #pragma unroll
       for (int i = 0; i < kPPT; ++i) rank[i] = atomicAdd(ent[i] < kMulti ? &hist[ent[i]] : my_qcount, 1);
+      // in the shadow of the eight atomics: the first word of the candidate list of this thread's
+      // queued point (previous tile), so that phase 1b does not start a global load in front of the
+      // group barrier.  One register; 0 = not loaded (two distinct ids never give 0).
+      if (pending && t < min(hist[k + (par ^ 1)], qcap)) {
+        const float2 qv = sorted[prev_q + t];
+        qid01 = __ldg(reinterpret_cast<const uint32_t *>(cand + (size_t)cell_of(qv.x, qv.y, g) * kMaxCand));
+      }
 #pragma unroll
       for (int i = 0; i < kPPT; ++i) {
         const uint32_t e = ent[i];
@@ -567,8 +581,10 @@ __global__ void __launch_bounds__(S::kThreads, 1)
         const float2 v = sorted[prev_q + u];
         // the candidate list alone decides (one global load; the 16-bit entry + list were two dependent
         // ones, in front of the group barrier: 0.733 -> 0.693 ms per 200 M points)
-        const uint4 ids = __ldg(reinterpret_cast<const uint4 *>(cand + (size_t)cell_of(v.x, v.y, g) * kMaxCand));
-        const int c = resolve_cand(v.x, v.y, ids, cent_s, k);
+        const uint16_t *list = cand + (size_t)cell_of(v.x, v.y, g) * kMaxCand;
+        uint32_t id01 = u == t ? qid01 : 0u;
+        if (id01 == 0u) id01 = __ldg(reinterpret_cast<const uint32_t *>(list));
+        const int c = resolve_cand(v.x, v.y, id01, list, cent_s, k);
         if (kAssign) assign[prev_base + lidx[prev_q + u]] = c;
         lost |= !place(v.x, v.y, c, par, kNoIndex);
       }
