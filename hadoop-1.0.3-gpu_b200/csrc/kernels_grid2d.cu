@@ -399,7 +399,11 @@ __global__ void __launch_bounds__(S::kThreads, 1)
 #pragma unroll
       for (int i = 0; i < kPPT / 2; ++i) {
         if (kVec4) {
-          buf[i] = __ldcs(reinterpret_cast<const float4 *>(src + 4 * i * kGT));
+          // streamed once: no L1 allocation (SASS LDG.E.NA.128), the little L1 left beside 227 KB of shared
+          // memory stays with the candidate lists
+          asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+                       : "=f"(buf[i].x), "=f"(buf[i].y), "=f"(buf[i].z), "=f"(buf[i].w)
+                       : "l"(src + 4 * i * kGT));
         } else {
           const float2 a = __ldcs(reinterpret_cast<const float2 *>(src + 4 * i * kGT));
           const float2 b = __ldcs(reinterpret_cast<const float2 *>(src + 4 * i * kGT + 2));
