@@ -226,43 +226,11 @@ __device__ __forceinline__ uint32_t cell_of(float x, float y, const Grid2D &g) {
   return uy * (uint32_t)g.G + ux;
 }
 
-// exact scan of one point over its cell's candidates (or over all k): ascending index,
-// strict '<' from (+inf, 0) -- the reference scan restricted to a superset of its winners.
-// Multi-candidate cells list at least two candidates; two is by far the common case.
-__device__ __forceinline__ int resolve_exact(float x, float y, uint32_t entry, uint32_t cell,
-                                             const float2 *cent_s, int k,
-                                             const uint16_t *__restrict__ cand) {
-  float best = INFINITY;
-  int arg = 0;
-  if (entry == kCellBrute) {
-    for (int c = 0; c < k; ++c) {
-      const float dd = dist2(x, y, cent_s[c]);
-      if (dd < best) { best = dd; arg = c; }
-    }
-  } else {
-    const int cnt = entry & 0x7FFF;
-    const uint4 ids = __ldg(reinterpret_cast<const uint4 *>(cand + (size_t)cell * kMaxCand));
-    const int c0 = ids.x & 0x7FFF, c1 = ids.x >> 16;  // bit 15 of the first id: kCandMore
-    const float d0 = dist2(x, y, cent_s[c0]), d1 = dist2(x, y, cent_s[c1]);
-    if (d0 < best) { best = d0; arg = c0; }
-    if (d1 < best) { best = d1; arg = c1; }
-    if (cnt > 2) {
-      const unsigned long long lo = ((unsigned long long)ids.y << 32) | ids.x;
-      const unsigned long long hi = ((unsigned long long)ids.w << 32) | ids.z;
-      for (int i = 2; i < cnt; ++i) {
-        const int c = (int)(((i < 4 ? lo : hi) >> (16 * (i & 3))) & 0xFFFF);
-        const float dd = dist2(x, y, cent_s[c]);
-        if (dd < best) { best = dd; arg = c; }
-      }
-    }
-  }
-  return arg;
-}
-
-// The same scan from the cell's candidate list alone (multi-candidate and scan-all cells only).  The
-// first 32-bit word of a list is the whole answer for a two-candidate cell (by far the common case):
-// two ids, kCandMore clear.  All ones = scan every centroid; kCandMore set = read the rest of the
-// kCandEnd-padded list.
+// exact scan of one point over its cell's candidates (or over all k): ascending index, strict '<' from
+// (+inf, 0) -- the reference scan restricted to a superset of its winners -- driven by the cell's
+// candidate list alone (multi-candidate and scan-all cells only).  The first 32-bit word of a list is the
+// whole answer for a two-candidate cell (by far the common case): two ids, kCandMore clear.  All ones =
+// scan every centroid; kCandMore set = read the rest of the kCandEnd-padded list.
 __device__ __forceinline__ int resolve_cand(float x, float y, uint32_t id01, const uint16_t *__restrict__ list,
                                             const float2 *cent_s, int k) {
   float best = INFINITY;
@@ -440,15 +408,15 @@ __global__ void __launch_bounds__(S::kThreads, 1)
     atomicAdd(&acc[2 * c], ax);
     atomicAdd(&acc[2 * c + 1], ay);
   };
-  // the 16-bit entry of a cell (the 8-bit shared table only says "multi")
-  auto entry16 = [&](uint32_t cell) -> uint32_t {
-    return kT8 ? (uint32_t)__ldg(table + cell) : (uint32_t)table_s[cell];
-  };
   // resolve one stored point exactly and add it with CAS (overflow region, packed path)
   auto settle = [&](float2 v, long long base, uint16_t li) {
     const uint32_t cell = cell_of(v.x, v.y, g);
-    const uint32_t e = entry16(cell);
-    const int c = e < kCellMulti ? (int)e : resolve_exact(v.x, v.y, e, cell, cent_s, k, cand);
+    const uint32_t e = table_s[cell];
+    int c = (int)e;
+    if (e >= kMulti) {
+      const uint16_t *list = cand + (size_t)cell * kMaxCand;
+      c = resolve_cand(v.x, v.y, __ldg(reinterpret_cast<const uint32_t *>(list)), list, cent_s, k);
+    }
     flush(c, (double)v.x, (double)v.y);
     atomicAdd(&late[c], 1);
     if (kAssign && li != kNoIndex) assign[base + li] = c;
