@@ -59,16 +59,17 @@ def parse_args():
 
 
 def ncu_traffic(kernel_family, d, k, n):
-    """DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture of exactly
-    this workload (profiles/ncu_traffic.json), else None."""
+    """(DRAM bytes per launch, what the capture says limits the kernel) for the dominant kernel, from the
+    committed ncu --set full capture of exactly this workload (profiles/ncu_traffic.json), else (None, None)."""
     from hgpumap import capi
 
     fam = {capi.KERNEL_GRID2D: "grid2d_map_kernel", capi.KERNEL_TENSOR: "tensor_assign_kernel"}.get(kernel_family)
     try:
         table = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
-        return table[f"{fam}:d={d}:k={k}:points={n}"]["bytes"]
+        entry = table[f"{fam}:d={d}:k={k}:points={n}"]
+        return entry["bytes"], entry.get("limiter")
     except (OSError, KeyError, ValueError):
-        return None
+        return None, None
 
 
 def workload_name(args):
@@ -447,7 +448,7 @@ def run_ours(args):
     if rank == 0:
         peak, peak_src = hbm_peak()
         achieved = n * d * 4 / (kernel_ms * 1e-3) / 1e9
-        traffic = ncu_traffic(kernel_family, d, k, n)
+        traffic, limiter = ncu_traffic(kernel_family, d, k, n)
         fam = {capi.KERNEL_GRID2D: "grid2d_map_kernel", capi.KERNEL_EXACT: "exact_map_kernel",
                capi.KERNEL_TENSOR: "tensor_assign_kernel"}.get(kernel_family, "?")
         if kernel_family == capi.KERNEL_TENSOR:
@@ -465,6 +466,8 @@ def run_ours(args):
             roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                         "traffic": traffic, "kernel": fam, "kernel_ms": kernel_ms, "peak_source": peak_src,
                         "algorithmic_bytes_per_point": 4 * d}
+            if limiter:  # what the committed ncu capture of this workload shows the kernel is bound by
+                roofline["limiter"] = limiter
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": elapsed_ms / args.steps, "higher_is_better": True,
