@@ -22,10 +22,11 @@
 // has a strictly larger COMPUTED distance than c0 everywhere in the cell and can never be a
 // minimiser of the scan, let alone its lowest-index one.
 //
-// Combiner: per tile of 4096 points a counting sort by cluster in shared memory (one native
-// integer ATOMS per point gives the rank; shared FP32/FP64 atomic adds are CAS loops on
-// sm_100), then each cluster's contiguous run is summed in FP64 by its owner threads.  The
-// per-CTA FP64 partials leave the SM once, as k*3 RED.ADD.F64/U64 to global.
+// Combiner: per tile (1024 points per thread group at k <= 128) a counting sort by cluster in
+// shared memory -- one native integer ATOMS per point gives the rank, the point goes to slot
+// [rank][cluster] of a striped buffer (shared FP32/FP64 atomic adds are CAS loops on sm_100) --
+// then each cluster's column is summed in FP64 by its owner lanes, which keep their partials in
+// registers for the whole kernel.  The FP64 partials leave the SM once, as k*3 RED.ADD.F64/U64.
 #include <stdlib.h>
 
 #include <type_traits>
