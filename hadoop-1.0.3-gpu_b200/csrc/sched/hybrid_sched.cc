@@ -84,6 +84,32 @@ extern "C" int hgs_assign(const hgs_job *jobs, int32_t n_jobs, const hgs_tracker
   return 0;
 }
 
+extern "C" int32_t hgs_pick_split(const int32_t *home, int32_t n, int32_t device, int32_t max_gpu_slots) {
+  if (n < 0 || (n > 0 && !home) || max_gpu_slots < 1 || max_gpu_slots > HGS_MAX_DEVICES || device < 0 ||
+      device >= max_gpu_slots)
+    return -22;
+  if (n == 0) return -1;
+  int first_unheld = -1;
+  int queued[HGS_MAX_DEVICES] = {};  // pending resident splits per device
+  int first_of[HGS_MAX_DEVICES];
+  for (int j = 0; j < HGS_MAX_DEVICES; ++j) first_of[j] = -1;
+  for (int i = 0; i < n; ++i) {
+    const int h = home[i];
+    if (h == device) return i;  // (1)
+    if (h < 0 || h >= max_gpu_slots) {  // held nowhere (or by a slot that no longer exists)
+      if (first_unheld < 0) first_unheld = i;
+    } else {
+      if (first_of[h] < 0) first_of[h] = i;
+      ++queued[h];
+    }
+  }
+  if (first_unheld >= 0) return first_unheld;  // (2)
+  int victim = -1;
+  for (int j = 0; j < max_gpu_slots; ++j)
+    if (queued[j] > 0 && (victim < 0 || queued[j] > queued[victim])) victim = j;
+  return first_of[victim];  // (3): every pending split is held by some other device
+}
+
 extern "C" int hgs_simulate(const hgs_sim_params *p, hgs_sim_result *out) {
   if (!p || !out || p->n_splits < 0 || p->iterations < 1 || p->cpu_slots < 0 || p->gpu_slots < 0 ||
       p->gpu_slots > HGS_MAX_DEVICES || p->heartbeat_ms <= 0)

@@ -55,6 +55,8 @@ def load() -> C.CDLL:
                                    C.c_int32, C.c_int32, C.POINTER(Decision)]
         lib.hgs_simulate.restype = C.c_int
         lib.hgs_simulate.argtypes = [C.POINTER(SimParams), C.POINTER(SimResult)]
+        lib.hgs_pick_split.restype = C.c_int32
+        lib.hgs_pick_split.argtypes = [C.POINTER(C.c_int32), C.c_int32, C.c_int32, C.c_int32]
         _LIB = lib
     return _LIB
 
@@ -76,3 +78,13 @@ def simulate(**kw) -> SimResult:
     if rc != 0:
         raise ValueError(f"hgs_simulate returned {rc}")
     return out
+
+
+def pick_split(home_device: list[int], device: int, max_gpu_slots: int) -> int:
+    """Index of the pending split to hand to GPU slot `device` (hgs_pick_split): one it already holds in
+    HBM, else one nobody holds, else one of the device with the longest queue.  -1 if nothing is pending."""
+    arr = (C.c_int32 * max(len(home_device), 1))(*home_device)
+    rc = load().hgs_pick_split(arr, len(home_device), device, max_gpu_slots)
+    if rc < -1:
+        raise ValueError(f"hgs_pick_split returned {rc}")
+    return rc

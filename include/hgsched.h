@@ -71,6 +71,19 @@ typedef struct {
 int hgs_assign(const hgs_job *jobs, int32_t n_jobs, const hgs_tracker *tracker, int32_t num_trackers,
                int32_t optional_scheduling, int32_t fixes, int32_t want, hgs_decision *out);
 
+/* Device-level locality for GPU map slots.  The reference stamps the first free device id on whatever
+ * task obtainNewNodeLocalMapTask returned (mapred/JobQueueTaskScheduler.java:350-361): it knows which NODE
+ * holds a split's blocks, not which DEVICE of the node holds its rows in HBM.  With one HBM split cache per
+ * device (hgm_cache_*, one hgm-worker per slot) iteration 2's task for a split then lands on another device
+ * seven times out of eight and is staged again (measured: 4.9 vs 9.4 G points/s on eight slots,
+ * profiles/r01_config3_job.md).  This is the pick one level below node locality, to be called with the
+ * device id hgs_assign chose: home_device[i] is the device whose cache holds pending split i, or -1.
+ * Order of preference: (1) a split this device holds; (2) a split no device holds (it has to be staged
+ * somewhere); (3) a split of the device with the most pending resident splits -- that device would finish
+ * last, so its queue is the one to shorten (lowest device id on a tie, lowest index within it).
+ * Returns the index into home_device[], -1 if n_pending == 0, -22 on a bad argument. */
+int32_t hgs_pick_split(const int32_t *home_device, int32_t n_pending, int32_t device, int32_t max_gpu_slots);
+
 /* Discrete-event run of `iterations` K-means map phases of `n_splits` map tasks each on ONE
  * TaskTracker with the given slots, driven by hgs_assign at every heartbeat. */
 typedef struct {

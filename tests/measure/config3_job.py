@@ -128,11 +128,8 @@ def main():
     cached_on = {}  # split -> device whose worker holds it
 
     def pick(dev, pending):
-        if args.affinity:
-            for want in (lambda s: cached_on.get(s) == dev, lambda s: s not in cached_on):
-                for i, s in enumerate(pending):
-                    if want(s):
-                        return pending.pop(i)
+        if args.affinity:  # device-level locality: include/hgsched.h hgs_pick_split
+            return pending.pop(sched.pick_split([cached_on.get(s, -1) for s in pending], dev, args.gpu_slots))
         return pending.pop(0)
 
     pool = ThreadPoolExecutor(max_workers=args.cpu_slots + args.gpu_slots)

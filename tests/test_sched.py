@@ -100,3 +100,75 @@ def test_simulation_rejects_bad_arguments():
         sched.simulate(n_splits=1, iterations=0, cpu_slots=1, gpu_slots=1, cpu_task_ms=1, gpu_task_ms_first=1,
                        gpu_task_ms_cached=1, task_overhead_ms=0, heartbeat_ms=1, out_of_band_heartbeat=0,
                        optional_scheduling=0, fixes=0, prior_acceleration=0.0)
+
+
+def test_hgsched_header_symbols_are_exported():
+    import os
+    import re
+
+    from conftest import ROOT
+
+    text = open(os.path.join(ROOT, "include", "hgsched.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    names = sorted(set(re.findall(r"\b(hgs_[a-z_]+)\s*\(", text)))
+    assert names == ["hgs_assign", "hgs_pick_split", "hgs_simulate"]
+    lib = sched.load()
+    for name in names:
+        assert hasattr(lib, name)
+
+
+def test_pick_split_prefers_own_then_unheld_then_longest_queue():
+    """Device-level locality below the reference's node locality (JobQueueTaskScheduler.java:350-361 stamps
+    the first free device on whatever split it got)."""
+    # (1) a split the device holds, wherever it sits in the pending list
+    assert sched.pick_split([3, -1, 5, 2, 5], device=5, max_gpu_slots=8) == 2
+    # (2) else a split nobody holds: it has to be staged somewhere anyway
+    assert sched.pick_split([3, -1, 2, -1], device=5, max_gpu_slots=8) == 1
+    # a home outside the tracker's slots (a worker that is gone) counts as held nowhere
+    assert sched.pick_split([3, 9, 2], device=5, max_gpu_slots=8) == 1
+    # (3) else steal from the device with the most pending resident splits; lowest id on a tie
+    assert sched.pick_split([3, 2, 2, 3, 2], device=5, max_gpu_slots=8) == 1
+    assert sched.pick_split([3, 2, 2, 3], device=5, max_gpu_slots=8) == 1
+    assert sched.pick_split([3, 3, 2], device=5, max_gpu_slots=8) == 0
+    # nothing pending, bad arguments
+    assert sched.pick_split([], device=0, max_gpu_slots=1) == -1
+    for dev, slots in ((8, 8), (-1, 8), (0, 0), (0, 33)):
+        with pytest.raises(ValueError):
+            sched.pick_split([0], device=dev, max_gpu_slots=slots)
+
+
+def test_device_affine_picks_keep_iteration_two_in_the_hbm_caches():
+    """128 splits on eight GPU slots, two iterations, task times jittered the way real tasks finish (a staged
+    split takes three times a cached one): handing a freed slot the NEXT split (the reference) finds it
+    cached on that device about one time in eight; hgs_pick_split finds nearly every split at home
+    (measured on eight B200s: 123 of 128, profiles/r01_config3_job.md)."""
+    import heapq
+    import random
+
+    n_splits, slots = 128, 8
+
+    def run_iteration(home, affine, seed):
+        rng = random.Random(seed)
+        pending = list(range(n_splits))
+        hits = 0
+        now_home = dict(home)
+        free_at = [(0.0, dev) for dev in range(slots)]
+        heapq.heapify(free_at)
+        while pending:
+            t, dev = heapq.heappop(free_at)          # the slot that frees up first
+            if affine:
+                i = sched.pick_split([now_home.get(s, -1) for s in pending], dev, slots)
+            else:
+                i = 0
+            s = pending.pop(i)
+            hit = home.get(s, -1) == dev
+            hits += hit
+            now_home[s] = dev                        # the worker of `dev` holds it from now on
+            heapq.heappush(free_at, (t + (1.0 if hit else 3.0) * rng.uniform(0.7, 1.3), dev))
+        return hits, now_home
+
+    _, home = run_iteration({}, affine=False, seed=1)        # iteration 1 stages everything
+    hits_ref, _ = run_iteration(home, affine=False, seed=2)
+    hits_aff, _ = run_iteration(home, affine=True, seed=2)
+    assert hits_aff >= 0.9 * n_splits                         # misses only where a device ran out of its own early
+    assert hits_ref <= 0.3 * n_splits
