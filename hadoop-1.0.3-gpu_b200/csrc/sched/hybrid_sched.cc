@@ -112,15 +112,25 @@ extern "C" int32_t hgs_pick_split(const int32_t *home, int32_t n, int32_t device
 
 extern "C" int hgs_simulate(const hgs_sim_params *p, hgs_sim_result *out) {
   if (!p || !out || p->n_splits < 0 || p->iterations < 1 || p->cpu_slots < 0 || p->gpu_slots < 0 ||
-      p->gpu_slots > HGS_MAX_DEVICES || p->heartbeat_ms <= 0)
+      p->gpu_slots > HGS_MAX_DEVICES || p->heartbeat_ms <= 0 || !(p->task_jitter >= 0.0 && p->task_jitter < 1.0))
     return -22;
+  // task-time scale in [1 - jitter, 1 + jitter]: an integer hash, the same on every run
+  auto jitter = [p](int it, int task) {
+    uint32_t h = (uint32_t)it * 0x9E3779B9u ^ ((uint32_t)task + 0x7F4A7C15u) * 0x85EBCA6Bu;
+    h ^= h >> 15; h *= 0x2C1B3C6Du; h ^= h >> 12; h *= 0x297A2D39u; h ^= h >> 15;
+    return 1.0 + p->task_jitter * ((double)h / 2147483648.0 - 1.0);
+  };
   *out = hgs_sim_result{};
   struct Running { double finish; bool gpu; int dev; double start; };
   auto later = [](const Running &a, const Running &b) { return a.finish > b.finish; };
   double now = 0.0;
+  std::vector<int32_t> home((size_t)p->n_splits, -1);  // device whose HBM cache holds the split
+  std::vector<int32_t> pending, pending_home;
   for (int it = 0; it < p->iterations; ++it) {
     std::priority_queue<Running, std::vector<Running>, decltype(later)> running(later);
     int finished = 0, started = 0;
+    pending.resize((size_t)p->n_splits);
+    for (int i = 0; i < p->n_splits; ++i) pending[(size_t)i] = i;
     long long cpu_time = 0, gpu_time = 0;  // integer milliseconds like JobInProgress sums them
     int cpu_done = 0, gpu_done = 0;
     uint32_t busy = 0;
@@ -152,12 +162,29 @@ extern "C" int hgs_simulate(const hgs_sim_params *p, hgs_sim_result *out) {
       out->cpu_pass_skips += d.cpu_pass_skipped;
       out->last_acceleration = d.acceleration;
       for (int i = 0; i < d.n_cpu; ++i) {
-        running.push(Running{now + p->task_overhead_ms + p->cpu_task_ms, false, -1, now});
+        pending.erase(pending.begin());  // a CPU slot takes the next split; it stays where it was cached
+        running.push(Running{now + p->task_overhead_ms + p->cpu_task_ms * jitter(it, started), false, -1, now});
         ++run_cpu; ++started; ++out->tasks_cpu;
       }
       for (int i = 0; i < d.n_gpu; ++i) {
-        running.push(Running{now + p->task_overhead_ms + gpu_ms, true, d.gpu_device[i], now});
-        busy |= 1u << d.gpu_device[i];
+        const int dev = d.gpu_device[i];
+        size_t at = 0;
+        if (p->per_device_cache && p->device_affinity) {
+          pending_home.resize(pending.size());
+          for (size_t j = 0; j < pending.size(); ++j) pending_home[j] = home[(size_t)pending[j]];
+          at = (size_t)hgs_pick_split(pending_home.data(), (int32_t)pending_home.size(), dev, p->gpu_slots);
+        }
+        const int32_t split = pending[at];
+        pending.erase(pending.begin() + (long)at);
+        double ms = gpu_ms;
+        if (p->per_device_cache) {
+          const bool hit = home[(size_t)split] == dev;
+          ms = hit ? p->gpu_task_ms_cached : p->gpu_task_ms_first;
+          out->gpu_cache_hits += hit;
+          home[(size_t)split] = dev;
+        }
+        running.push(Running{now + p->task_overhead_ms + ms * jitter(it, started), true, dev, now});
+        busy |= 1u << dev;
         ++run_gpu; ++started; ++out->tasks_gpu;
       }
       if (running.empty() && started >= p->n_splits) break;

@@ -31,13 +31,14 @@ class SimParams(C.Structure):
                 ("gpu_slots", C.c_int32), ("cpu_task_ms", C.c_double), ("gpu_task_ms_first", C.c_double),
                 ("gpu_task_ms_cached", C.c_double), ("task_overhead_ms", C.c_double), ("heartbeat_ms", C.c_double),
                 ("out_of_band_heartbeat", C.c_int32), ("optional_scheduling", C.c_int32), ("fixes", C.c_int32),
-                ("prior_acceleration", C.c_double)]
+                ("prior_acceleration", C.c_double), ("per_device_cache", C.c_int32), ("device_affinity", C.c_int32),
+                ("task_jitter", C.c_double)]
 
 
 class SimResult(C.Structure):
     _fields_ = [("makespan_ms", C.c_double), ("tasks_cpu", C.c_int64), ("tasks_gpu", C.c_int64),
                 ("heartbeats", C.c_int64), ("cpu_pass_skips", C.c_int64), ("last_acceleration", C.c_double),
-                ("points_per_sec", C.c_double)]
+                ("points_per_sec", C.c_double), ("gpu_cache_hits", C.c_int64)]
 
 
 _LIB = None

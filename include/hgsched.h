@@ -97,6 +97,15 @@ typedef struct {
   int32_t out_of_band_heartbeat; /* 1 = also heartbeat when a task finishes            */
   int32_t optional_scheduling, fixes;
   double prior_acceleration; /* handed to every job when HGS_FIX_PRIOR_ACCEL is set */
+  int32_t per_device_cache;  /* 0: every split is resident from iteration 2 on, whichever slot maps it
+                                (one cache per node); 1: a split is resident on the device that mapped it
+                                last (one HBM cache per slot's worker) -- a task on another device takes
+                                gpu_task_ms_first again and moves the split there */
+  int32_t device_affinity;   /* with per_device_cache: 0 = next split to the first free device, as the
+                                reference does; 1 = hgs_pick_split chooses the split for the device */
+  double task_jitter;        /* 0..1: every task time is scaled by 1 +- task_jitter (a fixed hash of
+                                iteration and task number, so runs repeat); without it equal task times
+                                hand device j the same splits every iteration by accident */
 } hgs_sim_params;
 
 typedef struct {
@@ -104,6 +113,7 @@ typedef struct {
   int64_t tasks_cpu, tasks_gpu, heartbeats, cpu_pass_skips;
   double last_acceleration;
   double points_per_sec;     /* filled by the caller's points-per-split if > 0 */
+  int64_t gpu_cache_hits;    /* GPU tasks that found their split resident (per_device_cache only) */
 } hgs_sim_result;
 
 int hgs_simulate(const hgs_sim_params *params, hgs_sim_result *out);

@@ -172,3 +172,23 @@ def test_device_affine_picks_keep_iteration_two_in_the_hbm_caches():
     hits_aff, _ = run_iteration(home, affine=True, seed=2)
     assert hits_aff >= 0.9 * n_splits                         # misses only where a device ran out of its own early
     assert hits_ref <= 0.3 * n_splits
+
+
+def test_simulation_per_device_cache_and_affinity():
+    """One HBM cache per slot's worker: as the reference orders tasks (next split to the first free device)
+    iteration 2 finds few splits at home and stages the rest again; with hgs_pick_split nearly all are hits.
+    per_device_cache=0 keeps the older one-cache-per-node behaviour."""
+    base = dict(n_splits=128, iterations=3, cpu_slots=0, gpu_slots=8, cpu_task_ms=11000.0, gpu_task_ms_first=6.8,
+                gpu_task_ms_cached=2.2, task_overhead_ms=0.0, heartbeat_ms=3000.0, out_of_band_heartbeat=1,
+                optional_scheduling=1, fixes=0, prior_acceleration=0.0, task_jitter=0.3)
+    node = sched.simulate(**base)
+    ref = sched.simulate(per_device_cache=1, device_affinity=0, **base)
+    aff = sched.simulate(per_device_cache=1, device_affinity=1, **base)
+    assert node.gpu_cache_hits == 0 and node.tasks_gpu == ref.tasks_gpu == aff.tasks_gpu == 3 * 128
+    assert aff.gpu_cache_hits >= 0.9 * 2 * 128
+    assert ref.gpu_cache_hits < aff.gpu_cache_hits
+    assert aff.makespan_ms < ref.makespan_ms
+    assert abs(aff.makespan_ms - node.makespan_ms) < 0.1 * node.makespan_ms
+    # CPU slots take splits too and leave them where they were cached
+    mixed = sched.simulate(per_device_cache=1, device_affinity=1, **{**base, "cpu_slots": 2, "cpu_task_ms": 50.0})
+    assert mixed.tasks_cpu > 0 and mixed.tasks_cpu + mixed.tasks_gpu == 3 * 128

@@ -3,7 +3,7 @@
 slots + host CPU slots on one TaskTracker) through the restated hybrid scheduler.
 
 This is a SIMULATION of the scheduling (libhgsched.so, include/hgsched.h) fed with per-task times
-MEASURED on the GPU box by bench.py (profiles/r01_v7_bench_line.json); no JVM exists in this
+MEASURED on the GPU box by bench.py (profiles/r01_v12_bench_line.json); no JVM exists in this
 environment, so no real TaskTracker can be run.  It answers what the reference's per-heartbeat,
 per-task-process design costs on this path, and what the persistent per-GPU worker removes
 (SURVEY.md section 7 H3).
@@ -26,7 +26,7 @@ ITERATIONS = 10
 
 
 def main():
-    path = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "profiles", "r01_v7_bench_line.json")
+    path = sys.argv[1] if len(sys.argv) > 1 else os.path.join(ROOT, "profiles", "r01_v12_bench_line.json")
     line = json.loads(open(path).read().strip().splitlines()[-1])
     gpu_resident = line["value"]                      # points/s, HBM-resident
     gpu_staged = line["e2e"]["value"]                 # points/s, split staged from pinned host memory
@@ -73,6 +73,25 @@ def main():
     print("|---|---|---|---|---|---|---|")
     for label, secs, pts, tc, tg, skips, hb in rows:
         print(f"| {label} | {secs:,.1f} | {pts / 1e9:.3f} G | {tc} | {tg} | {skips} | {hb} |")
+    # ---- one HBM split cache per GPU slot's worker: what device-level locality is worth on the full job ----
+    # whole-task times measured through real Pipes children against hgm-workers (profiles/r01_config3_job.md):
+    # 6.8 ms for a 64 MiB FileSplit staged from the page cache, 2.2 ms when the worker holds it
+    task_first_ms, task_cached_ms = 6.8, 2.2
+    per_dev = dict(n_splits=N_SPLITS, iterations=ITERATIONS, cpu_slots=0, gpu_slots=8, cpu_task_ms=cpu_ms,
+                   gpu_task_ms_first=task_first_ms, gpu_task_ms_cached=task_cached_ms, task_overhead_ms=0.0,
+                   heartbeat_ms=3000, out_of_band_heartbeat=1, optional_scheduling=1, fixes=0, prior_acceleration=0.0,
+                   per_device_cache=1, task_jitter=0.3)
+    print("\n## Eight GPU slots with one HBM split cache each (`per_device_cache`), whole-task times as measured "
+          f"({task_first_ms} ms staged, {task_cached_ms} ms from the worker's cache, +-30 % jitter)\n")
+    print("| split -> device | job time (s) | points/s | cache hits in iterations 2-10 |")
+    print("|---|---|---|---|")
+    for label, aff in (("as the reference assigns (next split to the first free device)", 0),
+                       ("`hgs_pick_split` (a slot is handed a split its worker holds)", 1)):
+        r = sched.simulate(device_affinity=aff, **per_dev)
+        pts = TOTAL_POINTS * ITERATIONS / (r.makespan_ms * 1e-3)
+        print(f"| {label} | {r.makespan_ms / 1e3:.2f} | {pts / 1e9:.1f} G | {r.gpu_cache_hits} of {N_SPLITS * (ITERATIONS - 1)} |")
+    print("\nThe same model at the measured job's size (128 splits, 3 iterations) gives 42 / 249 hits of 256 against 47 / 246 "
+          "measured on eight B200s (profiles/r01_config3_job.md), so the per-device-cache model is pinned by a measurement.")
     print("\nReading: with a 3 s heartbeat and a process launch per task, a GPU slot that maps a split in ~1 ms is idle "
           ">99.9 % of the time, and the CPU slots' 14 s tasks set the tail unless the acceleration-factor rule "
           "suppresses them -- and that rule starts every job with factor 0, so each iteration first fills the CPU slots "
