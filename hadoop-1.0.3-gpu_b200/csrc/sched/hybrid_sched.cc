@@ -84,6 +84,26 @@ extern "C" int hgs_assign(const hgs_job *jobs, int32_t n_jobs, const hgs_tracker
   return 0;
 }
 
+extern "C" int hgs_tracker_from_reports(const hgs_task_status *reports, int32_t n, int32_t max_cpu_slots,
+                                        int32_t max_gpu_slots, hgs_tracker *out) {
+  if (!out || n < 0 || (n > 0 && !reports) || max_cpu_slots < 0 || max_gpu_slots < 0 ||
+      max_gpu_slots > HGS_MAX_DEVICES)
+    return -22;
+  *out = hgs_tracker{max_cpu_slots, max_gpu_slots, 0, 0, 0u};
+  for (int i = 0; i < n; ++i) {
+    const hgs_task_status &ts = reports[i];
+    const bool cleanup = ts.cleanup_phase && (ts.run_state == HGS_STATE_FAILED_UNCLEAN ||
+                                              ts.run_state == HGS_STATE_KILLED_UNCLEAN);  // TaskStatus.java:242-246
+    const bool holds_slot = ts.run_state == HGS_STATE_RUNNING || ts.run_state == HGS_STATE_UNASSIGNED || cleanup;
+    if (!ts.is_map || !holds_slot) continue;
+    if (!ts.run_on_gpu) { ++out->running_cpu; continue; }
+    if (ts.gpu_device_id < 0 || ts.gpu_device_id >= max_gpu_slots) return -22;
+    ++out->running_gpu;
+    out->busy_devices |= 1u << ts.gpu_device_id;
+  }
+  return 0;
+}
+
 extern "C" int32_t hgs_pick_split(const int32_t *home, int32_t n, int32_t device, int32_t max_gpu_slots) {
   if (n < 0 || (n > 0 && !home) || max_gpu_slots < 1 || max_gpu_slots > HGS_MAX_DEVICES || device < 0 ||
       device >= max_gpu_slots)

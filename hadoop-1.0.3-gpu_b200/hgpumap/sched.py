@@ -21,6 +21,15 @@ class Tracker(C.Structure):
                 ("running_gpu", C.c_int32), ("busy_devices", C.c_uint32)]
 
 
+class TaskStatus(C.Structure):
+    _fields_ = [("is_map", C.c_int32), ("run_state", C.c_int32), ("cleanup_phase", C.c_int32),
+                ("run_on_gpu", C.c_int32), ("gpu_device_id", C.c_int32)]
+
+
+(STATE_RUNNING, STATE_SUCCEEDED, STATE_FAILED, STATE_UNASSIGNED, STATE_KILLED, STATE_COMMIT_PENDING,
+ STATE_FAILED_UNCLEAN, STATE_KILLED_UNCLEAN) = range(8)
+
+
 class Decision(C.Structure):
     _fields_ = [("n_cpu", C.c_int32), ("n_gpu", C.c_int32), ("gpu_device", C.c_int32 * MAX_DEVICES),
                 ("cpu_pass_skipped", C.c_int32), ("pending_map_load", C.c_int32), ("acceleration", C.c_double)]
@@ -56,6 +65,9 @@ def load() -> C.CDLL:
                                    C.c_int32, C.c_int32, C.POINTER(Decision)]
         lib.hgs_simulate.restype = C.c_int
         lib.hgs_simulate.argtypes = [C.POINTER(SimParams), C.POINTER(SimResult)]
+        lib.hgs_tracker_from_reports.restype = C.c_int
+        lib.hgs_tracker_from_reports.argtypes = [C.POINTER(TaskStatus), C.c_int32, C.c_int32, C.c_int32,
+                                                 C.POINTER(Tracker)]
         lib.hgs_pick_split.restype = C.c_int32
         lib.hgs_pick_split.argtypes = [C.POINTER(C.c_int32), C.c_int32, C.c_int32, C.c_int32]
         _LIB = lib
@@ -89,3 +101,14 @@ def pick_split(home_device: list[int], device: int, max_gpu_slots: int) -> int:
     if rc < -1:
         raise ValueError(f"hgs_pick_split returned {rc}")
     return rc
+
+
+def tracker_from_reports(reports: list[TaskStatus], max_cpu_slots: int, max_gpu_slots: int) -> Tracker:
+    """The heartbeat's slot accounting (TaskTrackerStatus.countCPUMapTasks / countGPUMapTasks /
+    availableGPUDevices) over its task reports."""
+    arr = (TaskStatus * max(len(reports), 1))(*reports)
+    out = Tracker()
+    rc = load().hgs_tracker_from_reports(arr, len(reports), max_cpu_slots, max_gpu_slots, C.byref(out))
+    if rc != 0:
+        raise ValueError(f"hgs_tracker_from_reports returned {rc}")
+    return out

@@ -45,6 +45,33 @@ typedef struct {
   uint32_t busy_devices;   /* bit j set = device j runs a GPU map      */
 } hgs_tracker;
 
+/* One entry of a heartbeat's task reports (mapred/TaskStatus.java: runState :46-47, phase :43,
+ * runOnGPU / GPUDeviceId :66-67, 390-395 -- the two fields the fork added to the wire format, :417-418). */
+#define HGS_STATE_RUNNING 0
+#define HGS_STATE_SUCCEEDED 1
+#define HGS_STATE_FAILED 2
+#define HGS_STATE_UNASSIGNED 3
+#define HGS_STATE_KILLED 4
+#define HGS_STATE_COMMIT_PENDING 5
+#define HGS_STATE_FAILED_UNCLEAN 6
+#define HGS_STATE_KILLED_UNCLEAN 7
+typedef struct {
+  int32_t is_map;         /* getIsMap()                                               */
+  int32_t run_state;      /* HGS_STATE_*                                              */
+  int32_t cleanup_phase;  /* phase == CLEANUP (inTaskCleanupPhase needs *_UNCLEAN too) */
+  int32_t run_on_gpu;     /* runOnGPU()                                               */
+  int32_t gpu_device_id;  /* GPUDeviceId()                                            */
+} hgs_task_status;
+
+/* The GPU-slot accounting of a heartbeat: countCPUMapTasks / countGPUMapTasks / availableGPUDevices of
+ * mapred/TaskTrackerStatus.java:504-551 over the task reports.  A map task occupies its slot (and a GPU
+ * task its device: slot i <-> device i) while RUNNING, UNASSIGNED, or in the cleanup phase of a
+ * *_UNCLEAN state (:524-528, 541-545).  Fills max_*_slots, running_cpu, running_gpu and busy_devices of
+ * *out.  Returns 0; -22 on a bad argument or a GPU task whose device id is outside 0..max_gpu_slots-1
+ * (the Java indexes a boolean[maxGPUMapSlots] with it, :546, and would throw). */
+int hgs_tracker_from_reports(const hgs_task_status *reports, int32_t n_reports, int32_t max_cpu_slots,
+                             int32_t max_gpu_slots, hgs_tracker *out);
+
 /* Behaviour switches.  All 0 = the reference as written, quirks included. */
 #define HGS_FIX_PENDING 1     /* pendingMapLoad per job instead of the running total (:139)        */
 #define HGS_FIX_PER_JOB_ACCEL 2 /* factor from every job's times, not only the last job's (:143-144) */

@@ -111,7 +111,7 @@ def test_hgsched_header_symbols_are_exported():
     text = open(os.path.join(ROOT, "include", "hgsched.h")).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
     names = sorted(set(re.findall(r"\b(hgs_[a-z_]+)\s*\(", text)))
-    assert names == ["hgs_assign", "hgs_pick_split", "hgs_simulate"]
+    assert names == ["hgs_assign", "hgs_pick_split", "hgs_simulate", "hgs_tracker_from_reports"]
     lib = sched.load()
     for name in names:
         assert hasattr(lib, name)
@@ -192,3 +192,28 @@ def test_simulation_per_device_cache_and_affinity():
     # CPU slots take splits too and leave them where they were cached
     mixed = sched.simulate(per_device_cache=1, device_affinity=1, **{**base, "cpu_slots": 2, "cpu_task_ms": 50.0})
     assert mixed.tasks_cpu > 0 and mixed.tasks_cpu + mixed.tasks_gpu == 3 * 128
+
+
+def test_tracker_accounting_from_task_reports():
+    """TaskTrackerStatus.java:504-551: a map task holds its slot (a GPU task its device) while RUNNING,
+    UNASSIGNED or cleaning up after an *_UNCLEAN end; reduces and finished tasks do not count."""
+    TS = sched.TaskStatus
+    reports = [
+        TS(1, sched.STATE_RUNNING, 0, 0, 0),          # CPU map, running
+        TS(1, sched.STATE_UNASSIGNED, 0, 1, 2),       # GPU map on device 2, launching
+        TS(1, sched.STATE_SUCCEEDED, 0, 1, 0),        # finished GPU map: device 0 is free again
+        TS(1, sched.STATE_FAILED_UNCLEAN, 1, 1, 5),   # GPU map in task cleanup: still holds device 5
+        TS(1, sched.STATE_KILLED_UNCLEAN, 0, 1, 6),   # *_UNCLEAN but not in the cleanup phase: released
+        TS(1, sched.STATE_COMMIT_PENDING, 0, 0, 0),   # not counted by the fork's getters (:524-528)
+        TS(0, sched.STATE_RUNNING, 0, 0, 0),          # a reduce
+    ]
+    tt = sched.tracker_from_reports(reports, 3, 8)
+    assert (tt.max_cpu_slots, tt.max_gpu_slots, tt.running_cpu, tt.running_gpu) == (3, 8, 1, 2)
+    assert tt.busy_devices == (1 << 2) | (1 << 5)
+    # the scheduler then hands out the free devices in id order
+    d = sched.assign([job()], tt)
+    assert d.n_cpu == 2 and list(d.gpu_device[:d.n_gpu]) == [0, 1, 3, 4, 6, 7]
+    # a device id outside the slot range indexes past boolean[maxGPUMapSlots] in the Java (:546)
+    with pytest.raises(ValueError):
+        sched.tracker_from_reports([TS(1, sched.STATE_RUNNING, 0, 1, 8)], 3, 8)
+    assert sched.tracker_from_reports([], 2, 0).busy_devices == 0
