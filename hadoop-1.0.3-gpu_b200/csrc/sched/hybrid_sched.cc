@@ -104,6 +104,20 @@ extern "C" int hgs_tracker_from_reports(const hgs_task_status *reports, int32_t 
   return 0;
 }
 
+extern "C" int32_t hgs_mean_map_time_ms(const int64_t *start_ms, const int64_t *finish_ms, const int32_t *ran_on_gpu,
+                                        int32_t n, int32_t want_gpu) {
+  if (n < 0 || (n > 0 && (!start_ms || !finish_ms || !ran_on_gpu))) return -22;
+  uint32_t total = 0;  // Java int arithmetic: two's-complement wrap, done unsigned here to stay defined
+  int32_t tasks = 0;
+  for (int i = 0; i < n; ++i) {
+    if (finish_ms[i] == 0 || (ran_on_gpu[i] != 0) != (want_gpu != 0)) continue;
+    total += (uint32_t)(uint64_t)(finish_ms[i] - start_ms[i]);  // totalTime += (int)(long difference)
+    ++tasks;
+  }
+  if (tasks == 0) return 0;
+  return (int32_t)total / tasks;  // Java's int division truncates toward zero, like C's
+}
+
 extern "C" int32_t hgs_pick_split(const int32_t *home, int32_t n, int32_t device, int32_t max_gpu_slots) {
   if (n < 0 || (n > 0 && !home) || max_gpu_slots < 1 || max_gpu_slots > HGS_MAX_DEVICES || device < 0 ||
       device >= max_gpu_slots)

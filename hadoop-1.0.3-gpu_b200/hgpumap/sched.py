@@ -68,6 +68,9 @@ def load() -> C.CDLL:
         lib.hgs_tracker_from_reports.restype = C.c_int
         lib.hgs_tracker_from_reports.argtypes = [C.POINTER(TaskStatus), C.c_int32, C.c_int32, C.c_int32,
                                                  C.POINTER(Tracker)]
+        lib.hgs_mean_map_time_ms.restype = C.c_int32
+        lib.hgs_mean_map_time_ms.argtypes = [C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int32),
+                                             C.c_int32, C.c_int32]
         lib.hgs_pick_split.restype = C.c_int32
         lib.hgs_pick_split.argtypes = [C.POINTER(C.c_int32), C.c_int32, C.c_int32, C.c_int32]
         _LIB = lib
@@ -112,3 +115,12 @@ def tracker_from_reports(reports: list[TaskStatus], max_cpu_slots: int, max_gpu_
     if rc != 0:
         raise ValueError(f"hgs_tracker_from_reports returned {rc}")
     return out
+
+
+def mean_map_time_ms(start_ms: list[int], finish_ms: list[int], ran_on_gpu: list[bool], want_gpu: bool) -> int:
+    """JobInProgress.getCPUMapTaskMeanTime / getGPUMapTaskMeanTime with their Java int arithmetic."""
+    n = len(start_ms)
+    a = (C.c_int64 * max(n, 1))(*start_ms)
+    b = (C.c_int64 * max(n, 1))(*finish_ms)
+    g = (C.c_int32 * max(n, 1))(*[int(x) for x in ran_on_gpu])
+    return load().hgs_mean_map_time_ms(a, b, g, n, int(want_gpu))

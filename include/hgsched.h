@@ -72,6 +72,14 @@ typedef struct {
 int hgs_tracker_from_reports(const hgs_task_status *reports, int32_t n_reports, int32_t max_cpu_slots,
                              int32_t max_gpu_slots, hgs_tracker *out);
 
+/* get{CPU,GPU}MapTaskMeanTime of mapred/JobInProgress.java:527-565: over the map task reports whose
+ * finish time is not 0 and whose successful attempt ran on the wanted kind of slot, the mean of
+ * finish - start in milliseconds -- summed in a Java `int` (the compound assignment narrows each long
+ * difference and the sum wraps at 2^31) and divided as integers; 0 when no such task has finished.
+ * These two numbers are all the scheduler knows about task speed (hgs_job.cpu_mean_ms / gpu_mean_ms). */
+int32_t hgs_mean_map_time_ms(const int64_t *start_ms, const int64_t *finish_ms, const int32_t *ran_on_gpu,
+                             int32_t n_reports, int32_t want_gpu);
+
 /* Behaviour switches.  All 0 = the reference as written, quirks included. */
 #define HGS_FIX_PENDING 1     /* pendingMapLoad per job instead of the running total (:139)        */
 #define HGS_FIX_PER_JOB_ACCEL 2 /* factor from every job's times, not only the last job's (:143-144) */

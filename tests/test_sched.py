@@ -111,7 +111,7 @@ def test_hgsched_header_symbols_are_exported():
     text = open(os.path.join(ROOT, "include", "hgsched.h")).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
     names = sorted(set(re.findall(r"\b(hgs_[a-z_]+)\s*\(", text)))
-    assert names == ["hgs_assign", "hgs_pick_split", "hgs_simulate", "hgs_tracker_from_reports"]
+    assert names == ["hgs_assign", "hgs_mean_map_time_ms", "hgs_pick_split", "hgs_simulate", "hgs_tracker_from_reports"]
     lib = sched.load()
     for name in names:
         assert hasattr(lib, name)
@@ -217,3 +217,20 @@ def test_tracker_accounting_from_task_reports():
     with pytest.raises(ValueError):
         sched.tracker_from_reports([TS(1, sched.STATE_RUNNING, 0, 1, 8)], 3, 8)
     assert sched.tracker_from_reports([], 2, 0).busy_devices == 0
+
+
+def test_mean_map_times_use_java_int_arithmetic():
+    """JobInProgress.java:527-565: finished tasks of the wanted kind only, integer milliseconds, int sum."""
+    t0 = 1_700_000_000_000
+    start = [t0, t0 + 10, t0 + 20, t0 + 30, t0 + 40]
+    finish = [t0 + 4000, t0 + 10 + 151, 0, t0 + 30 + 100, t0 + 40 + 5001]   # the third has not finished
+    gpu = [False, True, True, True, False]
+    assert sched.mean_map_time_ms(start, finish, gpu, want_gpu=False) == (4000 + 5001) // 2
+    assert sched.mean_map_time_ms(start, finish, gpu, want_gpu=True) == (151 + 100) // 2      # 125, not 125.5
+    assert sched.mean_map_time_ms([], [], [], want_gpu=True) == 0
+    assert sched.mean_map_time_ms([t0], [0], [True], want_gpu=True) == 0
+    # a GPU task shorter than a millisecond counts as 0 ms: the acceleration factor stays 0 (:175-177)
+    assert sched.mean_map_time_ms([t0, t0], [t0, t0], [True, True], want_gpu=True) == 0
+    # the int sum wraps: three tasks of 2^30 ms sum to -2^30 in a Java int
+    big = 1 << 30
+    assert sched.mean_map_time_ms([0, 0, 0], [big, big, big], [False] * 3, want_gpu=False) == -(1 << 30) // 3 + (1 if (-(1 << 30)) % 3 else 0)
