@@ -5,7 +5,10 @@
 // the downlink (START, SET_JOB_CONF, SET_INPUT_TYPES, RUN_MAP, MAP_ITEM..., CLOSE | RUN_REDUCE,
 // REDUCE_KEY, REDUCE_VALUE..., CLOSE | ABORT) and report on the uplink (OUTPUT,
 // PARTITIONED_OUTPUT, STATUS, PROGRESS, REGISTER/INCREMENT_COUNTER, DONE).  Codes and
-// framing: pipes/BinaryProtocol.java:66-84 and :262-368.  Behaviour restated from
+// framing: pipes/BinaryProtocol.java:66-84 and :262-368.  The reference's two debugging modes are here
+// as well: replay of a downlink file ($hadoop.pipes.command.file -> <file>.out, HadoopPipes.cc:1130-1136)
+// and, with neither variable set, the line-oriented text protocol on stdin/stdout (:181-295, 1137-1139),
+// byte for byte including its quirks (tests/test_pipes_runtime.py).  Behaviour restated from
 // c++/pipes/impl/HadoopPipes.cc (cited per function); none of its code is used.
 //
 // Differences that matter for a GPU child, all invisible on the wire:
@@ -213,6 +216,17 @@ class FdIn : public InStream {
 
  public:
   explicit FdIn(int fd) : fd_(fd), buf_(1 << 20) {}
+  // one byte, or -1 at end of file (the text protocol reads with getc, HadoopPipes.cc:189-199)
+  int getByte() {
+    while (lo_ == hi_) {
+      const ssize_t got = ::read(fd_, buf_.data(), buf_.size());
+      if (got < 0 && errno == EINTR) continue;
+      HADOOP_ASSERT(got >= 0, string("read error on command stream: ") + strerror(errno));
+      if (got == 0) return -1;
+      lo_ = 0; hi_ = (size_t)got;
+    }
+    return buf_[lo_++];
+  }
   void read(void *dst, size_t len) override {
     unsigned char *out = static_cast<unsigned char *>(dst);
     while (len) {
@@ -263,48 +277,73 @@ class FdOut : public OutStream {
   }
 };
 
-// ---- uplink (HadoopPipes.cc:302-366) ---------------------------------------------------------
+// ---- uplink: binary (HadoopPipes.cc:302-366) or, for a child started by hand with neither a command
+// port nor a command file, the text lines of TextUpwardProtocol (HadoopPipes.cc:122-179) ------------------
 class Uplink {
   FdOut out_;
+  bool text_ = false;
+
+  void put(const string &s) { out_.write(s.data(), s.size()); }
+  // keys and values are quoted (tab, newline, backslash, unprintables); the reference passes the quoted
+  // string to fprintf as the FORMAT (HadoopPipes.cc:128-130), so a '%' in a key is undefined there --
+  // it is written as it is here
+  void putQuoted(const string &s) { put(quoteString(s, "\t\n")); }
+  template <class... A>
+  void putf(const char *fmt, A... a) {
+    char buf[96];
+    const int n = snprintf(buf, sizeof buf, fmt, a...);
+    out_.write(buf, (size_t)n);
+  }
 
  public:
   explicit Uplink(int fd) : out_(fd) {}
+  void setText() { text_ = true; }
   void authenticate(const string &digest) {
     serializeInt(AUTHENTICATION_RESP, out_);
     serializeString(digest, out_);
     out_.flush();
   }
   void output(const string &k, const string &v) {
+    if (text_) { put("output\t"); putQuoted(k); put("\t"); putQuoted(v); put("\n"); return; }
     serializeInt(OUTPUT, out_);
     serializeString(k, out_);
     serializeString(v, out_);
   }
   void partitionedOutput(int reduce, const string &k, const string &v) {
+    if (text_) {  // the word is misspelt in the reference (HadoopPipes.cc:145) and a reader of it expects that
+      putf("parititionedOutput\t%d\t", reduce); putQuoted(k); put("\t"); putQuoted(v); put("\n");
+      return;
+    }
     serializeInt(PARTITIONED_OUTPUT, out_);
     serializeInt(reduce, out_);
     serializeString(k, out_);
     serializeString(v, out_);
   }
   void status(const string &msg) {
+    if (text_) { put("status\t" + msg + "\n"); return; }
     serializeInt(STATUS, out_);
     serializeString(msg, out_);
   }
   void progress(float p) {
+    if (text_) { putf("progress\t%f\n", (double)p); out_.flush(); return; }
     serializeInt(PROGRESS, out_);
     serializeFloat(p, out_);
     out_.flush();
   }
   void done() {
-    serializeInt(DONE, out_);
+    if (text_) put("done\n");
+    else serializeInt(DONE, out_);
     out_.flush();
   }
   void registerCounter(int id, const string &group, const string &name) {
+    if (text_) { putf("registerCounter\t%d\t", id); put(group + "\t" + name + "\n"); return; }
     serializeInt(REGISTER_COUNTER, out_);
     serializeInt(id, out_);
     serializeString(group, out_);
     serializeString(name, out_);
   }
   void incrementCounter(int id, uint64_t amount) {
+    if (text_) { putf("incrCounter\t%d\t%ld\n", id, (long)amount); return; }
     serializeInt(INCREMENT_COUNTER, out_);
     serializeInt(id, out_);
     serializeLong((int64_t)amount, out_);
@@ -389,7 +428,11 @@ class Task : public MapContext, public ReduceContext {
   bool statusSet = false;
   int nextCounterId = 0;
 
-  Task(const Factory &f, int inFd, int outFd) : factory(f), in(inFd), up(outFd) {
+  bool text = false;  // TextProtocol on stdin/stdout (HadoopPipes.cc:181-295, 1137-1139)
+
+  Task(const Factory &f, int inFd, int outFd, bool textProtocol = false)
+      : factory(f), in(inFd), up(outFd), text(textProtocol) {
+    if (text) up.setText();
     if (const char *path = getenv("hadoop.pipes.shared.secret.location")) {  // HadoopPipes.cc:375-393
       if (FILE *fp = fopen(path, "rb")) {
         char buf[512];
@@ -415,8 +458,110 @@ class Task : public MapContext, public ReduceContext {
     pthread_mutex_unlock(&doneLock);
   }
 
+  // text protocol: bytes up to a tab or newline; returns the separator, -1 at end of file.  Nothing is
+  // unquoted on the way in (HadoopPipes.cc:189-199), only the uplink quotes.
+  int readUpto(string &buffer) {
+    buffer.clear();
+    int ch;
+    while ((ch = in.getByte()) != -1) {
+      if (ch == '\t' || ch == '\n') return ch;
+      buffer += (char)ch;
+    }
+    return -1;
+  }
+  void wantSep(int sep, int wanted, const string &command) {
+    if (sep != wanted) throw Error(string(wanted == '\t' ? "Short" : "Long") + " text protocol command " + command);
+  }
+  // one line of the text downlink (HadoopPipes.cc:214-289): no authentication in this mode
+  void nextTextEvent() {
+    string command, arg;
+    int sep = readUpto(command);
+    if (command == "mapItem") {
+      wantSep(sep, '\t', command);
+      sep = readUpto(pendingKey);
+      wantSep(sep, '\t', command);
+      sep = readUpto(value);
+      wantSep(sep, '\n', command);
+      havePendingKey = true;
+    } else if (command == "reduceValue") {
+      wantSep(sep, '\t', command);
+      sep = readUpto(value);
+      wantSep(sep, '\n', command);
+      haveNewValue = true;
+    } else if (command == "reduceKey") {
+      wantSep(sep, '\t', command);
+      sep = readUpto(pendingKey);
+      wantSep(sep, '\n', command);
+      havePendingKey = true;
+    } else if (command == "start") {
+      wantSep(sep, '\t', command);
+      sep = readUpto(arg);
+      wantSep(sep, '\n', command);
+      const int version = toInt(arg);
+      if (version != 0) throw Error("Protocol version " + toString(version) + " not supported");
+    } else if (command == "setJobConf") {
+      wantSep(sep, '\t', command);
+      sep = readUpto(arg);
+      const int len = toInt(arg);
+      // as the reference builds it: `len` empty strings, then the `len` values read (HadoopPipes.cc:244-250),
+      // paired off two by two -- so an odd `len` pairs ("", first) and shifts the rest
+      vector<string> values((size_t)std::max(len, 0));
+      for (int i = 0; i < len; ++i) {
+        wantSep(sep, '\t', command);
+        sep = readUpto(arg);
+        values.push_back(arg);
+      }
+      wantSep(sep, '\n', command);
+      conf.reset(new Conf());
+      for (size_t i = 0; i + 1 < values.size(); i += 2) conf->set(values[i], values[i + 1]);
+    } else if (command == "setInputTypes") {
+      wantSep(sep, '\t', command);
+      sep = readUpto(keyClass);
+      wantSep(sep, '\t', command);
+      sep = readUpto(valueClass);
+      wantSep(sep, '\n', command);
+    } else if (command == "runMap") {
+      string reduces;
+      wantSep(sep, '\t', command);
+      sep = readUpto(split);
+      wantSep(sep, '\t', command);
+      sep = readUpto(reduces);
+      wantSep(sep, '\t', command);
+      sep = readUpto(arg);
+      wantSep(sep, '\n', command);
+      numReduces = toInt(reduces);
+      startMap(toBool(arg));
+    } else if (command == "runReduce") {
+      string piped;
+      wantSep(sep, '\t', command);
+      sep = readUpto(arg);
+      wantSep(sep, '\t', command);
+      sep = readUpto(piped);
+      wantSep(sep, '\n', command);
+      toInt(arg);  // partition number: informational
+      startReduce(toBool(piped));
+    } else if (command == "abort") {
+      wantSep(sep, '\n', command);
+      throw Error("Aborted by driver");
+    } else if (command == "close") {
+      wantSep(sep, '\n', command);
+      markDone();
+    } else {
+      throw Error("Illegal text protocol command " + command);
+    }
+  }
+
+  void startReduce(bool piped) {  // HadoopPipes.cc:817-826
+    reducer.reset(factory.createReducer(*this));
+    writer.reset(factory.createRecordWriter(*this));
+    HADOOP_ASSERT((writer == nullptr) == piped,
+                  piped ? "RecordWriter defined when not needed." : "RecordWriter not defined");
+    hasTask = true;
+  }
+
   // one downlink message (HadoopPipes.cc:464-552)
   void nextEvent() {
+    if (text) return nextTextEvent();
     const int32_t cmd = deserializeInt(in);
     if (!authenticated && cmd != AUTHENTICATION_REQ) {
       fprintf(stderr, "Command:%d received before authentication. Exiting..\n", cmd);
@@ -473,11 +618,7 @@ class Task : public MapContext, public ReduceContext {
       case RUN_REDUCE: {
         deserializeInt(in);  // partition number: informational
         const bool piped = deserializeInt(in) != 0;
-        reducer.reset(factory.createReducer(*this));
-        writer.reset(factory.createRecordWriter(*this));
-        HADOOP_ASSERT((writer == nullptr) == piped,
-                      piped ? "RecordWriter defined when not needed." : "RecordWriter not defined");
-        hasTask = true;
+        startReduce(piped);
         break;
       }
       case REDUCE_KEY:
@@ -669,6 +810,7 @@ void *keepAlive(void *arg) {
 // HadoopPipes.cc:1093-1179
 bool runTask(const Factory &factory) {
   int inFd = -1, outFd = -1, sock = -1;
+  bool textProtocol = false;
   try {
     if (const char *portStr = getenv("hadoop.pipes.command.port")) {
       sock = socket(PF_INET, SOCK_STREAM, 0);
@@ -686,11 +828,12 @@ bool runTask(const Factory &factory) {
       const string outName = string(file) + ".out";
       outFd = open(outName.c_str(), O_WRONLY | O_CREAT | O_TRUNC, 0644);
       HADOOP_ASSERT(outFd >= 0, "cannot create " + outName + ": " + strerror(errno));
-    } else {
-      throw Error("neither hadoop.pipes.command.port nor hadoop.pipes.command.file is set; "
-                  "the text protocol on stdin/stdout is not provided by this runtime");
+    } else {  // started by hand: the text protocol on stdin/stdout (HadoopPipes.cc:1137-1139)
+      inFd = STDIN_FILENO;
+      outFd = STDOUT_FILENO;
+      textProtocol = true;
     }
-    Task task(factory, inFd, outFd);
+    Task task(factory, inFd, outFd, textProtocol);
     pthread_t pinger;
     pthread_create(&pinger, nullptr, keepAlive, &task);
     bool ok = true;
@@ -710,7 +853,7 @@ bool runTask(const Factory &factory) {
     if (sock != -1) {
       shutdown(sock, SHUT_RDWR);
       close(sock);
-    } else {
+    } else if (!textProtocol) {
       close(inFd);
       close(outFd);
     }

@@ -121,3 +121,68 @@ def test_socket_mode_rejects_a_wrong_digest():
     rc, uplink, err, _ = ph.run_child_over_socket(_bin("wordcount-part-hgmrt"), body, bad_digest=True)
     assert b"Server failed to authenticate" in err and rc not in (0, 1)
     assert uplink == b""
+
+
+# ---- the text protocol: a child started by hand, neither command port nor command file -------------
+# (HadoopPipes.cc:1137-1139 -> TextProtocol :181-295, TextUpwardProtocol :122-179)
+
+TEXT_MAP = (b"start\t0\nsetJobConf\t2\tmapred.reduce.tasks\t2\nsetInputTypes\tk\tv\nrunMap\tsplit\t2\ttrue\n"
+            b"mapItem\t0\thello world hello\nmapItem\t12\tone two back\\slash  three \x01ctl caf\xc3\xa9\nclose\n")
+TEXT_REDUCE = (b"start\t0\nsetJobConf\t2\tmapred.reduce.tasks\t1\nsetInputTypes\tk\tv\nrunReduce\t0\ttrue\n"
+               b"reduceKey\tapple\nreduceValue\t1\nreduceValue\t41\nreduceKey\ttab\\there\nreduceValue\t7\nclose\n")
+TEXT_CASES = {
+    "map + combiner + partitioner": ("wordcount-part", TEXT_MAP),
+    "reduce": ("wordcount-simple", TEXT_REDUCE),
+    "odd setJobConf count": ("wordcount-simple", b"start\t0\nsetJobConf\t3\ta\tb\tc\nsetInputTypes\tk\tv\n"
+                                                  b"runMap\ts\t0\ttrue\nmapItem\t0\tx y\nclose\n"),
+    "abort": ("wordcount-part", b"start\t0\nabort\n"),
+    "short command": ("wordcount-part", b"start\t0\nsetInputTypes\tk\n"),
+    "long command": ("wordcount-part", b"start\t0\nsetInputTypes\tk\tv\textra\n"),
+    "illegal command": ("wordcount-part", b"start\t0\nbogus\n"),
+    "end of file": ("wordcount-part", b"start\t0\n"),
+    "bad version": ("wordcount-part", b"start\t3\n"),
+}
+
+
+@pytest.fixture(scope="module")
+def text_runs():
+    """Every case on both runtimes at once (the reference joins its ping thread for 5 s per child)."""
+    import subprocess
+
+    procs = {}
+    for name, (prog, stdin) in TEXT_CASES.items():
+        for rt, binary in (("ref", _bin(prog)), ("ours", _bin(prog + "-hgmrt"))):
+            p = subprocess.Popen([binary], env={}, stdin=subprocess.PIPE, stdout=subprocess.PIPE, stderr=subprocess.PIPE)
+            p.stdin.write(stdin)
+            p.stdin.close()
+            procs[name, rt] = p
+    out = {}
+    for key, p in procs.items():
+        stdout, stderr = p.stdout.read(), p.stderr.read()
+        p.wait(timeout=60)
+        out[key] = (p.returncode, stdout, stderr)
+    return out
+
+
+@pytest.mark.parametrize("name", list(TEXT_CASES))
+def test_text_protocol_same_bytes_and_outcome_as_the_reference_runtime(text_runs, name):
+    ref, ours = text_runs[name, "ref"], text_runs[name, "ours"]
+    assert ours[1] == ref[1], f"uplink text differs:\n{ours[1]!r}\n{ref[1]!r}"
+    assert ours[0] == ref[0]  # `return runTask(...)`: 1 = done, 0 = Hadoop Pipes Exception
+    failed = b"Hadoop Pipes Exception" in ref[2]
+    assert (b"Hadoop Pipes Exception" in ours[2]) == failed
+    if failed:  # same complaint; the reference appends its own file:line
+        msg = ref[2].split(b"Hadoop Pipes Exception: ")[1].split(b" at /")[0].strip()
+        assert msg in ours[2], (msg, ours[2])
+
+
+def test_text_protocol_output_is_what_the_source_says(text_runs):
+    rc, out, _ = text_runs["map + combiner + partitioner", "ours"]
+    assert rc == 1 and out.endswith(b"done\n")
+    assert b"parititionedOutput\t0\thello\t2\n" in out            # the reference's spelling (HadoopPipes.cc:145)
+    assert b"parititionedOutput\t0\tback\\\\slash\t1\n" in out    # backslash quoted, StringUtils.cc:97-127
+    assert b"parititionedOutput\t0\t\\01ctl\t1\n" in out          # unprintable byte as \\hex
+    assert out.startswith(b"registerCounter\t0\tWORDCOUNT\tINPUT_WORDS\n")
+    assert b"progress\t0.000000\n" in out
+    rc, out, _ = text_runs["reduce", "ours"]
+    assert b"output\tapple\t42\n" in out and b"output\ttab\\\\there\t7\n" in out
