@@ -144,6 +144,24 @@ TEXT_CASES = {
 }
 
 
+def _random_bytes_case():
+    """400 map items of words over every byte but tab, newline and '%' (the reference hands the quoted string
+    to fprintf as the format, HadoopPipes.cc:128-130): quoting of unprintables and high bytes must agree."""
+    import random
+
+    rng = random.Random(5)
+    alphabet = [bytes([b]) for b in range(1, 256) if b not in (9, 10, 37)]
+    lines = [b"start\t0\n", b"setJobConf\t2\tmapred.reduce.tasks\t0\n", b"setInputTypes\tk\tv\n", b"runMap\ts\t0\ttrue\n"]
+    for i in range(400):
+        words = [b"".join(rng.choice(alphabet) for _ in range(rng.randint(1, 6))).replace(b" ", b"_")
+                 for _ in range(rng.randint(1, 5))]
+        lines.append(b"mapItem\t%d\t" % i + b" ".join(words) + b"\n")
+    return b"".join(lines) + b"close\n"
+
+
+TEXT_CASES["random bytes"] = ("wordcount-simple", _random_bytes_case())
+
+
 @pytest.fixture(scope="module")
 def text_runs():
     """Every case on both runtimes at once (the reference joins its ping thread for 5 s per child)."""
