@@ -49,6 +49,7 @@ struct hgm_ctx {
   TextStats *h_tstats = nullptr;          // pinned, kStages entries
 
   int k = 0, d = 0;
+  std::vector<float> h_cent;    // host copy of the installed table (the d == 2 index is planned from it)
   float *d_cent = nullptr;      // k*d floats (+ pad to 16 B)
   void *d_partials = nullptr;   // [k*d double][k int64]
   bool grid_ok = false;
@@ -128,6 +129,7 @@ void free_job(hgm_ctx *c) {
   c->tensor_ok = false;
   c->grid_ok = false;
   c->k = c->d = 0;
+  c->h_cent.clear();
 }
 
 // ---- split-cache arena ----------------------------------------------------------------------
@@ -181,7 +183,7 @@ void cache_clear(hgm_ctx *c) {
 
 // Choose the d == 2 cell grid for a centroid table; false if the table is not indexable
 // (non-finite or astronomically large coordinates) and the exact scan must be used.
-bool plan_grid2d(const float *cent, int k, size_t smem_optin, Grid2D *out) {
+bool plan_grid2d(const float *cent, int k, size_t smem_optin, bool sort_form, Grid2D *out) {
   if (k > 1024) return false;
   double lo[2] = {INFINITY, INFINITY}, hi[2] = {-INFINITY, -INFINITY};
   for (int c = 0; c < k; ++c)
@@ -191,36 +193,56 @@ bool plan_grid2d(const float *cent, int k, size_t smem_optin, Grid2D *out) {
       lo[j] = std::min(lo[j], v);
       hi[j] = std::max(hi[j], v);
     }
-  int G = 0, shape = 0;
-  if (!grid2d_plan(k, smem_optin, &G, &shape)) return false;
-  float s[2], B[2];
+  float s[2], B[2], fs[2];
   int32_t b[2];
-  for (int j = 0; j < 2; ++j) {
-    double ext = hi[j] - lo[j];
-    const double mag = std::max(fabs(lo[j]), fabs(hi[j]));
-    if (!(ext > mag * 1e-4)) ext = std::max(mag * 1e-4, 1e-30);  // degenerate axis
-    const double margin = 0.125 * ext;
-    const double origin = lo[j] - margin;
-    const double scale = (double)(G - 1) / (ext + 2 * margin);
-    const float sf = (float)scale;
-    if (!(sf > 0.f) || !std::isfinite(sf)) return false;
-    const double off = -floor(origin * (double)sf + 0.5);  // RN(origin*s) + b == 0
-    if (fabs(off) > 4.0e6) return false;                   // keep b + 2^23 exact in FP32
-    s[j] = sf;
-    b[j] = (int32_t)off;
-    B[j] = (float)(off + 8388608.0);
+  // geometry of a G x G grid over the centroids' bounding box + 12.5 % margin; fs = the fixed-point
+  // scale of kernels_grid2d_fx.cu for that grid (0 where the coordinates' magnitude rules it out)
+  auto geometry = [&](int G) -> bool {
+    for (int j = 0; j < 2; ++j) {
+      double ext = hi[j] - lo[j];
+      const double mag = std::max(fabs(lo[j]), fabs(hi[j]));
+      if (!(ext > mag * 1e-4)) ext = std::max(mag * 1e-4, 1e-30);  // degenerate axis
+      const double margin = 0.125 * ext;
+      const double origin = lo[j] - margin;
+      const double scale = (double)(G - 1) / (ext + 2 * margin);
+      const float sf = (float)scale;
+      if (!(sf > 0.f) || !std::isfinite(sf)) return false;
+      const double off = -floor(origin * (double)sf + 0.5);  // RN(origin*s) + b == 0
+      if (fabs(off) > 4.0e6) return false;                   // keep b + 2^23 exact in FP32
+      s[j] = sf;
+      b[j] = (int32_t)off;
+      B[j] = (float)(off + 8388608.0);
+      // a point of an interior cell ix in [0, G-2] has |x*s + b - ix| <= 1/2 (one FMA, exponent of 2^23):
+      // |x| <= reach.  The scale puts 2^21 above it.
+      const double reach = std::max(fabs(off) + 0.5, fabs((double)G - 1.5 - off)) / (double)sf * 1.000001;
+      const int e = ilogb(reach) + 1;  // 2^e > reach
+      fs[j] = (reach > 0 && e >= -100 && e <= 100) ? (float)ldexp(1.0, 21 - e) : 0.f;
+    }
+    return true;
+  };
+  int G = sort_form ? 0 : grid2d_fx_table_size(k, smem_optin);
+  int shape = kShapeFx;
+  if (G > 0 && !(geometry(G) && fs[0] > 0.f && fs[1] > 0.f)) G = 0;
+  if (G == 0) {  // the counting-sort form
+    if (!grid2d_plan(k, smem_optin, &G, &shape) || !geometry(G)) return false;
+    fs[0] = fs[1] = 0.f;
   }
   out->sx = s[0]; out->sy = s[1];
   out->Bx = B[0]; out->By = B[1];
   out->bx = b[0]; out->by = b[1];
   out->G = G;
   out->shape = shape;
+  out->fsx = fs[0]; out->fsy = fs[1];
   return true;
 }
+
+// (re)build the d == 2 cell index of the installed table for the form the ctx is set to
+int build_grid_index(hgm_ctx *c);
 
 int pick_kernel(hgm_ctx *c) {
   if (c->forced == HGM_KERNEL_EXACT) return HGM_KERNEL_EXACT;
   if (c->forced == HGM_KERNEL_GRID2D) return c->grid_ok ? HGM_KERNEL_GRID2D : -1;
+  if (c->forced == HGM_KERNEL_GRID2D_SORT) return c->grid_ok && c->grid.shape != kShapeFx ? HGM_KERNEL_GRID2D_SORT : -1;
   if (c->forced == HGM_KERNEL_TENSOR) return c->tensor_ok ? HGM_KERNEL_TENSOR : -1;
   if (c->grid_ok) return HGM_KERNEL_GRID2D;
   // the GEMM-shaped path pays off once a point meets a few thousand centroid coordinates
@@ -237,7 +259,7 @@ int map_points_async(hgm_ctx *c, const float *d_pts, int64_t n, int32_t *d_assig
   if (kern < 0) return fail(c, HGM_EINVAL, "forced kernel %d does not fit k=%d d=%d", c->forced, c->k, c->d);
   cudaError_t e;
   int launches = 1;
-  if (kern != HGM_KERNEL_GRID2D) {  // scratch of the scan + segmented-sum paths: assignments, re-check list, cluster order
+  if (kern != HGM_KERNEL_GRID2D && kern != HGM_KERNEL_GRID2D_SORT) {  // scratch of the scan + segmented-sum paths: assignments, re-check list, cluster order
     if (c->tscratch_rows < (size_t)n) {
       CU(c, cudaStreamSynchronize(c->stream));
       cudaFree(c->d_tlist); cudaFree(c->d_tassign); cudaFree(c->d_torder);
@@ -257,7 +279,7 @@ int map_points_async(hgm_ctx *c, const float *d_pts, int64_t n, int32_t *d_assig
                           c->d_tlist, c->d_tflags + 1, c->d_tmeta, c->d_torder, sums_ptr(c), counts_ptr(c), c->sm_count,
                           c->smem_optin, c->stream);
     launches = 5;
-  } else if (kern == HGM_KERNEL_GRID2D) {
+  } else if (kern == HGM_KERNEL_GRID2D || kern == HGM_KERNEL_GRID2D_SORT) {
     e = launch_grid2d_map(d_pts, n, c->d_cent, c->k, c->grid, c->d_table, c->d_cand, sums_ptr(c),
                           counts_ptr(c), d_assign, c->sm_count, c->smem_optin, c->stream);
   } else {
@@ -269,6 +291,25 @@ int map_points_async(hgm_ctx *c, const float *d_pts, int64_t n, int32_t *d_assig
   c->last_kernel = kern;
   c->last_launches += launches;
   c->total_launches += launches;
+  return HGM_OK;
+}
+
+int build_grid_index(hgm_ctx *c) {
+  c->grid_ok = false;
+  if (c->d != 2) return HGM_OK;
+  Grid2D g;
+  if (!plan_grid2d(c->h_cent.data(), c->k, c->smem_optin, c->forced == HGM_KERNEL_GRID2D_SORT, &g)) return HGM_OK;
+  if (!c->d_table || g.G != c->grid.G) {
+    cudaFree(c->d_table); cudaFree(c->d_cand);
+    c->d_table = nullptr; c->d_cand = nullptr;
+    CU(c, cudaMalloc(&c->d_table, grid2d_table_bytes(g.G)));
+    CU(c, cudaMalloc(&c->d_cand, (size_t)g.G * g.G * kMaxCand * 2));
+  }
+  c->grid = g;
+  cudaError_t e = launch_grid2d_build(c->d_cent, c->k, g, c->d_table, c->d_cand, c->stream);
+  if (e != cudaSuccess) return fail(c, HGM_ECUDA, "grid2d build launch: %s", cudaGetErrorString(e));
+  c->total_launches += 1;
+  c->grid_ok = true;
   return HGM_OK;
 }
 
@@ -293,7 +334,7 @@ int ctx_fail(hgm_ctx *c, int code, const char *msg) { return fail(c, code, "%s",
 // for entry points that live in other translation units and have no ctx
 int report_error(int code, const char *msg) { return fail(nullptr, code, "%s", msg); }
 bool plan_grid2d_for(const float *cent, int k, size_t smem_optin, Grid2D *out) {
-  return plan_grid2d(cent, k, smem_optin, out);
+  return plan_grid2d(cent, k, smem_optin, false, out);
 }
 }  // namespace hgm
 
@@ -388,29 +429,24 @@ int hgm_set_centroids(hgm_ctx *c, const float *centroids, int32_t k, int32_t d) 
     if (d != c->d) cache_clear(c);  // cached rows are rows of the old d
     free_job(c);
     const size_t cent_bytes = (((size_t)k * d * 4) + 15) & ~size_t(15);
-    CU(c, cudaMalloc(&c->d_cent, cent_bytes));
-    CU(c, cudaMemsetAsync(c->d_cent, 0, cent_bytes, c->stream));
+    // the shape is recorded only once both buffers exist: a failed allocation leaves the ctx without a job
+    cudaError_t ea = cudaMalloc(&c->d_cent, cent_bytes);
+    if (ea == cudaSuccess) ea = cudaMalloc(&c->d_partials, (size_t)k * d * 8 + (size_t)k * 8);
+    if (ea != cudaSuccess) {
+      cudaGetLastError();
+      free_job(c);
+      return fail(c, ea == cudaErrorMemoryAllocation ? HGM_ENOMEM : HGM_ECUDA, "device memory for k=%d d=%d: %s", k, d,
+                  cudaGetErrorString(ea));
+    }
     c->k = k; c->d = d;
-    CU(c, cudaMalloc(&c->d_partials, partial_bytes(c)));
+    CU(c, cudaMemsetAsync(c->d_cent, 0, cent_bytes, c->stream));
   }
   CU(c, cudaMemcpyAsync(c->d_cent, centroids, (size_t)k * d * 4, cudaMemcpyHostToDevice, c->stream));
   CU(c, cudaMemsetAsync(c->d_partials, 0, partial_bytes(c), c->stream));
-  c->grid_ok = false;
-  if (d == 2) {
-    Grid2D g;
-    if (plan_grid2d(centroids, k, c->smem_optin, &g)) {
-      if (!c->d_table || g.G != c->grid.G) {
-        cudaFree(c->d_table); cudaFree(c->d_cand);
-        c->d_table = nullptr; c->d_cand = nullptr;
-        CU(c, cudaMalloc(&c->d_table, grid2d_table_bytes(g.G)));
-        CU(c, cudaMalloc(&c->d_cand, (size_t)g.G * g.G * kMaxCand * 2));
-      }
-      c->grid = g;
-      cudaError_t e = launch_grid2d_build(c->d_cent, k, g, c->d_table, c->d_cand, c->stream);
-      if (e != cudaSuccess) return fail(c, HGM_ECUDA, "grid2d build launch: %s", cudaGetErrorString(e));
-      c->total_launches += 1;
-      c->grid_ok = true;
-    }
+  c->h_cent.assign(centroids, centroids + (size_t)k * d);
+  {
+    const int rc = build_grid_index(c);
+    if (rc != HGM_OK) return rc;
   }
   c->tensor_ok = false;
   if (tensor_shape_ok(k, d, c->smem_optin)) {
@@ -429,9 +465,23 @@ int hgm_set_centroids(hgm_ctx *c, const float *centroids, int32_t k, int32_t d) 
 }
 
 int hgm_set_kernel(hgm_ctx *c, int32_t kernel) {
-  if (!c) return fail(nullptr, HGM_EINVAL, "ctx is NULL");
-  if (kernel < HGM_KERNEL_AUTO || kernel > HGM_KERNEL_TENSOR) return fail(c, HGM_EINVAL, "unknown kernel %d", kernel);
+  NEED_CTX(c);
+  if (kernel < HGM_KERNEL_AUTO || kernel > HGM_KERNEL_GRID2D_SORT) return fail(c, HGM_EINVAL, "unknown kernel %d", kernel);
+  const bool was_sort = c->forced == HGM_KERNEL_GRID2D_SORT;
   c->forced = kernel;
+  if (was_sort != (kernel == HGM_KERNEL_GRID2D_SORT) && c->d == 2 && !c->h_cent.empty()) {
+    CU(c, cudaStreamSynchronize(c->stream));  // maps in flight still read the old index
+    const int rc = build_grid_index(c);
+    if (rc != HGM_OK) return rc;
+    CU(c, cudaStreamSynchronize(c->stream));
+  }
+  return HGM_OK;
+}
+
+int hgm_grid2d_form(hgm_ctx *c, int32_t *form, int32_t *cells_per_side) {
+  if (!c || !form) return fail(c, HGM_EINVAL, "NULL argument");
+  *form = !c->grid_ok ? 0 : (c->grid.shape == kShapeFx ? 1 : 2);
+  if (cells_per_side) *cells_per_side = c->grid_ok ? c->grid.G : 0;
   return HGM_OK;
 }
 

@@ -27,8 +27,10 @@ struct Grid2D {
   float sx, Bx, sy, By;
   int32_t bx, by;  // the integer offsets inside Bx, By (builder needs them)
   int32_t G;       // cells per side
-  int32_t shape;   // map-kernel shape picked for this job (kernels_grid2d.cu)
+  int32_t shape;   // map-kernel shape picked for this job (kernels_grid2d.cu); kShapeFx = the fixed-point form
+  float fsx, fsy;  // fixed-point scales of kernels_grid2d_fx.cu: powers of two with |x * fsx| < 2^21 inside the grid; 0 = unusable
 };
+constexpr int32_t kShapeFx = 6;
 
 constexpr uint32_t kMagicBits = 0x4B000000u;  // bits of 2^23
 constexpr uint16_t kCellBrute = 0xFFFFu;      // cell entry: scan all k centroids
@@ -48,6 +50,12 @@ cudaError_t launch_grid2d_map(const float *d_pts, int64_t n, const float *d_cent
                               double *d_sums, unsigned long long *d_counts, int32_t *d_assign,
                               int sm_count, size_t smem_optin, cudaStream_t s);
 bool grid2d_plan(int k, size_t smem_optin, int *G_out, int *shape_out);
+// the fixed-point form (kernels_grid2d_fx.cu): table size it can hold for k clusters (0 = none), and its launcher
+int grid2d_fx_table_size(int k, size_t smem_optin);
+cudaError_t launch_grid2d_fx_map(const float *d_pts, int64_t n, const float *d_cent, int k, const Grid2D &g,
+                                 const uint16_t *d_table, const uint16_t *d_cand, double *d_sums,
+                                 unsigned long long *d_counts, int32_t *d_assign, int sm_count, size_t smem_optin,
+                                 cudaStream_t s);
 
 // scan (assign + per-launch counts in d_meta) followed by the segmented sums; d_assign must not be NULL
 cudaError_t launch_exact_map(const float *d_pts, int64_t n, int d, const float *d_cent, int k, int32_t *d_assign,

@@ -18,7 +18,8 @@ import os
 import numpy as np
 
 FMT_F32LE, FMT_F32BE, FMT_TEXT, FMT_SEQ_F32BE, FMT_SEQ_F32LE = 0, 1, 2, 3, 4
-KERNEL_AUTO, KERNEL_EXACT, KERNEL_GRID2D, KERNEL_TENSOR = 0, 1, 2, 3
+KERNEL_AUTO, KERNEL_EXACT, KERNEL_GRID2D, KERNEL_TENSOR, KERNEL_GRID2D_SORT = 0, 1, 2, 3, 4
+GRID2D_FORM_NONE, GRID2D_FORM_FIXED_POINT, GRID2D_FORM_SORT = 0, 1, 2
 
 _PKG_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 _LIB = None
@@ -46,6 +47,7 @@ SIGNATURES = {
     "hgm_set_centroids": (C.c_int, [_c_ctx, _p, C.c_int32, C.c_int32]),
     "hgm_set_kernel": (C.c_int, [_c_ctx, C.c_int32]),
     "hgm_last_kernel": (C.c_int, [_c_ctx, C.POINTER(C.c_int32)]),
+    "hgm_grid2d_form": (C.c_int, [_c_ctx, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "hgm_map_split": (C.c_int, [_c_ctx, _p, C.c_size_t, C.c_int32, _p, _p, _p, C.POINTER(C.c_int64)]),
     "hgm_map_file": (C.c_int, [_c_ctx, C.c_char_p, C.c_int64, C.c_int64, C.c_int32, _p, _p, _p,
                                C.POINTER(C.c_int64)]),
@@ -151,6 +153,12 @@ class GpuMapSlot:
 
     def set_kernel(self, kernel: int) -> None:
         self._check(self._lib.hgm_set_kernel(self._ctx, kernel))
+
+    def grid2d_form(self):
+        """(form, cells per side) of the installed d == 2 index: GRID2D_FORM_*."""
+        form, side = C.c_int32(0), C.c_int32(0)
+        self._check(self._lib.hgm_grid2d_form(self._ctx, C.byref(form), C.byref(side)))
+        return form.value, side.value
 
     def last_kernel(self) -> int:
         v = C.c_int32()

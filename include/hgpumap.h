@@ -68,8 +68,11 @@ typedef struct hgm_ctx hgm_ctx;
 /* Kernel families (hgm_set_kernel); AUTO picks by shape. */
 #define HGM_KERNEL_AUTO 0
 #define HGM_KERNEL_EXACT 1   /* brute-force FP32 scan, any d and k                          */
-#define HGM_KERNEL_GRID2D 2  /* d == 2: exact candidate pruning through a cell index        */
+#define HGM_KERNEL_GRID2D 2  /* d == 2: exact candidate pruning through a cell index; the    */
+                             /* combiner is the fixed-point form where it applies (k <= 254, */
+                             /* coordinates within 2^+-100), else the counting-sort form     */
 #define HGM_KERNEL_TENSOR 3  /* tcgen05 distance GEMM + FP32 re-check of near ties          */
+#define HGM_KERNEL_GRID2D_SORT 4 /* d == 2 cell index with the counting-sort combiner, any k <= 1024 */
 
 /* ---- library / device ------------------------------------------------------------- */
 
@@ -100,10 +103,16 @@ const char *hgm_last_error(hgm_ctx *ctx);
  * Builds the kernel-side index (cell table for d == 2) on the device. */
 int hgm_set_centroids(hgm_ctx *ctx, const float *centroids, int32_t k, int32_t d);
 
-/* Force a kernel family (tests and profiling); HGM_EINVAL if the shape does not fit it. */
+/* Force a kernel family (tests and profiling); HGM_EINVAL if the shape does not fit it.
+ * Changing to or from HGM_KERNEL_GRID2D_SORT rebuilds the d == 2 index of the installed table
+ * (the two combiners keep different table sizes in shared memory). */
 int hgm_set_kernel(hgm_ctx *ctx, int32_t kernel);
-/* Which family the last map call actually ran (one of HGM_KERNEL_*). */
+/* Which family the last map call actually ran (one of HGM_KERNEL_*; HGM_KERNEL_GRID2D_SORT only
+ * when that form was forced). */
 int hgm_last_kernel(hgm_ctx *ctx, int32_t *kernel);
+/* d == 2 only: which combiner the installed index drives -- 0 none (no index), 1 fixed-point
+ * (csrc/kernels_grid2d_fx.cu), 2 counting sort (csrc/kernels_grid2d.cu) -- and its table side G. */
+int hgm_grid2d_form(hgm_ctx *ctx, int32_t *form, int32_t *cells_per_side);
 
 /* ---- the map task ------------------------------------------------------------------- */
 

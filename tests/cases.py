@@ -65,6 +65,37 @@ def degenerate_axis_2d():
     return pts, cent
 
 
+def skewed_2d(n, k=128, share=0.9, seed=17):
+    """One cluster holds `share` of the points (the rest are spread over the others): its partial sums take
+    far more adds than any word of the fixed-point combiner may hold between two flushes, and its column
+    overflows the counting-sort combiner's striped rows."""
+    rng = np.random.default_rng(seed)
+    cent = rng.uniform(-100, 100, size=(k, 2)).astype(np.float32)
+    which = np.where(rng.random(n) < share, 5 % k, rng.integers(0, k, n))
+    pts = (cent[which] + rng.normal(0, 0.05, size=(n, 2))).astype(np.float32)
+    return pts, cent
+
+
+def tiny_values_2d(seed=19):
+    """Coordinates far below the grid's extent next to ordinary ones: values the fixed-point combiner's two limbs
+    cannot hold (non-zero, under 2^-20 of the extent) must take its FP64 path; exact zeros must not need to."""
+    rng = np.random.default_rng(seed)
+    cent = rng.uniform(-100, 100, size=(64, 2)).astype(np.float32)
+    cent[0] = (0.0, 0.0)
+    cent[1] = (0.0, 40.0)
+    cent[2] = (-35.0, 0.0)
+    n = 40000
+    pts = rng.uniform(-110, 110, size=(n, 2)).astype(np.float32)
+    scale = 10.0 ** rng.uniform(-44, -3, size=n)
+    pts[: n // 4, 0] = (rng.normal(0, 1, n // 4) * scale[: n // 4]).astype(np.float32)       # tiny x, any y
+    pts[n // 4 : n // 2, 1] = (rng.normal(0, 1, n // 4) * scale[n // 4 : n // 2]).astype(np.float32)  # tiny y
+    pts[n // 2 : n // 2 + 3000] = 0.0                                                          # exact zeros
+    pts[n // 2 + 3000 : n // 2 + 6000, 0] = 0.0
+    pts[n // 2 + 6000 : n // 2 + 9000, 1] = -0.0
+    rng.shuffle(pts, axis=0)
+    return pts, cent
+
+
 def general_d(n, d, k, seed):
     rng = np.random.default_rng(seed)
     cent = rng.normal(0, 4, size=(k, d)).astype(np.float32)

@@ -12,7 +12,7 @@ from hgpumap import capi, synth
 
 pytestmark = pytest.mark.gpu
 
-KERNELS_2D = [capi.KERNEL_GRID2D, capi.KERNEL_EXACT]
+KERNELS_2D = [capi.KERNEL_GRID2D, capi.KERNEL_GRID2D_SORT, capi.KERNEL_EXACT]
 
 
 @pytest.fixture(scope="module")
@@ -75,15 +75,44 @@ def test_ragged_sizes(slot, oracle, n, kernel):
     run_case(slot, oracle, pts.reshape(n, 2), cent, kernel)
 
 
-@pytest.mark.parametrize("k", [1, 2, 7, 31, 33, 100, 257, 1000, 1024])
+@pytest.mark.parametrize("k", [1, 2, 7, 31, 33, 100, 128, 129, 200, 254, 255, 257, 1000, 1024])
 @pytest.mark.parametrize("kernel", KERNELS_2D)
 def test_cluster_counts(slot, oracle, k, kernel):
     pts, cent = cases.blobs(30011, 2, k, seed=k)
     run_case(slot, oracle, pts, cent, kernel)
 
 
+def test_combiner_form_follows_the_shape(slot):
+    """Fixed-point combiner for k <= 254 with ordinary magnitudes; counting sort when forced, for larger k and
+    for coordinates whose scale a float cannot carry."""
+    pts, cent = cases.blobs(1000, 2, 128)
+    slot.set_centroids(cent)
+    assert slot.grid2d_form()[0] == capi.GRID2D_FORM_FIXED_POINT
+    slot.set_kernel(capi.KERNEL_GRID2D_SORT)  # rebuilds the installed index for the other form
+    assert slot.grid2d_form()[0] == capi.GRID2D_FORM_SORT
+    slot.map_split(pts)
+    assert slot.last_kernel() == capi.KERNEL_GRID2D_SORT
+    slot.set_kernel(capi.KERNEL_AUTO)
+    assert slot.grid2d_form()[0] == capi.GRID2D_FORM_FIXED_POINT
+    slot.set_centroids(cases.blobs(10, 2, 300)[1])
+    assert slot.grid2d_form()[0] == capi.GRID2D_FORM_SORT
+    slot.set_centroids((cent.astype(np.float64) * 1e-36).astype(np.float32))
+    assert slot.grid2d_form()[0] == capi.GRID2D_FORM_SORT
+    slot.set_centroids(cases.general_d(10, 3, 4, 1)[1])
+    assert slot.grid2d_form()[0] == capi.GRID2D_FORM_NONE
+
+
+@pytest.mark.parametrize("share,k", [(1.0, 1), (1.0, 128), (0.9, 128), (0.6, 200)])
+@pytest.mark.parametrize("kernel", [capi.KERNEL_GRID2D, capi.KERNEL_GRID2D_SORT])
+def test_one_cluster_holds_most_points(slot, oracle, share, k, kernel):
+    """Skew: 6 M points, most of them in one cluster -- tens of thousands of adds per (cluster, lane) word of the
+    fixed-point combiner (it must flush long before a word can wrap), thousands per tile for the counting sort."""
+    pts, cent = cases.skewed_2d(6_000_000, k=k, share=share)
+    run_case(slot, oracle, pts, cent, kernel)
+
+
 @pytest.mark.parametrize("maker", [cases.adversarial_2d, cases.tiny_scale_2d, cases.close_centroids_2d,
-                                   cases.degenerate_axis_2d])
+                                   cases.degenerate_axis_2d, cases.tiny_values_2d])
 @pytest.mark.parametrize("kernel", KERNELS_2D)
 def test_edge_cases_2d(slot, oracle, maker, kernel):
     pts, cent = maker()
