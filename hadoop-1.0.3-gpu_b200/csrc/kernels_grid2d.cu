@@ -134,7 +134,10 @@ __global__ void __launch_bounds__(256) grid2d_build_kernel(const float *__restri
     const double tx = 2.0 / (double)g.fsx, ty = 2.0 / (double)g.fsy;
     fx_slow = (xlo < tx && xhi > -tx) || (ylo < ty && yhi > -ty);
   }
-  table8[cell] = entry < kCellMulti && !fx_slow ? (uint8_t)(entry < kTable8Multi ? entry : kTable8Multi) : kTable8Multi;
+  // "not a single-candidate cell" is kTable8Multi for the counting-sort kernel and k for the fixed-point one, where
+  // it doubles as the index of the accumulator row that is never read
+  const uint8_t multi8 = g.shape == kShapeFx ? (uint8_t)k : kTable8Multi;
+  table8[cell] = entry < kCellMulti && !fx_slow ? (uint8_t)(entry < multi8 ? entry : multi8) : multi8;
 }
 
 // ---- the map kernel ---------------------------------------------------------------------

@@ -72,8 +72,8 @@ __host__ __device__ inline size_t fx_head_bytes(int G, int k) {
 }
 template <class S>
 __host__ __device__ inline size_t fx_body_bytes(int k, bool with_assign) {
-  // [acc k*5*lanes u32][tot k*5 i64][late sums k*2 f64][late counts k u64][queues warps*qcap float2][queue index u16]
-  return (size_t)k * kFxWords * S::kLanes * 4 + (size_t)k * kFxWords * 8 + (size_t)k * 16 + (size_t)k * 8 +
+  // [acc (k+1)*5*lanes u32][tot k*5 i64][late sums k*2 f64][late counts k u64][queues warps*qcap float2][queue index u16]
+  return (size_t)(k + 1) * kFxWords * S::kLanes * 4 + (size_t)k * kFxWords * 8 + (size_t)k * 16 + (size_t)k * 8 +
          (size_t)S::kWarps * S::kQCap * 8 + (with_assign ? align16((size_t)S::kWarps * S::kQCap * 2) : 0);
 }
 
@@ -83,30 +83,41 @@ struct FxParams {
   float limx, limy;  // 2^21 / S: at or beyond this the limbs would overflow
 };
 
-// the five adds of one point of cluster c into this lane's words; returns what the count word held before
+// The five adds of one point into this lane's words of row c, unconditionally: ptxas turns a predicated shared
+// atomic into a branch around it, and a branch per atomic costs more issue slots than everything else a point needs.
+// A point that must not be added here (multi-candidate cell, past the end of a ragged tile) is given row k instead, a
+// row nobody reads, and `one` = 0 so that row's count word never moves.  acc_lane = shared-memory address of this
+// lane's word of row 0, word 0.  Returns what the count word held before.
 template <int kLanes>
-__device__ __forceinline__ uint32_t fx_add_point(uint32_t *my_acc, const FxParams &fx, float x, float y, uint32_t c) {
+__device__ __forceinline__ uint32_t fx_add_point(uint32_t one, uint32_t acc_lane, const FxParams &fx, float x, float y, uint32_t c) {
   const float tx = __fmaf_rn(x, fx.sx, kFxMagic);         // mantissa = RN(x*S), offset by the magic bits
   const float rx = __fmaf_rn(x, fx.sx, kFxMagic - tx);    // x*S - RN(x*S): exact, |rx| <= 1/2
   const float ux = __fmaf_rn(rx, kFxLoScale, kFxMagic);   // mantissa = rx * 2^22 (an integer for non-tiny x)
   const float ty = __fmaf_rn(y, fx.sy, kFxMagic);
   const float ry = __fmaf_rn(y, fx.sy, kFxMagic - ty);
   const float uy = __fmaf_rn(ry, kFxLoScale, kFxMagic);
-  uint32_t *const p = my_acc + c * (kFxWords * kLanes);
+  const uint32_t addr = acc_lane + c * (uint32_t)(kFxWords * kLanes * 4);
+  uint32_t old;
   // the magic bits ride along in every add; the flush takes count * kFxMagicBits off again (mod 2^32)
-  atomicAdd(p, __float_as_uint(tx));
-  atomicAdd(p + kLanes, __float_as_uint(ux));
-  atomicAdd(p + 2 * kLanes, __float_as_uint(ty));
-  atomicAdd(p + 3 * kLanes, __float_as_uint(uy));
-  return atomicAdd(p + 4 * kLanes, 1u);
+  asm volatile(
+      "red.shared.add.u32 [%1], %2;\n\t"
+      "red.shared.add.u32 [%1+%7], %3;\n\t"
+      "red.shared.add.u32 [%1+%8], %4;\n\t"
+      "red.shared.add.u32 [%1+%9], %5;\n\t"
+      "atom.shared.add.u32 %0, [%1+%10], %6;"
+      : "=r"(old)
+      : "r"(addr), "r"(__float_as_uint(tx)), "r"(__float_as_uint(ux)), "r"(__float_as_uint(ty)),
+        "r"(__float_as_uint(uy)), "r"(one), "n"(kLanes * 4), "n"(2 * kLanes * 4), "n"(3 * kLanes * 4), "n"(4 * kLanes * 4)
+      : "memory");
+  return old;
 }
 
 // One tile of a warp: table lookups, then per point either the five adds (single-candidate cell) or a push
 // onto the warp's queue.  kFull = every point of the tile exists (no bounds tests in the straight-line code).
 // `seen` collects the OR of the counts found.
 template <class S, bool kAssign, bool kFull>
-__device__ __forceinline__ void fx_work_tile(const uint8_t *table_s, const Grid2D &g, const FxParams &fx, uint32_t *my_acc,
-                                             float2 *queue, uint16_t *qindex, int32_t *__restrict__ assign, long long base,
+__device__ __forceinline__ void fx_work_tile(const uint8_t *table_s, const Grid2D &g, const FxParams &fx, uint32_t acc_lane,
+                                             uint32_t k, float2 *queue, uint16_t *qindex, int32_t *__restrict__ assign, long long base,
                                              int live, int lane, uint32_t lt_mask, const float (&xs)[S::kPPT],
                                              const float (&ys)[S::kPPT], int &qn, uint32_t &seen) {
   constexpr int kPPT = S::kPPT;
@@ -119,11 +130,11 @@ __device__ __forceinline__ void fx_work_tile(const uint8_t *table_s, const Grid2
   for (int i = 0; i < kPPT; ++i) {
     const int local = 2 * ((i >> 1) * 32 + lane) + (i & 1);
     const bool valid = kFull || local < live;
-    const bool direct = valid && ent[i] < (uint32_t)kTable8Multi;
-    if (direct) {
-      if (kAssign) assign[base + local] = (int)ent[i];
-      seen |= fx_add_point<S::kLanes>(my_acc, fx, xs[i], ys[i], ent[i]);
-    }
+    // this form's table says k, the row nobody reads, for every cell that is not a single-candidate one
+    const uint32_t c = kFull ? ent[i] : (valid ? ent[i] : k);
+    const bool direct = c != k;
+    if (kAssign && direct) assign[base + local] = (int)c;
+    seen |= fx_add_point<S::kLanes>(direct ? 1u : 0u, acc_lane, fx, xs[i], ys[i], c);
     const uint32_t queued = __ballot_sync(0xFFFFFFFFu, valid && !direct);
     if (queued) {
       if (valid && !direct) {
@@ -145,7 +156,6 @@ __global__ void __launch_bounds__(S::kThreads, 1)
   constexpr int kPPT = S::kPPT;
   constexpr int kTile = S::kTile;
   constexpr int kLanes = S::kLanes;
-  constexpr uint32_t kMulti = (uint32_t)kTable8Multi;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -157,7 +167,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
   volatile int *const flag = reinterpret_cast<volatile int *>(bar + 2);
   unsigned char *const body = smem_raw + fx_head_bytes(g.G, k);
   uint32_t *const acc = reinterpret_cast<uint32_t *>(body);
-  long long *const tot = reinterpret_cast<long long *>(acc + (size_t)k * kFxWords * kLanes);
+  long long *const tot = reinterpret_cast<long long *>(acc + (size_t)(k + 1) * kFxWords * kLanes);
   double *const late_sum = reinterpret_cast<double *>(tot + (size_t)k * kFxWords);
   unsigned long long *const late_cnt = reinterpret_cast<unsigned long long *>(late_sum + 2 * (size_t)k);
   float2 *const queue = reinterpret_cast<float2 *>(late_cnt + k) + (size_t)warp * S::kQCap;
@@ -179,7 +189,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
     tma_bulk_g2s(cent_s, cent, cent_bytes, bar);
     *flag = 0;
   }
-  for (int i = threadIdx.x; i < k * kFxWords * kLanes; i += S::kThreads) acc[i] = 0u;
+  for (int i = threadIdx.x; i < (k + 1) * kFxWords * kLanes; i += S::kThreads) acc[i] = 0u;
   for (int i = threadIdx.x; i < k * kFxWords; i += S::kThreads) tot[i] = 0;
   for (int i = threadIdx.x; i < k; i += S::kThreads) {
     late_sum[2 * i] = 0.0;
@@ -189,7 +199,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
   mbar_wait(bar, 0);
   __syncthreads();
 
-  uint32_t *const my_acc = acc + (lane & (kLanes - 1));  // this lane's word of every (cluster, word) row
+  const uint32_t acc_lane = smem_u32(acc + (lane & (kLanes - 1)));  // this lane's word of every (cluster, word) row
   const uint32_t lt_mask = (1u << lane) - 1u;
 
   // a value the two limbs hold exactly: zero, or no bits below 2^-22 after scaling
@@ -209,9 +219,8 @@ __global__ void __launch_bounds__(S::kThreads, 1)
       if (e16 >= kCellMulti) c = (uint32_t)resolve_cand(v.x, v.y, id01, list, cent_s, k);
       if (kAssign) assign[base + qindex[first + lane]] = (int)c;
       const bool fits = fabsf(v.x) < fx.limx && fabsf(v.y) < fx.limy && !tiny(v.x, fx.tinyx) && !tiny(v.y, fx.tinyy);
-      if (fits) {
-        full = fx_add_point<kLanes>(my_acc, fx, v.x, v.y, c);
-      } else {  // shared FP64 / 64-bit atomics are CAS loops: the rare path only
+      full = fx_add_point<kLanes>(fits ? 1u : 0u, acc_lane, fx, v.x, v.y, fits ? c : (uint32_t)k);
+      if (!fits) {  // shared FP64 / 64-bit atomics are CAS loops: the rare path only
         atomicAdd(&late_sum[2 * c], (double)v.x);
         atomicAdd(&late_sum[2 * c + 1], (double)v.y);
         atomicAdd(&late_cnt[c], 1ull);
@@ -278,9 +287,9 @@ __global__ void __launch_bounds__(S::kThreads, 1)
 
       uint32_t seen = 0u;  // OR of the counts found: any bit at or above kFlushAt = a word is at the threshold
       if (live == kTile)
-        fx_work_tile<S, kAssign, true>(table_s, g, fx, my_acc, queue, qindex, assign, base, live, lane, lt_mask, xs, ys, qn, seen);
+        fx_work_tile<S, kAssign, true>(table_s, g, fx, acc_lane, (uint32_t)k, queue, qindex, assign, base, live, lane, lt_mask, xs, ys, qn, seen);
       else
-        fx_work_tile<S, kAssign, false>(table_s, g, fx, my_acc, queue, qindex, assign, base, live, lane, lt_mask, xs, ys, qn, seen);
+        fx_work_tile<S, kAssign, false>(table_s, g, fx, acc_lane, (uint32_t)k, queue, qindex, assign, base, live, lane, lt_mask, xs, ys, qn, seen);
       __syncwarp();
       // whole batches of 32 only (the rest waits for company), unless the points' tile-relative
       // indices are needed for the assignment output

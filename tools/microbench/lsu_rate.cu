@@ -11,6 +11,9 @@
 //   6  LDS.U8 random + 5 x pattern 0 (the lane-private fixed-point combiner, memory side only)
 //   7  ATOMS.ADD (no result), 16 private lanes (lane & 15): two lanes per bank pair
 //   8  pattern 6 with four of the five atomics only
+//   9  pattern 6 with the table byte fetched through the texture unit (tex1Dfetch from linear global memory)
+//  10  pattern 6 with the table byte loaded from global memory through L1 (ld.global.nc.u8)
+//  11  tex1Dfetch alone;  12  ld.global.nc.u8 alone
 #include <cstdio>
 #include <cuda_runtime.h>
 
@@ -18,7 +21,8 @@
 #define UNROLL 8
 
 template <int OP>
-__global__ void __launch_bounds__(768, 1) rate_kernel(unsigned *out, long long *cycles, unsigned seed, int rows) {
+__global__ void __launch_bounds__(768, 1) rate_kernel(unsigned *out, long long *cycles, unsigned seed, int rows,
+                                                      cudaTextureObject_t tex, const unsigned char *__restrict__ gtable) {
   extern __shared__ __align__(16) unsigned char smem[];
   unsigned *const words = reinterpret_cast<unsigned *>(smem);           // rows * 32 words
   unsigned char *const table = smem + (size_t)rows * 128;               // 36864 bytes
@@ -49,6 +53,15 @@ __global__ void __launch_bounds__(768, 1) rate_kernel(unsigned *out, long long *
         if (OP == 6) atomicAdd(p + 128, 1u);
       }
       if (OP == 7) atomicAdd(&words[row * 16 + (lane & 15)], r[u]);
+      if (OP == 9 || OP == 10) {
+        const unsigned cell = r[u] % 65536u;
+        const unsigned c = (OP == 9 ? (unsigned)tex1Dfetch<unsigned char>(tex, (int)cell) : (unsigned)__ldg(gtable + cell)) & 127u;
+        unsigned *p = &words[c * 5 * 32 + lane];
+        atomicAdd(p, r[u]); atomicAdd(p + 32, s); atomicAdd(p + 64, r[u] ^ s); atomicAdd(p + 96, r[u] + s);
+        atomicAdd(p + 128, 1u);
+      }
+      if (OP == 11) acc += tex1Dfetch<unsigned char>(tex, (int)(r[u] % 65536u));
+      if (OP == 12) acc += __ldg(gtable + r[u] % 65536u);
     }
   }
   const long long t1 = clock64();
@@ -62,8 +75,24 @@ void run(const char *name, int per_iter) {
   cudaMalloc(&out, 148 * 768 * 4); cudaMalloc(&cyc, 148 * 8);
   const int rows = 640;  // 128 clusters x 5 words, 80 KiB
   const size_t smem = (size_t)rows * 128 + 36864;
+  static unsigned char *gtable = nullptr;
+  static cudaTextureObject_t tex = 0;
+  if (!gtable) {
+    cudaMalloc(&gtable, 65536);
+    unsigned char h[65536];
+    for (int i = 0; i < 65536; ++i) h[i] = (unsigned char)((i * 2654435761u) >> 24);
+    cudaMemcpy(gtable, h, sizeof h, cudaMemcpyHostToDevice);
+    cudaResourceDesc rd{};
+    rd.resType = cudaResourceTypeLinear;
+    rd.res.linear.devPtr = gtable;
+    rd.res.linear.desc = cudaCreateChannelDesc<unsigned char>();
+    rd.res.linear.sizeInBytes = 65536;
+    cudaTextureDesc td{};
+    td.readMode = cudaReadModeElementType;
+    cudaCreateTextureObject(&tex, &rd, &td, nullptr);
+  }
   cudaFuncSetAttribute(rate_kernel<OP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-  for (int rep = 0; rep < 2; ++rep) rate_kernel<OP><<<148, 768, smem>>>(out, cyc, 12345u, rows);
+  for (int rep = 0; rep < 2; ++rep) rate_kernel<OP><<<148, 768, smem>>>(out, cyc, 12345u, rows, tex, gtable);
   long long h[148];
   cudaMemcpy(h, cyc, sizeof h, cudaMemcpyDeviceToHost);
   cudaError_t e = cudaGetLastError();
@@ -83,5 +112,9 @@ int main() {
   run<5>("STS.64 bank = lane", 1);
   run<6>("LDS.U8 random + 5 ATOMS bank = lane", 6);
   run<8>("LDS.U8 random + 4 ATOMS bank = lane", 5);
+  run<9>("tex1Dfetch u8 (64 KiB) + 5 ATOMS bank = lane", 6);
+  run<10>("ld.global.nc.u8 (64 KiB) + 5 ATOMS bank = lane", 6);
+  run<11>("tex1Dfetch u8 random byte of 64 KiB", 1);
+  run<12>("ld.global.nc.u8 random byte of 64 KiB", 1);
   return 0;
 }
