@@ -360,8 +360,7 @@ def run_ours(args):
         step()
     slot.sync()
     sums, counts = slot.read_partials()
-    if not os.environ.get("HGM_TENSOR_DEBUG"):  # kernel experiments (tools/microbench) produce no partials
-        assert int(counts.sum()) == n * world, f"partials count {int(counts.sum())} != {n * world}"
+    assert int(counts.sum()) == n * world, f"partials count {int(counts.sum())} != {n * world}"
     kernel_family = slot.last_kernel()
 
     # ---- value: K steps, HBM-resident, CUDA events on the library's stream -------------

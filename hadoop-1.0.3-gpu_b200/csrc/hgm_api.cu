@@ -29,6 +29,10 @@ constexpr size_t kChunkBytes = size_t(64) << 20;  // HBM chunk per pipeline stag
 constexpr int kStages = 3;
 constexpr size_t kBounceBytes = size_t(16) << 20;  // pinned bounce for pageable callers
 constexpr size_t kArenaBytes = size_t(2) << 30;    // split-cache arena block
+// Rows one launch group of the scan / tensor paths handles: their scratch (assignments, re-check list, cluster
+// order: 12 bytes per row) is allocated ONCE per job at this size and longer inputs are mapped piece by piece --
+// no cudaFree/cudaMalloc (a device-wide synchronisation under the other slots' kernels) inside a map call.
+constexpr size_t kScratchRows = size_t(1) << 25;
 }  // namespace
 
 struct hgm_ctx {
@@ -67,6 +71,7 @@ struct hgm_ctx {
   int forced = HGM_KERNEL_AUTO, last_kernel = HGM_KERNEL_AUTO;
   int last_launches = 0;
   int64_t total_launches = 0;
+  int64_t staged_bytes = 0;  // split bytes copied host -> device since hgm_open
   bool timing_open = false;
   void *nccl_comm = nullptr;
   // HBM-resident splits by id.  Rows live in arena blocks (one cudaMalloc per kArenaBytes, not per
@@ -121,11 +126,7 @@ void free_job(hgm_ctx *c) {
   cudaFree(c->d_cand); c->d_cand = nullptr;
   cudaFree(c->d_caug); c->d_caug = nullptr;
   cudaFree(c->d_tflags); c->d_tflags = nullptr;
-  cudaFree(c->d_tassign); c->d_tassign = nullptr;
-  cudaFree(c->d_tlist); c->d_tlist = nullptr;
-  cudaFree(c->d_torder); c->d_torder = nullptr;
-  cudaFree(c->d_tmeta); c->d_tmeta = nullptr;
-  c->tscratch_rows = 0;
+  cudaFree(c->d_tmeta); c->d_tmeta = nullptr;  // sized by k; the row scratch (d_tassign, d_tlist, d_torder) outlives jobs
   c->tensor_ok = false;
   c->grid_ok = false;
   c->k = c->d = 0;
@@ -193,7 +194,7 @@ bool plan_grid2d(const float *cent, int k, size_t smem_optin, bool sort_form, Gr
       lo[j] = std::min(lo[j], v);
       hi[j] = std::max(hi[j], v);
     }
-  float s[2], B[2], fs[2];
+  float s[2], B[2], fs[2] = {0.f, 0.f};
   int32_t b[2];
   // geometry of a G x G grid over the centroids' bounding box + 12.5 % margin; fs = the fixed-point
   // scale of kernels_grid2d_fx.cu for that grid (0 where the coordinates' magnitude rules it out)
@@ -252,33 +253,61 @@ int pick_kernel(hgm_ctx *c) {
   return HGM_KERNEL_EXACT;
 }
 
+// scratch of the scan + segmented-sum paths (assignments, re-check list, cluster order), once per job
+int ensure_scan_scratch(hgm_ctx *c) {
+  if (c->tscratch_rows == 0) {
+    cudaError_t e = cudaMalloc(&c->d_tlist, kScratchRows * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&c->d_tassign, kScratchRows * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&c->d_torder, kScratchRows * 4);
+    if (e != cudaSuccess) {
+      cudaGetLastError();
+      cudaFree(c->d_tlist); cudaFree(c->d_tassign); cudaFree(c->d_torder);
+      c->d_tlist = c->d_tassign = c->d_torder = nullptr;
+      return fail(c, e == cudaErrorMemoryAllocation ? HGM_ENOMEM : HGM_ECUDA, "scratch for the scan path: %s", cudaGetErrorString(e));
+    }
+    c->tscratch_rows = kScratchRows;
+  }
+  if (!c->d_tmeta) CU(c, cudaMalloc(&c->d_tmeta, tensor_meta_words(c->k) * 4));
+  return HGM_OK;
+}
+
+int map_piece_async(hgm_ctx *c, int kern, const float *d_pts, int64_t n, int32_t *d_assign);
+
+// d_tflags: [0] bits of max |c|, [1] points the last launch group re-checked, [2..3] the same summed over a map call
+__global__ void add_rechecks_kernel(unsigned int *flags) {
+  *reinterpret_cast<unsigned long long *>(flags + 2) += flags[1];
+}
+
 // queue the map of n device-resident points on ctx->stream; adds into the partials
 int map_points_async(hgm_ctx *c, const float *d_pts, int64_t n, int32_t *d_assign) {
   if (n == 0) return HGM_OK;
   const int kern = pick_kernel(c);
   if (kern < 0) return fail(c, HGM_EINVAL, "forced kernel %d does not fit k=%d d=%d", c->forced, c->k, c->d);
+  if (kern == HGM_KERNEL_GRID2D || kern == HGM_KERNEL_GRID2D_SORT) return map_piece_async(c, kern, d_pts, n, d_assign);
+  const int rc = ensure_scan_scratch(c);  // a no-op after hgm_set_centroids unless the kernel was forced later
+  if (rc != HGM_OK) return rc;
+  for (int64_t first = 0; first < n; first += (int64_t)kScratchRows) {
+    const int64_t m = std::min<int64_t>((int64_t)kScratchRows, n - first);
+    const int prc = map_piece_async(c, kern, d_pts + (size_t)first * c->d, m, d_assign ? d_assign + first : nullptr);
+    if (prc != HGM_OK) return prc;
+  }
+  return HGM_OK;
+}
+
+int map_piece_async(hgm_ctx *c, int kern, const float *d_pts, int64_t n, int32_t *d_assign) {
   cudaError_t e;
   int launches = 1;
-  if (kern != HGM_KERNEL_GRID2D && kern != HGM_KERNEL_GRID2D_SORT) {  // scratch of the scan + segmented-sum paths: assignments, re-check list, cluster order
-    if (c->tscratch_rows < (size_t)n) {
-      CU(c, cudaStreamSynchronize(c->stream));
-      cudaFree(c->d_tlist); cudaFree(c->d_tassign); cudaFree(c->d_torder);
-      c->d_tlist = c->d_tassign = c->d_torder = nullptr;
-      c->tscratch_rows = 0;
-      CU(c, cudaMalloc(&c->d_tlist, (size_t)n * 4));
-      CU(c, cudaMalloc(&c->d_tassign, (size_t)n * 4));
-      CU(c, cudaMalloc(&c->d_torder, (size_t)n * 4));
-      c->tscratch_rows = (size_t)n;
-    }
-    if (!c->d_tmeta) CU(c, cudaMalloc(&c->d_tmeta, tensor_meta_words(c->k) * 4));
-  }
   if (kern == HGM_KERNEL_TENSOR) {
     if (reinterpret_cast<uintptr_t>(d_pts) & 15)
       return fail(c, HGM_EINVAL, "the tensor path needs 16-byte aligned points");
     e = launch_tensor_map(d_pts, n, c->d, c->d_cent, c->k, c->d_caug, c->d_tflags, d_assign ? d_assign : c->d_tassign,
                           c->d_tlist, c->d_tflags + 1, c->d_tmeta, c->d_torder, sums_ptr(c), counts_ptr(c), c->sm_count,
                           c->smem_optin, c->stream);
-    launches = 5;
+    if (e == cudaSuccess) {
+      add_rechecks_kernel<<<1, 1, 0, c->stream>>>(c->d_tflags);
+      e = cudaGetLastError();
+    }
+    launches = 6;
   } else if (kern == HGM_KERNEL_GRID2D || kern == HGM_KERNEL_GRID2D_SORT) {
     e = launch_grid2d_map(d_pts, n, c->d_cent, c->k, c->grid, c->d_table, c->d_cand, sums_ptr(c),
                           counts_ptr(c), d_assign, c->sm_count, c->smem_optin, c->stream);
@@ -401,6 +430,7 @@ void hgm_close(hgm_ctx *c) {
   if (c->nccl_comm) { hgm::comm_destroy(c->nccl_comm); c->nccl_comm = nullptr; }
   cache_clear(c);
   free_job(c);
+  cudaFree(c->d_tassign); cudaFree(c->d_tlist); cudaFree(c->d_torder);
   for (int i = 0; i < kStages; ++i) {
     if (c->copy[i]) { cudaStreamSynchronize(c->copy[i]); cudaStreamDestroy(c->copy[i]); }
     if (c->ev_h2d[i]) cudaEventDestroy(c->ev_h2d[i]);
@@ -459,6 +489,10 @@ int hgm_set_centroids(hgm_ctx *c, const float *centroids, int32_t k, int32_t d) 
     c->total_launches += 1;
     c->tensor_ok = true;
   }
+  if (!c->grid_ok || c->forced == HGM_KERNEL_EXACT || c->forced == HGM_KERNEL_TENSOR) {
+    const int rc = ensure_scan_scratch(c);
+    if (rc != HGM_OK) return rc;
+  }
   // the caller's centroid buffer may be reused as soon as we return
   CU(c, cudaStreamSynchronize(c->stream));
   return HGM_OK;
@@ -475,6 +509,12 @@ int hgm_set_kernel(hgm_ctx *c, int32_t kernel) {
     if (rc != HGM_OK) return rc;
     CU(c, cudaStreamSynchronize(c->stream));
   }
+  return HGM_OK;
+}
+
+int hgm_set_tensor_form(int32_t form) {
+  if (form < HGM_TENSOR_FORM_AUTO || form > HGM_TENSOR_FORM_PAIR) return fail(nullptr, HGM_EINVAL, "unknown tensor form %d", form);
+  tensor_set_form(form);
   return HGM_OK;
 }
 
@@ -504,6 +544,7 @@ int hgm_map_device(hgm_ctx *c, const float *d_points, int64_t n, int32_t *d_assi
   if (n < 0 || (n > 0 && !d_points)) return fail(c, HGM_EINVAL, "bad points argument");
   if (reinterpret_cast<uintptr_t>(d_points) & 7) return fail(c, HGM_EINVAL, "d_points must be 8-byte aligned");
   c->last_launches = 0;
+  if (c->d_tflags) cudaMemsetAsync(c->d_tflags + 2, 0, 8, c->stream);  // re-check total of this map call
   CU(c, cudaEventRecord(c->ev_t0, c->stream));
   const int rc = map_points_async(c, d_points, n, d_assign);
   if (rc != HGM_OK) return rc;
@@ -555,10 +596,16 @@ int hgm_last_rechecks(hgm_ctx *c, int64_t *points) {
   if (!points) return fail(c, HGM_EINVAL, "points is NULL");
   *points = 0;
   if (c->last_kernel != HGM_KERNEL_TENSOR || !c->d_tflags) return HGM_OK;
-  unsigned int n = 0;
-  CU(c, cudaMemcpyAsync(&n, c->d_tflags + 1, 4, cudaMemcpyDeviceToHost, c->stream));
+  unsigned long long n = 0;
+  CU(c, cudaMemcpyAsync(&n, c->d_tflags + 2, 8, cudaMemcpyDeviceToHost, c->stream));
   CU(c, cudaStreamSynchronize(c->stream));
-  *points = n;
+  *points = (int64_t)n;
+  return HGM_OK;
+}
+
+int hgm_staged_bytes(hgm_ctx *c, int64_t *bytes) {
+  if (!c || !bytes) return fail(c, HGM_EINVAL, "NULL argument");
+  *bytes = c->staged_bytes;
   return HGM_OK;
 }
 
@@ -705,6 +752,7 @@ static int map_stream(hgm_ctx *c, SplitSource &src, int32_t fmt, double *sums, i
   if (rc != HGM_OK) return rc;
 
   c->last_launches = 0;
+  if (c->d_tflags) cudaMemsetAsync(c->d_tflags + 2, 0, 8, c->stream);  // re-check total of this map call
   CU(c, cudaMemsetAsync(c->d_partials, 0, partial_bytes(c), c->stream));
   CU(c, cudaEventRecord(c->ev_t0, c->stream));
   int64_t done = 0;
@@ -720,6 +768,7 @@ static int map_stream(hgm_ctx *c, SplitSource &src, int32_t fmt, double *sums, i
     if (stage_used[stage]) CU(c, cudaStreamWaitEvent(cs, c->ev_free[stage], 0));
     if (!bounce) {
       CU(c, cudaMemcpyAsync(c->d_chunk[stage], src.mem + (size_t)done * row, bytes, cudaMemcpyHostToDevice, cs));
+      c->staged_bytes += (int64_t)bytes;
     } else {
       size_t off = 0;
       while (off < bytes) {
@@ -729,6 +778,7 @@ static int map_stream(hgm_ctx *c, SplitSource &src, int32_t fmt, double *sums, i
           return fail(c, HGM_EIO, "short read from split file: %s", strerror(errno));
         CU(c, cudaMemcpyAsync(static_cast<unsigned char *>(c->d_chunk[stage]) + off, c->h_bounce[bounce_i], piece,
                               cudaMemcpyHostToDevice, cs));
+        c->staged_bytes += (int64_t)piece;
         CU(c, cudaEventRecord(c->ev_bounce[bounce_i], cs));
         bounce_used[bounce_i] = true;
         bounce_i = (bounce_i + 1) % kStages;
@@ -855,6 +905,7 @@ static int map_text_stream(hgm_ctx *c, SplitSource &src, double *sums, int64_t *
   if (rc != HGM_OK) return rc;
 
   c->last_launches = 0;
+  if (c->d_tflags) cudaMemsetAsync(c->d_tflags + 2, 0, 8, c->stream);  // re-check total of this map call
   CU(c, cudaMemsetAsync(c->d_partials, 0, partial_bytes(c), c->stream));
   CU(c, cudaEventRecord(c->ev_t0, c->stream));
   size_t remaining = src.nbytes, src_pos = 0;  // src_pos: source offset of the next fresh byte
@@ -881,6 +932,7 @@ static int map_text_stream(hgm_ctx *c, SplitSource &src, double *sums, int64_t *
     carry_len = n - cut;
 
     CU(c, cudaMemcpyAsync(c->d_text[stage], buf, cut, cudaMemcpyHostToDevice, cs));
+    c->staged_bytes += (int64_t)cut;
     CU(c, cudaEventRecord(c->ev_bounce[stage], cs));
     if (used[stage]) CU(c, cudaStreamWaitEvent(cs, c->ev_free[stage], 0));  // rows still being mapped
     cudaError_t e = launch_text_decode(static_cast<const unsigned char *>(c->d_text[stage]), cut, c->d,
@@ -956,6 +1008,7 @@ static int cache_store_text(hgm_ctx *c, int64_t split_id, SplitSource &src) {
     if (!stage_bytes(src, off, c->h_bounce[bi], piece))
       return cleanup(fail(c, HGM_EIO, "short read from split file: %s", strerror(errno)));
     e = cudaMemcpyAsync(d_text + off, c->h_bounce[bi], piece, cudaMemcpyHostToDevice, c->stream);
+    c->staged_bytes += (int64_t)piece;
     if (e == cudaSuccess) e = cudaEventRecord(c->ev_bounce[bi], c->stream);
     if (e != cudaSuccess) return cleanup(fail(c, HGM_ECUDA, "cache copy: %s", cudaGetErrorString(e)));
     bi = (bi + 1) % kStages;
@@ -1127,6 +1180,7 @@ static int decode_seq(hgm_ctx *c, FILE *f, int64_t start, int64_t stop, const Se
     if (!stage_bytes(src, off, c->h_bounce[bi], piece))
       return cleanup(fail(c, HGM_EIO, "short read from split file: %s", strerror(errno)));
     e = cudaMemcpyAsync(d_bytes + off, c->h_bounce[bi], piece, cudaMemcpyHostToDevice, c->stream);
+    c->staged_bytes += (int64_t)piece;
     if (e == cudaSuccess) e = cudaEventRecord(c->ev_bounce[bi], c->stream);
     if (e != cudaSuccess) return cleanup(fail(c, HGM_ECUDA, "split copy: %s", cudaGetErrorString(e)));
     bi = (bi + 1) % kStages;
@@ -1192,6 +1246,7 @@ static int map_seq_file(hgm_ctx *c, const char *path, int64_t offset, int64_t le
   const int64_t n = n_floats / c->d;
   if (n_points_out) *n_points_out = n;
   c->last_launches = 0;
+  if (c->d_tflags) cudaMemsetAsync(c->d_tflags + 2, 0, 8, c->stream);  // re-check total of this map call
   cudaError_t e = cudaMemsetAsync(c->d_partials, 0, partial_bytes(c), c->stream);
   if (e == cudaSuccess) e = cudaEventRecord(c->ev_t0, c->stream);
   if (e == cudaSuccess) rc = map_points_async(c, d_rows, n, nullptr);
@@ -1219,7 +1274,13 @@ static int cache_seq_file(hgm_ctx *c, int64_t split_id, const char *path, int64_
   int64_t start = 0, stop = 0, n_floats = 0;
   float *d_rows = nullptr;
   int block = -1;
-  CU(c, cudaStreamSynchronize(c->stream));
+  {
+    const cudaError_t es = cudaStreamSynchronize(c->stream);
+    if (es != cudaSuccess) {
+      fclose(f);
+      return fail(c, HGM_ECUDA, "cudaStreamSynchronize: %s", cudaGetErrorString(es));
+    }
+  }
   cache_erase(c, split_id);
   int rc = seq_split_bounds(c, f, offset, length, &h, &start, &stop);
   if (rc == HGM_OK) rc = decode_seq(c, f, start, stop, h, big_endian, &d_rows, &n_floats, &block);
@@ -1317,6 +1378,7 @@ static int cache_store(hgm_ctx *c, int64_t split_id, SplitSource &src, int32_t f
       }
       e = cudaMemcpyAsync(static_cast<unsigned char *>(d_rows) + off, c->h_bounce[bi], piece, cudaMemcpyHostToDevice,
                           c->stream);
+      c->staged_bytes += (int64_t)piece;
       if (e == cudaSuccess) e = cudaEventRecord(c->ev_bounce[bi], c->stream);
       if (e != cudaSuccess) rc = fail(c, HGM_ECUDA, "cache copy: %s", cudaGetErrorString(e));
       bi = (bi + 1) % kStages;
@@ -1324,6 +1386,7 @@ static int cache_store(hgm_ctx *c, int64_t split_id, SplitSource &src, int32_t f
     }
   } else if (src.nbytes) {
     e = cudaMemcpyAsync(d_rows, src.mem, src.nbytes, cudaMemcpyHostToDevice, c->stream);
+    c->staged_bytes += (int64_t)src.nbytes;
     if (e != cudaSuccess) rc = fail(c, HGM_ECUDA, "cache copy: %s", cudaGetErrorString(e));
   }
   if (rc == HGM_OK && fmt == HGM_FMT_F32BE) {

@@ -69,6 +69,7 @@ cudaError_t launch_segmented_sums(const float *d_pts, int64_t n, int d, int k, c
 // tcgen05 path (kernels_tensor.cu)
 bool tensor_shape_ok(int k, int d, size_t smem_optin);
 size_t tensor_caug_floats(int k, int d);
+void tensor_set_form(int form);  // HGM_TENSOR_FORM_*
 cudaError_t launch_tensor_prep(const float *d_cent, int k, int d, float *d_caug, unsigned int *d_cmax_bits,
                                cudaStream_t s);
 size_t tensor_meta_words(int k);  // uint32 words of per-launch cluster bookkeeping

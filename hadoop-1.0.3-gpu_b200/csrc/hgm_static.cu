@@ -20,7 +20,10 @@
 //    call before it is read.  Two calls of this process that overlap on one GPU (issued from
 //    different threads or on different streams) race on it: issue them one after the other;
 //  * the first call on a device looks the array's address up (cudaGetSymbolAddress) and
-//    reads the device attributes; make that first call outside any stream capture.
+//    reads the device attributes; make that first call outside any stream capture;
+//  * every call copies the centroids in and the results out of pageable host memory and waits for
+//    `cuda_stream` before it returns: the results are in the caller's host buffers then.  The
+//    caller's current device is put back before returning.
 #include <math.h>
 
 #include <mutex>
@@ -109,8 +112,14 @@ extern "C" int hgm_map_device_static(int device_id, const float *d_points, int64
   if (reinterpret_cast<uintptr_t>(d_points) & 7)
     return report_error(HGM_EINVAL, "hgm_map_device_static: d_points must be 8-byte aligned");
   if (device_id < 0 || device_id >= kMaxDevices) return report_error(HGM_ENODEV, "device id out of range");
+  int caller_device = -1;
+  cudaGetDevice(&caller_device);
   cudaError_t e = cudaSetDevice(device_id);
   if (e != cudaSuccess) return report_error(HGM_ENODEV, cudaGetErrorString(e));
+  struct RestoreDevice {  // leave the caller's current device as it was, on every path out
+    int device;
+    ~RestoreDevice() { if (device >= 0) cudaSetDevice(device); }
+  } restore{caller_device};
   DeviceSetup *dev = nullptr;
   int rc = setup_device(device_id, &dev);
   if (rc != HGM_OK) return rc;

@@ -661,13 +661,17 @@ using ShapeD = Shape<3, 256, true>;   // 768 threads, register prefetch
 using ShapeE = Shape<8, 128, false>;  // 1024 threads, eight groups of four warps: shorter barriers, smaller tiles
 using ShapeF = Shape<6, 128, false>;  // 768 threads, six groups
 
-// HGM_GRID2D_VARIANT forces a shape (tuning knob); otherwise the shape is picked per job.
+// Builds made with -DHGM_EXPERIMENTS let HGM_GRID2D_VARIANT force a shape; the product picks it per job.
 int forced_variant() {
+#ifdef HGM_EXPERIMENTS
   static const int variant = [] {
     const char *v = getenv("HGM_GRID2D_VARIANT");
     return v ? atoi(v) : -1;
   }();
   return variant;
+#else
+  return -1;
+#endif
 }
 
 // How the shared memory left after the table is split: slots of the sort buffer per group and

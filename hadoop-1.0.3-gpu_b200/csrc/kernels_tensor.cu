@@ -29,6 +29,8 @@
 #include <math.h>
 #include <stdlib.h>
 
+#include <atomic>
+
 #include "hgm_internal.h"
 
 namespace hgm {
@@ -194,6 +196,17 @@ __global__ void tensor_prep_kernel(const float *__restrict__ cent, int k, int k_
 }
 
 // ---- K2 ------------------------------------------------------------------------------------------
+std::atomic<int> g_tensor_form{HGM_TENSOR_FORM_AUTO};  // hgm_set_tensor_form: process-wide, tests and comparison runs
+// The experiment switches (skip the MMAs / TMEM loads / B tiles to time the roles apart; event log of CTA 0) exist
+// only in builds made with -DHGM_EXPERIMENTS (tools/microbench/*.sh).  The product build compiles them out: a stray
+// environment variable must not be able to make a map task return success with meaningless partials.
+#ifdef HGM_EXPERIMENTS
+#define HGM_DBG(a) ((a).debug)
+#define HGM_TRC(a) ((a).trace)
+#else
+#define HGM_DBG(a) 0
+#define HGM_TRC(a) (static_cast<long long *>(nullptr))
+#endif
 struct TensorArgs {
   long long n;
   int k, k_pad, d, stages;
@@ -276,7 +289,7 @@ __global__ void __launch_bounds__(kThreads, 1)
       }
       __syncwarp();
       a_phase ^= 1;
-      for (int tn = 0; tn < (a.debug == 3 ? 0 : ntiles_n); ++tn)
+      for (int tn = 0; tn < (HGM_DBG(a) == 3 ? 0 : ntiles_n); ++tn)
         for (int kb = 0; kb <= kblocks; ++kb) {
           mbar_wait_backoff(&empty[stage], phase ^ 1, 100);
           if (elect_one()) {
@@ -303,13 +316,13 @@ __global__ void __launch_bounds__(kThreads, 1)
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const uint32_t tacc0 = tmem_base + (uint32_t)(buf * 2 * kTileN), tacc1 = tacc0 + kTileN;
         for (int kb = 0; kb < kblocks; ++kb) {
-          if (a.debug != 3) mbar_wait_backoff(&full[stage], phase, 20);
+          if (HGM_DBG(a) != 3) mbar_wait_backoff(&full[stage], phase, 20);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           const uint64_t bd = b_desc0 + (uint64_t)(stage * (kBBytes >> 4));
           const uint64_t ad0 = a_desc0 + (uint64_t)(kb * (kABytes >> 4));
           const uint64_t ad1 = ad0 + (uint64_t)(kblocks * (kABytes >> 4));
           if (elect_one()) {
-            if (a.debug != 1) {
+            if (HGM_DBG(a) != 1) {
 #pragma unroll
             for (int ks = 0; ks < kBlockK / kUmmaK; ++ks) umma_tf32(tacc0, ad0 + 2 * ks, bd + 2 * ks, (kb | ks) != 0);
 #pragma unroll
@@ -321,11 +334,11 @@ __global__ void __launch_bounds__(kThreads, 1)
           if (++stage == (uint32_t)kStages) { stage = 0; phase ^= 1; }
         }
         {  // the |c|^2 K-block: x side = the constant tile, 3 live columns = one K-step
-          if (a.debug != 3) mbar_wait_backoff(&full[stage], phase, 20);
+          if (HGM_DBG(a) != 3) mbar_wait_backoff(&full[stage], phase, 20);
           asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
           const uint64_t bd = b_desc0 + (uint64_t)(stage * (kBBytes >> 4));
           if (elect_one()) {
-            if (a.debug != 1) {
+            if (HGM_DBG(a) != 1) {
               umma_tf32(tacc0, aug_desc, bd, 1);
               umma_tf32(tacc1, aug_desc, bd, 1);
             }
@@ -440,8 +453,8 @@ __global__ void __launch_bounds__(kThreads, 1)
           const float thr = 0.0078125f * xnorm * cmax + ((float)a.d * 2.3841858e-07f + 6.1035156e-05f) * reach * reach;
           a.assign[p] = bidx;
           if (second - best > thr) {
-            if (!a.debug) atomicAdd(a.lcounts + bidx, 1u);  // decided on the tensor cores
-          } else if (!a.debug) {  // inside the rounding bound (or NaN / inf): the exact scan decides
+            if (!HGM_DBG(a)) atomicAdd(a.lcounts + bidx, 1u);  // decided on the tensor cores
+          } else if (!HGM_DBG(a)) {  // inside the rounding bound (or NaN / inf): the exact scan decides
             const unsigned int slot = atomicAdd(a.flag_count, 1u);
             a.flag_list[slot] = (int32_t)p;  // p < 2^31 per launch (the host chunks larger inputs)
           }
@@ -584,7 +597,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
     // ===== TMA producer: in BOTH CTAs; every byte is counted on the leader's barriers =====
     uint32_t stage = 0, phase = 0, a_phase[2] = {0, 0};
     int ab = 0;
-    Trace tr{(a.trace && blockIdx.x == 0 && lane == 0) ? a.trace : nullptr, 0};
+    Trace tr{(HGM_TRC(a) && blockIdx.x == 0 && lane == 0) ? HGM_TRC(a) : nullptr, 0};
     for (long long tm = pair0; tm < tiles; tm += npairs) {
       tr(1, (int)tm);
       mbar_wait(&a_empty[ab], a_phase[ab] ^ 1);
@@ -617,7 +630,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
       const uint64_t a_desc0 = umma_desc(a_res, 0), aug_desc = umma_desc(a_aug, 0), b_desc0 = umma_desc(b_stage, 0);
       uint32_t stage = 0, phase = 0, a_phase[2] = {0, 0}, t_phase[2] = {0, 0};
       int buf = 0, ab = 0;
-      Trace tr{(a.trace && blockIdx.x == 0 && lane == 0) ? a.trace + 1024 : nullptr, 0};
+      Trace tr{(HGM_TRC(a) && blockIdx.x == 0 && lane == 0) ? HGM_TRC(a) + 1024 : nullptr, 0};
       for (long long tm = pair0; tm < tiles; tm += npairs) {
         tr(1, (int)tm);
         mbar_wait(&a_full[ab], a_phase[ab]);
@@ -638,7 +651,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
             if (elect_one()) {
 #pragma unroll
               for (int ks = 0; ks < kBlockK / kUmmaK; ++ks)
-                if (a.debug != 1) umma_tf32_pair(tacc, ad + 2 * ks, bd + 2 * ks, (kb | ks) != 0);
+                if (HGM_DBG(a) != 1) umma_tf32_pair(tacc, ad + 2 * ks, bd + 2 * ks, (kb | ks) != 0);
               umma_commit_pair(&empty[stage]);
             }
             __syncwarp();
@@ -649,7 +662,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
             const uint64_t bd = b_desc0 + (uint64_t)(stage * (kBBytes >> 4));
             if (elect_one()) {
-              if (a.debug != 1) umma_tf32_pair(tacc, aug_desc, bd, 1);
+              if (HGM_DBG(a) != 1) umma_tf32_pair(tacc, aug_desc, bd, 1);
               umma_commit_pair(&empty[stage]);
               umma_commit_pair(&t_full[buf]);
             }
@@ -675,7 +688,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
     const uint32_t keymask = a.keymask;
     uint32_t t_phase[2] = {0, 0}, d_phase[2] = {0, 0};
     int buf = 0, par = 0;
-    Trace tr{(a.trace && blockIdx.x == 0 && ew == 0 && lane == 0) ? a.trace + 2048 : nullptr, 0};
+    Trace tr{(HGM_TRC(a) && blockIdx.x == 0 && ew == 0 && lane == 0) ? HGM_TRC(a) + 2048 : nullptr, 0};
     for (long long tm = pair0; tm < tiles; tm += npairs) {
       tr(1, (int)tm);
       Top2 even, odd;
@@ -688,7 +701,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
         asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
         const uint32_t taddr = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)(buf * kPairN + colgroup * 64);
         uint32_t r0[32], r1[32];
-        if (a.debug == 2) {
+        if (HGM_DBG(a) == 2) {
           for (int i = 0; i < 32; ++i) r0[i] = r1[i] = 0x7F000000u + (uint32_t)tn;
         } else {
           tmem_ld32_issue(taddr, r0);
@@ -769,8 +782,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
           const float thr = 0.0078125f * xnorm * cmax + ((float)a.d * 2.3841858e-07f + 6.1035156e-05f) * reach * reach;
           a.assign[p] = bidx;
           if (second - best > thr) {
-            if (!a.debug) atomicAdd(a.lcounts + bidx, 1u);
-          } else if (!a.debug) {
+            if (!HGM_DBG(a)) atomicAdd(a.lcounts + bidx, 1u);
+          } else if (!HGM_DBG(a)) {
             const unsigned int slot = atomicAdd(a.flag_count, 1u);
             a.flag_list[slot] = (int32_t)p;
           }
@@ -1012,7 +1025,9 @@ size_t tensor_pair_smem_bytes(int d, int stages) {
 }
 int tensor_stages(int d, size_t smem_optin) {
   int stages = kMaxStages;
+#ifdef HGM_EXPERIMENTS
   if (const char *v = getenv("HGM_TENSOR_STAGES")) stages = atoi(v);  // tuning knob
+#endif
   if (stages > kMaxStages) stages = kMaxStages;
   while (stages > 2 && tensor_smem_bytes(d, stages) > smem_optin) --stages;
   return stages;
@@ -1142,9 +1157,9 @@ cudaError_t launch_tensor_map(const float *d_pts, int64_t n, int d, const float 
   // Which form: with the per-point decisions off the scan's critical path the pair kernel wins at both
   // benchmark shapes (A/B on one box: d = 64, k = 1024: 14.9 vs 15.3 ms for 40 M points; d = 128, k = 4096:
   // 14.3 vs 16.7 ms for 8 M); the single-CTA kernel keeps d <= 32, where a point tile is one K-block.
-  // HGM_TENSOR_FORM=single|pair overrides (comparison runs).
-  const char *form = getenv("HGM_TENSOR_FORM");
-  const bool pair = sm_count >= 2 && (form ? form[0] == 'p' : d > 32);
+  // hgm_set_tensor_form overrides (parity tests of both forms, comparison runs).
+  const int form = g_tensor_form.load();
+  const bool pair = sm_count >= 2 && (form == HGM_TENSOR_FORM_AUTO ? d > 32 : form == HGM_TENSOR_FORM_PAIR);
   int stages = tensor_stages(d, smem_optin);
   if (pair) {
     stages = kMaxStages;
@@ -1154,11 +1169,17 @@ cudaError_t launch_tensor_map(const float *d_pts, int64_t n, int d, const float 
   e = pair ? cudaFuncSetAttribute(tensor_assign_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
            : cudaFuncSetAttribute(tensor_assign_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  TensorArgs a{(long long)n, k, k_pad, d, stages, ~0x3Fu, nullptr, getenv("HGM_TENSOR_DEBUG") ? atoi(getenv("HGM_TENSOR_DEBUG")) : 0, d_cmax_bits, d_pts, d_meta, d_assign, d_flag_list, d_flag_count};
+  TensorArgs a{(long long)n, k, k_pad, d, stages, ~0x3Fu, nullptr, 0, d_cmax_bits, d_pts, d_meta, d_assign, d_flag_list, d_flag_count};
+#ifdef HGM_EXPERIMENTS
+  if (const char *v = getenv("HGM_TENSOR_DEBUG")) a.debug = atoi(v);
+#endif
   const long long tiles = (n + kTileM - 1) / kTileM;  // 256 points: one CTA's tile, or one pair's
   if (pair) {
     const long long pairs = tiles < sm_count / 2 ? tiles : sm_count / 2;
-    const char *trace_path = getenv("HGM_TENSOR_TRACE");  // experiments: event log of CTA 0, written after a sync
+    const char *trace_path = nullptr;
+#ifdef HGM_EXPERIMENTS
+    trace_path = getenv("HGM_TENSOR_TRACE");  // event log of CTA 0, written after a sync
+#endif
     if (trace_path) {
       long long *d_trace = nullptr;
       if (cudaMalloc(&d_trace, 3 * 1024 * 8) == cudaSuccess) {
@@ -1186,10 +1207,12 @@ cudaError_t launch_tensor_map(const float *d_pts, int64_t n, int d, const float 
     tensor_assign_kernel<<<grid, kThreads, smem, s>>>(map_x, map_c, a);
   }
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
-  if (a.debug) return cudaSuccess;  // experiments time K2 alone; its output is meaningless then
+  if (HGM_DBG(a)) return cudaSuccess;  // experiments time K2 alone; its output is meaningless then
   recheck_kernel<<<sm_count * 4, 256, 0, s>>>(d_pts, d, d_cent, k, d_flag_list, d_flag_count, d_assign, d_meta);
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
   return launch_segmented_sums(d_pts, n, d, k, d_assign, d_meta, d_order, d_sums, d_counts, sm_count, s);
 }
+
+void tensor_set_form(int form) { g_tensor_form.store(form); }
 
 }  // namespace hgm

@@ -3,6 +3,8 @@
 // Submitted exactly like the reference expects (pipes/Submitter.java:419-420, 349-379):
 //   bin/hadoop pipes -cpubin kmeans-pipes-cpu -gpubin kmeans-pipes-gpu -input ... -output ...
 //        -jobconf kmeans.k=128,kmeans.d=2,kmeans.centroids=centroids.bin
+// (no -inputformat / -reader: hadoop.pipes.java.recordreader is then absent, which Java reads as false,
+// pipes/Submitter.java:137-139 -- the C++ reader route below)
 // and started by pipes/Application.java:156-194 as `kmeans-pipes-gpu <GPUDeviceId>`.
 // It is written against the Pipes C++ API only (hadoop/Pipes.hh), so it builds against the
 // reference's libhadooppipes.a as well as against this repository's runtime, and reaches
@@ -123,7 +125,8 @@ class KMeansGpuMap : public HadoopPipes::Mapper {
   unsigned char *batch_ = nullptr;  // pinned
   size_t batch_cap_ = 0, batch_used_ = 0;
   int64_t points_ = 0;
-  HadoopPipes::TaskContext::Counter *pointsIn_, *gpuMicros_, *batches_;
+  HadoopPipes::TaskContext::Counter *pointsIn_, *gpuMicros_, *batches_, *rechecks_, *staged_;
+  int64_t staged_seen_ = 0;
 
   void fold() {
     for (size_t i = 0; i < sums_.size(); ++i) sums_[i] += part_sums_[i];
@@ -132,12 +135,22 @@ class KMeansGpuMap : public HadoopPipes::Mapper {
   void account(int64_t n, const hgmw::MapReply *from_worker = nullptr) {
     float ms = 0;
     int32_t launches = 0;
+    int64_t rechecks = 0, staged = 0;
     if (from_worker) {
       ms = from_worker->map_ms;
+      rechecks = from_worker->rechecks;
+      staged = from_worker->staged_bytes;
       if (from_worker->cache_hit) ctx_->incrementCounter(cacheHits_, 1);
     } else {
       hgm_last_map_ms(gpu_, &ms, &launches);
+      hgm_last_rechecks(gpu_, &rechecks);
+      int64_t total = 0;
+      hgm_staged_bytes(gpu_, &total);
+      staged = total - staged_seen_;
+      staged_seen_ = total;
     }
+    if (rechecks) ctx_->incrementCounter(rechecks_, (uint64_t)rechecks);
+    if (staged) ctx_->incrementCounter(staged_, (uint64_t)staged);
     points_ += n;
     ctx_->incrementCounter(pointsIn_, (uint64_t)n);
     ctx_->incrementCounter(gpuMicros_, (uint64_t)(ms * 1000.0f));
@@ -198,7 +211,9 @@ class KMeansGpuMap : public HadoopPipes::Mapper {
         fmt_code_ = formatCode(f);
       }
     }
-    if (conf->hasKey("hadoop.pipes.java.recordreader") && !conf->getBoolean("hadoop.pipes.java.recordreader"))
+    // absent = false, as Submitter.getIsJavaRecordReader reads it (pipes/Submitter.java:137-139): Java then sends
+    // RUN_MAP with pipedInput = false and no MAP_ITEMs, and the runtime asks the factory for a reader
+    if (!(conf->hasKey("hadoop.pipes.java.recordreader") && conf->getBoolean("hadoop.pipes.java.recordreader")))
       format_ = SPLIT;
     // a SequenceFile is decoded from the file (the sync marker is in its header); piped through Java's
     // SequenceFileRecordReader its BytesWritable values arrive as plain bytes: that is "binary-be"
@@ -223,6 +238,7 @@ class KMeansGpuMap : public HadoopPipes::Mapper {
       worker_cache_ = conf->hasKey("kmeans.gpu.worker.cache") && conf->getBoolean("kmeans.gpu.worker.cache");
       try {
         worker_ = new hgmw::Client(sock);
+        if (conf->hasKey("kmeans.gpu.worker.cache.epoch")) worker_->cache_epoch(conf->get("kmeans.gpu.worker.cache.epoch"));
         worker_->set_centroids(cent.data(), k_, d_);
       } catch (const std::exception &e) {
         throw HadoopUtils::Error(e.what());  // no worker, no task: the scheduler re-queues the split
@@ -251,6 +267,8 @@ class KMeansGpuMap : public HadoopPipes::Mapper {
     pointsIn_ = context.getCounter(KMEANS, "POINTS");
     gpuMicros_ = context.getCounter(KMEANS, "GPU_MAP_MICROS");
     batches_ = context.getCounter(KMEANS, "GPU_BATCHES");
+    rechecks_ = context.getCounter(KMEANS, "GPU_RECHECKS");      // points the tensor-core path re-scanned exactly
+    staged_ = context.getCounter(KMEANS, "GPU_BYTES_STAGED");    // split bytes copied host -> device
   }
 
   ~KMeansGpuMap() {
@@ -364,17 +382,19 @@ class KMeansPartitioner : public HadoopPipes::Partitioner {
   int partition(const std::string &key, int numOfReduces) { return HadoopUtils::toInt(key) % numOfReduces; }
 };
 
-// The C++ reader is created only when Java says the input is not piped.
+// The runtime creates the C++ reader only when Java says the input is not piped.
 class GpuFactory : public HadoopPipes::Factory {
  public:
   HadoopPipes::Mapper *createMapper(HadoopPipes::MapContext &c) const { return new KMeansGpuMap(c); }
   HadoopPipes::Reducer *createReducer(HadoopPipes::ReduceContext &c) const { return new KMeansReduce(c); }
   HadoopPipes::Partitioner *createPartitioner(HadoopPipes::MapContext &c) const { return new KMeansPartitioner(c); }
   HadoopPipes::RecordReader *createRecordReader(HadoopPipes::MapContext &c) const {
+    // The runtime asks on every map task and insists that a reader exists exactly when RUN_MAP said the input is
+    // not piped (HadoopPipes.cc:793-799).  The factory cannot see that flag, only the key Java derived it from:
+    // absent = false = not piped (pipes/Submitter.java:137-139).
     const HadoopPipes::JobConf *conf = c.getJobConf();
-    if (conf->hasKey("hadoop.pipes.java.recordreader") && !conf->getBoolean("hadoop.pipes.java.recordreader"))
-      return new WholeSplitReader(c);
-    return NULL;
+    if (conf->hasKey("hadoop.pipes.java.recordreader") && conf->getBoolean("hadoop.pipes.java.recordreader")) return NULL;
+    return new WholeSplitReader(c);
   }
 };
 

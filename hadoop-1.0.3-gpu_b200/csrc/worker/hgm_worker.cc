@@ -1,13 +1,16 @@
 // hgm_worker.cc -- the persistent GPU worker of one map slot (see worker_proto.hh).
 //
-//   hgm-worker --device 0 --socket /tmp/hgm-gpu0.sock [--max-batch-mib 64]
+//   hgm-worker --device 0 --socket /tmp/hgm-gpu0.sock [--max-batch-mib 1024]
 //
 // One process per device, started with the TaskTracker.  It reaches CUDA only
 // through the C ABI of libhgpumap.so; one client (= one map task) is served at a time, which is
 // exactly the slot discipline of the reference (one task per GPU slot, mapred/TaskTracker.java:
 // 2526-2562).  File splits mapped with use_cache=1 stay in the HBM split cache under
 // (path, offset, length, format, mtime, size): the next iteration's task for the same split maps
-// from HBM without touching the file (BASELINE config 3).
+// from HBM without touching the file (BASELINE config 3).  The cache is bounded by HBM: when a split does not
+// fit, stale versions of the same split (the file changed) and then the least recently used splits are dropped
+// until it does; kDropCache empties it (a new job's first task).  A MAP_BYTES batch is pinned host memory:
+// batches over --max-batch-mib are refused.
 #include <errno.h>
 #include <signal.h>
 #include <stdio.h>
@@ -56,8 +59,13 @@ struct Worker {
   std::vector<float> centroids;
   void *pinned = nullptr;
   size_t pinned_cap = 0;
-  std::map<std::string, int64_t> cache_ids;
+  struct Cached { int64_t id; uint64_t last_use; std::string split; };  // split = key without mtime and size
+  std::map<std::string, Cached> cache_ids;  // key: path|offset|length|format|mtime|size
   int64_t next_id = 0;
+  uint64_t tick = 0;
+  std::string epoch;  // the data set the cached splits belong to (kDropCache)
+  size_t max_batch = size_t(1024) << 20;
+  int64_t staged_before = 0;
   hgmw::WorkerStats stats{};
 
   bool reply(int fd, uint32_t op, int status, const void *payload, size_t n) {
@@ -76,6 +84,11 @@ struct Worker {
     r.n_points = n_points;
     r.cache_hit = cache_hit;
     hgm_last_map_ms(gpu, &r.map_ms, &r.launches);
+    hgm_last_rechecks(gpu, &r.rechecks);
+    int64_t staged = 0;
+    hgm_staged_bytes(gpu, &staged);
+    r.staged_bytes = staged - staged_before;
+    staged_before = staged;
     std::vector<char> out(sizeof r + sums.size() * 8 + counts.size() * 8);
     memcpy(out.data(), &r, sizeof r);
     memcpy(out.data() + sizeof r, sums.data(), sums.size() * 8);
@@ -106,17 +119,27 @@ struct Worker {
     int32_t fmt = 0;
     if (payload < 4 || !read_all(fd, &fmt, 4)) return false;
     const size_t nbytes = (size_t)(payload - 4);
+    auto skip_payload = [&]() {  // keep the stream in step, then report
+      std::vector<char> sink(1 << 20);
+      for (size_t left = nbytes; left;) {
+        const size_t m = left < sink.size() ? left : sink.size();
+        if (!read_all(fd, sink.data(), m)) return false;
+        left -= m;
+      }
+      return true;
+    };
+    if (nbytes > max_batch) {
+      if (!skip_payload()) return false;
+      char msg[160];
+      snprintf(msg, sizeof msg, "MAP_BYTES batch of %zu bytes is over the worker's --max-batch-mib %zu", nbytes, max_batch >> 20);
+      return reply_error(fd, hgmw::kMapBytes, HGM_EINVAL, msg);
+    }
     if (nbytes > pinned_cap) {
       if (pinned) hgm_host_free(gpu, pinned);
       pinned = nullptr;
       pinned_cap = 0;
       if (hgm_host_alloc(gpu, nbytes, &pinned) != HGM_OK) {
-        std::vector<char> sink(1 << 20);  // keep the stream in step, then report
-        for (size_t left = nbytes; left;) {
-          const size_t m = left < sink.size() ? left : sink.size();
-          if (!read_all(fd, sink.data(), m)) return false;
-          left -= m;
-        }
+        if (!skip_payload()) return false;
         return reply_gpu_error(fd, hgmw::kMapBytes, HGM_ENOMEM);
       }
       pinned_cap = nbytes;
@@ -149,21 +172,38 @@ struct Worker {
       struct stat st{};
       if (stat(path.c_str(), &st) != 0)
         return reply_error(fd, hgmw::kMapFile, HGM_EIO, "cannot stat " + path + ": " + strerror(errno));
-      char key[64];
-      snprintf(key, sizeof key, "|%lld|%lld|%d|%lld|%lld", (long long)off, (long long)len, fmt, (long long)st.st_mtime,
-               (long long)st.st_size);
-      const std::string id_key = path + key;
+      char key[64], version[64];
+      snprintf(key, sizeof key, "|%lld|%lld|%d", (long long)off, (long long)len, fmt);
+      snprintf(version, sizeof version, "|%lld|%lld", (long long)st.st_mtime, (long long)st.st_size);
+      const std::string split = path + key, id_key = split + version;
       auto it = cache_ids.find(id_key);
       int hit = 1;
       int64_t id;
       if (it == cache_ids.end()) {
         hit = 0;
         id = next_id++;
+        // other versions of this split are dead weight: the file has changed under them
+        for (auto v = cache_ids.begin(); v != cache_ids.end();) {
+          if (v->second.split == split) { hgm_cache_drop(gpu, v->second.id); v = cache_ids.erase(v); }
+          else ++v;
+        }
         rc = hgm_cache_put_file(gpu, id, path.c_str(), off, len, fmt);
-        if (rc == HGM_OK) cache_ids[id_key] = id;
+        // HBM is full: make room, least recently used first (arena blocks are returned to the driver as they
+        // empty, so a few drops may be needed before a block frees up)
+        while (rc == HGM_ENOMEM && !cache_ids.empty()) {
+          auto lru = cache_ids.begin();
+          for (auto v = cache_ids.begin(); v != cache_ids.end(); ++v)
+            if (v->second.last_use < lru->second.last_use) lru = v;
+          hgm_cache_drop(gpu, lru->second.id);
+          cache_ids.erase(lru);
+          stats.cache_evictions += 1;
+          rc = hgm_cache_put_file(gpu, id, path.c_str(), off, len, fmt);
+        }
+        if (rc == HGM_OK) cache_ids[id_key] = Cached{id, ++tick, split};
         else if (rc != HGM_ENOMEM) return reply_gpu_error(fd, hgmw::kMapFile, rc);
       } else {
-        id = it->second;
+        id = it->second.id;
+        it->second.last_use = ++tick;
       }
       if (hit || cache_ids.count(id_key)) {
         rc = hgm_reset_partials(gpu);
@@ -210,6 +250,16 @@ struct Worker {
           ok = reply(fd, h.op, 0, &stats, sizeof stats);
           break;
         }
+        case hgmw::kDropCache: {
+          const std::string asked(p.begin(), p.end());
+          if (asked.empty() || asked != epoch) {
+            for (auto &v : cache_ids) hgm_cache_drop(gpu, v.second.id);
+            cache_ids.clear();
+            epoch = asked;
+          }
+          ok = reply(fd, h.op, 0, nullptr, 0);
+          break;
+        }
         case hgmw::kShutdown:
           reply(fd, h.op, 0, nullptr, 0);
           return false;
@@ -224,12 +274,15 @@ struct Worker {
 
 int main(int argc, char **argv) {
   int device = 0;
+  long max_batch_mib = 1024;
   std::string path;
   for (int i = 1; i + 1 < argc; i += 2) {
     if (!strcmp(argv[i], "--device")) device = atoi(argv[i + 1]);
     else if (!strcmp(argv[i], "--socket")) path = argv[i + 1];
-    else { fprintf(stderr, "usage: hgm-worker --device N --socket PATH\n"); return 2; }
+    else if (!strcmp(argv[i], "--max-batch-mib")) max_batch_mib = atol(argv[i + 1]);
+    else { fprintf(stderr, "usage: hgm-worker --device N --socket PATH [--max-batch-mib M]\n"); return 2; }
   }
+  if (max_batch_mib < 1) { fprintf(stderr, "hgm-worker: --max-batch-mib must be at least 1\n"); return 2; }
   if (path.empty() || path.size() >= sizeof(sockaddr_un{}.sun_path)) {
     fprintf(stderr, "usage: hgm-worker --device N --socket PATH (PATH shorter than %zu bytes)\n", sizeof(sockaddr_un{}.sun_path));
     return 2;
@@ -237,6 +290,7 @@ int main(int argc, char **argv) {
   signal(SIGPIPE, SIG_IGN);
   Worker w;
   w.device = device;
+  w.max_batch = (size_t)max_batch_mib << 20;
   if (hgm_open(device, &w.gpu) != HGM_OK) {  // no device, no worker: tasks that need it fail loudly
     fprintf(stderr, "hgm-worker: hgm_open(%d): %s\n", device, hgm_last_error(nullptr));
     return 1;

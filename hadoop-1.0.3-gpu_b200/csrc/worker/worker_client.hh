@@ -114,6 +114,13 @@ class Client {
     put(path.data(), path.size());
     return map_reply(kMapFile, sums, counts, info);
   }
+  // kmeans.gpu.worker.cache.epoch: the cache holds splits of ONE data set; a task of another one clears it
+  void cache_epoch(const std::string &epoch) {
+    Header h{kMagic, kDropCache, 0, 0, epoch.size()};
+    put(&h, sizeof h);
+    if (!epoch.empty()) put(epoch.data(), epoch.size());
+    reply(kDropCache);
+  }
   WorkerStats stats() {
     Header h{kMagic, kStats, 0, 0, 0};
     put(&h, sizeof h);

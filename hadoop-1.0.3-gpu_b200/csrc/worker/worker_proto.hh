@@ -16,7 +16,7 @@
 namespace hgmw {
 
 constexpr uint32_t kMagic = 0x574D4748u;  // "HGMW"
-constexpr uint32_t kVersion = 1;
+constexpr uint32_t kVersion = 2;  // 2: MapReply carries re-checks and staged bytes; kDropCache
 
 enum Op : uint32_t {
   kHello = 1,         // payload: uint32 version                         -> reply payload: uint32 version, int32 device
@@ -25,6 +25,8 @@ enum Op : uint32_t {
   kMapFile = 4,       // payload: int32 fmt, int32 use_cache, int64 offset, int64 length, path bytes -> same
   kStats = 5,         // empty                                           -> WorkerStats
   kShutdown = 6,      // empty                                           -> empty, then the worker exits
+  kDropCache = 7,     // payload: epoch bytes (may be empty)                 -> empty; a non-empty epoch that differs from the
+                      //   worker's current one, or an empty payload, drops every cached split (a new data set)
 };
 
 struct Header {
@@ -41,10 +43,12 @@ struct MapReply {      // followed by k*d doubles (sums) and k int64 (counts)
   int32_t launches;
   int32_t cache_hit;   // the split came from the HBM cache
   int32_t reserved;
+  int64_t rechecks;      // points the tensor-core path re-scanned exactly (hgm_last_rechecks)
+  int64_t staged_bytes;  // bytes this call copied host -> device (0 on a cache hit)
 };
 
 struct WorkerStats {
-  int64_t tasks, map_calls, cache_hits, cache_misses, cached_splits, cached_bytes, kernel_launches;
+  int64_t tasks, map_calls, cache_hits, cache_misses, cached_splits, cached_bytes, kernel_launches, cache_evictions;
 };
 
 }  // namespace hgmw

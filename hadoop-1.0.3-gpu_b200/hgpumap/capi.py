@@ -20,6 +20,7 @@ import numpy as np
 FMT_F32LE, FMT_F32BE, FMT_TEXT, FMT_SEQ_F32BE, FMT_SEQ_F32LE = 0, 1, 2, 3, 4
 KERNEL_AUTO, KERNEL_EXACT, KERNEL_GRID2D, KERNEL_TENSOR, KERNEL_GRID2D_SORT = 0, 1, 2, 3, 4
 GRID2D_FORM_NONE, GRID2D_FORM_FIXED_POINT, GRID2D_FORM_SORT = 0, 1, 2
+TENSOR_FORM_AUTO, TENSOR_FORM_SINGLE, TENSOR_FORM_PAIR = 0, 1, 2
 
 _PKG_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 _LIB = None
@@ -47,6 +48,8 @@ SIGNATURES = {
     "hgm_set_centroids": (C.c_int, [_c_ctx, _p, C.c_int32, C.c_int32]),
     "hgm_set_kernel": (C.c_int, [_c_ctx, C.c_int32]),
     "hgm_last_kernel": (C.c_int, [_c_ctx, C.POINTER(C.c_int32)]),
+    "hgm_staged_bytes": (C.c_int, [_c_ctx, C.POINTER(C.c_int64)]),
+    "hgm_set_tensor_form": (C.c_int, [C.c_int32]),
     "hgm_grid2d_form": (C.c_int, [_c_ctx, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "hgm_map_split": (C.c_int, [_c_ctx, _p, C.c_size_t, C.c_int32, _p, _p, _p, C.POINTER(C.c_int64)]),
     "hgm_map_file": (C.c_int, [_c_ctx, C.c_char_p, C.c_int64, C.c_int64, C.c_int32, _p, _p, _p,
@@ -153,6 +156,10 @@ class GpuMapSlot:
 
     def set_kernel(self, kernel: int) -> None:
         self._check(self._lib.hgm_set_kernel(self._ctx, kernel))
+
+    def set_tensor_form(self, form: int) -> None:
+        """Process-wide: which form of the tcgen05 score kernel runs (TENSOR_FORM_*)."""
+        self._check(self._lib.hgm_set_tensor_form(form))
 
     def grid2d_form(self):
         """(form, cells per side) of the installed d == 2 index: GRID2D_FORM_*."""
@@ -275,6 +282,11 @@ class GpuMapSlot:
         ms, n = C.c_float(), C.c_int32()
         self._check(self._lib.hgm_last_map_ms(self._ctx, C.byref(ms), C.byref(n)))
         return ms.value, n.value
+
+    def staged_bytes(self) -> int:
+        n = C.c_int64()
+        self._check(self._lib.hgm_staged_bytes(self._ctx, C.byref(n)))
+        return n.value
 
     def last_rechecks(self) -> int:
         n = C.c_int64()

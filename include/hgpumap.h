@@ -10,7 +10,7 @@
  *
  * so each entry point below names the reference interface it stands under
  * (paths relative to /root/reference/hadoop-1.0.3/src).  Two hosts bind this header:
- * the Pipes child `kmeans-pipes-gpu` (the -gpubin; csrc/pipes_gpu_main.cc) and a JNI
+ * the Pipes child `kmeans-pipes-gpu` (the -gpubin; csrc/pipes/kmeans_pipes_gpu.cc) and a JNI
  * stub inside the task JVM.
  *
  * Conventions: plain C, no C++ or torch types; every function returns 0 or a negative
@@ -110,6 +110,12 @@ int hgm_set_kernel(hgm_ctx *ctx, int32_t kernel);
 /* Which family the last map call actually ran (one of HGM_KERNEL_*; HGM_KERNEL_GRID2D_SORT only
  * when that form was forced). */
 int hgm_last_kernel(hgm_ctx *ctx, int32_t *kernel);
+/* Which form of the tcgen05 score kernel runs (process-wide; parity tests of both forms and comparison runs):
+ * AUTO picks by d (one CTA per 256-point tile for d <= 32, a cta_group::2 pair above). */
+#define HGM_TENSOR_FORM_AUTO 0
+#define HGM_TENSOR_FORM_SINGLE 1
+#define HGM_TENSOR_FORM_PAIR 2
+int hgm_set_tensor_form(int32_t form);
 /* d == 2 only: which combiner the installed index drives -- 0 none (no index), 1 fixed-point
  * (csrc/kernels_grid2d_fx.cu), 2 counting sort (csrc/kernels_grid2d.cu) -- and its table side G. */
 int hgm_grid2d_form(hgm_ctx *ctx, int32_t *form, int32_t *cells_per_side);
@@ -195,6 +201,10 @@ int hgm_last_map_ms(hgm_ctx *ctx, float *ms, int32_t *launches);
  * inside the TF32 rounding bound and were re-scanned with the exact FP32 arithmetic
  * (0 for the other kernel families).  Synchronises the ctx stream. */
 int hgm_last_rechecks(hgm_ctx *ctx, int64_t *points);
+/* Bytes of input splits this ctx has copied host -> device since hgm_open (a split mapped from the HBM cache adds
+ * nothing).  The Pipes program exports the per-task difference as counter KMEANS/GPU_BYTES_STAGED and the
+ * re-checks as KMEANS/GPU_RECHECKS (mechanism: c++/pipes/impl/HadoopPipes.cc:346-359). */
+int hgm_staged_bytes(hgm_ctx *ctx, int64_t *bytes);
 /* Total kernels this ctx has launched since hgm_open. */
 int hgm_launch_count(hgm_ctx *ctx, int64_t *launches);
 
@@ -212,7 +222,9 @@ int hgm_launch_count(hgm_ctx *ctx, int64_t *launches);
  * All calls on one GPU share that array, which keeps the previous call's contents (the call
  * clears what it accumulates into): calls that overlap on a GPU race -- run them one at a
  * time.  The first call on a device also looks up the array's device address; make that
- * first call before starting any stream capture. */
+ * first call before starting any stream capture.  Every call waits for cuda_stream before it
+ * returns (sums_kxd and counts_k are host memory and are complete then) and leaves the caller's
+ * current device as it found it. */
 int hgm_map_device_static(int device_id, const float *d_points, int64_t n_points,
                           const float *centroids, int32_t k, int32_t d, double *sums_kxd,
                           int64_t *counts_k, int32_t *d_assign_or_null, void *cuda_stream);

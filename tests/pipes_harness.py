@@ -85,7 +85,8 @@ def kmeans_downlink(points, centroid_path, k, d, fmt="binary", num_reduces=1, pe
     import numpy as np
 
     conf = {"kmeans.k": str(k), "kmeans.d": str(d), "kmeans.centroids": centroid_path,
-            "kmeans.input.format": fmt, "io.sort.mb": str(io_sort_mb)}
+            "kmeans.input.format": fmt, "io.sort.mb": str(io_sort_mb),
+            "hadoop.pipes.java.recordreader": "true"}  # piped input (pipes/Submitter.java:128-139)
     conf.update(extra_conf or {})
     dl = (wire.Downlink().authenticate().start().set_job_conf(conf)
           .set_input_types("org.apache.hadoop.io.LongWritable", "org.apache.hadoop.io.BytesWritable")

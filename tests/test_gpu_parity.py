@@ -22,6 +22,15 @@ def slot():
     s.close()
 
 
+@pytest.fixture
+def tensor_form(slot):
+    """Force one form of the tcgen05 score kernel for a test; AUTO again afterwards."""
+    def force(name):
+        slot.set_tensor_form({"single": capi.TENSOR_FORM_SINGLE, "pair": capi.TENSOR_FORM_PAIR}[name])
+    yield force
+    slot.set_tensor_form(capi.TENSOR_FORM_AUTO)
+
+
 def run_case(slot, oracle, pts, cent, kernel, fmt=capi.FMT_F32LE, want_kernel=None):
     slot.set_kernel(kernel)
     slot.set_centroids(cent)
@@ -274,26 +283,27 @@ def test_idempotent_and_centroid_update_roundtrip(slot, oracle):
 
 # ---- the tcgen05 path (K2 scores + K3 exact re-check + K4 accumulate) ---------------------------
 
-@pytest.mark.parametrize("d,k,n", [(32, 128, 5000), (64, 1024, 20011), (128, 512, 6001), (96, 300, 4097),
+@pytest.mark.parametrize("d,k,n", [(128, 4096, 20011), (64, 1024, 200003),   # BASELINE configs 5 and 4 at their real d and k
+                                   (32, 128, 5000), (64, 1024, 20011), (128, 512, 6001), (96, 300, 4097),
                                    (64, 129, 255), (64, 256, 256), (64, 256, 1), (64, 100, 3001), (32, 9, 2000),
                                    (128, 8, 1000), (16, 200, 3000), (48, 64, 3001), (100, 300, 2500),
                                    (8, 1024, 4000), (20, 128, 2999), (124, 40, 1000), (36, 70, 777)])
 @pytest.mark.parametrize("form", ["single", "pair"])
-def test_tensor_path_matches_oracle(slot, oracle, monkeypatch, form, d, k, n):
+def test_tensor_path_matches_oracle(slot, oracle, tensor_form, form, d, k, n):
     """BASELINE config 4/5 shapes at test size: assignments bit-exact through the TF32 GEMM +
     FP32 re-check, counts exact, sums within tolerance -- in both forms of K2 (one CTA per tile,
-    and the cta_group::2 pair; the library picks by shape, HGM_TENSOR_FORM forces one)."""
-    monkeypatch.setenv("HGM_TENSOR_FORM", form)
+    and the cta_group::2 pair; the library picks by shape, hgm_set_tensor_form forces one)."""
+    tensor_form(form)
     pts, cent = cases.general_d(n, d, k, seed=d + k)
     run_case(slot, oracle, pts, cent, capi.KERNEL_TENSOR)
 
 
 @pytest.mark.parametrize("form", ["single", "pair"])
-def test_tensor_path_decides_almost_everything_on_the_tensor_cores(slot, oracle, monkeypatch, form):
+def test_tensor_path_decides_almost_everything_on_the_tensor_cores(slot, oracle, tensor_form, form):
     """If the GEMM scores were wrong every point would be flagged and the exact re-check would
     hide it: on well-separated data the re-check must stay rare, on duplicated centroids it
     must take (at least) the points of the duplicated clusters."""
-    monkeypatch.setenv("HGM_TENSOR_FORM", form)
+    tensor_form(form)
     pts, cent = cases.general_d(50000, 64, 1024, seed=77)
     slot.set_kernel(capi.KERNEL_TENSOR)
     slot.set_centroids(cent)
@@ -344,10 +354,34 @@ def test_tensor_path_near_ties_are_rechecked_exactly(slot, oracle):
 
 
 @pytest.mark.parametrize("form", ["single", "pair"])
-def test_tensor_path_with_non_finite_centroids(slot, oracle, monkeypatch, form):
+def test_tensor_path_near_ties_across_centroid_tiles_at_k4096(slot, oracle, tensor_form, form):
+    """Config 5's k: 32 centroid tiles (16 pair tiles) per point tile.  Duplicates and one-ulp neighbours are
+    planted in DIFFERENT tiles (and at tile edges), so the running (best, second, tile) of a row has to be merged
+    across tiles correctly and the lowest index has to win through the exact re-check."""
+    tensor_form(form)
+    rng = np.random.default_rng(4096)
+    d, k = 128, 4096
+    cent = rng.normal(0, 4, size=(k, d)).astype(np.float32)
+    pairs = [(5, 4000), (127, 128), (255, 256), (128, 3967), (1000, 3000), (2047, 2048), (4095, 0), (300, 2348)]
+    for lo, hi in pairs[:5]:
+        cent[max(lo, hi)] = cent[min(lo, hi)]                       # exact duplicates, far apart in index
+    for lo, hi in pairs[5:]:
+        cent[hi] = np.nextafter(cent[lo], np.float32(np.inf))       # one ulp apart
+    owners = np.array([min(p) for p in pairs] + [max(p) for p in pairs])
+    which = np.concatenate([rng.choice(owners, 6000), rng.integers(0, k, 6000)])
+    pts = (cent[which] + rng.normal(0, 0.5, size=(len(which), d))).astype(np.float32)
+    pts = np.concatenate([pts, cent[owners]])                        # points exactly on the planted centroids
+    run_case(slot, oracle, pts, cent, capi.KERNEL_TENSOR)
+    assert slot.last_rechecks() >= 6000
+    a = oracle.assign(pts, cent)
+    assert not np.isin(a, [max(p) for p in pairs[:5]]).any()
+
+
+@pytest.mark.parametrize("form", ["single", "pair"])
+def test_tensor_path_with_non_finite_centroids(slot, oracle, tensor_form, form):
     """A NaN or infinite centroid poisons every score bound: nothing may be decided on the tensor
     cores then, and the exact re-check must reproduce the scan (NaN and +inf distances never win)."""
-    monkeypatch.setenv("HGM_TENSOR_FORM", form)
+    tensor_form(form)
     pts, cent = cases.general_d(1500, 64, 256, seed=12)
     cent = cent.copy()
     cent[3, 5] = np.nan

@@ -17,7 +17,10 @@ GPU_BIN_REFRT = os.path.join(REF_DIR, "kmeans-pipes-gpu-refrt")
 
 
 def gpu_conf(cpath, k, d, fmt="binary", **extra):
-    conf = {"kmeans.k": str(k), "kmeans.d": str(d), "kmeans.centroids": cpath, "kmeans.input.format": fmt}
+    # piped input unless a test says otherwise: a job whose records come through Java's reader carries
+    # hadoop.pipes.java.recordreader=true (pipes/Submitter.java:128-139; absent means false)
+    conf = {"kmeans.k": str(k), "kmeans.d": str(d), "kmeans.centroids": cpath, "kmeans.input.format": fmt,
+            "hadoop.pipes.java.recordreader": "true"}
     conf.update({key.replace("_", "."): str(v) for key, v in extra.items()})
     return conf
 
@@ -45,6 +48,7 @@ def check_records(up, pts, cent, oracle, num_reduces):
         assert all(p == int(key) % num_reduces for p, key, _ in recs)
     assert up.counter("KMEANS", "POINTS") == len(pts)
     assert up.counter("KMEANS", "GPU_BATCHES") >= 1
+    assert up.counter("KMEANS", "GPU_BYTES_STAGED") == pts.astype("<f4").nbytes  # every row crossed to the device once
 
 
 @pytest.mark.parametrize("binary", [GPU_BIN, GPU_BIN_REFRT], ids=["own-runtime", "reference-runtime"])
@@ -82,16 +86,22 @@ def test_gpubin_matches_cpubin_record_for_record(oracle, tmp_path):
         np.testing.assert_allclose([float(x) for x in gf[1:]], [float(x) for x in cf[1:]], rtol=1e-9, atol=1e-6)
 
 
-def test_gpubin_cpp_record_reader_route_with_filesplit(oracle, tmp_path):
-    """hadoop.pipes.java.recordreader=false: Java sends only the FileSplit; the child maps the
-    byte range itself (hgm_map_file).  Two splits of one file = the whole file."""
+@pytest.mark.parametrize("key", ["false", None], ids=["key-false", "key-absent"])
+def test_gpubin_cpp_record_reader_route_with_filesplit(oracle, tmp_path, key):
+    """hadoop.pipes.java.recordreader=false, or absent -- Submitter.getIsJavaRecordReader defaults to false
+    (pipes/Submitter.java:137-139), which is what the command in kmeans_pipes_gpu.cc's header submits: Java sends
+    only the FileSplit with pipedInput = false; the child maps the byte range itself (hgm_map_file).  Two splits of
+    one file = the whole file."""
     pts, cent = cases.blobs(50000, 2, 64, seed=29)
     cpath = str(tmp_path / "cent.bin")
     cent.astype("<f4").tofile(cpath)
     data = str(tmp_path / "points.bin")
     pts.astype("<f4").tofile(data)
-    conf = gpu_conf(cpath, 64, 2, hadoop_pipes_java_recordreader="false")
-    conf["hadoop.pipes.java.recordreader"] = "false"
+    conf = gpu_conf(cpath, 64, 2)
+    if key is None:
+        del conf["hadoop.pipes.java.recordreader"]
+    else:
+        conf["hadoop.pipes.java.recordreader"] = key
     total_counts = np.zeros(64, np.int64)
     total_sums = np.zeros((64, 2))
     for off, length in ((0, 20000 * 8), (20000 * 8, 30000 * 8)):
@@ -129,6 +139,23 @@ def test_gpubin_path_records_and_no_reduces(oracle, tmp_path):
     up = wire.parse_uplink(out)
     assert up.done and not up.partitioned, proc.stderr
     check_records(up, pts, cent, oracle, 0)
+
+
+def test_gpubin_exports_recheck_counter(oracle, tmp_path):
+    """the GPU program reports how many points the tensor-core path had to re-scan exactly
+    (KMEANS/GPU_RECHECKS, registered like any Pipes counter: HadoopPipes.cc:346-359)."""
+    pts, cent = cases.general_d(6000, 64, 256, seed=41)
+    cent = cent.copy()
+    cent[9] = cent[8]  # a duplicated centroid: every point of cluster 8 is a tie the scores cannot break
+    cpath = str(tmp_path / "cent.bin")
+    cent.astype("<f4").tofile(cpath)
+    proc, data, _ = ph.run_child(GPU_BIN, piped_downlink(pts, gpu_conf(cpath, 256, 64), 1, 100), args=("0",))
+    up = wire.parse_uplink(data)
+    assert up.done, proc.stderr
+    counts, _ = wire.kmeans_partials([(key, v) for _, key, v in up.partitioned], 256, 64)
+    assert counts[9] == 0 and counts[8] > 0
+    assert up.counter("KMEANS", "GPU_RECHECKS") >= counts[8]
+    assert up.counter("KMEANS", "GPU_BYTES_STAGED") == pts.nbytes
 
 
 def test_gpubin_fails_the_task_loudly(tmp_path):

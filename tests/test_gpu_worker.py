@@ -37,7 +37,7 @@ def worker(tmp_path):
 
 def conf_for(cpath, k, d, sock, fmt="binary", cache=False):
     conf = {"kmeans.k": str(k), "kmeans.d": str(d), "kmeans.centroids": cpath, "kmeans.input.format": fmt,
-            "kmeans.gpu.worker.socket": sock.replace("gpu0", "gpu%d")}
+            "kmeans.gpu.worker.socket": sock.replace("gpu0", "gpu%d"), "hadoop.pipes.java.recordreader": "true"}
     if cache:
         conf["kmeans.gpu.worker.cache"] = "true"
     return conf

@@ -43,7 +43,7 @@ class StandInWorker(threading.Thread):
         if self.fail:
             return self._reply(conn, op, -1002, b"stand-in says no")
         sums, counts, _, _ = self.oracle.map_combine(rows, self.cent)
-        head = struct.pack("<qfiii", len(rows), 0.25, 1, hit, 0)
+        head = struct.pack("<qfiiiqq", len(rows), 0.25, 1, hit, 0, 3, 0 if hit else rows.nbytes)  # MapReply, protocol 2
         self._reply(conn, op, 0, head + sums.astype("<f8").tobytes() + counts.astype("<i8").tobytes())
 
     def run(self):
@@ -55,7 +55,7 @@ class StandInWorker(threading.Thread):
                 p = self._read(conn, n)
                 self.log.append(op)
                 if op == 1:
-                    self._reply(conn, op, 0, struct.pack("<Ii", 1, 3))
+                    self._reply(conn, op, 0, struct.pack("<Ii", 2, 3))
                 elif op == 2:
                     k, d = struct.unpack("<ii", p[:8])
                     self.cent = np.frombuffer(p[8:], "<f4").reshape(k, d).copy()
@@ -69,6 +69,9 @@ class StandInWorker(threading.Thread):
                     self.file_request = (fmt, use_cache, off, length, p[24:].decode())
                     raw = open(p[24:].decode(), "rb").read()[off:off + length]
                     self._map(conn, op, np.frombuffer(raw, "<f4").reshape(-1, self.cent.shape[1]), hit=use_cache)
+                elif op == 7:
+                    self.epoch = p.decode()
+                    self._reply(conn, op, 0)
                 else:
                     self._reply(conn, op, -22, b"unknown")
         except EOFError:
@@ -80,7 +83,7 @@ class StandInWorker(threading.Thread):
 
 def job_conf(cpath, k, d, sock):
     return {"kmeans.k": str(k), "kmeans.d": str(d), "kmeans.centroids": cpath, "kmeans.input.format": "binary",
-            "kmeans.gpu.worker.socket": sock}
+            "kmeans.gpu.worker.socket": sock, "hadoop.pipes.java.recordreader": "true"}  # piped input, as Submitter sets it for a Java reader
 
 
 @pytest.mark.skipif(not os.path.exists(GPU_BIN), reason="kmeans-pipes-gpu not built")
