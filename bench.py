@@ -55,21 +55,28 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--kernel", type=int, default=0, help="force a kernel family (hgpumap.h HGM_KERNEL_*)")
+    ap.add_argument("--tensor-form", choices=["auto", "single", "pair"], default="auto")
+    ap.add_argument("--no-extra", action="store_true", help="skip the `extra` lines (other inputs, configs 4 and 5)")
     return ap.parse_args()
 
 
 def ncu_traffic(kernel_family, d, k, n):
     """(DRAM bytes per launch, what the capture says limits the kernel) for the dominant kernel, from the
     committed ncu --set full capture of exactly this workload (profiles/ncu_traffic.json), else (None, None)."""
-    from hgpumap import capi
-
-    fam = {capi.KERNEL_GRID2D: "grid2d_map_kernel", capi.KERNEL_TENSOR: "tensor_assign_kernel"}.get(kernel_family)
+    fam = kernel_family
     try:
         table = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
         entry = table[f"{fam}:d={d}:k={k}:points={n}"]
         return entry["bytes"], entry.get("limiter")
     except (OSError, KeyError, ValueError):
         return None, None
+
+
+def kernel_name(capi, slot, family):
+    """The dominant kernel of a family as it is named in the library (and in the ncu launch lists)."""
+    if family in (capi.KERNEL_GRID2D, capi.KERNEL_GRID2D_SORT):
+        return "grid2d_fx_kernel" if slot.grid2d_form()[0] == capi.GRID2D_FORM_FIXED_POINT else "grid2d_map_kernel"
+    return {capi.KERNEL_EXACT: "exact_map_kernel", capi.KERNEL_TENSOR: "tensor_assign_kernel"}.get(family, "?")
 
 
 def workload_name(args):
@@ -182,6 +189,58 @@ def run_reference_arm(args):
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+def cpu_direct(args, threads, points_per_thread=1 << 18):
+    """B-direct of BASELINE.md section 3: the mapper + combiner arithmetic called directly (the oracle's C
+    restatement, no Pipes protocol, no per-record framing), one slice per host thread.  The arithmetic-only CPU
+    rate, printed beside the protocol-bound B-pipes figure."""
+    import ctypes as C
+    from concurrent.futures import ThreadPoolExecutor
+
+    from hgpumap import synth
+
+    so = os.path.join(ROOT, "oracle", "libkmeans_oracle.so")
+    if not os.path.exists(so):
+        subprocess.run(["make", "-C", os.path.join(ROOT, "oracle"), "oracle"], check=True, capture_output=True)
+    lib = C.CDLL(so)
+    centres = synth.centres(synth.SEED_POINTS, args.k, args.d)
+    cent = synth.perturb(synth.SEED_CENTROIDS, centres)
+    slices = [synth.points(synth.SEED_POINTS, i * points_per_thread, points_per_thread, centres) for i in range(threads)]
+    p = lambda a: a.ctypes.data_as(C.c_void_p)  # noqa: E731
+
+    def one(pts):
+        sums = np.zeros((args.k, args.d))
+        counts = np.zeros(args.k, np.int64)
+        lib.hgo_map_combine(p(pts), C.c_int64(len(pts)), args.d, p(cent), args.k, p(sums), p(counts), None, None)
+        return int(counts.sum())
+
+    with ThreadPoolExecutor(threads) as pool:
+        list(pool.map(one, slices[:threads]))  # warm
+        t0 = time.perf_counter()
+        done = sum(pool.map(one, slices))      # ctypes releases the GIL: the threads run on separate cores
+        dt = time.perf_counter() - t0
+    return {"value": done / dt, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": f"{threads} threads x {points_per_thread:,} points through the C restatement of the mapper + combiner "
+                      "(oracle/kmeans_oracle.c), called directly: no Pipes protocol"}
+
+
+def other_points(torch, dev, kind, n, centres, seed=20261108):
+    """Inputs a map task does not choose (d = 2): `uniform` = points uniform over the centroids' box + 20 %, ~13 %
+    of them in multi-candidate cells of the index and a few outside it; `skew` = 60 % of the points in ONE cluster,
+    the rest spread over the others."""
+    g = torch.Generator(device=dev)
+    g.manual_seed(seed)
+    c = torch.as_tensor(centres, device=dev)
+    if kind in ("uniform", "uniform_in"):
+        lo, hi = c.min(0).values, c.max(0).values
+        pad = (0.2 if kind == "uniform" else 0.0) * (hi - lo)
+        return (torch.rand(n, c.shape[1], device=dev, generator=g) * (hi - lo + 2 * pad) + (lo - pad)).float()
+    if kind == "skew":
+        ids = torch.randint(0, c.shape[0], (n,), device=dev, generator=g)
+        ids[torch.rand(n, device=dev, generator=g) < 0.6] = 5 % c.shape[0]
+        return (c[ids] + torch.randn(n, c.shape[1], device=dev, generator=g)).float()
+    raise ValueError(kind)
 
 
 # ---------------------------------------------------------------------------------------
@@ -309,6 +368,114 @@ def bind_to_gpu_numa_node(local_rank):
         return None
 
 
+def timed_steps(torch, dist, slot, stream, ptr, n, steps, world, warm=3):
+    """`steps` passes of reset -> map -> (allreduce) over n HBM-resident points: (ms per step, map ms per step),
+    CUDA events on the library's stream, barrier on both sides, max over ranks."""
+    def one():
+        slot.reset_partials()
+        slot.map_device(ptr, n)
+        if world > 1:
+            slot.allreduce_partials()
+
+    for _ in range(warm):
+        one()
+    slot.sync()
+    k_a = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+    k_b = [torch.cuda.Event(enable_timing=True) for _ in range(steps)]
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ev0.record(stream)
+    for i in range(steps):
+        slot.reset_partials()
+        k_a[i].record(stream)
+        slot.map_device(ptr, n)
+        k_b[i].record(stream)
+        if world > 1:
+            slot.allreduce_partials()
+    ev1.record(stream)
+    slot.sync()
+    if world > 1:
+        dist.barrier()
+    t = torch.tensor([ev0.elapsed_time(ev1) / steps, statistics.mean(a.elapsed_time(b) for a, b in zip(k_a, k_b))],
+                     dtype=torch.float64, device=torch.device("cuda", torch.cuda.current_device()))
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return t.tolist()
+
+
+def run_extras(args, torch, dist, slot, stream, dev, rank, world, points, centres, peak):
+    """The lines the headline does not show (same JSON line, key `extra`): configs[1]'s kernel on inputs a map task
+    does not choose, the round-1 combiner beside the new one, and BASELINE configs 4 and 5 at a per-GPU shard that
+    fits the step budget, with their kernels timed apart and the cost of the exact re-check at 0 / 0.1 / 1 / 10 %."""
+    from hgpumap import capi, synth
+
+    extra = []
+    n, k = args.points, args.k
+    steps = max(3, min(args.steps, 10))
+
+    def d2_line(name, family=capi.KERNEL_AUTO):
+        slot.set_kernel(family)
+        ms, kms = timed_steps(torch, dist, slot, stream, points.data_ptr(), n, steps, world)
+        _, counts = slot.read_partials()
+        assert int(counts.sum()) == n * world
+        extra.append({"workload": name, "points_per_gpu": n, "d": 2, "k": k, "value": world * n / (ms * 1e-3),
+                      "unit": UNIT, "ms_per_step": ms, "kernel": kernel_name(capi, slot, slot.last_kernel()),
+                      "kernel_ms": kms, "roofline_frac_hbm": n * 8 / (kms * 1e-3) / 1e9 / peak})
+        slot.set_kernel(capi.KERNEL_AUTO)
+
+    if args.d == 2:
+        d2_line("configs[1] input, counting-sort combiner (the round-1 kernel, HGM_KERNEL_GRID2D_SORT)", capi.KERNEL_GRID2D_SORT)
+        points.view(n, 2).copy_(other_points(torch, dev, "uniform", n, centres, seed=20261108 + rank))
+        d2_line("uniform points over the centroids' box + 20 % (~13 % in multi-candidate cells, some outside the index)")
+        points.view(n, 2).copy_(other_points(torch, dev, "skew", n, centres, seed=20261108 + rank))
+        d2_line("skewed points: one cluster holds 60 % of every tile")
+        d2_line("skewed points, counting-sort combiner", capi.KERNEL_GRID2D_SORT)
+
+    # ---- BASELINE configs 4 and 5: the tcgen05 path ------------------------------------------------------
+    tf32 = tf32_peak_tflops(torch, dev)
+    try:
+        bf16 = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["bf16_tflops_sustained"])
+    except Exception:
+        bf16 = None
+    for d, kk, m in ((64, 1024, 40_000_000), (128, 4096, 8_000_000)):
+        cen = synth.centres(synth.SEED_POINTS, kk, d)
+        cent = synth.perturb(synth.SEED_CENTROIDS, cen)
+        buf = torch.empty(m * d, dtype=torch.float32, device=dev)
+        slot.set_centroids(cent)
+        slot.synth_points_device(synth.SEED_POINTS, rank * m, m, cen, buf.data_ptr())
+        entry = None
+        for dup in (0, max(1, kk // 1000), kk // 100, kk // 10):  # duplicated centroids: their clusters' points are ties
+            c2 = cent.copy()
+            if dup:
+                c2[kk - dup:] = c2[:dup]
+                slot.set_centroids(c2)
+            ms, kms = timed_steps(torch, dist, slot, stream, buf.data_ptr(), m, max(3, steps // 2), world)
+            _, counts = slot.read_partials()
+            assert int(counts.sum()) == m * world
+            phases = slot.last_tensor_phases()
+            flagged = slot.last_rechecks()
+            if dup == 0:
+                tf = 2.0 * d * kk * m / (kms * 1e-3) / 1e12
+                entry = {"workload": f"BASELINE configs[{3 if d == 64 else 4}] shape: d={d}, k={kk}, {m:,} points per GPU",
+                         "points_per_gpu": m, "d": d, "k": kk, "value": world * m / (ms * 1e-3), "unit": UNIT,
+                         "ms_per_step": ms, "kernel": "tensor_assign_pair_kernel" if d > 32 else "tensor_assign_kernel",
+                         "kernel_ms": {"map_call": kms, "K2_scores_tcgen05": phases[0], "K3_exact_recheck": phases[1],
+                                       "K4_segmented_sums": phases[2]},
+                         "rechecked_points": flagged, "achieved_tflops": tf,
+                         "roofline_frac_tf32_measured_in_run": tf / tf32, "tf32_tflops_cublas_in_run": tf32,
+                         "roofline_frac_bf16_sustained": tf / bf16 if bf16 else None, "bf16_tflops_sustained": bf16,
+                         "recheck_sensitivity": []}
+            else:
+                entry["recheck_sensitivity"].append(
+                    {"duplicated_centroids": dup, "rechecked_points": flagged, "rechecked_frac": flagged / m,
+                     "value": world * m / (ms * 1e-3), "K3_exact_recheck_ms": phases[1], "map_call_ms": kms})
+        extra.append(entry)
+        del buf
+    return extra
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -341,6 +508,8 @@ def run_ours(args):
     slot = capi.GpuMapSlot(local_rank)
     if args.kernel:
         slot.set_kernel(args.kernel)
+    slot.set_tensor_form({"auto": capi.TENSOR_FORM_AUTO, "single": capi.TENSOR_FORM_SINGLE,
+                          "pair": capi.TENSOR_FORM_PAIR}[args.tensor_form])
     slot.set_centroids(centroids)
     points = torch.empty(n * d, dtype=torch.float32, device=dev)  # device memory: plumbing only
     slot.synth_points_device(synth.SEED_POINTS, rank * n, n, centres, points.data_ptr())
@@ -444,12 +613,16 @@ def run_ours(args):
                "api": "hgm_map_split (pinned host split -> chunked async H2D -> kernel -> partials D2H)"}
         del host
 
+    peak, peak_src = hbm_peak()
+    main_kernel = kernel_name(capi, slot, kernel_family)
+    extra = None
+    main_rechecks = slot.last_rechecks() if kernel_family == capi.KERNEL_TENSOR else 0
+    if not args.no_extra and d == 2:  # every rank takes part: the steps hold a collective
+        extra = run_extras(args, torch, dist, slot, stream, dev, rank, world, points, centres, peak)
     if rank == 0:
-        peak, peak_src = hbm_peak()
         achieved = n * d * 4 / (kernel_ms * 1e-3) / 1e9
-        traffic, limiter = ncu_traffic(kernel_family, d, k, n)
-        fam = {capi.KERNEL_GRID2D: "grid2d_map_kernel", capi.KERNEL_EXACT: "exact_map_kernel",
-               capi.KERNEL_TENSOR: "tensor_assign_kernel"}.get(kernel_family, "?")
+        fam = main_kernel
+        traffic, limiter = ncu_traffic(fam, d, k, n)
         if kernel_family == capi.KERNEL_TENSOR:
             # GEMM-shaped: algorithmic flops = 2*d*k per point, against the
             # TF32 tensor-pipe rate measured in this run; kernel_ms spans the score kernel and the
@@ -460,7 +633,7 @@ def run_ours(args):
                         "frac": achieved_tf / tf32, "traffic": traffic, "kernel": fam, "kernel_ms": kernel_ms,
                         "peak_source": "measured in this run: cuBLAS TF32 8192^3, best of 5 (the path runs "
                                        "tcgen05 kind::tf32; MEASURED_PEAKS.json holds only the bf16 rate)",
-                        "algorithmic_flops_per_point": 2 * d * k, "rechecked_points_last_step": slot.last_rechecks()}
+                        "algorithmic_flops_per_point": 2 * d * k, "rechecked_points_last_step": main_rechecks}
         else:
             roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                         "traffic": traffic, "kernel": fam, "kernel_ms": kernel_ms, "peak_source": peak_src,
@@ -482,12 +655,15 @@ def run_ours(args):
         }
         if e2e:
             line["e2e"] = e2e
+        if extra is not None:
+            line["extra"] = extra
         if world == 1 and not args.no_cpu_baseline:
             cores = min(host_cores(), 32)
             ref = CpuReference(args, procs=cores, points=args.cpu_points)
             p, s = ref.step()
             line["cpu_baseline"] = {"value": p / s, "unit": UNIT, "cores": ref.procs, "kind": ref.kind,
-                                    "sample": ref.sample()}
+                                    "sample": ref.sample(),
+                                    "direct": cpu_direct(args, cores)}  # the arithmetic alone, no protocol (B-direct)
         print(json.dumps(line), flush=True)
     slot.close()
     if world > 1:

@@ -32,7 +32,7 @@ constexpr size_t kArenaBytes = size_t(2) << 30;    // split-cache arena block
 // Rows one launch group of the scan / tensor paths handles: their scratch (assignments, re-check list, cluster
 // order: 12 bytes per row) is allocated ONCE per job at this size and longer inputs are mapped piece by piece --
 // no cudaFree/cudaMalloc (a device-wide synchronisation under the other slots' kernels) inside a map call.
-constexpr size_t kScratchRows = size_t(1) << 25;
+constexpr size_t kScratchRows = size_t(1) << 26;
 }  // namespace
 
 struct hgm_ctx {
@@ -42,6 +42,8 @@ struct hgm_ctx {
   cudaStream_t stream = nullptr;          // kernels
   cudaStream_t copy[kStages] = {};        // H2D / D2H
   cudaEvent_t ev_h2d[kStages] = {}, ev_free[kStages] = {}, ev_t0 = nullptr, ev_t1 = nullptr;
+  cudaEvent_t ev_phase[4] = {};  // tensor path: before K2, after K2 (scores), after K3 (re-check), after K4 (sums)
+  bool phases_open = false;
   void *d_chunk[kStages] = {};            // kChunkBytes each
   int32_t *d_assign_chunk[kStages] = {};  // lazily allocated
   size_t assign_chunk_cap = 0;
@@ -60,6 +62,8 @@ struct hgm_ctx {
   Grid2D grid{};
   uint16_t *d_table = nullptr;  // G*G
   uint16_t *d_cand = nullptr;   // G*G*8
+  Grid2D outer_grid{};          // the coarse index around the fine one (fixed-point form); G == 0: none
+  uint16_t *d_otable = nullptr, *d_ocand = nullptr;
   bool tensor_ok = false;       // tcgen05 path prepared for this centroid table
   float *d_caug = nullptr;      // [k_pad][d+32] augmented centroid matrix
   unsigned int *d_tflags = nullptr;  // [0] max |c| bits, [1] re-check counter
@@ -124,6 +128,9 @@ void free_job(hgm_ctx *c) {
   cudaFree(c->d_partials); c->d_partials = nullptr;
   cudaFree(c->d_table); c->d_table = nullptr;
   cudaFree(c->d_cand); c->d_cand = nullptr;
+  cudaFree(c->d_otable); c->d_otable = nullptr;
+  cudaFree(c->d_ocand); c->d_ocand = nullptr;
+  c->outer_grid = Grid2D{};
   cudaFree(c->d_caug); c->d_caug = nullptr;
   cudaFree(c->d_tflags); c->d_tflags = nullptr;
   cudaFree(c->d_tmeta); c->d_tmeta = nullptr;  // sized by k; the row scratch (d_tassign, d_tlist, d_torder) outlives jobs
@@ -184,7 +191,7 @@ void cache_clear(hgm_ctx *c) {
 
 // Choose the d == 2 cell grid for a centroid table; false if the table is not indexable
 // (non-finite or astronomically large coordinates) and the exact scan must be used.
-bool plan_grid2d(const float *cent, int k, size_t smem_optin, bool sort_form, Grid2D *out) {
+bool plan_grid2d(const float *cent, int k, size_t smem_optin, bool sort_form, Grid2D *out, Grid2D *outer_out = nullptr) {
   if (k > 1024) return false;
   double lo[2] = {INFINITY, INFINITY}, hi[2] = {-INFINITY, -INFINITY};
   for (int c = 0; c < k; ++c)
@@ -198,12 +205,12 @@ bool plan_grid2d(const float *cent, int k, size_t smem_optin, bool sort_form, Gr
   int32_t b[2];
   // geometry of a G x G grid over the centroids' bounding box + 12.5 % margin; fs = the fixed-point
   // scale of kernels_grid2d_fx.cu for that grid (0 where the coordinates' magnitude rules it out)
-  auto geometry = [&](int G) -> bool {
+  auto geometry = [&](int G, double margin_frac) -> bool {
     for (int j = 0; j < 2; ++j) {
       double ext = hi[j] - lo[j];
       const double mag = std::max(fabs(lo[j]), fabs(hi[j]));
       if (!(ext > mag * 1e-4)) ext = std::max(mag * 1e-4, 1e-30);  // degenerate axis
-      const double margin = 0.125 * ext;
+      const double margin = margin_frac * ext;
       const double origin = lo[j] - margin;
       const double scale = (double)(G - 1) / (ext + 2 * margin);
       const float sf = (float)scale;
@@ -221,11 +228,19 @@ bool plan_grid2d(const float *cent, int k, size_t smem_optin, bool sort_form, Gr
     }
     return true;
   };
+  if (outer_out) *outer_out = Grid2D{};
   int G = sort_form ? 0 : grid2d_fx_table_size(k, smem_optin);
   int shape = kShapeFx;
-  if (G > 0 && !(geometry(G) && fs[0] > 0.f && fs[1] > 0.f)) G = 0;
+  if (G > 0 && outer_out && geometry(kOuterCells, 1.5)) {  // the coarse index: four times the box on each axis
+    outer_out->sx = s[0]; outer_out->sy = s[1];
+    outer_out->Bx = B[0]; outer_out->By = B[1];
+    outer_out->bx = b[0]; outer_out->by = b[1];
+    outer_out->G = kOuterCells;
+  }
+  if (G > 0 && !(geometry(G, 0.125) && fs[0] > 0.f && fs[1] > 0.f)) G = 0;
   if (G == 0) {  // the counting-sort form
-    if (!grid2d_plan(k, smem_optin, &G, &shape) || !geometry(G)) return false;
+    if (outer_out) *outer_out = Grid2D{};
+    if (!grid2d_plan(k, smem_optin, &G, &shape) || !geometry(G, 0.125)) return false;
     fs[0] = fs[1] = 0.f;
   }
   out->sx = s[0]; out->sy = s[1];
@@ -258,7 +273,7 @@ int ensure_scan_scratch(hgm_ctx *c) {
   if (c->tscratch_rows == 0) {
     cudaError_t e = cudaMalloc(&c->d_tlist, kScratchRows * 4);
     if (e == cudaSuccess) e = cudaMalloc(&c->d_tassign, kScratchRows * 4);
-    if (e == cudaSuccess) e = cudaMalloc(&c->d_torder, kScratchRows * 4);
+    if (e == cudaSuccess) e = cudaMalloc(&c->d_torder, kScratchRows * 8);  // 8: the re-check keeps a 64-bit key per flagged row there
     if (e != cudaSuccess) {
       cudaGetLastError();
       cudaFree(c->d_tlist); cudaFree(c->d_tassign); cudaFree(c->d_torder);
@@ -302,15 +317,17 @@ int map_piece_async(hgm_ctx *c, int kern, const float *d_pts, int64_t n, int32_t
       return fail(c, HGM_EINVAL, "the tensor path needs 16-byte aligned points");
     e = launch_tensor_map(d_pts, n, c->d, c->d_cent, c->k, c->d_caug, c->d_tflags, d_assign ? d_assign : c->d_tassign,
                           c->d_tlist, c->d_tflags + 1, c->d_tmeta, c->d_torder, sums_ptr(c), counts_ptr(c), c->sm_count,
-                          c->smem_optin, c->stream);
+                          c->smem_optin, c->stream, c->ev_phase);
+    c->phases_open = e == cudaSuccess;
     if (e == cudaSuccess) {
       add_rechecks_kernel<<<1, 1, 0, c->stream>>>(c->d_tflags);
       e = cudaGetLastError();
     }
-    launches = 6;
+    launches = 8;
   } else if (kern == HGM_KERNEL_GRID2D || kern == HGM_KERNEL_GRID2D_SORT) {
+    const Grid2DOuter outer{c->outer_grid, c->d_otable, c->d_ocand};
     e = launch_grid2d_map(d_pts, n, c->d_cent, c->k, c->grid, c->d_table, c->d_cand, sums_ptr(c),
-                          counts_ptr(c), d_assign, c->sm_count, c->smem_optin, c->stream);
+                          counts_ptr(c), d_assign, c->sm_count, c->smem_optin, c->stream, &outer);
   } else {
     e = launch_exact_map(d_pts, n, c->d, c->d_cent, c->k, d_assign ? d_assign : c->d_tassign, c->d_tmeta, c->d_torder,
                          sums_ptr(c), counts_ptr(c), c->sm_count, c->smem_optin, c->stream);
@@ -327,7 +344,8 @@ int build_grid_index(hgm_ctx *c) {
   c->grid_ok = false;
   if (c->d != 2) return HGM_OK;
   Grid2D g;
-  if (!plan_grid2d(c->h_cent.data(), c->k, c->smem_optin, c->forced == HGM_KERNEL_GRID2D_SORT, &g)) return HGM_OK;
+  Grid2D outer;
+  if (!plan_grid2d(c->h_cent.data(), c->k, c->smem_optin, c->forced == HGM_KERNEL_GRID2D_SORT, &g, &outer)) return HGM_OK;
   if (!c->d_table || g.G != c->grid.G) {
     cudaFree(c->d_table); cudaFree(c->d_cand);
     c->d_table = nullptr; c->d_cand = nullptr;
@@ -338,6 +356,16 @@ int build_grid_index(hgm_ctx *c) {
   cudaError_t e = launch_grid2d_build(c->d_cent, c->k, g, c->d_table, c->d_cand, c->stream);
   if (e != cudaSuccess) return fail(c, HGM_ECUDA, "grid2d build launch: %s", cudaGetErrorString(e));
   c->total_launches += 1;
+  c->outer_grid = outer;
+  if (outer.G != 0) {
+    if (!c->d_otable) {
+      CU(c, cudaMalloc(&c->d_otable, grid2d_table_bytes(kOuterCells)));
+      CU(c, cudaMalloc(&c->d_ocand, (size_t)kOuterCells * kOuterCells * kMaxCand * 2));
+    }
+    e = launch_grid2d_build(c->d_cent, c->k, outer, c->d_otable, c->d_ocand, c->stream);
+    if (e != cudaSuccess) return fail(c, HGM_ECUDA, "grid2d outer build launch: %s", cudaGetErrorString(e));
+    c->total_launches += 1;
+  }
   c->grid_ok = true;
   return HGM_OK;
 }
@@ -412,6 +440,7 @@ int hgm_open(int device_id, hgm_ctx **out) {
   CUO(cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking));
   CUO(cudaEventCreate(&c->ev_t0));
   CUO(cudaEventCreate(&c->ev_t1));
+  for (int i = 0; i < 4; ++i) CUO(cudaEventCreate(&c->ev_phase[i]));
   for (int i = 0; i < kStages; ++i) {
     CUO(cudaStreamCreateWithFlags(&c->copy[i], cudaStreamNonBlocking));
     CUO(cudaEventCreateWithFlags(&c->ev_h2d[i], cudaEventDisableTiming));
@@ -446,6 +475,7 @@ void hgm_close(hgm_ctx *c) {
   if (c->h_tstats) cudaFreeHost(c->h_tstats);
   if (c->ev_t0) cudaEventDestroy(c->ev_t0);
   if (c->ev_t1) cudaEventDestroy(c->ev_t1);
+  for (int i = 0; i < 4; ++i) if (c->ev_phase[i]) cudaEventDestroy(c->ev_phase[i]);
   if (c->stream) cudaStreamDestroy(c->stream);
   delete c;
 }
@@ -600,6 +630,15 @@ int hgm_last_rechecks(hgm_ctx *c, int64_t *points) {
   CU(c, cudaMemcpyAsync(&n, c->d_tflags + 2, 8, cudaMemcpyDeviceToHost, c->stream));
   CU(c, cudaStreamSynchronize(c->stream));
   *points = (int64_t)n;
+  return HGM_OK;
+}
+
+int hgm_last_tensor_phases(hgm_ctx *c, float *ms3) {
+  NEED_CTX(c);
+  if (!ms3) return fail(c, HGM_EINVAL, "ms3 is NULL");
+  if (!c->phases_open) return fail(c, HGM_EINVAL, "the tensor-core path has not run on this ctx");
+  CU(c, cudaEventSynchronize(c->ev_phase[3]));
+  for (int i = 0; i < 3; ++i) CU(c, cudaEventElapsedTime(&ms3[i], c->ev_phase[i], c->ev_phase[i + 1]));
   return HGM_OK;
 }
 

@@ -42,20 +42,29 @@ constexpr uint8_t kTable8Multi = 0xFF;
 // bytes of the table buffer for a G x G grid: 16-bit table, then the 8-bit copy
 inline size_t grid2d_table_bytes(int G) { return (size_t)G * G * 3 + 32; }
 
+// A second, coarse index over several times the centroids' box: a point outside the fine grid is resolved from its
+// cell there instead of by a scan over all k centroids (fixed-point form only; built by the same builder kernel).
+struct Grid2DOuter {
+  Grid2D g;               // G == 0: none
+  const uint16_t *table;  // G*G 16-bit entries
+  const uint16_t *cand;   // G*G*kMaxCand
+};
+constexpr int kOuterCells = 96;  // cells per side of the coarse index
+
 // launchers (each returns the CUDA error of its launch)
 cudaError_t launch_grid2d_build(const float *d_cent, int k, const Grid2D &g, uint16_t *d_table,
                                 uint16_t *d_cand, cudaStream_t s);
 cudaError_t launch_grid2d_map(const float *d_pts, int64_t n, const float *d_cent, int k,
                               const Grid2D &g, const uint16_t *d_table, const uint16_t *d_cand,
                               double *d_sums, unsigned long long *d_counts, int32_t *d_assign,
-                              int sm_count, size_t smem_optin, cudaStream_t s);
+                              int sm_count, size_t smem_optin, cudaStream_t s, const Grid2DOuter *outer = nullptr);
 bool grid2d_plan(int k, size_t smem_optin, int *G_out, int *shape_out);
 // the fixed-point form (kernels_grid2d_fx.cu): table size it can hold for k clusters (0 = none), and its launcher
 int grid2d_fx_table_size(int k, size_t smem_optin);
 cudaError_t launch_grid2d_fx_map(const float *d_pts, int64_t n, const float *d_cent, int k, const Grid2D &g,
                                  const uint16_t *d_table, const uint16_t *d_cand, double *d_sums,
                                  unsigned long long *d_counts, int32_t *d_assign, int sm_count, size_t smem_optin,
-                                 cudaStream_t s);
+                                 cudaStream_t s, const Grid2DOuter *outer = nullptr);
 
 // scan (assign + per-launch counts in d_meta) followed by the segmented sums; d_assign must not be NULL
 cudaError_t launch_exact_map(const float *d_pts, int64_t n, int d, const float *d_cent, int k, int32_t *d_assign,
@@ -76,7 +85,8 @@ size_t tensor_meta_words(int k);  // uint32 words of per-launch cluster bookkeep
 cudaError_t launch_tensor_map(const float *d_pts, int64_t n, int d, const float *d_cent, int k, const float *d_caug,
                               const unsigned int *d_cmax_bits, int32_t *d_assign, int32_t *d_flag_list,
                               unsigned int *d_flag_count, unsigned int *d_meta, int32_t *d_order, double *d_sums,
-                              unsigned long long *d_counts, int sm_count, size_t smem_optin, cudaStream_t s);
+                              unsigned long long *d_counts, int sm_count, size_t smem_optin, cudaStream_t s,
+                              cudaEvent_t *phase /* 4 events or NULL */);
 
 // text decode (kernels_text.cu)
 struct TextStats {

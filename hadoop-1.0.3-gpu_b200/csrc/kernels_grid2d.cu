@@ -785,7 +785,7 @@ cudaError_t launch_grid2d_build(const float *d_cent, int k, const Grid2D &g, uin
 cudaError_t launch_grid2d_map(const float *d_pts, int64_t n, const float *d_cent, int k,
                               const Grid2D &g, const uint16_t *d_table, const uint16_t *d_cand,
                               double *d_sums, unsigned long long *d_counts, int32_t *d_assign,
-                              int sm_count, size_t smem_optin, cudaStream_t s) {
+                              int sm_count, size_t smem_optin, cudaStream_t s, const Grid2DOuter *outer) {
   if (n <= 0) return cudaSuccess;
   if (k > kMaxK) return cudaErrorInvalidValue;
 #define HGM_ARGS d_pts, n, d_cent, k, g, d_table, d_cand, d_sums, d_counts, d_assign, sm_count, smem_optin, s
@@ -795,7 +795,7 @@ cudaError_t launch_grid2d_map(const float *d_pts, int64_t n, const float *d_cent
     case 3: return launch_shape<ShapeD>(HGM_ARGS);
     case 4: return launch_shape<ShapeE>(HGM_ARGS);
     case 5: return launch_shape<ShapeF>(HGM_ARGS);
-    case kShapeFx: return launch_grid2d_fx_map(HGM_ARGS);
+    case kShapeFx: return launch_grid2d_fx_map(HGM_ARGS, outer);
     default: return launch_shape<ShapeC>(HGM_ARGS);
   }
 #undef HGM_ARGS

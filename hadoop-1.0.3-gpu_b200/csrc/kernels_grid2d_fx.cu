@@ -151,7 +151,7 @@ template <class S, bool kVec4, bool kAssign>
 __global__ void __launch_bounds__(S::kThreads, 1)
     grid2d_fx_kernel(const float *__restrict__ pts, long long n, const float *__restrict__ cent, int k, Grid2D g,
                      FxParams fx, const uint16_t *__restrict__ table, const uint16_t *__restrict__ cand,
-                     double *__restrict__ g_sums, unsigned long long *__restrict__ g_counts,
+                     Grid2DOuter outer, double *__restrict__ g_sums, unsigned long long *__restrict__ g_counts,
                      int32_t *__restrict__ assign) {
   constexpr int kPPT = S::kPPT;
   constexpr int kTile = S::kTile;
@@ -207,16 +207,55 @@ __global__ void __launch_bounds__(S::kThreads, 1)
   // settle up to 32 queued points, one per lane: exact candidate scan, then the limbs or an FP64 add
   auto settle = [&](int first, int count, long long base) -> uint32_t {
     uint32_t full = 0u;
-    if (lane < count) {
-      const float2 v = queue[first + lane];
-      const uint32_t cell = cell_of(v.x, v.y, g);
-      // the 16-bit entry tells a single-candidate cell that is only marked for its tiny values from a
-      // multi-candidate one; both loads go out together
-      const uint16_t *list = cand + (size_t)cell * kMaxCand;
-      const uint32_t e16 = __ldg(table + cell);
-      const uint32_t id01 = __ldg(reinterpret_cast<const uint32_t *>(list));
-      uint32_t c = e16;
-      if (e16 >= kCellMulti) c = (uint32_t)resolve_cand(v.x, v.y, id01, list, cent_s, k);
+    const bool live = lane < count;
+    const float2 v = live ? queue[first + lane] : make_float2(0.f, 0.f);
+    const uint32_t last = (uint32_t)(g.G - 1);
+    const uint32_t ux = min(__float_as_uint(__fmaf_rn(v.x, g.sx, g.Bx)) - kMagicBits, last);  // cell_of, taken apart
+    const uint32_t uy = min(__float_as_uint(__fmaf_rn(v.y, g.sy, g.By)) - kMagicBits, last);
+    const uint32_t cell = uy * (uint32_t)g.G + ux;
+    // the 16-bit entry tells a single-candidate cell that is only marked for its tiny values from a
+    // multi-candidate one; both loads go out together
+    const uint16_t *list = cand + (size_t)cell * kMaxCand;
+    const uint16_t *entry = table + cell;
+    // outside the fine grid (its last row and column collect everything out of range): the coarse index over
+    // several times the box knows the few centroids that can win out there
+    if (outer.g.G != 0 && (ux == last || uy == last)) {
+      const uint32_t far = cell_of(v.x, v.y, outer.g);
+      list = outer.cand + (size_t)far * kMaxCand;
+      entry = outer.table + far;
+    }
+    const uint32_t e16 = __ldg(entry);
+    const uint32_t id01 = __ldg(reinterpret_cast<const uint32_t *>(list));
+    uint32_t c = e16;
+    // "scan every centroid" points (outside the index, NaN/inf, a cell with more candidates than a list holds):
+    // one at a time with the whole warp on it -- lane l scans centroids l, l + 32, ... in ascending order, the
+    // lexicographic (distance, index) minimum over the lanes is the scan's winner.  Left to its own lane such a
+    // point kept the other 31 waiting for k distance evaluations.
+    bool scan_all = live && e16 >= kCellMulti && id01 == 0xFFFFFFFFu;
+    uint32_t todo = __ballot_sync(0xFFFFFFFFu, scan_all);
+    if (__popc(todo) > 10) {  // many of them: k evaluations on every lane at once cost less than 32 cooperative rounds
+      todo = 0u;
+      scan_all = false;
+    }
+    for (; todo; todo &= todo - 1) {
+      const int src = __ffs(todo) - 1;
+      const float px = __shfl_sync(0xFFFFFFFFu, v.x, src), py = __shfl_sync(0xFFFFFFFFu, v.y, src);
+      float best = INFINITY;
+      int arg = 0x7FFFFFFF;
+      for (int cc = lane; cc < k; cc += 32) {
+        const float dd = dist2(px, py, cent_s[cc]);
+        if (dd < best) { best = dd; arg = cc; }
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        const float ob = __shfl_xor_sync(0xFFFFFFFFu, best, o);
+        const int oa = __shfl_xor_sync(0xFFFFFFFFu, arg, o);
+        if (ob < best || (ob == best && oa < arg)) { best = ob; arg = oa; }
+      }
+      if (lane == src) c = best < INFINITY ? (uint32_t)arg : 0u;  // nothing beat +inf: the scan keeps index 0
+    }
+    if (live) {
+      if (e16 >= kCellMulti && !scan_all) c = (uint32_t)resolve_cand(v.x, v.y, id01, list, cent_s, k);
       if (kAssign) assign[base + qindex[first + lane]] = (int)c;
       const bool fits = fabsf(v.x) < fx.limx && fabsf(v.y) < fx.limy && !tiny(v.x, fx.tinyx) && !tiny(v.y, fx.tinyy);
       full = fx_add_point<kLanes>(fits ? 1u : 0u, acc_lane, fx, v.x, v.y, fits ? c : (uint32_t)k);
@@ -363,14 +402,14 @@ size_t fx_smem(int G, int k, bool with_assign) {
 
 template <class S>
 cudaError_t launch_fx(const float *d_pts, int64_t n, const float *d_cent, int k, const Grid2D &g, const FxParams &fx,
-                      const uint16_t *d_table, const uint16_t *d_cand, double *d_sums, unsigned long long *d_counts,
-                      int32_t *d_assign, int sm_count, size_t smem_optin, cudaStream_t s) {
+                      const uint16_t *d_table, const uint16_t *d_cand, const Grid2DOuter &outer, double *d_sums,
+                      unsigned long long *d_counts, int32_t *d_assign, int sm_count, size_t smem_optin, cudaStream_t s) {
   const bool asg = d_assign != nullptr;
   const size_t smem = fx_smem<S>(g.G, k, asg);
   if (smem > smem_optin) return cudaErrorInvalidValue;
   const bool vec4 = (reinterpret_cast<uintptr_t>(d_pts) & 15) == 0;
   void (*kern)(const float *, long long, const float *, int, Grid2D, FxParams, const uint16_t *, const uint16_t *,
-               double *, unsigned long long *, int32_t *);
+               Grid2DOuter, double *, unsigned long long *, int32_t *);
   kern = vec4 ? (asg ? grid2d_fx_kernel<S, true, true> : grid2d_fx_kernel<S, true, false>)
               : (asg ? grid2d_fx_kernel<S, false, true> : grid2d_fx_kernel<S, false, false>);
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -378,7 +417,7 @@ cudaError_t launch_fx(const float *d_pts, int64_t n, const float *d_cent, int k,
   const long long ntiles = (n + S::kTile - 1) / S::kTile;
   const long long want = (ntiles + S::kWarps - 1) / S::kWarps;
   const int grid = (int)(want < sm_count ? want : sm_count);
-  kern<<<grid, S::kThreads, smem, s>>>(d_pts, (long long)n, d_cent, k, g, fx, d_table, d_cand, d_sums, d_counts,
+  kern<<<grid, S::kThreads, smem, s>>>(d_pts, (long long)n, d_cent, k, g, fx, d_table, d_cand, outer, d_sums, d_counts,
                                        d_assign);
   return cudaGetLastError();
 }
@@ -398,17 +437,19 @@ int grid2d_fx_table_size(int k, size_t smem_optin) {
 cudaError_t launch_grid2d_fx_map(const float *d_pts, int64_t n, const float *d_cent, int k, const Grid2D &g,
                                  const uint16_t *d_table, const uint16_t *d_cand, double *d_sums,
                                  unsigned long long *d_counts, int32_t *d_assign, int sm_count, size_t smem_optin,
-                                 cudaStream_t s) {
+                                 cudaStream_t s, const Grid2DOuter *outer) {
   if (n <= 0) return cudaSuccess;
   if (k > kTable8MaxK || !(g.fsx > 0.f) || !(g.fsy > 0.f)) return cudaErrorInvalidValue;
   FxParams fx;
   fx.sx = g.fsx; fx.sy = g.fsy;
   fx.tinyx = 2.0f / g.fsx; fx.tinyy = 2.0f / g.fsy;
   fx.limx = 2097152.0f / g.fsx; fx.limy = 2097152.0f / g.fsy;
+  Grid2DOuter none{};
+  const Grid2DOuter &o = outer ? *outer : none;
   if (k <= 128)
-    return launch_fx<FxWide>(d_pts, n, d_cent, k, g, fx, d_table, d_cand, d_sums, d_counts, d_assign, sm_count,
+    return launch_fx<FxWide>(d_pts, n, d_cent, k, g, fx, d_table, d_cand, o, d_sums, d_counts, d_assign, sm_count,
                              smem_optin, s);
-  return launch_fx<FxNarrow>(d_pts, n, d_cent, k, g, fx, d_table, d_cand, d_sums, d_counts, d_assign, sm_count,
+  return launch_fx<FxNarrow>(d_pts, n, d_cent, k, g, fx, d_table, d_cand, o, d_sums, d_counts, d_assign, sm_count,
                              smem_optin, s);
 }
 

@@ -174,6 +174,10 @@ __global__ void tensor_prep_kernel(const float *__restrict__ cent, int k, int k_
   if (c >= k_pad) return;
   const int dp = (d + kBlockK - 1) / kBlockK * kBlockK;  // coordinates padded with zeros to whole K-blocks
   float *row = caug + (size_t)c * (dp + kBlockK);
+  // K3's copy: the exact FP32 table transposed to [j][centroid], behind the augmented matrix; columns past k hold
+  // +inf, whose distance is +inf or NaN and can never win a strict '<'
+  float *const ct = caug + (size_t)k_pad * (dp + kBlockK);
+  for (int j = 0; j < d; ++j) ct[(size_t)j * k_pad + c] = c < k ? cent[(size_t)c * d + j] : INFINITY;
   if (c >= k) {  // padding rows: a score no real centroid can undercut
     for (int j = 0; j < dp + kBlockK; ++j) row[j] = 0.f;
     row[dp] = 3.0e38f;
@@ -802,34 +806,112 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
   }
 }
 
-// ---- K3: exact re-check of the flagged points, one warp per point ---------------------------------
-__global__ void recheck_kernel(const float *__restrict__ pts, int d, const float *__restrict__ cent, int k,
-                               const int32_t *__restrict__ flag_list, const unsigned int *__restrict__ flag_count,
-                               int32_t *__restrict__ assign, unsigned int *__restrict__ lcounts) {
+// ---- K3: exact re-check of the flagged points ---------------------------------------------------------
+// The first version gave every flagged point to one warp, which read the whole centroid table for it: 0.24 us
+// per point at d = 64 / k = 1024 and 2 us at d = 128 / k = 4096 (the table crosses L2 -> SM once per point), i.e.
+// 1 % of flagged points cost ten times the score kernel.  This one is a register-tiled exact "distance GEMM" on
+// the FP32 pipes: a CTA holds 64 flagged points in shared memory (transposed, [j][point]) and streams the
+// centroids through in tiles of 64 from a transposed FP32 copy of the table ([j][centroid], written once per
+// hgm_set_centroids by tensor_prep_kernel), so a centroid tile is read once per 64 points and every thread keeps
+// 4 x 4 (point, centroid) sums in registers.  The arithmetic is the scan's, unchanged: per pair the terms
+// (x_j - c_j)^2 are added in ascending j, each operation rounded on its own; per thread the centroids come in
+// ascending index with strict '<'; across threads and CTAs the winner is the lexicographic (distance, index)
+// minimum -- the scan's winner.  When few points are flagged the centroid range of a point tile is split across
+// CTAs (the decomposition is computed on the device from the flag count: the host never waits for it) and the
+// partial winners meet in a 64-bit atomicMin on (distance bits, index): non-negative floats order like their bits,
+// NaN sorts above +inf, and "nothing beat +inf" decodes to index 0 exactly like the scan.
+constexpr int kRcPoints = 64, kRcCents = 64, kRcXStride = kRcPoints + 4;
+
+__global__ void recheck_init_kernel(const unsigned int *__restrict__ flag_count, unsigned long long *__restrict__ best64) {
   const unsigned int nflag = *flag_count;
-  const int lane = threadIdx.x % 32;
-  const unsigned int warps = (gridDim.x * blockDim.x) / 32;
-  for (unsigned int f = (blockIdx.x * blockDim.x + threadIdx.x) / 32; f < nflag; f += warps) {
-    const long long p = flag_list[f];
-    const float *x = pts + p * d;
-    float best = INFINITY;
-    int arg = 0x7FFFFFFF;
-    for (int c = lane; c < k; c += 32) {  // each lane scans its centroids in ascending order
-      const float *cc = cent + (size_t)c * d;
-      float acc = 0.0f;
-      for (int j = 0; j < d; ++j) acc = __fadd_rn(acc, sqdiff(x[j], cc[j]));
-      if (acc < best) { best = acc; arg = c; }
+  for (unsigned int f = blockIdx.x * blockDim.x + threadIdx.x; f < nflag; f += gridDim.x * blockDim.x) best64[f] = ~0ull;
+}
+
+__global__ void __launch_bounds__(256) recheck_tile_kernel(const float *__restrict__ pts, int d, const float *__restrict__ cT,
+                                                           int kt, const int32_t *__restrict__ flag_list,
+                                                           const unsigned int *__restrict__ flag_count,
+                                                           unsigned long long *__restrict__ best64) {
+  extern __shared__ __align__(16) float rc_smem[];
+  float *const xs = rc_smem;                    // [d][kRcXStride]
+  float *const cs = rc_smem + d * kRcXStride;   // [d][kRcCents]
+  const unsigned int nflag = *flag_count;
+  if (nflag == 0) return;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;  // centroids 4*tx.., points 4*ty.. of the 64 x 64 tile
+  const unsigned int ptiles = (nflag + kRcPoints - 1) / kRcPoints;
+  const unsigned int ctiles = (unsigned int)kt / kRcCents;
+  // few point tiles: split the centroid tiles of each among the CTAs that would otherwise idle
+  unsigned int chunks = ptiles >= gridDim.x ? 1u : min(ctiles, (gridDim.x + ptiles - 1) / ptiles);
+  const unsigned int per = (ctiles + chunks - 1) / chunks;
+  chunks = (ctiles + per - 1) / per;
+  for (unsigned int w = blockIdx.x; w < ptiles * chunks; w += gridDim.x) {
+    const unsigned int f0 = (w / chunks) * kRcPoints;
+    const unsigned int t0 = (w % chunks) * per, t1 = min(ctiles, t0 + per);
+    __syncthreads();  // the previous item's tiles are no longer read
+    for (int p = warp; p < kRcPoints; p += 8) {  // gather the flagged rows, transposed
+      const bool live = f0 + p < nflag;
+      const long long row = live ? flag_list[f0 + p] : 0;
+      for (int j = lane; j < d; j += 32) xs[j * kRcXStride + p] = live ? __ldg(pts + row * d + j) : 0.f;
     }
-    for (int o = 16; o > 0; o >>= 1) {    // lexicographic (distance, index) minimum = the scan's winner
-      const float ob = __shfl_xor_sync(0xFFFFFFFFu, best, o);
-      const int oa = __shfl_xor_sync(0xFFFFFFFFu, arg, o);
-      if (ob < best || (ob == best && oa < arg)) { best = ob; arg = oa; }
+    float best[4];
+    int arg[4];
+#pragma unroll
+    for (int a = 0; a < 4; ++a) { best[a] = INFINITY; arg[a] = 0x7FFFFFFF; }
+    for (unsigned int t = t0; t < t1; ++t) {
+      __syncthreads();  // xs is complete / the previous centroid tile is no longer read
+      for (int i = threadIdx.x; i < d * (kRcCents / 4); i += 256) {
+        const int j = i / (kRcCents / 4), q = i % (kRcCents / 4);
+        reinterpret_cast<float4 *>(cs + j * kRcCents)[q] =
+            __ldg(reinterpret_cast<const float4 *>(cT + (size_t)j * kt + (size_t)t * kRcCents) + q);
+      }
+      __syncthreads();
+      float acc[4][4];
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = 0.0f;
+#pragma unroll 4
+      for (int j = 0; j < d; ++j) {
+        const float4 xv = *reinterpret_cast<const float4 *>(xs + j * kRcXStride + 4 * ty);
+        const float4 cv = *reinterpret_cast<const float4 *>(cs + j * kRcCents + 4 * tx);
+        const float x[4] = {xv.x, xv.y, xv.z, xv.w}, c[4] = {cv.x, cv.y, cv.z, cv.w};
+#pragma unroll
+        for (int a = 0; a < 4; ++a)
+#pragma unroll
+          for (int b = 0; b < 4; ++b) acc[a][b] = __fadd_rn(acc[a][b], sqdiff(x[a], c[b]));
+      }
+      const int c0 = (int)t * kRcCents + 4 * tx;
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b)
+          if (acc[a][b] < best[a]) { best[a] = acc[a][b]; arg[a] = c0 + b; }
     }
-    const int c = (best < INFINITY) ? arg : 0;  // nothing beat +inf: the scan keeps index 0
-    if (lane == 0) {
-      assign[p] = c;
-      atomicAdd(&lcounts[c], 1u);
+    // the 16 threads of a point row meet: lexicographic minimum over their (distance, index) winners
+#pragma unroll
+    for (int a = 0; a < 4; ++a) {
+      unsigned long long key = ((unsigned long long)__float_as_uint(best[a]) << 32) | (unsigned int)arg[a];
+#pragma unroll
+      for (int o = 8; o > 0; o >>= 1) {
+        const unsigned long long other = __shfl_xor_sync(0xFFFFFFFFu, key, o);  // tx lives in the low 4 lane bits
+        key = other < key ? other : key;
+      }
+      const unsigned int f = f0 + 4 * ty + a;
+      if (tx == 0 && f < nflag) atomicMin(&best64[f], key);
     }
+  }
+}
+
+__global__ void recheck_final_kernel(const int32_t *__restrict__ flag_list, const unsigned int *__restrict__ flag_count,
+                                     const unsigned long long *__restrict__ best64, int32_t *__restrict__ assign,
+                                     unsigned int *__restrict__ lcounts) {
+  const unsigned int nflag = *flag_count;
+  for (unsigned int f = blockIdx.x * blockDim.x + threadIdx.x; f < nflag; f += gridDim.x * blockDim.x) {
+    const unsigned long long key = best64[f];
+    // distance bits below those of +inf: a finite winner; otherwise nothing beat +inf and the scan keeps index 0
+    const int c = (unsigned int)(key >> 32) < 0x7F800000u ? (int)(unsigned int)key : 0;
+    assign[flag_list[f]] = c;
+    atomicAdd(&lcounts[c], 1u);
   }
 }
 
@@ -1042,7 +1124,9 @@ bool tensor_shape_ok(int k, int d, size_t smem_optin) {
   return d % 4 == 0 && d >= 8 && d <= 128 && k >= 8 && tensor_smem_bytes(d, 2) <= smem_optin;
 }
 int tensor_k_pad(int k) { return (k + kPairN - 1) / kPairN * kPairN; }  // whole tiles of either kernel form
-size_t tensor_caug_floats(int k, int d) { return (size_t)tensor_k_pad(k) * ((d + kBlockK - 1) / kBlockK * kBlockK + kBlockK); }
+size_t tensor_caug_rows_floats(int k, int d) { return (size_t)tensor_k_pad(k) * ((d + kBlockK - 1) / kBlockK * kBlockK + kBlockK); }
+// the augmented TF32 matrix K2 multiplies by, then K3's transposed exact copy [d][k_pad]
+size_t tensor_caug_floats(int k, int d) { return tensor_caug_rows_floats(k, d) + (size_t)d * tensor_k_pad(k); }
 
 cudaError_t launch_tensor_prep(const float *d_cent, int k, int d, float *d_caug, unsigned int *d_cmax_bits,
                                cudaStream_t s) {
@@ -1141,7 +1225,8 @@ size_t tensor_meta_words(int k) { return (size_t)4 * k + 2; }
 cudaError_t launch_tensor_map(const float *d_pts, int64_t n, int d, const float *d_cent, int k, const float *d_caug,
                               const unsigned int *d_cmax_bits, int32_t *d_assign, int32_t *d_flag_list,
                               unsigned int *d_flag_count, unsigned int *d_meta, int32_t *d_order, double *d_sums,
-                              unsigned long long *d_counts, int sm_count, size_t smem_optin, cudaStream_t s) {
+                              unsigned long long *d_counts, int sm_count, size_t smem_optin, cudaStream_t s,
+                              cudaEvent_t *phase) {
   if (n <= 0) return cudaSuccess;
   if (n > 0x7FFFFFFFll) return cudaErrorInvalidValue;
   if ((reinterpret_cast<uintptr_t>(d_pts) & 15) != 0 || !d_assign) return cudaErrorInvalidValue;
@@ -1152,6 +1237,7 @@ cudaError_t launch_tensor_map(const float *d_pts, int64_t n, int d, const float 
     return cudaErrorInvalidValue;
   cudaError_t e = cudaMemsetAsync(d_flag_count, 0, 4, s);
   if (e != cudaSuccess) return e;
+  if (phase) cudaEventRecord(phase[0], s);  // phase[0..3]: before K2, after K2, after K3, after K4 (hgm_last_tensor_phases)
   e = cudaMemsetAsync(d_meta, 0, (size_t)k * 4, s);  // the launch's per-cluster counts
   if (e != cudaSuccess) return e;
   // Which form: with the per-point decisions off the scan's critical path the pair kernel wins at both
@@ -1208,9 +1294,25 @@ cudaError_t launch_tensor_map(const float *d_pts, int64_t n, int d, const float 
   }
   if ((e = cudaGetLastError()) != cudaSuccess) return e;
   if (HGM_DBG(a)) return cudaSuccess;  // experiments time K2 alone; its output is meaningless then
-  recheck_kernel<<<sm_count * 4, 256, 0, s>>>(d_pts, d, d_cent, k, d_flag_list, d_flag_count, d_assign, d_meta);
-  if ((e = cudaGetLastError()) != cudaSuccess) return e;
-  return launch_segmented_sums(d_pts, n, d, k, d_assign, d_meta, d_order, d_sums, d_counts, sm_count, s);
+  if (phase) cudaEventRecord(phase[1], s);
+  {
+    // K3; d_order (8 bytes per row) is free until K4 fills it: the (distance, index) keys of the flagged points live there
+    unsigned long long *best64 = reinterpret_cast<unsigned long long *>(d_order);
+    const float *d_ct = d_caug + tensor_caug_rows_floats(k, d);
+    const size_t rc_smem = ((size_t)d * kRcXStride + (size_t)d * kRcCents) * 4;
+    if (rc_smem > 48 * 1024) {
+      e = cudaFuncSetAttribute(recheck_tile_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)rc_smem);
+      if (e != cudaSuccess) return e;
+    }
+    recheck_init_kernel<<<sm_count, 256, 0, s>>>(d_flag_count, best64);
+    recheck_tile_kernel<<<sm_count * 3, 256, rc_smem, s>>>(d_pts, d, d_ct, k_pad, d_flag_list, d_flag_count, best64);
+    recheck_final_kernel<<<sm_count, 256, 0, s>>>(d_flag_list, d_flag_count, best64, d_assign, d_meta);
+    if ((e = cudaGetLastError()) != cudaSuccess) return e;
+  }
+  if (phase) cudaEventRecord(phase[2], s);
+  e = launch_segmented_sums(d_pts, n, d, k, d_assign, d_meta, d_order, d_sums, d_counts, sm_count, s);
+  if (phase) cudaEventRecord(phase[3], s);
+  return e;
 }
 
 void tensor_set_form(int form) { g_tensor_form.store(form); }

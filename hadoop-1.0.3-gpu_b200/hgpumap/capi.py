@@ -48,6 +48,7 @@ SIGNATURES = {
     "hgm_set_centroids": (C.c_int, [_c_ctx, _p, C.c_int32, C.c_int32]),
     "hgm_set_kernel": (C.c_int, [_c_ctx, C.c_int32]),
     "hgm_last_kernel": (C.c_int, [_c_ctx, C.POINTER(C.c_int32)]),
+    "hgm_last_tensor_phases": (C.c_int, [_c_ctx, C.POINTER(C.c_float)]),
     "hgm_staged_bytes": (C.c_int, [_c_ctx, C.POINTER(C.c_int64)]),
     "hgm_set_tensor_form": (C.c_int, [C.c_int32]),
     "hgm_grid2d_form": (C.c_int, [_c_ctx, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
@@ -282,6 +283,12 @@ class GpuMapSlot:
         ms, n = C.c_float(), C.c_int32()
         self._check(self._lib.hgm_last_map_ms(self._ctx, C.byref(ms), C.byref(n)))
         return ms.value, n.value
+
+    def last_tensor_phases(self):
+        """(scores K2, re-check K3, sums K4) in ms for the last launch group of the tensor-core path."""
+        ms = (C.c_float * 3)()
+        self._check(self._lib.hgm_last_tensor_phases(self._ctx, ms))
+        return [float(v) for v in ms]
 
     def staged_bytes(self) -> int:
         n = C.c_int64()

@@ -201,6 +201,10 @@ int hgm_last_map_ms(hgm_ctx *ctx, float *ms, int32_t *launches);
  * inside the TF32 rounding bound and were re-scanned with the exact FP32 arithmetic
  * (0 for the other kernel families).  Synchronises the ctx stream. */
 int hgm_last_rechecks(hgm_ctx *ctx, int64_t *points);
+/* CUDA-event times (ms) of the last launch group of the tensor-core path, by phase: [0] scores + assignment on
+ * tcgen05 (K2), [1] exact re-check of the flagged points (K3), [2] per-cluster sums by segmented reduction (K4).
+ * Synchronises on the group's last event. */
+int hgm_last_tensor_phases(hgm_ctx *ctx, float *ms3);
 /* Bytes of input splits this ctx has copied host -> device since hgm_open (a split mapped from the HBM cache adds
  * nothing).  The Pipes program exports the per-task difference as counter KMEANS/GPU_BYTES_STAGED and the
  * re-checks as KMEANS/GPU_RECHECKS (mechanism: c++/pipes/impl/HadoopPipes.cc:346-359). */

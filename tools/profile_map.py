@@ -9,7 +9,7 @@ import os
 import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-sys.path[:0] = [os.path.join(ROOT, "hadoop-1.0.3-gpu_b200"), os.path.join(ROOT, "tests")]
+sys.path[:0] = [ROOT, os.path.join(ROOT, "hadoop-1.0.3-gpu_b200"), os.path.join(ROOT, "tests")]
 
 import numpy as np  # noqa: E402
 
@@ -22,11 +22,14 @@ def main():
     ap.add_argument("--kernel", type=int, default=0)
     ap.add_argument("--launches", type=int, default=6)
     ap.add_argument("--data", default="blobs")
+    ap.add_argument("--lib", default=None, help="another build of libhgpumap.so (same-box A/B runs)")
     args = ap.parse_args()
     import torch
 
     from hgpumap import capi, synth
 
+    if args.lib:
+        capi.load_library(args.lib)
     n, k, d = args.points, args.k, args.dims
     dev = torch.device("cuda", 0)
     centres = synth.centres(synth.SEED_POINTS, k, d)
