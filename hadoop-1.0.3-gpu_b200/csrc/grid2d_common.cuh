@@ -4,8 +4,28 @@
 
 #include "hgm_internal.h"
 
+// `make CHECKED=1` (-DHGM_CHECKED): every data-dependent shared-memory index of the d == 2 kernels and every
+// centroid id read from a candidate list is tested against its bound; a miss is counted in a device word the host
+// reads back (hgm_checked_failures) and the access is clamped, so a run ends with a number instead of a fault.
+// compute-sanitizer is closed on this pool: this build, small cases and the oracle comparison stand in for memcheck.
+#ifdef HGM_CHECKED
+#define HGM_BOUND(i, limit) hgm::checked_index((i), (limit), __LINE__)
+#else
+#define HGM_BOUND(i, limit) (i)
+#endif
+
 namespace hgm {
 namespace {
+
+#ifdef HGM_CHECKED
+__device__ unsigned int g_check_failures[2];  // [0] count, [1] source line of the first one
+template <class T, class U>
+__device__ __forceinline__ T checked_index(T i, U limit, int line) {
+  if ((long long)i >= 0 && (long long)i < (long long)limit) return i;
+  if (atomicAdd(&g_check_failures[0], 1u) == 0u) g_check_failures[1] = (unsigned int)line;
+  return (T)0;
+}
+#endif
 
 constexpr int kMaxK = 1024;
 constexpr uint16_t kCandEnd = 0xFFFF;  // pads a candidate list; a list of nothing else = scan all k
@@ -77,12 +97,12 @@ __device__ __forceinline__ int resolve_cand(float x, float y, uint32_t id01, con
   int arg = 0;
   if (id01 == 0xFFFFFFFFu) {
     for (int c = 0; c < k; ++c) {
-      const float dd = dist2(x, y, cent_s[c]);
+      const float dd = dist2(x, y, cent_s[HGM_BOUND(c, k)]);
       if (dd < best) { best = dd; arg = c; }
     }
   } else {
     const int c0 = id01 & 0x7FFF, c1 = id01 >> 16;
-    const float d0 = dist2(x, y, cent_s[c0]), d1 = dist2(x, y, cent_s[c1]);
+    const float d0 = dist2(x, y, cent_s[HGM_BOUND(c0, k)]), d1 = dist2(x, y, cent_s[HGM_BOUND(c1, k)]);
     if (d0 < best) { best = d0; arg = c0; }
     if (d1 < best) { best = d1; arg = c1; }
     if (id01 & kCandMore) {
@@ -92,7 +112,7 @@ __device__ __forceinline__ int resolve_cand(float x, float y, uint32_t id01, con
       for (int i = 2; i < kMaxCand; ++i) {
         const int c = (int)(((i < 4 ? lo : hi) >> (16 * (i & 3))) & 0xFFFF);
         if (c == kCandEnd) break;
-        const float dd = dist2(x, y, cent_s[c]);
+        const float dd = dist2(x, y, cent_s[HGM_BOUND(c, k)]);
         if (dd < best) { best = dd; arg = c; }
       }
     }

@@ -542,6 +542,23 @@ int hgm_set_kernel(hgm_ctx *c, int32_t kernel) {
   return HGM_OK;
 }
 
+// Bound misses counted by a `make CHECKED=1` build of the d == 2 kernels (always 0, line 0 in the product build).
+int hgm_checked_failures(int32_t *count, int32_t *first_line) {
+  unsigned int a[2] = {0, 0}, b[2] = {0, 0};
+#ifdef HGM_CHECKED
+  cudaDeviceSynchronize();
+  grid2d_checked_failures(a);
+  grid2d_fx_checked_failures(b);
+#endif
+  if (count) *count = (int32_t)(a[0] + b[0]);
+  if (first_line) *first_line = (int32_t)(a[0] ? a[1] : b[1]);
+#ifdef HGM_CHECKED
+  return HGM_OK;
+#else
+  return fail(nullptr, HGM_EINVAL, "this library was not built with CHECKED=1");
+#endif
+}
+
 int hgm_set_tensor_form(int32_t form) {
   if (form < HGM_TENSOR_FORM_AUTO || form > HGM_TENSOR_FORM_PAIR) return fail(nullptr, HGM_EINVAL, "unknown tensor form %d", form);
   tensor_set_form(form);

@@ -59,6 +59,10 @@ cudaError_t launch_grid2d_map(const float *d_pts, int64_t n, const float *d_cent
                               double *d_sums, unsigned long long *d_counts, int32_t *d_assign,
                               int sm_count, size_t smem_optin, cudaStream_t s, const Grid2DOuter *outer = nullptr);
 bool grid2d_plan(int k, size_t smem_optin, int *G_out, int *shape_out);
+#ifdef HGM_CHECKED
+void grid2d_checked_failures(unsigned int out[2]);
+void grid2d_fx_checked_failures(unsigned int out[2]);
+#endif
 // the fixed-point form (kernels_grid2d_fx.cu): table size it can hold for k clusters (0 = none), and its launcher
 int grid2d_fx_table_size(int k, size_t smem_optin);
 cudaError_t launch_grid2d_fx_map(const float *d_pts, int64_t n, const float *d_cent, int k, const Grid2D &g,

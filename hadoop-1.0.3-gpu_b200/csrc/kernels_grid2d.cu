@@ -348,14 +348,14 @@ __global__ void __launch_bounds__(S::kThreads, 1)
   // rank a resolved point in cluster c and store it; ranks beyond the striped rows go to the
   // overflow region of parity `par`; returns false if even that is full
   auto place = [&](float x, float y, int c, int par, uint16_t li) -> bool {
-    const int r = atomicAdd(&hist[c], 1);
+    const int r = atomicAdd(&hist[HGM_BOUND(c, k)], 1);
     int pos = r * rs + c;
     if (r >= rcap) {
       const int r2 = atomicAdd(&hist[k + 2 + par], 1);
       if (r2 >= tend) return false;
       pos = slots - 1 - r2;
     }
-    sorted[pos] = make_float2(x, y);
+    sorted[HGM_BOUND(pos, slots)] = make_float2(x, y);
     if (kAssign) lidx[pos] = li;
     return true;
   };
@@ -411,7 +411,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
       for (int i = 0; i < kPPT; ++i) ent[i] = table_s[cell_of(xs[i], ys[i], g)];
       wait_free();
 #pragma unroll
-      for (int i = 0; i < kPPT; ++i) rank[i] = atomicAdd(ent[i] < kMulti ? &hist[ent[i]] : my_qcount, 1);
+      for (int i = 0; i < kPPT; ++i) rank[i] = atomicAdd(ent[i] < kMulti ? &hist[HGM_BOUND(ent[i], k)] : my_qcount, 1);
       // in the shadow of the eight atomics: the first word of the candidate list of this thread's
       // queued point (previous tile), so that phase 1b does not start a global load in front of the
       // group barrier.  One register; 0 = not loaded (two distinct ids never give 0).
@@ -437,7 +437,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
           lost |= !ok;
         }
         if (ok) {
-          sorted[pos] = make_float2(xs[i], ys[i]);
+          sorted[HGM_BOUND(pos, slots)] = make_float2(xs[i], ys[i]);
           if (kAssign) lidx[pos] = resolved ? kNoIndex : (uint16_t)local;
         }
       }
@@ -461,7 +461,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
               pos = slots - 1 - r2;
             }
             if (ok) {
-              sorted[pos] = make_float2(xs[i], ys[i]);
+              sorted[HGM_BOUND(pos, slots)] = make_float2(xs[i], ys[i]);
               if (kAssign) lidx[pos] = (uint16_t)local;
             }
             lost |= !ok;
@@ -566,7 +566,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
         if (local < live) {
           const uint32_t e = table_s[cell_of(xs[i], ys[i], g)];
           const bool resolved = e < kMulti;
-          const int r = atomicAdd(resolved ? &hist[e] : ucount, 1);
+          const int r = atomicAdd(resolved ? &hist[HGM_BOUND(e, k)] : ucount, 1);
           key[i] = (resolved ? e : (uint32_t)k) | ((uint32_t)r << 16);
         }
       }
@@ -595,7 +595,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
       for (int i = 0; i < kPPT; ++i) {
         if (key[i] != 0xFFFFFFFFu) {
           const int pos = offs[key[i] & 0xFFFF] + (int)(key[i] >> 16);
-          sorted[pos] = make_float2(xs[i], ys[i]);
+          sorted[HGM_BOUND(pos, slots)] = make_float2(xs[i], ys[i]);
           if (kAssign) lidx[pos] = (uint16_t)(2 * ((i >> 1) * kGT + t) + (i & 1));
         }
       }
@@ -800,5 +800,9 @@ cudaError_t launch_grid2d_map(const float *d_pts, int64_t n, const float *d_cent
   }
 #undef HGM_ARGS
 }
+
+#ifdef HGM_CHECKED
+void grid2d_checked_failures(unsigned int out[2]) { cudaMemcpyFromSymbol(out, g_check_failures, 8); }
+#endif
 
 }  // namespace hgm

@@ -81,6 +81,7 @@ struct FxParams {
   float sx, sy;      // fixed-point scales S (powers of two)
   float tinyx, tinyy;  // 2 / S: a non-zero |x| below this has bits the limbs cannot hold
   float limx, limy;  // 2^21 / S: at or beyond this the limbs would overflow
+  uint32_t rows;     // accumulator rows: k clusters + the one nobody reads (bound of the checked build)
 };
 
 // The five adds of one point into this lane's words of row c, unconditionally: ptxas turns a predicated shared
@@ -96,7 +97,7 @@ __device__ __forceinline__ uint32_t fx_add_point(uint32_t one, uint32_t acc_lane
   const float ty = __fmaf_rn(y, fx.sy, kFxMagic);
   const float ry = __fmaf_rn(y, fx.sy, kFxMagic - ty);
   const float uy = __fmaf_rn(ry, kFxLoScale, kFxMagic);
-  const uint32_t addr = acc_lane + c * (uint32_t)(kFxWords * kLanes * 4);
+  const uint32_t addr = acc_lane + HGM_BOUND(c, fx.rows) * (uint32_t)(kFxWords * kLanes * 4);
   uint32_t old;
   // the magic bits ride along in every add; the flush takes count * kFxMagicBits off again (mod 2^32)
   asm volatile(
@@ -139,7 +140,7 @@ __device__ __forceinline__ void fx_work_tile(const uint8_t *table_s, const Grid2
     if (queued) {
       if (valid && !direct) {
         const int pos = qn + __popc(queued & lt_mask);
-        queue[pos] = make_float2(xs[i], ys[i]);
+        queue[HGM_BOUND(pos, S::kQCap)] = make_float2(xs[i], ys[i]);
         if (kAssign) qindex[pos] = (uint16_t)local;
       }
       qn += __popc(queued);
@@ -260,9 +261,9 @@ __global__ void __launch_bounds__(S::kThreads, 1)
       const bool fits = fabsf(v.x) < fx.limx && fabsf(v.y) < fx.limy && !tiny(v.x, fx.tinyx) && !tiny(v.y, fx.tinyy);
       full = fx_add_point<kLanes>(fits ? 1u : 0u, acc_lane, fx, v.x, v.y, fits ? c : (uint32_t)k);
       if (!fits) {  // shared FP64 / 64-bit atomics are CAS loops: the rare path only
-        atomicAdd(&late_sum[2 * c], (double)v.x);
-        atomicAdd(&late_sum[2 * c + 1], (double)v.y);
-        atomicAdd(&late_cnt[c], 1ull);
+        atomicAdd(&late_sum[2 * HGM_BOUND(c, k)], (double)v.x);
+        atomicAdd(&late_sum[2 * HGM_BOUND(c, k) + 1], (double)v.y);
+        atomicAdd(&late_cnt[HGM_BOUND(c, k)], 1ull);
       }
     }
     return full;
@@ -444,6 +445,7 @@ cudaError_t launch_grid2d_fx_map(const float *d_pts, int64_t n, const float *d_c
   fx.sx = g.fsx; fx.sy = g.fsy;
   fx.tinyx = 2.0f / g.fsx; fx.tinyy = 2.0f / g.fsy;
   fx.limx = 2097152.0f / g.fsx; fx.limy = 2097152.0f / g.fsy;
+  fx.rows = (uint32_t)k + 1u;
   Grid2DOuter none{};
   const Grid2DOuter &o = outer ? *outer : none;
   if (k <= 128)
@@ -452,5 +454,9 @@ cudaError_t launch_grid2d_fx_map(const float *d_pts, int64_t n, const float *d_c
   return launch_fx<FxNarrow>(d_pts, n, d_cent, k, g, fx, d_table, d_cand, o, d_sums, d_counts, d_assign, sm_count,
                              smem_optin, s);
 }
+
+#ifdef HGM_CHECKED
+void grid2d_fx_checked_failures(unsigned int out[2]) { cudaMemcpyFromSymbol(out, g_check_failures, 8); }
+#endif
 
 }  // namespace hgm

@@ -51,6 +51,7 @@ SIGNATURES = {
     "hgm_last_tensor_phases": (C.c_int, [_c_ctx, C.POINTER(C.c_float)]),
     "hgm_staged_bytes": (C.c_int, [_c_ctx, C.POINTER(C.c_int64)]),
     "hgm_set_tensor_form": (C.c_int, [C.c_int32]),
+    "hgm_checked_failures": (C.c_int, [C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "hgm_grid2d_form": (C.c_int, [_c_ctx, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "hgm_map_split": (C.c_int, [_c_ctx, _p, C.c_size_t, C.c_int32, _p, _p, _p, C.POINTER(C.c_int64)]),
     "hgm_map_file": (C.c_int, [_c_ctx, C.c_char_p, C.c_int64, C.c_int64, C.c_int32, _p, _p, _p,

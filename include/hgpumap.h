@@ -116,6 +116,9 @@ int hgm_last_kernel(hgm_ctx *ctx, int32_t *kernel);
 #define HGM_TENSOR_FORM_SINGLE 1
 #define HGM_TENSOR_FORM_PAIR 2
 int hgm_set_tensor_form(int32_t form);
+/* Diagnostics build only (`make CHECKED=1`): how many shared-memory indices / centroid ids of the d == 2 kernels
+ * missed their bound since the library was loaded, and the source line of the first.  HGM_EINVAL in the product build. */
+int hgm_checked_failures(int32_t *count, int32_t *first_line);
 /* d == 2 only: which combiner the installed index drives -- 0 none (no index), 1 fixed-point
  * (csrc/kernels_grid2d_fx.cu), 2 counting sort (csrc/kernels_grid2d.cu) -- and its table side G. */
 int hgm_grid2d_form(hgm_ctx *ctx, int32_t *form, int32_t *cells_per_side);
