@@ -340,8 +340,10 @@ def tf32_peak_tflops(torch, dev):
 def bind_to_gpu_numa_node(local_rank):
     """One process per GPU: run on, and allocate pinned memory from, the NUMA node the GPU hangs off
     (sysfs local_cpulist of its PCI function), so that the e2e copies do not cross a socket interconnect.
-    On this pool's boxes (one NUMA node, numa_node = -1) it changes nothing: e2e at N=8 is 23 G points/s
-    = 185 GB/s of aggregate host reads, the host's limit, against 55 GB/s = PCIe for one GPU.
+    On this pool's boxes (one virtual socket, numa_node = -1) it changes nothing, and the e2e rate is the platform's
+    own: a plain pinned cudaMemcpyAsync sweep (tools/h2d_sweep.py, profiles/r02_h2d_sweep.md) gives 55.5 GB/s per GPU
+    at 1 and 2 GPUs, 28.8 at 4 (115 aggregate) and 23.2-35.6 at 8 (235 aggregate); hgm_map_split reaches 55 / 55 / 28.7 /
+    23.3 (max over ranks = the slowest GPU).
     Returns a description of the placement or None."""
     try:
         import pynvml
