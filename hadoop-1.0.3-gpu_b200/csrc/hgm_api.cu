@@ -78,6 +78,7 @@ struct hgm_ctx {
   int64_t staged_bytes = 0;  // split bytes copied host -> device since hgm_open
   bool timing_open = false;
   void *nccl_comm = nullptr;
+  void *peer_state = nullptr;  // hgm_comm.cu: the peer-memory exchange of small partials (hgm_peer_open)
   // HBM-resident splits by id.  Rows live in arena blocks (one cudaMalloc per kArenaBytes, not per
   // split) and are appended back to back, so that neighbours can be mapped by ONE launch
   // (hgm_cache_map_all); a block is returned to the driver when its last split is dropped.
@@ -383,6 +384,9 @@ bool is_pinned(const void *p) {
 
 namespace hgm {
 void comm_destroy(void *comm);
+void peer_destroy(void *state);
+void **ctx_peer_slot(hgm_ctx *c) { return &c->peer_state; }
+void ctx_count_launches(hgm_ctx *c, int n) { c->last_launches += n; c->total_launches += n; }
 int ctx_shape(hgm_ctx *c, int *device, int *k, int *d, cudaStream_t *stream, void ***comm_slot) {
   *device = c->device; *k = c->k; *d = c->d; *stream = c->stream; *comm_slot = &c->nccl_comm;
   return 0;
@@ -456,6 +460,7 @@ void hgm_close(hgm_ctx *c) {
   if (!c) return;
   cudaSetDevice(c->device);
   if (c->stream) cudaStreamSynchronize(c->stream);
+  if (c->peer_state) { hgm::peer_destroy(c->peer_state); c->peer_state = nullptr; }
   if (c->nccl_comm) { hgm::comm_destroy(c->nccl_comm); c->nccl_comm = nullptr; }
   cache_clear(c);
   free_job(c);

@@ -51,6 +51,9 @@ SIGNATURES = {
     "hgm_last_tensor_phases": (C.c_int, [_c_ctx, C.POINTER(C.c_float)]),
     "hgm_staged_bytes": (C.c_int, [_c_ctx, C.POINTER(C.c_int64)]),
     "hgm_set_tensor_form": (C.c_int, [C.c_int32]),
+    "hgm_peer_handle": (C.c_int, [_c_ctx, C.c_int32, C.c_void_p]),
+    "hgm_peer_open": (C.c_int, [_c_ctx, C.c_int32, C.c_void_p]),
+    "hgm_peer_close": (C.c_int, [_c_ctx]),
     "hgm_checked_failures": (C.c_int, [C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "hgm_grid2d_form": (C.c_int, [_c_ctx, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "hgm_map_split": (C.c_int, [_c_ctx, _p, C.c_size_t, C.c_int32, _p, _p, _p, C.POINTER(C.c_int64)]),
@@ -342,6 +345,21 @@ class GpuMapSlot:
     def comm_init(self, n_ranks: int, rank: int, comm_id: bytes) -> None:
         buf = C.create_string_buffer(bytes(comm_id), 128)
         self._check(self._lib.hgm_comm_init(self._ctx, n_ranks, rank, buf))
+
+    def peer_handle(self, n_ranks: int) -> bytes:
+        """This rank's inbox handle (64 bytes) for the peer-memory exchange of small partials."""
+        buf = C.create_string_buffer(64)
+        self._check(self._lib.hgm_peer_handle(self._ctx, n_ranks, buf))
+        return buf.raw
+
+    def peer_open(self, rank: int, handles) -> None:
+        """handles: the n_ranks 64-byte handles in rank order."""
+        blob = b"".join(bytes(h) for h in handles)
+        buf = C.create_string_buffer(blob, len(blob))
+        self._check(self._lib.hgm_peer_open(self._ctx, rank, buf))
+
+    def peer_close(self) -> None:
+        self._check(self._lib.hgm_peer_close(self._ctx))
 
     def allreduce_partials(self) -> None:
         self._check(self._lib.hgm_allreduce_partials(self._ctx))

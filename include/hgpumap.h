@@ -256,6 +256,19 @@ int hgm_memcpy_d2h(hgm_ctx *ctx, void *h_dst, const void *d_src, size_t nbytes);
 int hgm_comm_id(void *id128);
 int hgm_comm_init(hgm_ctx *ctx, int32_t n_ranks, int32_t rank, const void *id128);
 int hgm_allreduce_partials(hgm_ctx *ctx);
+/* Optional, for the small partials of the d == 2 shapes (up to 64 KiB: k*(d+1)*8 bytes), where NCCL's launch
+ * latency (23-38 us) shows against a 0.45 ms map kernel: an exchange through peer memory.  Every rank calls
+ * hgm_peer_handle (allocates its inbox, fills 64 bytes), the host gathers the n_ranks handles in rank order (the
+ * way it distributes the NCCL id) and every rank calls hgm_peer_open with all of them.  From then on
+ * hgm_allreduce_partials of partials that fit uses ONE one-CTA kernel on the ctx stream that stores the partials
+ * into every rank's inbox over NVLink and adds the n_ranks slots up in rank order (bit-identical on every rank);
+ * larger partials, or a ctx without hgm_peer_open, go through NCCL as before.  All ranks are processes of one box
+ * with peer access between their GPUs (CUDA IPC); a failure to map a peer is reported and leaves the NCCL path. */
+int hgm_peer_handle(hgm_ctx *ctx, int32_t n_ranks, void *handle64);
+int hgm_peer_open(hgm_ctx *ctx, int32_t rank, const void *handles_n_x_64);
+/* Back to NCCL for every size.  If hgm_peer_open failed on ANY rank, every rank must call this (the exchange is
+ * collective: a rank left on the peer path would wait for the others until its kernel gives up). */
+int hgm_peer_close(hgm_ctx *ctx);
 
 /* ---- synthetic workload of the benchmark -------------------- */
 

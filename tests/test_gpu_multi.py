@@ -24,7 +24,25 @@ def _n_devices():
         return 0
 
 
-def _worker(rank, world, comm_id, tmp, d, k, n, iterations):
+def _exchange_handles(tmp, rank, world, mine, timeout=60.0):
+    """All-gather of the 64-byte inbox handles through files (the host's job: JobConf / a file / torch.distributed)."""
+    import time
+
+    with open(os.path.join(tmp, f"handle{rank}.tmp"), "wb") as f:
+        f.write(mine)
+    os.replace(os.path.join(tmp, f"handle{rank}.tmp"), os.path.join(tmp, f"handle{rank}"))
+    t0, out = time.time(), []
+    for r in range(world):
+        path = os.path.join(tmp, f"handle{r}")
+        while not os.path.exists(path):
+            if time.time() - t0 > timeout:
+                raise TimeoutError(path)
+            time.sleep(0.01)
+        out.append(open(path, "rb").read())
+    return out
+
+
+def _worker(rank, world, comm_id, tmp, d, k, n, iterations, use_peer):
     here = os.path.dirname(os.path.abspath(__file__))
     sys.path[:0] = [here, os.path.join(here, "..", "hadoop-1.0.3-gpu_b200")]
     from hgpumap import capi, shard
@@ -35,6 +53,8 @@ def _worker(rank, world, comm_id, tmp, d, k, n, iterations):
     with capi.GpuMapSlot(rank) as slot:
         slot.set_centroids(cent)
         slot.comm_init(world, rank, comm_id)
+        if use_peer:  # small partials go through peer memory, larger ones still through NCCL
+            slot.peer_open(rank, _exchange_handles(tmp, rank, world, slot.peer_handle(world)))
         row = 4 * d
         for it in range(iterations):  # the second iteration checks that the counts came back as integers
             slot.reset_partials()
@@ -54,20 +74,24 @@ def _worker(rank, world, comm_id, tmp, d, k, n, iterations):
 
 
 @pytest.mark.skipif(_n_devices() < 2, reason="needs at least two GPUs")
+@pytest.mark.parametrize("use_peer", [False, True], ids=["nccl", "peer-memory"])
 @pytest.mark.parametrize("d,k,n", [(2, 128, 300001), (2, 1000, 50001), (64, 1024, 30011), (5, 7, 20001)])
-def test_allreduce_of_partials_matches_oracle_on_the_whole_input(oracle, tmp_path, d, k, n):
+def test_allreduce_of_partials_matches_oracle_on_the_whole_input(oracle, tmp_path, d, k, n, use_peer):
     import torch.multiprocessing as mp
 
     from hgpumap import capi
 
     world = min(_n_devices(), 8)
     comm_id = capi.GpuMapSlot.comm_id()
-    mp.spawn(_worker, args=(world, comm_id, str(tmp_path), d, k, n, 2), nprocs=world, join=True)
+    mp.spawn(_worker, args=(world, comm_id, str(tmp_path), d, k, n, 3, use_peer), nprocs=world, join=True)
     pts, cent = (cases.blobs(n, 2, k, seed=21) if d == 2 else cases.general_d(n, d, k, seed=d + k))
     r_sums, r_counts, r_abs, _ = oracle.map_combine(pts, cent)
     local_total = np.zeros(k, np.int64)
+    first = np.load(tmp_path / "rank0.npz")
     for rank in range(world):
         got = np.load(tmp_path / f"rank{rank}.npz")
+        if use_peer and (k * d + k) * 8 <= 64 * 1024:  # summed in rank order on every rank: bit-identical everywhere
+            np.testing.assert_array_equal(got["sums"].view(np.uint64), first["sums"].view(np.uint64))
         check_partials(got["sums"], got["counts"], r_sums, r_counts, r_abs)
         local_total += got["local_counts"]
     np.testing.assert_array_equal(local_total, r_counts)  # the shards covered every point exactly once
