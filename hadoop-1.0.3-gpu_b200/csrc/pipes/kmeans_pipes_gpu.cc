@@ -140,7 +140,7 @@ class KMeansGpuMap : public HadoopPipes::Mapper {
       ms = from_worker->map_ms;
       rechecks = from_worker->rechecks;
       staged = from_worker->staged_bytes;
-      if (from_worker->cache_hit) ctx_->incrementCounter(cacheHits_, 1);
+      if (from_worker->cache_hit) ctx_->incrementCounter(cacheHits_, (uint64_t)from_worker->cache_hit);
     } else {
       hgm_last_map_ms(gpu_, &ms, &launches);
       hgm_last_rechecks(gpu_, &rechecks);
@@ -177,8 +177,29 @@ class KMeansGpuMap : public HadoopPipes::Mapper {
     account(n);
     batch_used_ = 0;
   }
+  std::vector<hgmw::Client::FileSplit> worker_files_;  // path records of this task, sent to the worker in one request
+
+  void flushFiles() {
+    if (worker_files_.empty()) return;
+    hgmw::MapReply info;
+    int64_t n = 0;
+    try {
+      n = worker_->map_files(worker_files_, fmt_code_, worker_cache_, part_sums_.data(), part_counts_.data(), &info);
+    } catch (const std::exception &e) {
+      throw HadoopUtils::Error(e.what());
+    }
+    worker_files_.clear();
+    fold();
+    account(n, &info);
+  }
+
   void mapFile(const std::string &path, int64_t off, int64_t len) {
     int64_t n = 0;
+    if (worker_ && format_ == PATH) {  // a batch of splits per task: one round trip to the worker for all of them
+      worker_files_.push_back(hgmw::Client::FileSplit{path, off, len});
+      if (worker_files_.size() >= 4096) flushFiles();
+      return;
+    }
     if (worker_) {
       hgmw::MapReply info;
       try {
@@ -316,6 +337,7 @@ class KMeansGpuMap : public HadoopPipes::Mapper {
   // the mapper before the uplink says DONE)
   void close() {
     flush();
+    flushFiles();
     std::vector<std::string> keys;
     for (int c = 0; c < k_; ++c)
       if (counts_[c] != 0) keys.push_back(HadoopUtils::toString(c));

@@ -3,6 +3,11 @@
 #include "../../../include/hgsched.h"
 
 #include <algorithm>
+#include <chrono>
+#include <condition_variable>
+#include <memory>
+#include <mutex>
+#include <new>
 #include <queue>
 #include <vector>
 
@@ -144,6 +149,90 @@ extern "C" int32_t hgs_pick_split(const int32_t *home, int32_t n, int32_t device
   return first_of[victim];  // (3): every pending split is held by some other device
 }
 
+// ---- TaskLauncher's free-slot counters + releaseSlot (mapred/TaskTracker.java:2434-2629, 3397-3408) -----------
+struct hgs_slots {
+  std::mutex lock;
+  std::condition_variable freed;  // the Java has one monitor per counter; one condition serves both here
+  int32_t max_cpu, max_gpu, free_cpu, free_gpu;
+  uint32_t busy_devices = 0;
+};
+
+extern "C" hgs_slots *hgs_slots_new(int32_t max_cpu_slots, int32_t max_gpu_slots) {
+  if (max_cpu_slots < 0 || max_gpu_slots < 0 || max_gpu_slots > HGS_MAX_DEVICES) return nullptr;
+  hgs_slots *s = new (std::nothrow) hgs_slots();
+  if (!s) return nullptr;
+  s->max_cpu = s->free_cpu = max_cpu_slots;  // TaskLauncher(...) :2445-2453
+  s->max_gpu = s->free_gpu = max_gpu_slots;
+  return s;
+}
+extern "C" void hgs_slots_delete(hgs_slots *s) { delete s; }
+
+extern "C" int32_t hgs_slots_acquire(hgs_slots *s, int32_t on_gpu, int32_t need, int32_t device, int32_t timeout_ms,
+                                     const volatile int32_t *cancelled) {
+  if (!s || need < 1) return -22;
+  if (device >= 0 && (!on_gpu || device >= s->max_gpu)) return -22;
+  if (need > (on_gpu ? s->max_gpu : s->max_cpu)) return -34;  // the launcher would wait for ever
+  std::unique_lock<std::mutex> hold(s->lock);
+  int32_t &free_slots = on_gpu ? s->free_gpu : s->free_cpu;
+  const auto deadline = std::chrono::steady_clock::now() + std::chrono::milliseconds(timeout_ms < 0 ? 0 : timeout_ms);
+  while (free_slots < need) {  // :2529, :2568
+    if (cancelled && *cancelled) return 1;  // !tip.canBeLaunched(): killed while still in the launcher queue
+    if (timeout_ms == 0) return 1;
+    if (timeout_ms < 0) s->freed.wait(hold);
+    else if (s->freed.wait_until(hold, deadline) == std::cv_status::timeout && free_slots < need) return 1;
+  }
+  if (cancelled && *cancelled) return 1;
+  if (device >= 0) {
+    if (s->busy_devices & (1u << device)) return -34;  // two tasks on one device: slot i <-> device i is broken
+    s->busy_devices |= 1u << device;
+  }
+  free_slots -= need;  // :2560, :2597; the Java asserts the result >= 0, which the loop above guarantees
+  return 0;
+}
+
+extern "C" int32_t hgs_slots_release(hgs_slots *s, int32_t on_gpu, int32_t n, int32_t device) {
+  if (!s || n < 1) return -22;
+  if (device >= 0 && (!on_gpu || device >= s->max_gpu)) return -22;
+  std::lock_guard<std::mutex> hold(s->lock);
+  int32_t &free_slots = on_gpu ? s->free_gpu : s->free_cpu;
+  if (free_slots + n > (on_gpu ? s->max_gpu : s->max_cpu)) return -34;  // assert (free <= max) :2472, :2482
+  if (device >= 0) {
+    if (!(s->busy_devices & (1u << device))) return -34;
+    s->busy_devices &= ~(1u << device);
+  }
+  free_slots += n;
+  s->freed.notify_all();
+  return 0;
+}
+
+extern "C" int32_t hgs_slots_release_task(hgs_slots *s, int32_t on_gpu, int32_t n, int32_t device, int32_t *slot_taken) {
+  if (!s || !slot_taken) return -22;
+  if (*slot_taken) {  // :3398-3407
+    const int32_t rc = hgs_slots_release(s, on_gpu, n, device);
+    if (rc == 0) *slot_taken = 0;
+    return rc;
+  }
+  hgs_slots_notify(s);  // "wake up the launcher. it may be waiting to block slots for this task."
+  return 0;
+}
+
+extern "C" void hgs_slots_notify(hgs_slots *s) {
+  if (!s) return;
+  std::lock_guard<std::mutex> hold(s->lock);
+  s->freed.notify_all();
+}
+
+extern "C" int32_t hgs_slots_snapshot(hgs_slots *s, hgs_tracker *out) {
+  if (!s || !out) return -22;
+  std::lock_guard<std::mutex> hold(s->lock);
+  out->max_cpu_slots = s->max_cpu;
+  out->max_gpu_slots = s->max_gpu;
+  out->running_cpu = s->max_cpu - s->free_cpu;
+  out->running_gpu = s->max_gpu - s->free_gpu;
+  out->busy_devices = s->busy_devices;
+  return 0;
+}
+
 extern "C" int hgs_simulate(const hgs_sim_params *p, hgs_sim_result *out) {
   if (!p || !out || p->n_splits < 0 || p->iterations < 1 || p->cpu_slots < 0 || p->gpu_slots < 0 ||
       p->gpu_slots > HGS_MAX_DEVICES || p->heartbeat_ms <= 0 || !(p->task_jitter >= 0.0 && p->task_jitter < 1.0))
@@ -167,8 +256,10 @@ extern "C" int hgs_simulate(const hgs_sim_params *p, hgs_sim_result *out) {
     for (int i = 0; i < p->n_splits; ++i) pending[(size_t)i] = i;
     long long cpu_time = 0, gpu_time = 0;  // integer milliseconds like JobInProgress sums them
     int cpu_done = 0, gpu_done = 0;
-    uint32_t busy = 0;
-    int run_cpu = 0, run_gpu = 0;
+    // the TaskTracker's slot accounting: the same unit a live tracker would use (never blocks here: the scheduler
+    // only hands out what the heartbeat reported free)
+    std::unique_ptr<hgs_slots, void (*)(hgs_slots *)> slots(hgs_slots_new(p->cpu_slots, p->gpu_slots), hgs_slots_delete);
+    if (!slots) return -22;
     double next_hb = now;
     const double gpu_ms = it == 0 ? p->gpu_task_ms_first : p->gpu_task_ms_cached;
     while (finished < p->n_splits) {
@@ -180,17 +271,20 @@ extern "C" int hgs_simulate(const hgs_sim_params *p, hgs_sim_result *out) {
         now = std::max(now, r.finish);
         ++finished;
         const long long took = (long long)(r.finish - r.start);  // finishTime - startTime, ms
-        if (r.gpu) { gpu_time += took; ++gpu_done; --run_gpu; busy &= ~(1u << r.dev); }
-        else { cpu_time += took; ++cpu_done; --run_cpu; }
+        if (r.gpu) { gpu_time += took; ++gpu_done; }
+        else { cpu_time += took; ++cpu_done; }
+        int32_t taken = 1;
+        if (hgs_slots_release_task(slots.get(), r.gpu, 1, r.gpu ? r.dev : -1, &taken) != 0) return -34;
         if (p->out_of_band_heartbeat) next_hb = now;
         continue;
       }
       now = std::max(now, t_next);
       next_hb = now + p->heartbeat_ms;
       ++out->heartbeats;
-      hgs_job job{p->n_splits, finished, run_cpu + run_gpu, cpu_done ? (int)(cpu_time / cpu_done) : 0,
+      hgs_tracker tt;
+      hgs_slots_snapshot(slots.get(), &tt);
+      hgs_job job{p->n_splits, finished, tt.running_cpu + tt.running_gpu, cpu_done ? (int)(cpu_time / cpu_done) : 0,
                   gpu_done ? (int)(gpu_time / gpu_done) : 0, 1, p->prior_acceleration};
-      hgs_tracker tt{p->cpu_slots, p->gpu_slots, run_cpu, run_gpu, busy};
       hgs_decision d;
       hgs_assign(&job, 1, &tt, 1, p->optional_scheduling, p->fixes, p->n_splits - started, &d);
       out->cpu_pass_skips += d.cpu_pass_skipped;
@@ -198,7 +292,8 @@ extern "C" int hgs_simulate(const hgs_sim_params *p, hgs_sim_result *out) {
       for (int i = 0; i < d.n_cpu; ++i) {
         pending.erase(pending.begin());  // a CPU slot takes the next split; it stays where it was cached
         running.push(Running{now + p->task_overhead_ms + p->cpu_task_ms * jitter(it, started), false, -1, now});
-        ++run_cpu; ++started; ++out->tasks_cpu;
+        if (hgs_slots_acquire(slots.get(), 0, 1, -1, 0, nullptr) != 0) return -34;  // the rule handed out a busy slot
+        ++started; ++out->tasks_cpu;
       }
       for (int i = 0; i < d.n_gpu; ++i) {
         const int dev = d.gpu_device[i];
@@ -218,8 +313,8 @@ extern "C" int hgs_simulate(const hgs_sim_params *p, hgs_sim_result *out) {
           home[(size_t)split] = dev;
         }
         running.push(Running{now + p->task_overhead_ms + ms * jitter(it, started), true, dev, now});
-        busy |= 1u << dev;
-        ++run_gpu; ++started; ++out->tasks_gpu;
+        if (hgs_slots_acquire(slots.get(), 1, 1, dev, 0, nullptr) != 0) return -34;  // ... or a busy device
+        ++started; ++out->tasks_gpu;
       }
       if (running.empty() && started >= p->n_splits) break;
     }

@@ -64,6 +64,7 @@ struct Worker {
   int64_t next_id = 0;
   uint64_t tick = 0;
   std::string epoch;  // the data set the cached splits belong to (kDropCache)
+  std::string stat_error;
   size_t max_batch = size_t(1024) << 20;
   int64_t staged_before = 0;
   hgmw::WorkerStats stats{};
@@ -154,6 +155,53 @@ struct Worker {
     return reply_map(fd, hgmw::kMapBytes, n, 0, sums, counts);
   }
 
+  // The split in the HBM cache: its id, or -1 if it does not fit even after evictions (the caller streams it).
+  // *hit = it was there already.  A non-zero *rc (with -1) is an error to report.
+  int64_t ensure_cached(const std::string &path, int64_t off, int64_t len, int32_t fmt, int *hit, int *rc) {
+    *rc = HGM_OK;
+    *hit = 0;
+    struct stat st{};
+    if (stat(path.c_str(), &st) != 0) {
+      stat_error = "cannot stat " + path + ": " + strerror(errno);
+      *rc = HGM_EIO;
+      return -1;
+    }
+    char key[64], version[64];
+    snprintf(key, sizeof key, "|%lld|%lld|%d", (long long)off, (long long)len, fmt);
+    snprintf(version, sizeof version, "|%lld|%lld", (long long)st.st_mtime, (long long)st.st_size);
+    const std::string split = path + key, id_key = split + version;
+    auto it = cache_ids.find(id_key);
+    if (it != cache_ids.end()) {
+      *hit = 1;
+      it->second.last_use = ++tick;
+      return it->second.id;
+    }
+    const int64_t id = next_id++;
+    // other versions of this split are dead weight: the file has changed under them
+    for (auto v = cache_ids.begin(); v != cache_ids.end();) {
+      if (v->second.split == split) { hgm_cache_drop(gpu, v->second.id); v = cache_ids.erase(v); }
+      else ++v;
+    }
+    int put = hgm_cache_put_file(gpu, id, path.c_str(), off, len, fmt);
+    // HBM is full: make room, least recently used first (arena blocks are returned to the driver as they
+    // empty, so a few drops may be needed before a block frees up)
+    while (put == HGM_ENOMEM && !cache_ids.empty()) {
+      auto lru = cache_ids.begin();
+      for (auto v = cache_ids.begin(); v != cache_ids.end(); ++v)
+        if (v->second.last_use < lru->second.last_use) lru = v;
+      hgm_cache_drop(gpu, lru->second.id);
+      cache_ids.erase(lru);
+      stats.cache_evictions += 1;
+      put = hgm_cache_put_file(gpu, id, path.c_str(), off, len, fmt);
+    }
+    if (put == HGM_OK) {
+      cache_ids[id_key] = Cached{id, ++tick, split};
+      return id;
+    }
+    if (put != HGM_ENOMEM) *rc = put;  // did not fit: the cache is only a cache
+    return -1;
+  }
+
   bool handle_map_file(int fd, const std::vector<char> &p) {
     if (p.size() < 24) return reply_error(fd, hgmw::kMapFile, HGM_EINVAL, "short MAP_FILE");
     int32_t fmt, use_cache;
@@ -169,43 +217,11 @@ struct Worker {
     int64_t n = 0;
     int rc;
     if (use_cache) {
-      struct stat st{};
-      if (stat(path.c_str(), &st) != 0)
-        return reply_error(fd, hgmw::kMapFile, HGM_EIO, "cannot stat " + path + ": " + strerror(errno));
-      char key[64], version[64];
-      snprintf(key, sizeof key, "|%lld|%lld|%d", (long long)off, (long long)len, fmt);
-      snprintf(version, sizeof version, "|%lld|%lld", (long long)st.st_mtime, (long long)st.st_size);
-      const std::string split = path + key, id_key = split + version;
-      auto it = cache_ids.find(id_key);
-      int hit = 1;
-      int64_t id;
-      if (it == cache_ids.end()) {
-        hit = 0;
-        id = next_id++;
-        // other versions of this split are dead weight: the file has changed under them
-        for (auto v = cache_ids.begin(); v != cache_ids.end();) {
-          if (v->second.split == split) { hgm_cache_drop(gpu, v->second.id); v = cache_ids.erase(v); }
-          else ++v;
-        }
-        rc = hgm_cache_put_file(gpu, id, path.c_str(), off, len, fmt);
-        // HBM is full: make room, least recently used first (arena blocks are returned to the driver as they
-        // empty, so a few drops may be needed before a block frees up)
-        while (rc == HGM_ENOMEM && !cache_ids.empty()) {
-          auto lru = cache_ids.begin();
-          for (auto v = cache_ids.begin(); v != cache_ids.end(); ++v)
-            if (v->second.last_use < lru->second.last_use) lru = v;
-          hgm_cache_drop(gpu, lru->second.id);
-          cache_ids.erase(lru);
-          stats.cache_evictions += 1;
-          rc = hgm_cache_put_file(gpu, id, path.c_str(), off, len, fmt);
-        }
-        if (rc == HGM_OK) cache_ids[id_key] = Cached{id, ++tick, split};
-        else if (rc != HGM_ENOMEM) return reply_gpu_error(fd, hgmw::kMapFile, rc);
-      } else {
-        id = it->second.id;
-        it->second.last_use = ++tick;
-      }
-      if (hit || cache_ids.count(id_key)) {
+      int hit = 0;
+      const int64_t id = ensure_cached(path, off, len, fmt, &hit, &rc);
+      if (id < 0 && rc == HGM_EIO) return reply_error(fd, hgmw::kMapFile, HGM_EIO, stat_error);
+      if (id < 0 && rc != HGM_OK) return reply_gpu_error(fd, hgmw::kMapFile, rc);
+      if (id >= 0) {
         rc = hgm_reset_partials(gpu);
         if (rc == HGM_OK) rc = hgm_cache_map(gpu, id, nullptr, &n);
         if (rc == HGM_OK) rc = hgm_read_partials(gpu, sums.data(), counts.data());
@@ -213,12 +229,72 @@ struct Worker {
         (hit ? stats.cache_hits : stats.cache_misses) += 1;
         return reply_map(fd, hgmw::kMapFile, n, hit, sums, counts);
       }
-      // did not fit: the cache is only a cache, stream the split
+      // did not fit: stream the split
     }
     rc = hgm_map_file(gpu, path.c_str(), off, len, fmt, sums.data(), counts.data(), nullptr, &n);
     if (rc != HGM_OK) return reply_gpu_error(fd, hgmw::kMapFile, rc);
     stats.cache_misses += use_cache ? 1 : 0;
     return reply_map(fd, hgmw::kMapFile, n, 0, sums, counts);
+  }
+
+  // A task's whole batch of file splits in one request: the cached ones are mapped back to back into the device
+  // partials and read once; a per-split round trip (request, launch, synchronise, 3 KB reply: ~70 us) was most of a
+  // batched task's time once its splits were resident.
+  bool handle_map_files(int fd, const std::vector<char> &p) {
+    if (p.size() < 12) return reply_error(fd, hgmw::kMapFiles, HGM_EINVAL, "short MAP_FILES");
+    int32_t fmt, use_cache, count;
+    memcpy(&fmt, p.data(), 4);
+    memcpy(&use_cache, p.data() + 4, 4);
+    memcpy(&count, p.data() + 8, 4);
+    if (k == 0) return reply_error(fd, hgmw::kMapFiles, HGM_EINVAL, "MAP_FILES before SET_CENTROIDS");
+    std::vector<double> sums((size_t)k * d, 0.0), part((size_t)k * d);
+    std::vector<int64_t> counts(k, 0), part_counts(k);
+    std::vector<int64_t> resident;
+    int64_t n_total = 0;
+    int hits = 0;
+    size_t at = 12;
+    for (int32_t i = 0; i < count; ++i) {
+      if (at + 20 > p.size()) return reply_error(fd, hgmw::kMapFiles, HGM_EINVAL, "truncated MAP_FILES entry");
+      int64_t off, len;
+      int32_t plen;
+      memcpy(&off, p.data() + at, 8);
+      memcpy(&len, p.data() + at + 8, 8);
+      memcpy(&plen, p.data() + at + 16, 4);
+      at += 20;
+      if (plen < 0 || at + (size_t)plen > p.size()) return reply_error(fd, hgmw::kMapFiles, HGM_EINVAL, "truncated MAP_FILES path");
+      const std::string path(p.data() + at, (size_t)plen);
+      at += (size_t)plen;
+      int rc = HGM_OK, hit = 0;
+      const int64_t id = use_cache ? ensure_cached(path, off, len, fmt, &hit, &rc) : -1;
+      if (id < 0 && rc == HGM_EIO) return reply_error(fd, hgmw::kMapFiles, HGM_EIO, stat_error);
+      if (id < 0 && rc != HGM_OK) return reply_gpu_error(fd, hgmw::kMapFiles, rc);
+      if (id >= 0) {
+        resident.push_back(id);
+        hits += hit;
+        (hit ? stats.cache_hits : stats.cache_misses) += 1;
+        continue;
+      }
+      int64_t n = 0;  // not cacheable: streamed on its own, folded on the host
+      rc = hgm_map_file(gpu, path.c_str(), off, len, fmt, part.data(), part_counts.data(), nullptr, &n);
+      if (rc != HGM_OK) return reply_gpu_error(fd, hgmw::kMapFiles, rc);
+      stats.cache_misses += use_cache ? 1 : 0;
+      for (size_t j = 0; j < sums.size(); ++j) sums[j] += part[j];
+      for (size_t j = 0; j < counts.size(); ++j) counts[j] += part_counts[j];
+      n_total += n;
+    }
+    if (!resident.empty()) {
+      int rc = hgm_reset_partials(gpu);
+      for (size_t i = 0; rc == HGM_OK && i < resident.size(); ++i) {
+        int64_t n = 0;
+        rc = hgm_cache_map(gpu, resident[i], nullptr, &n);  // queued on the stream; adds into the device partials
+        n_total += n;
+      }
+      if (rc == HGM_OK) rc = hgm_read_partials(gpu, part.data(), part_counts.data());
+      if (rc != HGM_OK) return reply_gpu_error(fd, hgmw::kMapFiles, rc);
+      for (size_t j = 0; j < sums.size(); ++j) sums[j] += part[j];
+      for (size_t j = 0; j < counts.size(); ++j) counts[j] += part_counts[j];
+    }
+    return reply_map(fd, hgmw::kMapFiles, n_total, hits, sums, counts);
   }
 
   // returns false when the worker should exit
@@ -244,6 +320,7 @@ struct Worker {
         }
         case hgmw::kSetCentroids: ok = handle_set_centroids(fd, p); break;
         case hgmw::kMapFile: ok = handle_map_file(fd, p); break;
+        case hgmw::kMapFiles: ok = handle_map_files(fd, p); break;
         case hgmw::kStats: {
           hgm_cache_info(gpu, &stats.cached_splits, &stats.cached_bytes);
           hgm_launch_count(gpu, &stats.kernel_launches);

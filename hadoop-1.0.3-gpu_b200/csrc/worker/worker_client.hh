@@ -114,6 +114,25 @@ class Client {
     put(path.data(), path.size());
     return map_reply(kMapFile, sums, counts, info);
   }
+  struct FileSplit { std::string path; int64_t offset, length; };
+  // a task's batch of file splits in one request (kMapFiles); info->cache_hit = how many were resident
+  int64_t map_files(const std::vector<FileSplit> &splits, int32_t fmt, bool use_cache, double *sums, int64_t *counts,
+                    MapReply *info = nullptr) {
+    std::vector<char> body;
+    const int32_t head[3] = {fmt, use_cache ? 1 : 0, (int32_t)splits.size()};
+    body.insert(body.end(), reinterpret_cast<const char *>(head), reinterpret_cast<const char *>(head) + sizeof head);
+    for (const FileSplit &f : splits) {
+      const int64_t range[2] = {f.offset, f.length};
+      const int32_t plen = (int32_t)f.path.size();
+      body.insert(body.end(), reinterpret_cast<const char *>(range), reinterpret_cast<const char *>(range) + sizeof range);
+      body.insert(body.end(), reinterpret_cast<const char *>(&plen), reinterpret_cast<const char *>(&plen) + 4);
+      body.insert(body.end(), f.path.begin(), f.path.end());
+    }
+    Header h{kMagic, kMapFiles, 0, 0, body.size()};
+    put(&h, sizeof h);
+    put(body.data(), body.size());
+    return map_reply(kMapFiles, sums, counts, info);
+  }
   // kmeans.gpu.worker.cache.epoch: the cache holds splits of ONE data set; a task of another one clears it
   void cache_epoch(const std::string &epoch) {
     Header h{kMagic, kDropCache, 0, 0, epoch.size()};

@@ -25,6 +25,8 @@ enum Op : uint32_t {
   kMapFile = 4,       // payload: int32 fmt, int32 use_cache, int64 offset, int64 length, path bytes -> same
   kStats = 5,         // empty                                           -> WorkerStats
   kShutdown = 6,      // empty                                           -> empty, then the worker exits
+  kMapFiles = 8,      // payload: int32 fmt, int32 use_cache, int32 n, then n x (int64 offset, int64 length, int32 path
+                      //   bytes, path) -> MapReply + sums + counts over all n splits; cache_hit = how many were resident
   kDropCache = 7,     // payload: epoch bytes (may be empty)                 -> empty; a non-empty epoch that differs from the
                       //   worker's current one, or an empty payload, drops every cached split (a new data set)
 };

@@ -71,6 +71,20 @@ def load() -> C.CDLL:
         lib.hgs_mean_map_time_ms.restype = C.c_int32
         lib.hgs_mean_map_time_ms.argtypes = [C.POINTER(C.c_int64), C.POINTER(C.c_int64), C.POINTER(C.c_int32),
                                              C.c_int32, C.c_int32]
+        lib.hgs_slots_new.restype = C.c_void_p
+        lib.hgs_slots_new.argtypes = [C.c_int32, C.c_int32]
+        lib.hgs_slots_delete.restype = None
+        lib.hgs_slots_delete.argtypes = [C.c_void_p]
+        lib.hgs_slots_acquire.restype = C.c_int32
+        lib.hgs_slots_acquire.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_int32)]
+        lib.hgs_slots_release.restype = C.c_int32
+        lib.hgs_slots_release.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32]
+        lib.hgs_slots_release_task.restype = C.c_int32
+        lib.hgs_slots_release_task.argtypes = [C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.POINTER(C.c_int32)]
+        lib.hgs_slots_notify.restype = None
+        lib.hgs_slots_notify.argtypes = [C.c_void_p]
+        lib.hgs_slots_snapshot.restype = C.c_int32
+        lib.hgs_slots_snapshot.argtypes = [C.c_void_p, C.POINTER(Tracker)]
         lib.hgs_pick_split.restype = C.c_int32
         lib.hgs_pick_split.argtypes = [C.POINTER(C.c_int32), C.c_int32, C.c_int32, C.c_int32]
         _LIB = lib
@@ -94,6 +108,55 @@ def simulate(**kw) -> SimResult:
     if rc != 0:
         raise ValueError(f"hgs_simulate returned {rc}")
     return out
+
+
+class SlotError(Exception):
+    """An hgs_slots call that would break an assertion of TaskTracker.java (-34) or got a bad argument (-22)."""
+
+
+class Slots:
+    """The TaskTracker's free-slot counters (TaskLauncher, mapred/TaskTracker.java:2434-2629) + releaseSlot
+    (:3397-3408) + the device of each GPU task (hgs_slots_*).  acquire blocks like the launcher thread does."""
+
+    def __init__(self, max_cpu_slots: int, max_gpu_slots: int):
+        self._lib = load()
+        self._h = self._lib.hgs_slots_new(max_cpu_slots, max_gpu_slots)
+        if not self._h:
+            raise SlotError("bad slot counts")
+
+    def close(self):
+        if self._h:
+            self._lib.hgs_slots_delete(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def _rc(self, rc: int) -> bool:
+        if rc < 0:
+            raise SlotError(rc)
+        return rc == 0
+
+    def acquire(self, on_gpu: bool, need: int = 1, device: int = -1, timeout_ms: int = -1, cancelled=None) -> bool:
+        """True = slots taken; False = timed out or cancelled.  cancelled: a ctypes c_int32 another thread sets."""
+        flag = C.byref(cancelled) if cancelled is not None else None
+        return self._rc(self._lib.hgs_slots_acquire(self._h, int(on_gpu), need, device, timeout_ms, flag))
+
+    def release(self, on_gpu: bool, n: int = 1, device: int = -1) -> None:
+        self._rc(self._lib.hgs_slots_release(self._h, int(on_gpu), n, device))
+
+    def release_task(self, on_gpu: bool, slot_taken: bool, n: int = 1, device: int = -1) -> bool:
+        """TaskInProgress.releaseSlot; returns the new slotTaken (always False)."""
+        taken = C.c_int32(int(slot_taken))
+        self._rc(self._lib.hgs_slots_release_task(self._h, int(on_gpu), n, device, C.byref(taken)))
+        return bool(taken.value)
+
+    def notify(self) -> None:
+        self._lib.hgs_slots_notify(self._h)
+
+    def snapshot(self) -> Tracker:
+        out = Tracker()
+        self._rc(self._lib.hgs_slots_snapshot(self._h, C.byref(out)))
+        return out
 
 
 def pick_split(home_device: list[int], device: int, max_gpu_slots: int) -> int:

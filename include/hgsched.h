@@ -80,6 +80,34 @@ int hgs_tracker_from_reports(const hgs_task_status *reports, int32_t n_reports, 
 int32_t hgs_mean_map_time_ms(const int64_t *start_ms, const int64_t *finish_ms, const int32_t *ran_on_gpu,
                              int32_t n_reports, int32_t want_gpu);
 
+/* ---- the TaskTracker's slot accounting as a unit -------------------------------------------------------------
+ * TaskLauncher (mapred/TaskTracker.java:2434-2629): two counters of free slots, CPU and GPU, that the launcher
+ * thread blocks on before it starts a task (:2526-2600: wait while free < needed, then subtract, assert >= 0) and
+ * that a finishing task gives back (addFree{CPU,GPU}Slots :2467-2485: add, assert <= maximum, notifyAll);
+ * TaskInProgress.releaseSlot (:3397-3408) gives a slot back only if the task had taken one (slotTaken), else it
+ * only wakes the launcher.  On top of the reference: the device of a GPU task is tracked (slot i <-> device i,
+ * mapred/TaskTrackerStatus.java:536-551), and taking a device that is already taken is an error -- the state the
+ * device-affinity patch (patches/) exists to prevent.  Thread-safe; acquire blocks like the launcher does.
+ * Return codes: 0 done; 1 not done (timeout, or cancelled while waiting = the task was killed in the queue,
+ * :2535-2541); -22 bad argument; -34 the call would break an assertion of the Java (free > maximum on release,
+ * more slots needed than exist, device already busy / not busy). */
+typedef struct hgs_slots hgs_slots;
+hgs_slots *hgs_slots_new(int32_t max_cpu_slots, int32_t max_gpu_slots);
+void hgs_slots_delete(hgs_slots *s);
+/* Wait until `need` slots of the kind are free and take them.  timeout_ms: < 0 wait without limit, 0 do not wait.
+ * cancelled (may be NULL) is read every time the waiter wakes: non-zero = give up without taking anything.
+ * device: for a GPU task the device id it was assigned (0..max_gpu_slots-1, marked busy), -1 for none. */
+int32_t hgs_slots_acquire(hgs_slots *s, int32_t on_gpu, int32_t need, int32_t device, int32_t timeout_ms,
+                          const volatile int32_t *cancelled);
+/* addFreeCPUSlots / addFreeGPUSlots; device as given to acquire (its bit is cleared) or -1. */
+int32_t hgs_slots_release(hgs_slots *s, int32_t on_gpu, int32_t n, int32_t device);
+/* TaskInProgress.releaseSlot: gives the slots back iff *slot_taken, which it clears; otherwise only wakes waiters. */
+int32_t hgs_slots_release_task(hgs_slots *s, int32_t on_gpu, int32_t n, int32_t device, int32_t *slot_taken);
+/* notifySlots: wake every waiter (it re-reads its `cancelled`). */
+void hgs_slots_notify(hgs_slots *s);
+/* What a heartbeat reports: fills max_*_slots, running_cpu, running_gpu (slots in use) and busy_devices. */
+int32_t hgs_slots_snapshot(hgs_slots *s, hgs_tracker *out);
+
 /* Behaviour switches.  All 0 = the reference as written, quirks included. */
 #define HGS_FIX_PENDING 1     /* pendingMapLoad per job instead of the running total (:139)        */
 #define HGS_FIX_PER_JOB_ACCEL 2 /* factor from every job's times, not only the last job's (:143-144) */

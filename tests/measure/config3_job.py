@@ -15,8 +15,16 @@ It lives under tests/measure/ because the CPU slots run a program of oracle/.  T
 (mean CPU / GPU task times) are the measured wall times of the tasks of this very job, as
 JobInProgress keeps them (mapred/JobInProgress.java:527-565).
 
-    python tests/measure/config3_job.py [--splits 24] [--split-mib 16] [--iterations 3]
+Task batching (--batch B): a GPU map task carries B splits instead of one -- `kmeans.input.format=path` records
+`file \t offset \t length`, the shipped NLineInputFormat route (conf/mapred-site.xml:13-22) with
+mapred.line.input.format.linespermap = B -- so the 2-3.5 ms it costs to start a Pipes child
+(pipes/Application.java:156-194) is paid once per B splits; it is what JVM reuse
+(mapred.job.reuse.jvm.num.tasks) does for the Java half of a task.  The slot bookkeeping is libhgsched's
+hgs_slots_* (TaskLauncher + releaseSlot restated), the same unit hgs_simulate uses.
+
+    python tests/measure/config3_job.py [--splits 24] [--split-mib 16] [--iterations 3] [--batch 1]
                                         [--cpu-slots 4] [--gpu-slots 1] [--optional 1] [--fixes 0]
+                                        [--data-dir DIR] [--gen host|gpu]
 """
 import argparse
 import json
@@ -63,12 +71,21 @@ def run_task(binary, downlink, args, tmp):
     return up, wall
 
 
-def gpu_downlink(path, nbytes, cpath, k, d, sock):
-    conf = {"kmeans.k": str(k), "kmeans.d": str(d), "kmeans.centroids": cpath, "kmeans.input.format": "binary",
-            "hadoop.pipes.java.recordreader": "false", "kmeans.gpu.worker.socket": sock,
-            "kmeans.gpu.worker.cache": "true"}
-    return (wire.Downlink().authenticate().start().set_job_conf(conf).set_input_types("k", "v")
-            .run_map(wire.file_split("file:" + path, 0, nbytes), 1, False))
+def gpu_downlink(paths, cpath, k, d, sock, epoch):
+    """One GPU map task over the splits `paths` (whole files): a FileSplit through the C++ reader for one split,
+    path records (piped Text values, NLineInputFormat) for a batch."""
+    conf = {"kmeans.k": str(k), "kmeans.d": str(d), "kmeans.centroids": cpath, "kmeans.gpu.worker.socket": sock,
+            "kmeans.gpu.worker.cache": "true", "kmeans.gpu.worker.cache.epoch": epoch}
+    if len(paths) == 1:
+        conf.update({"kmeans.input.format": "binary", "hadoop.pipes.java.recordreader": "false"})
+        return (wire.Downlink().authenticate().start().set_job_conf(conf).set_input_types("k", "v")
+                .run_map(wire.file_split("file:" + paths[0], 0, os.path.getsize(paths[0])), 1, False))
+    conf.update({"kmeans.input.format": "path", "kmeans.file.format": "binary", "hadoop.pipes.java.recordreader": "true"})
+    dl = (wire.Downlink().authenticate().start().set_job_conf(conf)
+          .set_input_types("org.apache.hadoop.io.LongWritable", "org.apache.hadoop.io.Text").run_map(b"split", 1, True))
+    for i, path in enumerate(paths):
+        dl.map_item(i.to_bytes(8, "big"), f"{path}\t0\t{os.path.getsize(path)}")
+    return dl.close()
 
 
 def cpu_downlink(path, cpath, k, d):
@@ -94,19 +111,36 @@ def main():
                          "analogue of obtainNewNodeLocalMapTask; the reference picks splits without regard to devices)")
     ap.add_argument("--k", type=int, default=128)
     ap.add_argument("--out", default="")
+    ap.add_argument("--batch", type=int, default=1, help="splits per GPU map task (path records; 1 = one FileSplit per task)")
+    ap.add_argument("--data-dir", default="", help="where the split files go (default gpurun_out/job_tmp; use /dev/shm for 20 GB)")
+    ap.add_argument("--gen", choices=["host", "gpu"], default="host", help="generate the splits on the host or on GPU 0")
     args = ap.parse_args()
     k, d = args.k, 2
-    tmp = os.path.join(ROOT, "gpurun_out", "job_tmp")
+    tmp = args.data_dir or os.path.join(ROOT, "gpurun_out", "job_tmp")
     os.makedirs(tmp, exist_ok=True)
     centres = synth.centres(synth.SEED_POINTS, k, d)
     cent = synth.perturb(synth.SEED_CENTROIDS, centres)
     pts_per_split = args.split_mib * (1 << 20) // (4 * d)
     files = []
-    for s in range(args.splits):
-        path = os.path.join(tmp, f"part-{s:05d}")
-        capi.synth_points_host(synth.SEED_POINTS, s * pts_per_split, pts_per_split, centres).tofile(path)
-        files.append(path)
+    t_gen = time.perf_counter()
+    if args.gen == "gpu":  # the generator is bit-identical on host and device (csrc/synth.cu); the device is just faster
+        with capi.GpuMapSlot(0) as gen:
+            d_buf = gen.device_alloc(pts_per_split * d * 4)
+            host = np.empty((pts_per_split, d), np.float32)
+            for s in range(args.splits):
+                gen.synth_points_device(synth.SEED_POINTS, s * pts_per_split, pts_per_split, centres, d_buf)
+                gen.memcpy_d2h(host, d_buf)
+                path = os.path.join(tmp, f"part-{s:05d}")
+                host.tofile(path)
+                files.append(path)
+            gen.device_free(d_buf)
+    else:
+        for s in range(args.splits):
+            path = os.path.join(tmp, f"part-{s:05d}")
+            capi.synth_points_host(synth.SEED_POINTS, s * pts_per_split, pts_per_split, centres).tofile(path)
+            files.append(path)
     n_points = args.splits * pts_per_split
+    print(json.dumps({"generated_gb": n_points * d * 4 / 1e9, "seconds": time.perf_counter() - t_gen}), flush=True)
 
     workers, socks = [], []
     for g in range(args.gpu_slots):
@@ -123,7 +157,9 @@ def main():
 
     report = {"workload": f"{args.splits} splits x {args.split_mib} MiB = {n_points:,} 2-D points, k={k}, "
                           f"{args.iterations} iterations; {args.gpu_slots} GPU + {args.cpu_slots} CPU map slots, "
-                          f"optional={args.optional}, fixes={args.fixes}, affinity={args.affinity}", "iterations": []}
+                          f"optional={args.optional}, fixes={args.fixes}, affinity={args.affinity}, "
+                          f"{args.batch} split(s) per GPU map task", "iterations": []}
+    epoch = f"config3-{os.getpid()}"  # the workers' caches hold this data set only
     prior = 0.0
     cached_on = {}  # split -> device whose worker holds it
 
@@ -133,51 +169,53 @@ def main():
         return pending.pop(0)
 
     pool = ThreadPoolExecutor(max_workers=args.cpu_slots + args.gpu_slots)
+    slots = sched.Slots(args.cpu_slots, args.gpu_slots)
     t_job = time.perf_counter()
     try:
         for it in range(args.iterations):
             cpath = os.path.join(tmp, f"centroids-{it}.bin")
             cent.astype("<f4").tofile(cpath)
             pending = list(range(args.splits))
-            running = {}  # future -> (kind, device, split)
+            running = {}  # future -> (kind, device, splits of the task)
             cpu_times, gpu_times = [], []
             sums = np.zeros((k, d))
             counts = np.zeros(k, np.int64)
             hits = skips = beats = 0
+            finished_tasks = 0
             t_it = time.perf_counter()
             while pending or running:
-                # one heartbeat: the tracker reports its slots, the rule answers with tasks to start
-                busy = 0
-                for kind, dev, _ in running.values():
-                    if kind == "gpu":
-                        busy |= 1 << dev
-                job = sched.Job(args.splits, args.splits - len(pending) - len(running), len(running),
+                # one heartbeat: the tracker reports its slots, the rule answers with tasks to start.  A task is a
+                # batch of splits; the rule counts tasks, as the JobTracker does
+                tasks_left = (len(pending) + args.batch - 1) // args.batch
+                job = sched.Job(finished_tasks + len(running) + tasks_left, finished_tasks, len(running),
                                 int(np.mean(cpu_times)) if cpu_times else 0, int(max(np.mean(gpu_times), 1)) if gpu_times else 0,
                                 1, prior)
-                tracker = sched.Tracker(args.cpu_slots, args.gpu_slots,
-                                        sum(1 for v in running.values() if v[0] == "cpu"),
-                                        sum(1 for v in running.values() if v[0] == "gpu"), busy)
-                dec = sched.assign([job], tracker, 1, bool(args.optional), args.fixes, want=len(pending))
+                dec = sched.assign([job], slots.snapshot(), 1, bool(args.optional), args.fixes, want=tasks_left)
                 beats += 1
                 skips += dec.cpu_pass_skipped
                 for i in range(dec.n_gpu):
                     if not pending:
                         break
                     dev = dec.gpu_device[i]
-                    s = pick(dev, pending)
-                    cached_on[s] = dev
-                    dl = gpu_downlink(files[s], os.path.getsize(files[s]), cpath, k, d, socks[dev])
-                    running[pool.submit(run_task, GPU_BIN, dl, (str(dev),), tmp)] = ("gpu", dev, s)
+                    assert slots.acquire(True, device=dev, timeout_ms=0)  # the launcher: the rule only hands out free slots
+                    batch = [pick(dev, pending) for _ in range(min(args.batch, len(pending)))]
+                    for s_ in batch:
+                        cached_on[s_] = dev
+                    dl = gpu_downlink([files[s_] for s_ in batch], cpath, k, d, socks[dev], epoch)
+                    running[pool.submit(run_task, GPU_BIN, dl, (str(dev),), tmp)] = ("gpu", dev, batch)
                 for _ in range(dec.n_cpu):
                     if not pending:
                         break
-                    s = pending.pop(0)
-                    running[pool.submit(run_task, CPU_BIN, cpu_downlink(files[s], cpath, k, d), (), tmp)] = ("cpu", -1, s)
+                    assert slots.acquire(False, timeout_ms=0)
+                    s_ = pending.pop(0)
+                    running[pool.submit(run_task, CPU_BIN, cpu_downlink(files[s_], cpath, k, d), (), tmp)] = ("cpu", -1, [s_])
                 if not running:
                     raise RuntimeError("the scheduler assigned nothing although slots are free and maps are pending")
                 done, _ = wait(list(running), return_when=FIRST_COMPLETED)
                 for fut in done:
-                    kind, dev, s = running.pop(fut)
+                    kind, dev, batch = running.pop(fut)
+                    slots.release_task(kind == "gpu", slot_taken=True, device=dev)  # TaskInProgress.releaseSlot
+                    finished_tasks += 1
                     up, wall = fut.result()
                     (cpu_times if kind == "cpu" else gpu_times).append(wall * 1e3)
                     c, sm = wire.kmeans_partials([(key, v) for _, key, v in up.partitioned], k, d)

@@ -141,6 +141,55 @@ def test_worker_errors_reach_the_task(worker, tmp_path):
     assert proc.poll() is None  # the worker survives a failed task
 
 
+def test_a_batch_of_path_records_is_one_request_to_the_worker(worker, oracle, tmp_path):
+    """Task batching: a map task whose records name several splits (kmeans.input.format=path, the NLineInputFormat
+    route) sends them to the worker in ONE request; the second task finds all of them in the HBM cache, a rewritten
+    file is staged again, and a new cache epoch empties the cache."""
+    sock, _ = worker
+    pts, cent = cases.blobs(60000, 2, 64, seed=113)
+    cpath = str(tmp_path / "cent.bin")
+    cent.astype("<f4").tofile(cpath)
+    files = []
+    for i, part in enumerate(np.array_split(pts, 5)):
+        path = str(tmp_path / f"part-{i}")
+        part.astype("<f4").tofile(path)
+        files.append(path)
+    conf = conf_for(cpath, 64, 2, sock, fmt="path", cache=True)
+    conf["kmeans.file.format"] = "binary"
+    conf["kmeans.gpu.worker.cache.epoch"] = "data-set-A"
+
+    def task():
+        dl = (wire.Downlink().authenticate().start().set_job_conf(conf)
+              .set_input_types("org.apache.hadoop.io.LongWritable", "org.apache.hadoop.io.Text").run_map(b"split", 1, True))
+        for i, path in enumerate(files):
+            size = os.path.getsize(path)
+            dl.map_item(i.to_bytes(8, "big"), path if i == 0 else f"{path}\t0\t{size}")
+        proc, out, _ = ph.run_child(GPU_BIN, dl.close(), args=("0",))
+        up = wire.parse_uplink(out)
+        assert up.done, proc.stderr
+        c, s = wire.kmeans_partials([(k, v) for _, k, v in up.partitioned], 64, 2)
+        return up, c, s
+
+    o = oracle.map_combine(pts, cent)
+    up, c, s = task()
+    check_partials(s, c, o[0], o[1], o[2])
+    assert up.counter("KMEANS", "GPU_CACHE_HITS") == 0 and up.counter("KMEANS", "GPU_BATCHES") == 1
+    assert up.counter("KMEANS", "GPU_BYTES_STAGED") == pts.nbytes
+    up, c, s = task()
+    check_partials(s, c, o[0], o[1], o[2])
+    assert up.counter("KMEANS", "GPU_CACHE_HITS") == 5 and up.counter("KMEANS", "GPU_BYTES_STAGED") == 0
+    (pts[:12000] * 0.5).astype("<f4").tofile(files[0])  # same size, new content: mtime decides
+    os.utime(files[0], (1, 1))
+    up, c, s = task()
+    o2 = oracle.map_combine(np.concatenate([pts[:12000] * 0.5, pts[12000:]]).astype(np.float32), cent)
+    check_partials(s, c, o2[0], o2[1], o2[2])
+    assert up.counter("KMEANS", "GPU_CACHE_HITS") == 4
+    conf["kmeans.gpu.worker.cache.epoch"] = "data-set-B"
+    up, c, s = task()
+    check_partials(s, c, o2[0], o2[1], o2[2])
+    assert up.counter("KMEANS", "GPU_CACHE_HITS") == 0
+
+
 @pytest.mark.parametrize("fmt", ["text", "sequencefile"])
 def test_text_and_sequencefile_splits_through_the_worker(worker, oracle, tmp_path, fmt):
     import seqfile

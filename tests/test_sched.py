@@ -111,7 +111,9 @@ def test_hgsched_header_symbols_are_exported():
     text = open(os.path.join(ROOT, "include", "hgsched.h")).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
     names = sorted(set(re.findall(r"\b(hgs_[a-z_]+)\s*\(", text)))
-    assert names == ["hgs_assign", "hgs_mean_map_time_ms", "hgs_pick_split", "hgs_simulate", "hgs_tracker_from_reports"]
+    assert names == ["hgs_assign", "hgs_mean_map_time_ms", "hgs_pick_split", "hgs_simulate", "hgs_slots_acquire",
+                     "hgs_slots_delete", "hgs_slots_new", "hgs_slots_notify", "hgs_slots_release",
+                     "hgs_slots_release_task", "hgs_slots_snapshot", "hgs_tracker_from_reports"]
     lib = sched.load()
     for name in names:
         assert hasattr(lib, name)
@@ -234,3 +236,82 @@ def test_mean_map_times_use_java_int_arithmetic():
     # the int sum wraps: three tasks of 2^30 ms sum to -2^30 in a Java int
     big = 1 << 30
     assert sched.mean_map_time_ms([0, 0, 0], [big, big, big], [False] * 3, want_gpu=False) == -(1 << 30) // 3 + (1 if (-(1 << 30)) % 3 else 0)
+
+
+# ---- the slot accounting unit (hgs_slots_*) -------------------------------------------------------------------
+
+def test_slots_replay_one_heartbeat_of_launches_and_completions():
+    """A TaskTracker with 2 CPU + 3 GPU map slots: the launcher takes slots in the order the heartbeat's actions
+    arrive (TaskTracker.java:2526-2600), finishing tasks give them back (:2467-2485 via releaseSlot :3397-3408), and
+    what the next heartbeat reports is what TaskTrackerStatus would count."""
+    s = sched.Slots(2, 3)
+    d = sched.assign([job(100, finished=0, running=0)], s.snapshot(), optional=False)
+    assert (d.n_cpu, d.n_gpu) == (2, 3) and list(d.gpu_device[:3]) == [0, 1, 2]
+    for _ in range(d.n_cpu):
+        assert s.acquire(False, timeout_ms=0)
+    for dev in d.gpu_device[:d.n_gpu]:
+        assert s.acquire(True, device=dev, timeout_ms=0)
+    t = s.snapshot()
+    assert (t.running_cpu, t.running_gpu, t.busy_devices) == (2, 3, 0b111)
+    assert sched.assign([job(100, running=5)], t, optional=False).n_gpu == 0  # nothing free, nothing handed out
+    assert not s.acquire(True, device=1, timeout_ms=0) and not s.acquire(False, timeout_ms=0)
+    assert s.release_task(True, slot_taken=True, device=1) is False          # GPU task on device 1 finishes
+    t = s.snapshot()
+    assert (t.running_gpu, t.busy_devices) == (2, 0b101)
+    d = sched.assign([job(100, finished=1, running=4)], t, optional=False)
+    assert d.n_gpu == 1 and d.gpu_device[0] == 1                              # the first free device id (:354-361)
+    assert s.acquire(True, device=1, timeout_ms=0)
+    # a task killed before the launcher got to it never took a slot: releaseSlot only wakes the launcher
+    before = s.snapshot()
+    assert s.release_task(False, slot_taken=False) is False
+    after = s.snapshot()
+    assert (before.running_cpu, before.running_gpu) == (after.running_cpu, after.running_gpu)
+    s.close()
+
+
+def test_slots_refuse_what_the_java_asserts_against():
+    s = sched.Slots(1, 2)
+    with pytest.raises(sched.SlotError):      # addFreeCPUSlots: assert (numCPUFreeSlots <= maxCPUSlots) :2472
+        s.release(False)
+    with pytest.raises(sched.SlotError):      # more slots than the tracker has: the launcher would wait for ever
+        s.acquire(True, need=3, timeout_ms=0)
+    assert s.acquire(True, device=0, timeout_ms=0)
+    with pytest.raises(sched.SlotError):      # a second task stamped with a busy device (slot i <-> device i)
+        s.acquire(True, device=0, timeout_ms=0)
+    with pytest.raises(sched.SlotError):      # giving back a device nobody holds
+        s.release(True, device=1)
+    with pytest.raises(sched.SlotError):
+        s.acquire(True, device=5, timeout_ms=0)
+    s.release(True, device=0)
+    assert s.snapshot().busy_devices == 0
+    s.close()
+
+
+def test_slots_launcher_blocks_until_a_task_finishes_or_is_killed():
+    """The launcher thread waits on the counter (:2529-2553): a completion wakes it; a kill of the queued task
+    (canBeLaunched() false) makes it give up without taking a slot."""
+    import ctypes
+    import threading
+    import time
+
+    s = sched.Slots(1, 1)
+    assert s.acquire(True, device=0)
+    got = []
+    th = threading.Thread(target=lambda: got.append(s.acquire(True, device=0, timeout_ms=5000)))
+    th.start()
+    time.sleep(0.05)
+    assert th.is_alive() and not got          # blocked: no free GPU slot
+    s.release(True, device=0)
+    th.join(timeout=5)
+    assert got == [True] and s.snapshot().busy_devices == 1
+    killed = ctypes.c_int32(0)
+    th = threading.Thread(target=lambda: got.append(s.acquire(True, device=0, timeout_ms=5000, cancelled=killed)))
+    th.start()
+    time.sleep(0.05)
+    killed.value = 1
+    s.notify()                                # releaseSlot of a task that never took one: notifySlots
+    th.join(timeout=5)
+    assert got == [True, False] and s.snapshot().running_gpu == 1
+    assert not s.acquire(False, need=1, timeout_ms=0) is False  # the CPU counter is untouched
+    s.close()
+

@@ -69,6 +69,18 @@ class StandInWorker(threading.Thread):
                     self.file_request = (fmt, use_cache, off, length, p[24:].decode())
                     raw = open(p[24:].decode(), "rb").read()[off:off + length]
                     self._map(conn, op, np.frombuffer(raw, "<f4").reshape(-1, self.cent.shape[1]), hit=use_cache)
+                elif op == 8:  # MAP_FILES: a batch of splits in one request, one reply over all of them
+                    fmt, use_cache, count = struct.unpack("<iii", p[:12])
+                    at, rows = 12, []
+                    self.batch = []
+                    for _ in range(count):
+                        off, length, plen = struct.unpack("<qqi", p[at:at + 20])
+                        path = p[at + 20:at + 20 + plen].decode()
+                        at += 20 + plen
+                        raw = open(path, "rb").read()
+                        rows.append(np.frombuffer(raw[off:] if length < 0 else raw[off:off + length], "<f4"))
+                        self.batch.append((path, off, length))
+                    self._map(conn, op, np.concatenate(rows).reshape(-1, self.cent.shape[1]), hit=0)
                 elif op == 7:
                     self.epoch = p.decode()
                     self._reply(conn, op, 0)
@@ -120,6 +132,39 @@ def test_batches_and_file_splits_reach_the_worker(oracle, tmp_path):
     assert up.done, proc.stderr
     assert w.file_request == (0, 1, 800, 8000, data)
     assert up.counter("KMEANS", "POINTS") == 1000 and up.counter("KMEANS", "GPU_CACHE_HITS") == 1
+
+
+@pytest.mark.skipif(not os.path.exists(GPU_BIN), reason="kmeans-pipes-gpu not built")
+def test_path_records_travel_as_one_batch(oracle, tmp_path):
+    """kmeans.input.format=path with a worker: the task's records are gathered and sent in one MAP_FILES request
+    (after the cache epoch and the centroids), whatever their number."""
+    pts, cent = cases.blobs(3000, 2, 16, seed=115)
+    cpath = str(tmp_path / "cent.bin")
+    cent.astype("<f4").tofile(cpath)
+    files = []
+    for i, part in enumerate(np.array_split(pts, 3)):
+        path = str(tmp_path / f"part-{i}")
+        part.astype("<f4").tofile(path)
+        files.append(path)
+    sock = str(tmp_path / "gpu0.sock")
+    w = StandInWorker(sock, oracle)
+    w.start()
+    conf = job_conf(cpath, 16, 2, sock)
+    conf.update({"kmeans.input.format": "path", "kmeans.file.format": "binary", "kmeans.gpu.worker.cache.epoch": "run-7"})
+    dl = (wire.Downlink().authenticate().start().set_job_conf(conf)
+          .set_input_types("org.apache.hadoop.io.LongWritable", "org.apache.hadoop.io.Text").run_map(b"split", 1, True))
+    dl.map_item((0).to_bytes(8, "big"), files[0])
+    dl.map_item((1).to_bytes(8, "big"), f"{files[1]}\t0\t{os.path.getsize(files[1])}")
+    dl.map_item((2).to_bytes(8, "big"), "file:" + files[2])
+    proc, out, _ = ph.run_child(GPU_BIN, dl.close(), args=("0",))
+    up = wire.parse_uplink(out)
+    assert up.done, proc.stderr
+    counts, sums = wire.kmeans_partials([(k, v) for _, k, v in up.partitioned], 16, 2)
+    o = oracle.map_combine(pts, cent)
+    check_partials(sums, counts, o[0], o[1], o[2])
+    assert w.log == [1, 7, 2, 8] and w.epoch == "run-7"
+    assert w.batch == [(files[0], 0, -1), (files[1], 0, os.path.getsize(files[1])), (files[2], 0, -1)]
+    assert up.counter("KMEANS", "GPU_BATCHES") == 1 and up.counter("KMEANS", "GPU_RECHECKS") == 3
 
 
 @pytest.mark.skipif(not os.path.exists(GPU_BIN), reason="kmeans-pipes-gpu not built")
