@@ -45,7 +45,77 @@
 #include "hgpumap.h"
 #include "../worker/worker_client.hh"
 
+#include <dlfcn.h>
+#include <unistd.h>
+
 static int g_device = 0;
+
+// libhgpumap.so is loaded on first use, not linked: a task that hands its splits to the slot's worker never
+// touches CUDA, and loading the library (9 MB of device code to register) was 1.8 of the 2.6 ms such a child
+// takes to start and exit.  Looked for beside this executable, where the reference-runtime build keeps it, then
+// on the loader's path.  There is still no CPU fallback: no library, no task.
+namespace gpulib {
+decltype(&::hgm_open) fn_hgm_open = nullptr;
+decltype(&::hgm_close) fn_hgm_close = nullptr;
+decltype(&::hgm_last_error) fn_hgm_last_error = nullptr;
+decltype(&::hgm_set_centroids) fn_hgm_set_centroids = nullptr;
+decltype(&::hgm_map_split) fn_hgm_map_split = nullptr;
+decltype(&::hgm_map_file) fn_hgm_map_file = nullptr;
+decltype(&::hgm_host_alloc) fn_hgm_host_alloc = nullptr;
+decltype(&::hgm_host_free) fn_hgm_host_free = nullptr;
+decltype(&::hgm_last_map_ms) fn_hgm_last_map_ms = nullptr;
+decltype(&::hgm_last_rechecks) fn_hgm_last_rechecks = nullptr;
+decltype(&::hgm_staged_bytes) fn_hgm_staged_bytes = nullptr;
+void load() {
+  if (fn_hgm_open) return;
+  char exe[4096];
+  const ssize_t n = readlink("/proc/self/exe", exe, sizeof exe - 1);
+  std::string dir = n > 0 ? std::string(exe, (size_t)n) : std::string(".");
+  dir = dir.substr(0, dir.find_last_of('/'));
+  const std::string tries[] = {dir + "/libhgpumap.so", dir + "/../../hadoop-1.0.3-gpu_b200/libhgpumap.so", "libhgpumap.so"};
+  void *lib = NULL;
+  std::string why;
+  for (const std::string &path : tries) {
+    lib = dlopen(path.c_str(), RTLD_NOW | RTLD_LOCAL);
+    if (lib) break;
+    why += std::string(dlerror()) + "; ";
+  }
+  if (!lib) throw HadoopUtils::Error("cannot load libhgpumap.so (there is no CPU fallback in a GPU map slot): " + why);
+  fn_hgm_close = reinterpret_cast<decltype(fn_hgm_close)>(dlsym(lib, "hgm_close"));
+  if (!fn_hgm_close) throw HadoopUtils::Error("libhgpumap.so lacks hgm_close");
+  fn_hgm_last_error = reinterpret_cast<decltype(fn_hgm_last_error)>(dlsym(lib, "hgm_last_error"));
+  if (!fn_hgm_last_error) throw HadoopUtils::Error("libhgpumap.so lacks hgm_last_error");
+  fn_hgm_set_centroids = reinterpret_cast<decltype(fn_hgm_set_centroids)>(dlsym(lib, "hgm_set_centroids"));
+  if (!fn_hgm_set_centroids) throw HadoopUtils::Error("libhgpumap.so lacks hgm_set_centroids");
+  fn_hgm_map_split = reinterpret_cast<decltype(fn_hgm_map_split)>(dlsym(lib, "hgm_map_split"));
+  if (!fn_hgm_map_split) throw HadoopUtils::Error("libhgpumap.so lacks hgm_map_split");
+  fn_hgm_map_file = reinterpret_cast<decltype(fn_hgm_map_file)>(dlsym(lib, "hgm_map_file"));
+  if (!fn_hgm_map_file) throw HadoopUtils::Error("libhgpumap.so lacks hgm_map_file");
+  fn_hgm_host_alloc = reinterpret_cast<decltype(fn_hgm_host_alloc)>(dlsym(lib, "hgm_host_alloc"));
+  if (!fn_hgm_host_alloc) throw HadoopUtils::Error("libhgpumap.so lacks hgm_host_alloc");
+  fn_hgm_host_free = reinterpret_cast<decltype(fn_hgm_host_free)>(dlsym(lib, "hgm_host_free"));
+  if (!fn_hgm_host_free) throw HadoopUtils::Error("libhgpumap.so lacks hgm_host_free");
+  fn_hgm_last_map_ms = reinterpret_cast<decltype(fn_hgm_last_map_ms)>(dlsym(lib, "hgm_last_map_ms"));
+  if (!fn_hgm_last_map_ms) throw HadoopUtils::Error("libhgpumap.so lacks hgm_last_map_ms");
+  fn_hgm_last_rechecks = reinterpret_cast<decltype(fn_hgm_last_rechecks)>(dlsym(lib, "hgm_last_rechecks"));
+  if (!fn_hgm_last_rechecks) throw HadoopUtils::Error("libhgpumap.so lacks hgm_last_rechecks");
+  fn_hgm_staged_bytes = reinterpret_cast<decltype(fn_hgm_staged_bytes)>(dlsym(lib, "hgm_staged_bytes"));
+  if (!fn_hgm_staged_bytes) throw HadoopUtils::Error("libhgpumap.so lacks hgm_staged_bytes");
+  fn_hgm_open = reinterpret_cast<decltype(fn_hgm_open)>(dlsym(lib, "hgm_open"));
+  if (!fn_hgm_open) throw HadoopUtils::Error("libhgpumap.so lacks hgm_open");
+}
+}  // namespace gpulib
+#define hgm_open gpulib::fn_hgm_open
+#define hgm_close gpulib::fn_hgm_close
+#define hgm_last_error gpulib::fn_hgm_last_error
+#define hgm_set_centroids gpulib::fn_hgm_set_centroids
+#define hgm_map_split gpulib::fn_hgm_map_split
+#define hgm_map_file gpulib::fn_hgm_map_file
+#define hgm_host_alloc gpulib::fn_hgm_host_alloc
+#define hgm_host_free gpulib::fn_hgm_host_free
+#define hgm_last_map_ms gpulib::fn_hgm_last_map_ms
+#define hgm_last_rechecks gpulib::fn_hgm_last_rechecks
+#define hgm_staged_bytes gpulib::fn_hgm_staged_bytes
 
 namespace {
 
@@ -265,6 +335,7 @@ class KMeansGpuMap : public HadoopPipes::Mapper {
         throw HadoopUtils::Error(e.what());  // no worker, no task: the scheduler re-queues the split
       }
     } else {
+      gpulib::load();
       check(nullptr, hgm_open(g_device, &gpu_), "hgm_open");
       check(gpu_, hgm_set_centroids(gpu_, cent.data(), k_, d_), "hgm_set_centroids");
     }

@@ -105,6 +105,9 @@ struct Worker {
     memcpy(&nd, p.data() + 4, 4);
     if (nk <= 0 || nd <= 0 || p.size() != 8 + (size_t)nk * nd * 4)
       return reply_error(fd, hgmw::kSetCentroids, HGM_EINVAL, "SET_CENTROIDS payload does not match k*d");
+    // every task of an iteration brings the same table: the index built for the first one serves the rest
+    if (nk == k && nd == d && memcmp(centroids.data(), p.data() + 8, centroids.size() * 4) == 0)
+      return reply(fd, hgmw::kSetCentroids, 0, nullptr, 0);
     if (nd != d) cache_ids.clear();  // the library drops cached rows of another d
     centroids.assign((size_t)nk * nd, 0.f);
     memcpy(centroids.data(), p.data() + 8, centroids.size() * 4);

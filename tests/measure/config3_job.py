@@ -33,7 +33,6 @@ import subprocess
 import sys
 import tempfile
 import time
-from concurrent.futures import FIRST_COMPLETED, ThreadPoolExecutor, wait
 
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 PKG = os.path.join(ROOT, "hadoop-1.0.3-gpu_b200")
@@ -48,27 +47,50 @@ CPU_BIN = os.path.join(ROOT, "oracle", "_ref", "kmeans-pipes-cpu-hgmrt")
 WORKER = os.path.join(PKG, "hgm-worker")
 
 
-def run_task(binary, downlink, args, tmp):
-    """One map task: child process + command file; returns (uplink bytes, wall seconds)."""
-    fd, cmd = tempfile.mkstemp(prefix="task_", dir=tmp)
-    os.close(fd)
-    downlink.write(cmd)
-    env = {"hadoop.pipes.command.file": cmd, "PATH": os.environ.get("PATH", "")}
-    for key in ("LD_LIBRARY_PATH", "CUDA_VISIBLE_DEVICES"):
-        if key in os.environ:
-            env[key] = os.environ[key]
-    t0 = time.perf_counter()
-    proc = subprocess.run([binary, *args], env=env, capture_output=True, timeout=3600)
-    wall = time.perf_counter() - t0
-    out = cmd + ".out"
-    data = open(out, "rb").read() if os.path.exists(out) else b""
-    for path in (cmd, out):
-        if os.path.exists(path):
-            os.remove(path)
-    up = wire.parse_uplink(data)
-    if not up.done:
-        raise RuntimeError(f"map task failed: {proc.stderr.decode()[-400:]}")
-    return up, wall
+class Task:
+    """One map task = one Pipes child on a command file (hadoop.pipes.command.file).  Started without a thread or a
+    pipe of its own -- the TaskTracker's launcher is a fork + exec, and so is this -- and reaped by the job loop."""
+
+    def __init__(self, binary, downlink, args, tmp):
+        fd, self.cmd = tempfile.mkstemp(prefix="task_", dir=tmp)
+        os.close(fd)
+        downlink.write(self.cmd)
+        env = {"hadoop.pipes.command.file": self.cmd, "PATH": os.environ.get("PATH", "")}
+        for key in ("LD_LIBRARY_PATH", "CUDA_VISIBLE_DEVICES"):
+            if key in os.environ:
+                env[key] = os.environ[key]
+        self.err = open(self.cmd + ".err", "wb")
+        self.t0 = time.perf_counter()
+        self.proc = subprocess.Popen([binary, *args], env=env, stdout=subprocess.DEVNULL, stderr=self.err)
+
+    def finish(self):
+        """After the child has exited: (uplink, wall seconds)."""
+        wall = time.perf_counter() - self.t0
+        self.err.close()
+        out = self.cmd + ".out"
+        data = open(out, "rb").read() if os.path.exists(out) else b""
+        up = wire.parse_uplink(data)
+        if not up.done:
+            raise RuntimeError(f"map task failed: {open(self.cmd + '.err', 'rb').read().decode()[-400:]}")
+        for path in (self.cmd, out, self.cmd + ".err"):
+            if os.path.exists(path):
+                os.remove(path)
+        return up, wall
+
+
+def reap(running):
+    """Block until at least one child of `running` (pid -> ...) has exited; returns the pids that have."""
+    done = []
+    while not done:
+        for pid, (task, *_rest) in running.items():
+            if task.proc.poll() is not None:
+                done.append(pid)
+        if not done:
+            try:
+                os.waitid(os.P_ALL, 0, os.WEXITED | os.WNOWAIT)  # sleep until some child changes state
+            except ChildProcessError:
+                time.sleep(0.0002)
+    return done
 
 
 def gpu_downlink(paths, cpath, k, d, sock, epoch):
@@ -113,6 +135,8 @@ def main():
     ap.add_argument("--out", default="")
     ap.add_argument("--batch", type=int, default=1, help="splits per GPU map task (path records; 1 = one FileSplit per task)")
     ap.add_argument("--data-dir", default="", help="where the split files go (default gpurun_out/job_tmp; use /dev/shm for 20 GB)")
+    ap.add_argument("--devices", type=int, default=0, help="physical GPUs the slots are spread over (slot g -> device g %% N); "
+                    "0 = one device per slot.  For trying the 8-slot job on a smaller box")
     ap.add_argument("--gen", choices=["host", "gpu"], default="host", help="generate the splits on the host or on GPU 0")
     args = ap.parse_args()
     k, d = args.k, 2
@@ -147,7 +171,8 @@ def main():
         sock = os.path.join(tmp, f"gpu{g}.sock")
         if os.path.exists(sock):
             os.remove(sock)  # a stale socket of an earlier run would end the wait below too early
-        workers.append(subprocess.Popen([WORKER, "--device", str(g), "--socket", sock], stderr=subprocess.DEVNULL))
+        device = g % args.devices if args.devices else g
+        workers.append(subprocess.Popen([WORKER, "--device", str(device), "--socket", sock], stderr=subprocess.DEVNULL))
         socks.append(sock)
     for sock in socks:
         for _ in range(1200):
@@ -168,7 +193,6 @@ def main():
             return pending.pop(sched.pick_split([cached_on.get(s, -1) for s in pending], dev, args.gpu_slots))
         return pending.pop(0)
 
-    pool = ThreadPoolExecutor(max_workers=args.cpu_slots + args.gpu_slots)
     slots = sched.Slots(args.cpu_slots, args.gpu_slots)
     t_job = time.perf_counter()
     try:
@@ -176,7 +200,7 @@ def main():
             cpath = os.path.join(tmp, f"centroids-{it}.bin")
             cent.astype("<f4").tofile(cpath)
             pending = list(range(args.splits))
-            running = {}  # future -> (kind, device, splits of the task)
+            running = {}  # pid -> (task, kind, device, splits of the task)
             cpu_times, gpu_times = [], []
             sums = np.zeros((k, d))
             counts = np.zeros(k, np.int64)
@@ -202,21 +226,22 @@ def main():
                     for s_ in batch:
                         cached_on[s_] = dev
                     dl = gpu_downlink([files[s_] for s_ in batch], cpath, k, d, socks[dev], epoch)
-                    running[pool.submit(run_task, GPU_BIN, dl, (str(dev),), tmp)] = ("gpu", dev, batch)
+                    task = Task(GPU_BIN, dl, (str(dev),), tmp)
+                    running[task.proc.pid] = (task, "gpu", dev, batch)
                 for _ in range(dec.n_cpu):
                     if not pending:
                         break
                     assert slots.acquire(False, timeout_ms=0)
                     s_ = pending.pop(0)
-                    running[pool.submit(run_task, CPU_BIN, cpu_downlink(files[s_], cpath, k, d), (), tmp)] = ("cpu", -1, [s_])
+                    task = Task(CPU_BIN, cpu_downlink(files[s_], cpath, k, d), (), tmp)
+                    running[task.proc.pid] = (task, "cpu", -1, [s_])
                 if not running:
                     raise RuntimeError("the scheduler assigned nothing although slots are free and maps are pending")
-                done, _ = wait(list(running), return_when=FIRST_COMPLETED)
-                for fut in done:
-                    kind, dev, batch = running.pop(fut)
+                for pid in reap(running):
+                    task, kind, dev, batch = running.pop(pid)
                     slots.release_task(kind == "gpu", slot_taken=True, device=dev)  # TaskInProgress.releaseSlot
                     finished_tasks += 1
-                    up, wall = fut.result()
+                    up, wall = task.finish()
                     (cpu_times if kind == "cpu" else gpu_times).append(wall * 1e3)
                     c, sm = wire.kmeans_partials([(key, v) for _, key, v in up.partitioned], k, d)
                     counts += c
@@ -237,7 +262,8 @@ def main():
             report["iterations"].append(rec)
             print(json.dumps(rec))
     finally:
-        pool.shutdown(wait=False)
+        for task, *_ in list(locals().get("running", {}).values()):
+            task.proc.kill()
         for w in workers:
             w.terminate()
         for path in files:

@@ -116,6 +116,23 @@ def test_socket_mode_with_hmac_authentication():
     assert outs["wordcount-part-hgmrt"][len(resp) + 28:] == golden
 
 
+@pytest.mark.parametrize("password,challenge", [
+    (b"Jefe", b"what do ya want for nothing?"),                       # RFC 2202 case 2 (key shorter than a block)
+    (b"\xaa" * 80, b"Test Using Larger Than Block-Size Key - Hash Key First"),  # RFC 2202 case 6 (key is hashed first)
+    (b"k" * 64, b"c" * 55), (b"k" * 65, b"c" * 56), (b"x", b"c" * 119), (b"p" * 20, b"c" * 120),  # SHA-1 padding edges
+])
+def test_socket_mode_digest_is_hmac_sha1_for_any_key_and_challenge(password, challenge):
+    """The runtime carries its own SHA-1/HMAC (no libcrypto): the AUTHENTICATION_RESP must equal
+    base64(HMAC-SHA1(password, digest)) as Python's hmac computes it, for short and over-long keys and for
+    message lengths on both sides of the padding boundary -- and the child must accept the server's digest."""
+    body = wire.Downlink().start().close()
+    rc, uplink, err, expected = ph.run_child_over_socket(_bin("wordcount-part-hgmrt"), body, password=password,
+                                                         challenge=challenge)
+    up = wire.parse_uplink(uplink)
+    assert up.done, err
+    assert up.auth_response == expected.decode()
+
+
 def test_socket_mode_rejects_a_wrong_digest():
     body = wire.Downlink().start().close()
     rc, uplink, err, _ = ph.run_child_over_socket(_bin("wordcount-part-hgmrt"), body, bad_digest=True)
