@@ -170,7 +170,7 @@ def run_reference_arm(args):
         return
     cores = host_cores()
     ref = CpuReference(args, procs=cores, points=1 << 18)
-    for _ in range(min(args.warmup, 1)):
+    for _ in range(max(args.warmup, 3)):  # as many warm-up steps as the GPU arm takes (each is a bounded sample)
         ref.step()
     pts, secs = 0, 0.0
     for _ in range(args.steps):
@@ -180,7 +180,7 @@ def run_reference_arm(args):
     value = pts / secs
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": min(args.warmup, 1), "ms_per_step": 1e3 * secs / args.steps,
+        "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": 1e3 * secs / args.steps,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(args), "k": args.k, "d": args.d,
                    "sample_points_per_step": pts // args.steps},
