@@ -125,6 +125,7 @@ __device__ __forceinline__ void fx_work_tile(const uint8_t *table_s, const Grid2
   // the table is a byte array: keep its loads in a pass of their own, ahead of every shared-memory
   // write of the tile, or the compiler chains load -> atomics -> load
   uint32_t ent[kPPT];
+  uint32_t old[kPPT];  // what each count word held: looked at after the tile, not behind each atomic's round trip
 #pragma unroll
   for (int i = 0; i < kPPT; ++i) ent[i] = table_s[cell_of(xs[i], ys[i], g)];
 #pragma unroll
@@ -135,7 +136,7 @@ __device__ __forceinline__ void fx_work_tile(const uint8_t *table_s, const Grid2
     const uint32_t c = kFull ? ent[i] : (valid ? ent[i] : k);
     const bool direct = c != k;
     if (kAssign && direct) assign[base + local] = (int)c;
-    seen |= fx_add_point<S::kLanes>(direct ? 1u : 0u, acc_lane, fx, xs[i], ys[i], c);
+    old[i] = fx_add_point<S::kLanes>(direct ? 1u : 0u, acc_lane, fx, xs[i], ys[i], c);
     const uint32_t queued = __ballot_sync(0xFFFFFFFFu, valid && !direct);
     if (queued) {
       if (valid && !direct) {
@@ -146,6 +147,8 @@ __device__ __forceinline__ void fx_work_tile(const uint8_t *table_s, const Grid2
       qn += __popc(queued);
     }
   }
+#pragma unroll
+  for (int i = 0; i < kPPT; ++i) seen |= old[i];
 }
 
 template <class S, bool kVec4, bool kAssign>
