@@ -192,7 +192,8 @@ void cache_clear(hgm_ctx *c) {
 
 // Choose the d == 2 cell grid for a centroid table; false if the table is not indexable
 // (non-finite or astronomically large coordinates) and the exact scan must be used.
-bool plan_grid2d(const float *cent, int k, size_t smem_optin, bool sort_form, Grid2D *out, Grid2D *outer_out = nullptr) {
+bool plan_grid2d(const float *cent, int k, size_t smem_optin, bool sort_form, Grid2D *out, Grid2D *outer_out = nullptr,
+                 size_t table_cap = 0) {
   if (k > 1024) return false;
   double lo[2] = {INFINITY, INFINITY}, hi[2] = {-INFINITY, -INFINITY};
   for (int c = 0; c < k; ++c)
@@ -230,7 +231,7 @@ bool plan_grid2d(const float *cent, int k, size_t smem_optin, bool sort_form, Gr
     return true;
   };
   if (outer_out) *outer_out = Grid2D{};
-  int G = sort_form ? 0 : grid2d_fx_table_size(k, smem_optin);
+  int G = sort_form ? 0 : grid2d_fx_table_size(k, smem_optin, table_cap);
   int shape = kShapeFx;
   if (G > 0 && outer_out && geometry(kOuterCells, 1.5)) {  // the coarse index: four times the box on each axis
     outer_out->sx = s[0]; outer_out->sy = s[1];
@@ -394,8 +395,8 @@ int ctx_shape(hgm_ctx *c, int *device, int *k, int *d, cudaStream_t *stream, voi
 int ctx_fail(hgm_ctx *c, int code, const char *msg) { return fail(c, code, "%s", msg); }
 // for entry points that live in other translation units and have no ctx
 int report_error(int code, const char *msg) { return fail(nullptr, code, "%s", msg); }
-bool plan_grid2d_for(const float *cent, int k, size_t smem_optin, Grid2D *out) {
-  return plan_grid2d(cent, k, smem_optin, false, out);
+bool plan_grid2d_for(const float *cent, int k, size_t smem_optin, Grid2D *out, size_t table_cap) {
+  return plan_grid2d(cent, k, smem_optin, false, out, nullptr, table_cap);
 }
 }  // namespace hgm
 

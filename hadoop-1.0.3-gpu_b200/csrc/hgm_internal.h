@@ -39,8 +39,9 @@ constexpr int kMaxCand = 8;
 // 8-bit copy of the table for k <= kTable8MaxK: cluster id, or kTable8Multi = "look at the 16-bit entry"
 constexpr int kTable8MaxK = 254;
 constexpr uint8_t kTable8Multi = 0xFF;
-// bytes of the table buffer for a G x G grid: 16-bit table, then the 8-bit copy
-inline size_t grid2d_table_bytes(int G) { return (size_t)G * G * 3 + 32; }
+// bytes of the table buffer for a G x G grid: 16-bit table, then the 8-bit copy (counting-sort form) or the
+// fixed-point form's own 16-bit table
+inline size_t grid2d_table_bytes(int G) { return (size_t)G * G * 4 + 32; }
 
 // A second, coarse index over several times the centroids' box: a point outside the fine grid is resolved from its
 // cell there instead of by a scan over all k centroids (fixed-point form only; built by the same builder kernel).
@@ -64,7 +65,7 @@ void grid2d_checked_failures(unsigned int out[2]);
 void grid2d_fx_checked_failures(unsigned int out[2]);
 #endif
 // the fixed-point form (kernels_grid2d_fx.cu): table size it can hold for k clusters (0 = none), and its launcher
-int grid2d_fx_table_size(int k, size_t smem_optin);
+int grid2d_fx_table_size(int k, size_t smem_optin, size_t table_cap = 0);
 cudaError_t launch_grid2d_fx_map(const float *d_pts, int64_t n, const float *d_cent, int k, const Grid2D &g,
                                  const uint16_t *d_table, const uint16_t *d_cand, double *d_sums,
                                  unsigned long long *d_counts, int32_t *d_assign, int sm_count, size_t smem_optin,

@@ -32,7 +32,7 @@
 
 namespace hgm {
 // defined in hgm_api.cu: the same planner hgm_set_centroids uses
-bool plan_grid2d_for(const float *cent, int k, size_t smem_optin, Grid2D *out);
+bool plan_grid2d_for(const float *cent, int k, size_t smem_optin, Grid2D *out, size_t table_cap);
 int report_error(int code, const char *msg);
 }  // namespace hgm
 
@@ -125,7 +125,8 @@ extern "C" int hgm_map_device_static(int device_id, const float *d_points, int64
   if (rc != HGM_OK) return rc;
 
   Grid2D grid;
-  if (!plan_grid2d_for(centroids, k, dev->smem_optin, &grid) || grid.G > kStaticMaxG)
+  if (!plan_grid2d_for(centroids, k, dev->smem_optin, &grid, kTableBytes) || grid.G > kStaticMaxG ||
+      grid2d_table_bytes(grid.G) > kTableBytes + (grid.shape == kShapeFx ? 0 : (size_t)grid.G * grid.G))
     return report_error(HGM_EINVAL, "hgm_map_device_static: this centroid table cannot be indexed (non-finite or "
                                     "huge coordinates); use hgm_open/hgm_map_device, which fall back to the exact scan");
 

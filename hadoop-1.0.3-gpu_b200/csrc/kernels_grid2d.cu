@@ -134,10 +134,17 @@ __global__ void __launch_bounds__(256) grid2d_build_kernel(const float *__restri
     const double tx = 2.0 / (double)g.fsx, ty = 2.0 / (double)g.fsy;
     fx_slow = (xlo < tx && xhi > -tx) || (ylo < ty && yhi > -ty);
   }
-  // "not a single-candidate cell" is kTable8Multi for the counting-sort kernel and k for the fixed-point one, where
-  // it doubles as the index of the accumulator row that is never read
-  const uint8_t multi8 = g.shape == kShapeFx ? (uint8_t)k : kTable8Multi;
-  table8[cell] = entry < kCellMulti && !fx_slow ? (uint8_t)(entry < multi8 ? entry : multi8) : multi8;
+  if (g.shape == kShapeFx) {
+    // that form's own table, 16 bits per cell in place of the 8-bit copy: the only candidate, or both candidates of
+    // a two-candidate cell (id0 | id1 << 8, ascending, so >= 256), or 0xFFFF = ask the index in global memory
+    uint16_t *const fx_table = table + (size_t)g.G * g.G;
+    uint16_t e = 0xFFFFu;
+    if (!fx_slow && entry < kCellMulti) e = entry;
+    else if (!fx_slow && entry == (kCellMulti | 2)) e = (uint16_t)(list[0] | (list[1] << 8));
+    fx_table[cell] = e;
+  } else {
+    table8[cell] = entry < kCellMulti ? (uint8_t)(entry < kTable8Multi ? entry : kTable8Multi) : kTable8Multi;
+  }
 }
 
 // ---- the map kernel ---------------------------------------------------------------------

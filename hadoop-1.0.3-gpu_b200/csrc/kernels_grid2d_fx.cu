@@ -22,11 +22,14 @@
 // 7.6 cycles per 32 points against 20.7+ before).  The representation is exact for every x with
 // |x * S| >= 2 (or x == 0): a float there has no bits below 2^-22.  Smaller non-zero values
 // (|x| below 2^-20 of the grid's extent) can only occur in the cell column that contains x = 0 and
-// the row that contains y = 0: the index builder marks those cells "not direct" in this form's 8-bit
+// the row that contains y = 0: the index builder marks those cells "ask the index" in this form's
 // table, so the hot path needs no test of its own.  Their points, the points of multi-candidate
 // cells, points outside the grid and NaN/inf go to a per-warp queue in shared memory and are settled
-// 32 at a time: exact candidate scan, then the same five atomics, or -- out of range / too small --
-// an FP64 CAS add.
+// 32 at a time, twice per tile: exact candidate scan, then the same five atomics, or -- out of range /
+// too small -- an FP64 CAS add.  The table in shared memory has 16 bits per cell: a two-candidate cell
+// (most queued points sit on a single Voronoi edge) names both centroids there and is settled without
+// touching global memory; only cells with more candidates, the strips and the outside go to the
+// candidate lists in global memory.
 //
 // A word takes at most kFxMaxAdds adds between two flushes (1000 * (2^21 + 1) < 2^31: the signed
 // sum cannot wrap).  The count word of each (cluster, lane) says how many it has had: the add that
@@ -47,6 +50,9 @@ constexpr uint32_t kFxMagicBits = 0x4B400000u;  // bits of 1.5 * 2^23
 constexpr float kFxMagic = 12582912.0f;         // 1.5 * 2^23: RN(v + magic) - magic = RN(v) for |v| < 2^22
 constexpr float kFxLoScale = 4194304.0f;        // 2^22
 constexpr int kFxMaxAdds = 1000;
+// This form's cell table, 16 bits per cell: id (< 256) = the cell's only candidate; id0 | id1 << 8 (id0 < id1, so
+// >= 256) = its two candidates; kFxOther = ask the index in global memory.
+constexpr uint32_t kFxOther = 0xFFFFu;
 
 template <int kWarpsT, int kPPTT, int kLanesT, int kFlushAtT>
 struct FxShape {
@@ -55,7 +61,7 @@ struct FxShape {
   static constexpr int kPPT = kPPTT;      // points per lane per tile (even)
   static constexpr int kTile = 32 * kPPTT;  // points per warp tile
   static constexpr int kLanes = kLanesT;  // private words per (cluster, word): 32, or 16 when k is large
-  static constexpr int kQCap = kTile + 32;  // a warp's queue: what one tile can add on top of < 32 left over
+  static constexpr int kQCap = kTile / 2 + 32;  // a warp's queue: what half a tile can add on top of < 32 left over
   // every add to a count word returns its old value, so some lane sees kFlushAt exactly when a word has
   // had that many adds; after that each warp adds at most what one tile can: kPPT direct adds and kPPT
   // queue batches (+ 1 at the very end) per lane, times the lanes that share a word.  A power of two, so
@@ -67,8 +73,8 @@ struct FxShape {
 };
 
 __host__ __device__ inline size_t fx_head_bytes(int G, int k) {
-  // [table8 G*G][centroids k float2][mbarrier 16 B][flag 16 B]
-  return align16((size_t)G * G) + align16((size_t)k * 8) + 32;
+  // [table G*G u16][centroids k float2][mbarrier 16 B][flag 16 B]
+  return align16((size_t)G * G * 2) + align16((size_t)k * 8) + 32;
 }
 template <class S>
 __host__ __device__ inline size_t fx_body_bytes(int k, bool with_assign) {
@@ -116,24 +122,26 @@ __device__ __forceinline__ uint32_t fx_add_point(uint32_t one, uint32_t acc_lane
 // One tile of a warp: table lookups, then per point either the five adds (single-candidate cell) or a push
 // onto the warp's queue.  kFull = every point of the tile exists (no bounds tests in the straight-line code).
 // `seen` collects the OR of the counts found.
-template <class S, bool kAssign, bool kFull>
-__device__ __forceinline__ void fx_work_tile(const uint8_t *table_s, const Grid2D &g, const FxParams &fx, uint32_t acc_lane,
+template <class S, bool kAssign, bool kFull, int kFirst>
+__device__ __forceinline__ void fx_work_tile(const uint16_t *table_s, const Grid2D &g, const FxParams &fx, uint32_t acc_lane,
                                              uint32_t k, float2 *queue, uint16_t *qindex, int32_t *__restrict__ assign, long long base,
                                              int live, int lane, uint32_t lt_mask, const float (&xs)[S::kPPT],
                                              const float (&ys)[S::kPPT], int &qn, uint32_t &seen) {
-  constexpr int kPPT = S::kPPT;
-  // the table is a byte array: keep its loads in a pass of their own, ahead of every shared-memory
-  // write of the tile, or the compiler chains load -> atomics -> load
+  // half a tile per call (points kFirst .. kFirst + kPPT/2 - 1 of every lane): the queue is drained in between, so
+  // it needs room for half a tile only and the table can have that much more of the shared memory
+  constexpr int kPPT = S::kPPT, kEnd = kFirst + S::kPPT / 2;
+  // keep the table loads in a pass of their own, ahead of every shared-memory write of the half tile, or the
+  // compiler chains load -> atomics -> load
   uint32_t ent[kPPT];
-  uint32_t old[kPPT];  // what each count word held: looked at after the tile, not behind each atomic's round trip
+  uint32_t old[kPPT];  // what each count word held: looked at after the half tile, not behind each atomic's round trip
 #pragma unroll
-  for (int i = 0; i < kPPT; ++i) ent[i] = table_s[cell_of(xs[i], ys[i], g)];
+  for (int i = kFirst; i < kEnd; ++i) ent[i] = table_s[cell_of(xs[i], ys[i], g)];
 #pragma unroll
-  for (int i = 0; i < kPPT; ++i) {
+  for (int i = kFirst; i < kEnd; ++i) {
     const int local = 2 * ((i >> 1) * 32 + lane) + (i & 1);
     const bool valid = kFull || local < live;
-    // this form's table says k, the row nobody reads, for every cell that is not a single-candidate one
-    const uint32_t c = kFull ? ent[i] : (valid ? ent[i] : k);
+    // single-candidate cells hold their cluster id (< k); every other entry is >= 256 > k: row k, the one nobody reads
+    const uint32_t c = kFull ? min(ent[i], k) : (valid ? min(ent[i], k) : k);
     const bool direct = c != k;
     if (kAssign && direct) assign[base + local] = (int)c;
     old[i] = fx_add_point<S::kLanes>(direct ? 1u : 0u, acc_lane, fx, xs[i], ys[i], c);
@@ -148,7 +156,7 @@ __device__ __forceinline__ void fx_work_tile(const uint8_t *table_s, const Grid2
     }
   }
 #pragma unroll
-  for (int i = 0; i < kPPT; ++i) seen |= old[i];
+  for (int i = kFirst; i < kEnd; ++i) seen |= old[i];
 }
 
 template <class S, bool kVec4, bool kAssign>
@@ -164,8 +172,8 @@ __global__ void __launch_bounds__(S::kThreads, 1)
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
 
-  const size_t table_bytes_al = align16((size_t)g.G * g.G);
-  uint8_t *const table_s = smem_raw;
+  const size_t table_bytes_al = align16((size_t)g.G * g.G * 2);
+  uint16_t *const table_s = reinterpret_cast<uint16_t *>(smem_raw);
   float2 *const cent_s = reinterpret_cast<float2 *>(smem_raw + table_bytes_al);
   uint64_t *const bar = reinterpret_cast<uint64_t *>(reinterpret_cast<unsigned char *>(cent_s) + align16((size_t)k * 8));
   volatile int *const flag = reinterpret_cast<volatile int *>(bar + 2);
@@ -178,7 +186,8 @@ __global__ void __launch_bounds__(S::kThreads, 1)
   uint16_t *const qindex = reinterpret_cast<uint16_t *>(reinterpret_cast<float2 *>(late_cnt + k) + (size_t)S::kWarps * S::kQCap) +
                            (size_t)warp * S::kQCap;
 
-  // stage the 8-bit cell table and the centroids with TMA bulk copies (SASS: UBLKCP)
+  // stage this form's cell table (it follows the 16-bit index table in the same buffer) and the centroids with TMA
+  // bulk copies (SASS: UBLKCP)
   const unsigned char *table_src = reinterpret_cast<const unsigned char *>(table + (size_t)g.G * g.G);
   const uint32_t table_bytes = (uint32_t)table_bytes_al;
   const uint32_t cent_bytes = (uint32_t)align16((size_t)k * 8);
@@ -188,7 +197,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
     mbar_expect_tx(bar, table_bytes + cent_bytes);
     for (uint32_t o = 0; o < table_bytes; o += 32768) {
       const uint32_t sz = table_bytes - o < 32768 ? table_bytes - o : 32768;
-      tma_bulk_g2s(table_s + o, table_src + o, sz, bar);
+      tma_bulk_g2s(smem_raw + o, table_src + o, sz, bar);
     }
     tma_bulk_g2s(cent_s, cent, cent_bytes, bar);
     *flag = 0;
@@ -217,51 +226,71 @@ __global__ void __launch_bounds__(S::kThreads, 1)
     const uint32_t ux = min(__float_as_uint(__fmaf_rn(v.x, g.sx, g.Bx)) - kMagicBits, last);  // cell_of, taken apart
     const uint32_t uy = min(__float_as_uint(__fmaf_rn(v.y, g.sy, g.By)) - kMagicBits, last);
     const uint32_t cell = uy * (uint32_t)g.G + ux;
-    // the 16-bit entry tells a single-candidate cell that is only marked for its tiny values from a
-    // multi-candidate one; both loads go out together
-    const uint16_t *list = cand + (size_t)cell * kMaxCand;
-    const uint16_t *entry = table + cell;
-    // outside the fine grid (its last row and column collect everything out of range): the coarse index over
-    // several times the box knows the few centroids that can win out there
-    if (outer.g.G != 0 && (ux == last || uy == last)) {
-      const uint32_t far = cell_of(v.x, v.y, outer.g);
-      list = outer.cand + (size_t)far * kMaxCand;
-      entry = outer.table + far;
-    }
-    const uint32_t e16 = __ldg(entry);
-    const uint32_t id01 = __ldg(reinterpret_cast<const uint32_t *>(list));
-    uint32_t c = e16;
-    // "scan every centroid" points (outside the index, NaN/inf, a cell with more candidates than a list holds):
-    // one at a time with the whole warp on it -- lane l scans centroids l, l + 32, ... in ascending order, the
-    // lexicographic (distance, index) minimum over the lanes is the scan's winner.  Left to its own lane such a
-    // point kept the other 31 waiting for k distance evaluations.
-    bool scan_all = live && e16 >= kCellMulti && id01 == 0xFFFFFFFFu;
-    uint32_t todo = __ballot_sync(0xFFFFFFFFu, scan_all);
-    if (__popc(todo) > 10) {  // many of them: k evaluations on every lane at once cost less than 32 cooperative rounds
-      todo = 0u;
-      scan_all = false;
-    }
-    for (; todo; todo &= todo - 1) {
-      const int src = __ffs(todo) - 1;
-      const float px = __shfl_sync(0xFFFFFFFFu, v.x, src), py = __shfl_sync(0xFFFFFFFFu, v.y, src);
+    const uint32_t ent = table_s[cell];
+    uint32_t c = ent;   // < 256: a single-candidate cell (only the tail of a ragged tile queues those)
+    bool fits = true;   // an interior cell outside the strips around the axes: the limbs hold its points exactly
+    // a two-candidate cell -- by far the most common kind of queued point -- is settled from shared memory alone:
+    // the table entry names both centroids; ascending index, strict '<' from (+inf, 0), as the scan does it
+    if (ent >= 256u && ent != kFxOther) {
+      const uint32_t c0 = ent & 0xFFu, c1 = ent >> 8;
+      const float d0 = dist2(v.x, v.y, cent_s[HGM_BOUND(c0, k)]), d1 = dist2(v.x, v.y, cent_s[HGM_BOUND(c1, k)]);
       float best = INFINITY;
-      int arg = 0x7FFFFFFF;
-      for (int cc = lane; cc < k; cc += 32) {
-        const float dd = dist2(px, py, cent_s[cc]);
-        if (dd < best) { best = dd; arg = cc; }
+      c = 0u;
+      if (d0 < best) { best = d0; c = c0; }
+      if (d1 < best) { best = d1; c = c1; }
+    }
+    // everything else asks the index in global memory: more than two candidates, the strips around x = 0 and y = 0,
+    // points outside the fine grid (the coarse index), NaN / inf
+    const bool far = live && ent == kFxOther;
+    if (__any_sync(0xFFFFFFFFu, far)) {
+      const uint16_t *list = cand + (size_t)cell * kMaxCand;
+      const uint16_t *entry = table + cell;
+      // outside the fine grid (its last row and column collect everything out of range): the coarse index over
+      // several times the box knows the few centroids that can win out there
+      if (outer.g.G != 0 && (ux == last || uy == last)) {
+        const uint32_t out_cell = cell_of(v.x, v.y, outer.g);
+        list = outer.cand + (size_t)out_cell * kMaxCand;
+        entry = outer.table + out_cell;
       }
+      // the 16-bit entry tells a single-candidate cell that is only marked for its tiny values from a
+      // multi-candidate one; both loads go out together
+      const uint32_t e16 = far ? (uint32_t)__ldg(entry) : 0u;
+      const uint32_t id01 = far ? __ldg(reinterpret_cast<const uint32_t *>(list)) : 0u;
+      if (far) c = e16;
+      // "scan every centroid" points (outside both indexes, NaN/inf, a cell with more candidates than a list holds):
+      // one at a time with the whole warp on it -- lane l scans centroids l, l + 32, ... in ascending order, the
+      // lexicographic (distance, index) minimum over the lanes is the scan's winner.  Left to its own lane such a
+      // point kept the other 31 waiting for k distance evaluations.
+      bool scan_all = far && e16 >= kCellMulti && id01 == 0xFFFFFFFFu;
+      uint32_t todo = __ballot_sync(0xFFFFFFFFu, scan_all);
+      if (__popc(todo) > 10) {  // many of them: k evaluations on every lane at once cost less than 32 cooperative rounds
+        todo = 0u;
+        scan_all = false;
+      }
+      for (; todo; todo &= todo - 1) {
+        const int src = __ffs(todo) - 1;
+        const float px = __shfl_sync(0xFFFFFFFFu, v.x, src), py = __shfl_sync(0xFFFFFFFFu, v.y, src);
+        float best = INFINITY;
+        int arg = 0x7FFFFFFF;
+        for (int cc = lane; cc < k; cc += 32) {
+          const float dd = dist2(px, py, cent_s[cc]);
+          if (dd < best) { best = dd; arg = cc; }
+        }
 #pragma unroll
-      for (int o = 16; o > 0; o >>= 1) {
-        const float ob = __shfl_xor_sync(0xFFFFFFFFu, best, o);
-        const int oa = __shfl_xor_sync(0xFFFFFFFFu, arg, o);
-        if (ob < best || (ob == best && oa < arg)) { best = ob; arg = oa; }
+        for (int o = 16; o > 0; o >>= 1) {
+          const float ob = __shfl_xor_sync(0xFFFFFFFFu, best, o);
+          const int oa = __shfl_xor_sync(0xFFFFFFFFu, arg, o);
+          if (ob < best || (ob == best && oa < arg)) { best = ob; arg = oa; }
+        }
+        if (lane == src) c = best < INFINITY ? (uint32_t)arg : 0u;  // nothing beat +inf: the scan keeps index 0
       }
-      if (lane == src) c = best < INFINITY ? (uint32_t)arg : 0u;  // nothing beat +inf: the scan keeps index 0
+      if (far) {
+        if (e16 >= kCellMulti && !scan_all) c = (uint32_t)resolve_cand(v.x, v.y, id01, list, cent_s, k);
+        fits = fabsf(v.x) < fx.limx && fabsf(v.y) < fx.limy && !tiny(v.x, fx.tinyx) && !tiny(v.y, fx.tinyy);
+      }
     }
     if (live) {
-      if (e16 >= kCellMulti && !scan_all) c = (uint32_t)resolve_cand(v.x, v.y, id01, list, cent_s, k);
       if (kAssign) assign[base + qindex[first + lane]] = (int)c;
-      const bool fits = fabsf(v.x) < fx.limx && fabsf(v.y) < fx.limy && !tiny(v.x, fx.tinyx) && !tiny(v.y, fx.tinyy);
       full = fx_add_point<kLanes>(fits ? 1u : 0u, acc_lane, fx, v.x, v.y, fits ? c : (uint32_t)k);
       if (!fits) {  // shared FP64 / 64-bit atomics are CAS loops: the rare path only
         atomicAdd(&late_sum[2 * HGM_BOUND(c, k)], (double)v.x);
@@ -330,12 +359,21 @@ __global__ void __launch_bounds__(S::kThreads, 1)
 
       uint32_t seen = 0u;  // OR of the counts found: any bit at or above kFlushAt = a word is at the threshold
       if (live == kTile)
-        fx_work_tile<S, kAssign, true>(table_s, g, fx, acc_lane, (uint32_t)k, queue, qindex, assign, base, live, lane, lt_mask, xs, ys, qn, seen);
+        fx_work_tile<S, kAssign, true, 0>(table_s, g, fx, acc_lane, (uint32_t)k, queue, qindex, assign, base, live, lane, lt_mask, xs, ys, qn, seen);
       else
-        fx_work_tile<S, kAssign, false>(table_s, g, fx, acc_lane, (uint32_t)k, queue, qindex, assign, base, live, lane, lt_mask, xs, ys, qn, seen);
+        fx_work_tile<S, kAssign, false, 0>(table_s, g, fx, acc_lane, (uint32_t)k, queue, qindex, assign, base, live, lane, lt_mask, xs, ys, qn, seen);
       __syncwarp();
-      // whole batches of 32 only (the rest waits for company), unless the points' tile-relative
-      // indices are needed for the assignment output
+      while (qn >= 32) {  // whole batches of 32 only: the rest waits for company
+        qn -= 32;
+        seen |= settle(qn, 32, base);
+        __syncwarp();
+      }
+      if (live == kTile)
+        fx_work_tile<S, kAssign, true, kPPT / 2>(table_s, g, fx, acc_lane, (uint32_t)k, queue, qindex, assign, base, live, lane, lt_mask, xs, ys, qn, seen);
+      else
+        fx_work_tile<S, kAssign, false, kPPT / 2>(table_s, g, fx, acc_lane, (uint32_t)k, queue, qindex, assign, base, live, lane, lt_mask, xs, ys, qn, seen);
+      __syncwarp();
+      // ... unless the points' tile-relative indices are needed for the assignment output
       while (kAssign ? qn > 0 : qn >= 32) {
         const int take = min(qn, 32);
         qn -= take;
@@ -429,9 +467,10 @@ cudaError_t launch_fx(const float *d_pts, int64_t n, const float *d_cent, int k,
 }  // namespace
 
 // Largest table the fixed-point form can keep beside its accumulators (0 = this k does not fit it).
-int grid2d_fx_table_size(int k, size_t smem_optin) {
+int grid2d_fx_table_size(int k, size_t smem_optin, size_t table_cap) {
   if (k > kTable8MaxK) return 0;
-  for (int G = 256; G >= 128; G -= 32) {
+  for (int G = 240; G >= 96; G -= 8) {
+    if (table_cap && grid2d_table_bytes(G) > table_cap) continue;  // a caller with a fixed-size table buffer
     const size_t need = k <= 128 ? fx_smem<FxWide>(G, k, true) : fx_smem<FxNarrow>(G, k, true);
     if (need <= smem_optin) return G;
   }
