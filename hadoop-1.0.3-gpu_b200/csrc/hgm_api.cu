@@ -402,7 +402,7 @@ bool plan_grid2d_for(const float *cent, int k, size_t smem_optin, Grid2D *out, s
 
 extern "C" {
 
-int hgm_version(void) { return 1000; }
+int hgm_version(void) { return 1001; }  // 1.1: + peer exchange, grid2d form / tensor form, phases, staged bytes
 
 int hgm_device_count(int *count) {
   if (!count) return fail(nullptr, HGM_EINVAL, "count is NULL");

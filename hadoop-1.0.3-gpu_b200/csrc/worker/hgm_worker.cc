@@ -63,6 +63,7 @@ struct Worker {
   std::map<std::string, Cached> cache_ids;  // key: path|offset|length|format|mtime|size
   int64_t next_id = 0;
   uint64_t tick = 0;
+  uint64_t request_tick = 0;  // value of `tick` when the current request began: entries used since are in use by it
   std::string epoch;  // the data set the cached splits belong to (kDropCache)
   std::string stat_error;
   size_t max_batch = size_t(1024) << 20;
@@ -188,10 +189,12 @@ struct Worker {
     int put = hgm_cache_put_file(gpu, id, path.c_str(), off, len, fmt);
     // HBM is full: make room, least recently used first (arena blocks are returned to the driver as they
     // empty, so a few drops may be needed before a block frees up)
-    while (put == HGM_ENOMEM && !cache_ids.empty()) {
-      auto lru = cache_ids.begin();
+    while (put == HGM_ENOMEM) {
+      // never a split the request being served has already been promised (MAP_FILES maps them all at its end)
+      auto lru = cache_ids.end();
       for (auto v = cache_ids.begin(); v != cache_ids.end(); ++v)
-        if (v->second.last_use < lru->second.last_use) lru = v;
+        if (v->second.last_use <= request_tick && (lru == cache_ids.end() || v->second.last_use < lru->second.last_use)) lru = v;
+      if (lru == cache_ids.end()) break;  // everything left belongs to this request: stream the split instead
       hgm_cache_drop(gpu, lru->second.id);
       cache_ids.erase(lru);
       stats.cache_evictions += 1;
@@ -206,6 +209,7 @@ struct Worker {
   }
 
   bool handle_map_file(int fd, const std::vector<char> &p) {
+    request_tick = tick;
     if (p.size() < 24) return reply_error(fd, hgmw::kMapFile, HGM_EINVAL, "short MAP_FILE");
     int32_t fmt, use_cache;
     int64_t off, len;
@@ -244,6 +248,7 @@ struct Worker {
   // partials and read once; a per-split round trip (request, launch, synchronise, 3 KB reply: ~70 us) was most of a
   // batched task's time once its splits were resident.
   bool handle_map_files(int fd, const std::vector<char> &p) {
+    request_tick = tick;
     if (p.size() < 12) return reply_error(fd, hgmw::kMapFiles, HGM_EINVAL, "short MAP_FILES");
     int32_t fmt, use_cache, count;
     memcpy(&fmt, p.data(), 4);

@@ -76,7 +76,7 @@ typedef struct hgm_ctx hgm_ctx;
 
 /* ---- library / device ------------------------------------------------------------- */
 
-/* ABI version of this header (major*1000 + minor). */
+/* ABI version of this header (major*1000 + minor); 1001 = 1.1: entry points added since 1.0, none changed. */
 int hgm_version(void);
 
 /* Number of CUDA devices visible; the TaskTracker sizes
