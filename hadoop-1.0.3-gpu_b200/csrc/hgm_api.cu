@@ -1498,17 +1498,45 @@ int hgm_cache_map(hgm_ctx *c, int64_t split_id, int32_t *d_assign, int64_t *n_po
   return hgm_map_device(c, static_cast<const float *>(it->second.d_rows), it->second.n_points, d_assign);
 }
 
+// map the given cached splits; those that sit back to back in an arena block go out as one launch
+static int map_cached(hgm_ctx *c, std::vector<const hgm_ctx::CachedSplit *> &order, int64_t *n_points_out,
+                      int32_t *n_launch_groups_out);
+
 int hgm_cache_map_all(hgm_ctx *c, int64_t *n_points_out, int32_t *n_launch_groups_out) {
   NEED_CTX(c);
   if (!c->d_partials) return fail(c, HGM_EINVAL, "hgm_set_centroids has not been called");
   std::vector<const hgm_ctx::CachedSplit *> order;
   order.reserve(c->cache.size());
   for (auto &kv : c->cache) order.push_back(&kv.second);
+  return map_cached(c, order, n_points_out, n_launch_groups_out);
+}
+
+int hgm_cache_map_many(hgm_ctx *c, const int64_t *split_ids, int32_t n_ids, int64_t *n_points_out,
+                       int32_t *n_launch_groups_out) {
+  NEED_CTX(c);
+  if (!c->d_partials) return fail(c, HGM_EINVAL, "hgm_set_centroids has not been called");
+  if (n_ids < 0 || (n_ids > 0 && !split_ids)) return fail(c, HGM_EINVAL, "bad split id list");
+  std::vector<const hgm_ctx::CachedSplit *> order;
+  order.reserve((size_t)n_ids);
+  for (int32_t i = 0; i < n_ids; ++i) {
+    auto it = c->cache.find(split_ids[i]);
+    if (it == c->cache.end()) return fail(c, HGM_EINVAL, "split %lld is not in the cache", (long long)split_ids[i]);
+    order.push_back(&it->second);
+  }
+  return map_cached(c, order, n_points_out, n_launch_groups_out);
+}
+
+static int map_cached(hgm_ctx *c, std::vector<const hgm_ctx::CachedSplit *> &order, int64_t *n_points_out,
+                      int32_t *n_launch_groups_out) {
   std::sort(order.begin(), order.end(),
             [](const hgm_ctx::CachedSplit *a, const hgm_ctx::CachedSplit *b) { return a->d_rows < b->d_rows; });
   int64_t total = 0;
   int32_t groups = 0;
   size_t i = 0;
+  // one timed region over all the launches (hgm_last_map_ms)
+  c->last_launches = 0;
+  if (c->d_tflags) cudaMemsetAsync(c->d_tflags + 2, 0, 8, c->stream);
+  CU(c, cudaEventRecord(c->ev_t0, c->stream));
   while (i < order.size()) {  // splits that sit back to back in an arena block go out as one launch
     const unsigned char *begin = static_cast<const unsigned char *>(order[i]->d_rows);
     const unsigned char *end = begin + order[i]->nbytes;
@@ -1520,13 +1548,15 @@ int hgm_cache_map_all(hgm_ctx *c, int64_t *n_points_out, int32_t *n_launch_group
       ++j;
     }
     if (n > 0) {
-      const int rc = hgm_map_device(c, reinterpret_cast<const float *>(begin), n, nullptr);
+      const int rc = map_points_async(c, reinterpret_cast<const float *>(begin), n, nullptr);
       if (rc != HGM_OK) return rc;
       ++groups;
     }
     total += n;
     i = j;
   }
+  CU(c, cudaEventRecord(c->ev_t1, c->stream));
+  c->timing_open = true;
   if (n_points_out) *n_points_out = total;
   if (n_launch_groups_out) *n_launch_groups_out = groups;
   return HGM_OK;

@@ -292,11 +292,10 @@ struct Worker {
     }
     if (!resident.empty()) {
       int rc = hgm_reset_partials(gpu);
-      for (size_t i = 0; rc == HGM_OK && i < resident.size(); ++i) {
-        int64_t n = 0;
-        rc = hgm_cache_map(gpu, resident[i], nullptr, &n);  // queued on the stream; adds into the device partials
-        n_total += n;
-      }
+      int64_t n = 0;
+      // neighbours in the cache's arena (splits staged one after the other, as a task's splits are) share a launch
+      if (rc == HGM_OK) rc = hgm_cache_map_many(gpu, resident.data(), (int32_t)resident.size(), &n, nullptr);
+      n_total += n;
       if (rc == HGM_OK) rc = hgm_read_partials(gpu, part.data(), part_counts.data());
       if (rc != HGM_OK) return reply_gpu_error(fd, hgmw::kMapFiles, rc);
       for (size_t j = 0; j < sums.size(); ++j) sums[j] += part[j];

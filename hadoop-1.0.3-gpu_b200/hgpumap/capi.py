@@ -49,6 +49,7 @@ SIGNATURES = {
     "hgm_set_kernel": (C.c_int, [_c_ctx, C.c_int32]),
     "hgm_last_kernel": (C.c_int, [_c_ctx, C.POINTER(C.c_int32)]),
     "hgm_last_tensor_phases": (C.c_int, [_c_ctx, C.POINTER(C.c_float)]),
+    "hgm_cache_map_many": (C.c_int, [_c_ctx, C.POINTER(C.c_int64), C.c_int32, C.POINTER(C.c_int64), C.POINTER(C.c_int32)]),
     "hgm_staged_bytes": (C.c_int, [_c_ctx, C.POINTER(C.c_int64)]),
     "hgm_set_tensor_form": (C.c_int, [C.c_int32]),
     "hgm_peer_handle": (C.c_int, [_c_ctx, C.c_int32, C.c_void_p]),
@@ -239,6 +240,13 @@ class GpuMapSlot:
         """Map every cached split; returns (points, launch groups)."""
         n, g = C.c_int64(), C.c_int32()
         self._check(self._lib.hgm_cache_map_all(self._ctx, C.byref(n), C.byref(g)))
+        return n.value, g.value
+
+    def cache_map_many(self, split_ids) -> tuple[int, int]:
+        """Map the listed cached splits (neighbours in the arena share a launch); returns (points, launch groups)."""
+        ids = (C.c_int64 * max(len(split_ids), 1))(*split_ids)
+        n, g = C.c_int64(), C.c_int32()
+        self._check(self._lib.hgm_cache_map_many(self._ctx, ids, len(split_ids), C.byref(n), C.byref(g)))
         return n.value, g.value
 
     def cache_read(self, split_id: int) -> np.ndarray:

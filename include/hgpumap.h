@@ -176,6 +176,8 @@ int hgm_partials_device(hgm_ctx *ctx, double **d_sums, int64_t **d_counts);
  *   hgm_cache_map_all   map every cached split; splits that lie back to back in the cache's
  *                       arena (2 GiB blocks, filled in put order) share one launch, so an
  *                       iteration over a resident input costs a handful of launches
+ *   hgm_cache_map_many  the same for a list of split ids (a task that names several splits); an id that is
+ *                       listed twice is mapped twice
  *   hgm_cache_drop      forget one split, or all of them with split_id < 0 (an arena block
  *                       goes back to the driver when its last split is dropped)
  *   hgm_cache_info      number of cached splits and their bytes
@@ -187,6 +189,8 @@ int hgm_cache_put_file(hgm_ctx *ctx, int64_t split_id, const char *path, int64_t
                        int32_t fmt);
 int hgm_cache_map(hgm_ctx *ctx, int64_t split_id, int32_t *d_assign_or_null, int64_t *n_points_out);
 int hgm_cache_map_all(hgm_ctx *ctx, int64_t *n_points_out, int32_t *n_launch_groups_out);
+int hgm_cache_map_many(hgm_ctx *ctx, const int64_t *split_ids, int32_t n_ids, int64_t *n_points_out,
+                       int32_t *n_launch_groups_out);
 int hgm_cache_drop(hgm_ctx *ctx, int64_t split_id);
 int hgm_cache_info(hgm_ctx *ctx, int64_t *n_splits, int64_t *bytes);
 int hgm_cache_read(hgm_ctx *ctx, int64_t split_id, float *rows_out, int64_t cap_floats, int64_t *n_floats_out);

@@ -4,6 +4,8 @@ child driven through the protocol (command-file replay), placed on CPU and GPU m
 own hybrid rule (JobQueueTaskScheduler.assignTasks restated in libhgsched.so, `hgs_assign`), one call
 per "heartbeat" = per task completion.  What the Java side would do and cannot do here (no JVM):
 
+  every slot   one long-lived process (the per-slot child JVM of a TaskTracker with JVM reuse) that builds each task's
+               downlink, starts its Pipes child and hands the partial records back
   GPU slot i   `kmeans-pipes-gpu <i>` child per task, C++ record reader route (FileSplit), talking to the
                slot's persistent worker (`hgm-worker`), file splits kept in its HBM cache
   CPU slot     the CPU K-means Pipes program (oracle/_ref/kmeans-pipes-cpu-hgmrt: the reference's
@@ -78,21 +80,6 @@ class Task:
         return up, wall
 
 
-def reap(running):
-    """Block until at least one child of `running` (pid -> ...) has exited; returns the pids that have."""
-    done = []
-    while not done:
-        for pid, (task, *_rest) in running.items():
-            if task.proc.poll() is not None:
-                done.append(pid)
-        if not done:
-            try:
-                os.waitid(os.P_ALL, 0, os.WEXITED | os.WNOWAIT)  # sleep until some child changes state
-            except ChildProcessError:
-                time.sleep(0.0002)
-    return done
-
-
 def gpu_downlink(paths, cpath, k, d, sock, epoch):
     """One GPU map task over the splits `paths` (whole files): a FileSplit through the C++ reader for one split,
     path records (piped Text values, NLineInputFormat) for a batch."""
@@ -119,6 +106,29 @@ def cpu_downlink(path, cpath, k, d):
     return dl.close()
 
 
+def slot_process(conn, tmp, k, d):
+    """The long-lived process of one map slot -- the child JVM a TaskTracker keeps per slot when JVM reuse is on
+    (mapred.job.reuse.jvm.num.tasks = -1).  For every task it is handed it does what PipesGPUMapRunner / PipesMapRunner
+    does: build the downlink, start the Pipes child, collect its uplink; the partial records go back to the job as
+    arrays.  The slots work side by side, as the JVMs of a TaskTracker do."""
+    while True:
+        job = conn.recv()
+        if job is None:
+            return
+        kind, dev, paths, cpath, sock, epoch = job
+        try:
+            if kind == "gpu":
+                task = Task(GPU_BIN, gpu_downlink(paths, cpath, k, d, sock, epoch), (str(dev),), tmp)
+            else:
+                task = Task(CPU_BIN, cpu_downlink(paths[0], cpath, k, d), (), tmp)
+            task.proc.wait()
+            up, wall = task.finish()
+            counts, sums = wire.kmeans_partials([(key, v) for _, key, v in up.partitioned], k, d)
+            conn.send((counts, sums, wall, up.counter("KMEANS", "GPU_CACHE_HITS") if kind == "gpu" else 0, None))
+        except Exception as exc:  # noqa: BLE001 -- reported to the job, which fails
+            conn.send((None, None, 0.0, 0, repr(exc)))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--splits", type=int, default=24)
@@ -142,6 +152,19 @@ def main():
     k, d = args.k, 2
     tmp = args.data_dir or os.path.join(ROOT, "gpurun_out", "job_tmp")
     os.makedirs(tmp, exist_ok=True)
+    # one long-lived process per map slot, forked before this process touches CUDA
+    import multiprocessing as mp
+    from multiprocessing.connection import wait as wait_ready
+
+    slot_conns = {}
+    slot_procs = []
+    for name in [("gpu", g) for g in range(args.gpu_slots)] + [("cpu", i) for i in range(args.cpu_slots)]:
+        here, there = mp.Pipe()
+        proc = mp.Process(target=slot_process, args=(there, tmp, k, d), daemon=True)
+        proc.start()
+        slot_conns[name] = here
+        slot_procs.append(proc)
+    free_cpu = list(range(args.cpu_slots))
     centres = synth.centres(synth.SEED_POINTS, k, d)
     cent = synth.perturb(synth.SEED_CENTROIDS, centres)
     pts_per_split = args.split_mib * (1 << 20) // (4 * d)
@@ -200,7 +223,7 @@ def main():
             cpath = os.path.join(tmp, f"centroids-{it}.bin")
             cent.astype("<f4").tofile(cpath)
             pending = list(range(args.splits))
-            running = {}  # pid -> (task, kind, device, splits of the task)
+            running = {}  # slot connection -> (kind, device or cpu slot, splits of the task)
             cpu_times, gpu_times = [], []
             sums = np.zeros((k, d))
             counts = np.zeros(k, np.int64)
@@ -225,29 +248,33 @@ def main():
                     batch = [pick(dev, pending) for _ in range(min(args.batch, len(pending)))]
                     for s_ in batch:
                         cached_on[s_] = dev
-                    dl = gpu_downlink([files[s_] for s_ in batch], cpath, k, d, socks[dev], epoch)
-                    task = Task(GPU_BIN, dl, (str(dev),), tmp)
-                    running[task.proc.pid] = (task, "gpu", dev, batch)
+                    conn = slot_conns[("gpu", dev)]
+                    conn.send(("gpu", dev, [files[s_] for s_ in batch], cpath, socks[dev], epoch))
+                    running[conn] = ("gpu", dev, batch)
                 for _ in range(dec.n_cpu):
                     if not pending:
                         break
                     assert slots.acquire(False, timeout_ms=0)
                     s_ = pending.pop(0)
-                    task = Task(CPU_BIN, cpu_downlink(files[s_], cpath, k, d), (), tmp)
-                    running[task.proc.pid] = (task, "cpu", -1, [s_])
+                    cpu_slot = free_cpu.pop()
+                    conn = slot_conns[("cpu", cpu_slot)]
+                    conn.send(("cpu", -1, [files[s_]], cpath, "", epoch))
+                    running[conn] = ("cpu", cpu_slot, [s_])
                 if not running:
                     raise RuntimeError("the scheduler assigned nothing although slots are free and maps are pending")
-                for pid in reap(running):
-                    task, kind, dev, batch = running.pop(pid)
-                    slots.release_task(kind == "gpu", slot_taken=True, device=dev)  # TaskInProgress.releaseSlot
+                for conn in wait_ready(list(running)):
+                    kind, dev, batch = running.pop(conn)
+                    c, sm, wall, task_hits, error = conn.recv()
+                    if error:
+                        raise RuntimeError(error)
+                    slots.release_task(kind == "gpu", slot_taken=True, device=dev if kind == "gpu" else -1)  # releaseSlot
+                    if kind == "cpu":
+                        free_cpu.append(dev)
                     finished_tasks += 1
-                    up, wall = task.finish()
                     (cpu_times if kind == "cpu" else gpu_times).append(wall * 1e3)
-                    c, sm = wire.kmeans_partials([(key, v) for _, key, v in up.partitioned], k, d)
                     counts += c
                     sums += sm
-                    if kind == "gpu":
-                        hits += up.counter("KMEANS", "GPU_CACHE_HITS")
+                    hits += task_hits
             assert counts.sum() == n_points, (counts.sum(), n_points)
             dt = time.perf_counter() - t_it
             if cpu_times and gpu_times:
@@ -262,8 +289,15 @@ def main():
             report["iterations"].append(rec)
             print(json.dumps(rec))
     finally:
-        for task, *_ in list(locals().get("running", {}).values()):
-            task.proc.kill()
+        for conn in slot_conns.values():
+            try:
+                conn.send(None)
+            except (BrokenPipeError, OSError):
+                pass
+        for proc in slot_procs:
+            proc.join(timeout=5)
+            if proc.is_alive():
+                proc.terminate()
         for w in workers:
             w.terminate()
         for path in files:

@@ -53,6 +53,19 @@ def test_map_all_merges_neighbours_into_one_launch(oracle):
         sums, counts = slot.read_partials()
         o = oracle.map_combine(pts, cent)
         check_partials(sums, counts, o[0], o[1], o[2])
+        # a task's list of splits: neighbours share a launch, a gap starts a new one, a repeated id is mapped twice
+        slot.reset_partials()
+        assert slot.cache_map_many([14, 10, 11, 13]) == (4 * 40000, 2)
+        sums, counts = slot.read_partials()
+        o = oracle.map_combine(np.concatenate([parts[i] for i in (0, 1, 3, 4)]), cent)
+        check_partials(sums, counts, o[0], o[1], o[2])
+        ms, launches = slot.last_map_ms()
+        assert ms > 0 and launches == 2  # one timed region over both launches
+        slot.reset_partials()
+        assert slot.cache_map_many([12, 12]) == (2 * 40000, 2)
+        assert slot.read_partials()[1].sum() == 2 * 40000
+        with pytest.raises(capi.HgmError):
+            slot.cache_map_many([10, 77])
         slot.cache_drop(12)  # a hole: two runs now
         slot.reset_partials()
         n, groups = slot.cache_map_all()
