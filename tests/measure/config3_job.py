@@ -216,6 +216,21 @@ def main():
             return pending.pop(sched.pick_split([cached_on.get(s, -1) for s in pending], dev, args.gpu_slots))
         return pending.pop(0)
 
+    def pick_batch(dev, pending, want):
+        """`want` splits for GPU slot `dev`.  Rule (1) of hgs_pick_split -- a split this device holds, lowest index first --
+        applied in one pass while it lasts (the rule is applied per split by the library; asking it 38 times over 298
+        pending splits from Python cost more than the tasks it was scheduling); the library decides the rest."""
+        batch = []
+        if args.affinity:
+            mine = [s_ for s_ in pending if cached_on.get(s_, -1) == dev][:want]
+            if mine:
+                taken = set(mine)
+                pending[:] = [s_ for s_ in pending if s_ not in taken]
+                batch = mine
+        while len(batch) < want and pending:
+            batch.append(pick(dev, pending))
+        return batch
+
     slots = sched.Slots(args.cpu_slots, args.gpu_slots)
     t_job = time.perf_counter()
     try:
@@ -245,7 +260,7 @@ def main():
                         break
                     dev = dec.gpu_device[i]
                     assert slots.acquire(True, device=dev, timeout_ms=0)  # the launcher: the rule only hands out free slots
-                    batch = [pick(dev, pending) for _ in range(min(args.batch, len(pending)))]
+                    batch = pick_batch(dev, pending, min(args.batch, len(pending)))
                     for s_ in batch:
                         cached_on[s_] = dev
                     conn = slot_conns[("gpu", dev)]
