@@ -55,7 +55,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--kernel", type=int, default=0, help="force a kernel family (hgpumap.h HGM_KERNEL_*)")
-    ap.add_argument("--tensor-form", choices=["auto", "single", "pair"], default="auto")
+    ap.add_argument("--tensor-form", choices=["auto", "single", "pair", "pair_fused", "pair_segmented"], default="auto")
     ap.add_argument("--no-extra", action="store_true", help="skip the `extra` lines (other inputs, configs 4 and 5)")
     return ap.parse_args()
 
@@ -448,6 +448,8 @@ def run_extras(args, torch, dist, slot, stream, dev, rank, world, points, centre
         slot.set_centroids(cent)
         slot.synth_points_device(synth.SEED_POINTS, rank * m, m, cen, buf.data_ptr())
         entry = None
+        fused = (args.tensor_form == "pair_fused" or  # launch_tensor_map's rule
+                 (args.tensor_form in ("auto", "pair") and d > 32 and kk >= (1024 if d <= 64 else 2048)))
         for dup in (0, max(1, kk // 1000), kk // 100, kk // 10):  # duplicated centroids: their clusters' points are ties
             c2 = cent.copy()
             if dup:
@@ -463,8 +465,9 @@ def run_extras(args, torch, dist, slot, stream, dev, rank, world, points, centre
                 entry = {"workload": f"BASELINE configs[{3 if d == 64 else 4}] shape: d={d}, k={kk}, {m:,} points per GPU",
                          "points_per_gpu": m, "d": d, "k": kk, "value": world * m / (ms * 1e-3), "unit": UNIT,
                          "ms_per_step": ms, "kernel": "tensor_assign_pair_kernel" if d > 32 else "tensor_assign_kernel",
+                         "sums": "inside K2 (decided rows leave as FP64 reductions from shared memory)" if fused else "K4 segmented second pass",
                          "kernel_ms": {"map_call": kms, "K2_scores_tcgen05": phases[0], "K3_exact_recheck": phases[1],
-                                       "K4_segmented_sums": phases[2]},
+                                       "K4_counts_and_rechecked_rows" if fused else "K4_segmented_sums": phases[2]},
                          "rechecked_points": flagged, "achieved_tflops": tf,
                          "roofline_frac_tf32_measured_in_run": tf / tf32, "tf32_tflops_cublas_in_run": tf32,
                          "roofline_frac_bf16_sustained": tf / bf16 if bf16 else None, "bf16_tflops_sustained": bf16,
@@ -473,6 +476,15 @@ def run_extras(args, torch, dist, slot, stream, dev, rank, world, points, centre
                 entry["recheck_sensitivity"].append(
                     {"duplicated_centroids": dup, "rechecked_points": flagged, "rechecked_frac": flagged / m,
                      "value": world * m / (ms * 1e-3), "K3_exact_recheck_ms": phases[1], "map_call_ms": kms})
+        if fused and args.tensor_form == "auto":  # the same call with the sums made by K4's second pass over the rows
+            slot.set_centroids(cent)
+            slot.set_tensor_form(capi.TENSOR_FORM_PAIR_SEGMENTED)
+            ms, kms = timed_steps(torch, dist, slot, stream, buf.data_ptr(), m, max(3, steps // 2), world)
+            phases = slot.last_tensor_phases()
+            slot.set_tensor_form(capi.TENSOR_FORM_AUTO)
+            entry["same_call_with_K4_second_pass"] = {
+                "value": world * m / (ms * 1e-3), "map_call_ms": kms, "K2_scores_tcgen05": phases[0],
+                "K3_exact_recheck": phases[1], "K4_segmented_sums": phases[2]}
         extra.append(entry)
         del buf
     return extra
@@ -511,7 +523,8 @@ def run_ours(args):
     if args.kernel:
         slot.set_kernel(args.kernel)
     slot.set_tensor_form({"auto": capi.TENSOR_FORM_AUTO, "single": capi.TENSOR_FORM_SINGLE,
-                          "pair": capi.TENSOR_FORM_PAIR}[args.tensor_form])
+                          "pair": capi.TENSOR_FORM_PAIR, "pair_fused": capi.TENSOR_FORM_PAIR_FUSED,
+                          "pair_segmented": capi.TENSOR_FORM_PAIR_SEGMENTED}[args.tensor_form])
     slot.set_centroids(centroids)
     points = torch.empty(n * d, dtype=torch.float32, device=dev)  # device memory: plumbing only
     slot.synth_points_device(synth.SEED_POINTS, rank * n, n, centres, points.data_ptr())

@@ -319,13 +319,13 @@ int map_piece_async(hgm_ctx *c, int kern, const float *d_pts, int64_t n, int32_t
       return fail(c, HGM_EINVAL, "the tensor path needs 16-byte aligned points");
     e = launch_tensor_map(d_pts, n, c->d, c->d_cent, c->k, c->d_caug, c->d_tflags, d_assign ? d_assign : c->d_tassign,
                           c->d_tlist, c->d_tflags + 1, c->d_tmeta, c->d_torder, sums_ptr(c), counts_ptr(c), c->sm_count,
-                          c->smem_optin, c->stream, c->ev_phase);
+                          c->smem_optin, c->stream, c->ev_phase, &launches);
     c->phases_open = e == cudaSuccess;
     if (e == cudaSuccess) {
       add_rechecks_kernel<<<1, 1, 0, c->stream>>>(c->d_tflags);
       e = cudaGetLastError();
     }
-    launches = 8;
+    launches += 1;  // add_rechecks_kernel
   } else if (kern == HGM_KERNEL_GRID2D || kern == HGM_KERNEL_GRID2D_SORT) {
     const Grid2DOuter outer{c->outer_grid, c->d_otable, c->d_ocand};
     e = launch_grid2d_map(d_pts, n, c->d_cent, c->k, c->grid, c->d_table, c->d_cand, sums_ptr(c),
@@ -566,7 +566,7 @@ int hgm_checked_failures(int32_t *count, int32_t *first_line) {
 }
 
 int hgm_set_tensor_form(int32_t form) {
-  if (form < HGM_TENSOR_FORM_AUTO || form > HGM_TENSOR_FORM_PAIR) return fail(nullptr, HGM_EINVAL, "unknown tensor form %d", form);
+  if (form < HGM_TENSOR_FORM_AUTO || form > HGM_TENSOR_FORM_PAIR_SEGMENTED) return fail(nullptr, HGM_EINVAL, "unknown tensor form %d", form);
   tensor_set_form(form);
   return HGM_OK;
 }

@@ -91,7 +91,7 @@ cudaError_t launch_tensor_map(const float *d_pts, int64_t n, int d, const float 
                               const unsigned int *d_cmax_bits, int32_t *d_assign, int32_t *d_flag_list,
                               unsigned int *d_flag_count, unsigned int *d_meta, int32_t *d_order, double *d_sums,
                               unsigned long long *d_counts, int sm_count, size_t smem_optin, cudaStream_t s,
-                              cudaEvent_t *phase /* 4 events or NULL */);
+                              cudaEvent_t *phase /* 4 events or NULL */, int *launches /* kernels launched, or NULL */);
 
 // text decode (kernels_text.cu)
 struct TextStats {

@@ -19,6 +19,10 @@
 //       FP64 RED per coordinate per 1024 points).  Adding every point with d REDs from K2's
 //       epilogue -- the first version -- was bound by the SM's RED issue rate (~41 cycles per
 //       warp instruction) and stalled the MMA pipeline behind the epilogue warps.
+//       Where a tile is scored for longer than that takes (k >= 1024, or 2048 for d > 64: configs 4
+//       and 5) the pair form's DECIDER warps -- off the scan's critical path -- now do add the
+//       decided rows themselves, a warp per row from shared memory, so the rows are not read from HBM
+//       a second time (PairRowAdder below); K4 then only joins the counts and adds K3's rows.
 //
 // Rounding bound: the score of (x, c) is off by at most 2^-8 |x| |c| (x truncated to TF32 by
 // the tensor core: 2^-10; c rounded to TF32 here: 2^-11; doubled by the factor 2) plus FP32
@@ -223,6 +227,8 @@ struct TensorArgs {
   int32_t *assign;              // [n] best index per point
   int32_t *flag_list;           // indices of points that need the exact re-check
   unsigned int *flag_count;
+  double *sums;                 // pair form: non-null = the deciders add the decided rows to sums[k][d] themselves (no K4 pass)
+  int abufs;                    // pair form: point-tile buffers per CTA, 2 or 3 (3: the deciders may keep a tile's rows a whole tile longer)
 };
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -540,6 +546,158 @@ struct Trace {
   }
 };
 
+// The deciders' second job when the sums are fused into this kernel (TensorArgs::sums): the decided rows of a
+// warp's 64 leave as FP64 reductions into sums[cluster][d] while they still sit in shared memory, instead of being
+// read from HBM a second time by K4.  A warp per row: lane l owns coordinates l, l + 32, ... so that one warp
+// instruction covers 256 contiguous bytes; 148 SMs push ~500 G such adds per second into an L2-resident table
+// (tools/microbench/red_f64_rate.cu), 5 ms for config 4's shard, all of it under the score pipeline.  What does not
+// scale is one LINE: it takes a reduction every ~16 ns, so a cluster that holds more than ~2 % of the points would
+// pace the kernel if every row went out on its own.  Rows of one cluster are therefore added up in registers first:
+// key = the row's cluster (bit 31 set = not decided here: K3's, or past the end), match.any groups equal keys within
+// each half of 32 rows, a group's lowest lane leads it; a cluster met in both halves is merged when it has more than
+// one row in the first.  `rows` = this tile's [kblocks][128 rows][128 B, swizzled] in shared memory, row0 = first of
+// the warp's rows.
+__device__ __forceinline__ float lds_f32(uint32_t addr) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(addr));
+  return v;
+}
+template <int KB, bool kFull>  // K-blocks of 32 coordinates per row; kFull: d fills the last one (d == 32 KB)
+struct PairRowAdder {
+  uint32_t rows;     // shared-memory address of the tile's rows + this lane's 4 bytes inside a 16-byte chunk
+  uint32_t chunk16;  // (lane / 4) * 16: this lane's chunk of an unswizzled row
+  char *out_lane;    // &sums[0][lane]
+  uint32_t row_bytes;  // d * 8
+  bool last_on;      // this lane's coordinate of the last K-block exists
+  __device__ __forceinline__ void flush(uint32_t cl, const double (&acc)[KB]) const {
+    double *out = reinterpret_cast<double *>(out_lane + (uint64_t)cl * row_bytes);  // one IMAD.WIDE
+#pragma unroll
+    for (int i = 0; i < KB - 1; ++i) atomicAdd(out + i * 32, acc[i]);  // result unused: RED.E.ADD.F64
+    if (kFull || last_on) atomicAdd(out + (KB - 1) * 32, acc[KB - 1]);
+  }
+  __device__ __forceinline__ void add(int r, double (&acc)[KB]) const {
+    const uint32_t p = rows + (uint32_t)r * 128u + (chunk16 ^ ((uint32_t)(r & 7) << 4));
+#pragma unroll
+    for (int i = 0; i < KB; ++i) acc[i] += (double)lds_f32(p + (uint32_t)i * kABytes);
+  }
+  struct Round {  // eight rows: their clusters and this lane's coordinates of them
+    uint32_t cl[8];
+    float v[8][KB];
+  };
+  // row0 is a multiple of 8, so the swizzle term of row 8 g + q is q, and a block of eight rows starts on a
+  // 1 KiB boundary: XOR-ing q into the chunk bits of the address is the swizzle
+  __device__ __forceinline__ void load(Round &r, uint32_t at, uint32_t key, int g) const {
+#pragma unroll
+    for (int q = 0; q < 8; ++q) {
+      r.cl[q] = __shfl_sync(0xFFFFFFFFu, key, 8 * g + q);
+      const uint32_t p = (at ^ ((uint32_t)q << 4)) + (uint32_t)q * 128u;
+#pragma unroll
+      for (int i = 0; i < KB; ++i) r.v[q][i] = lds_f32(p + (uint32_t)i * kABytes);
+    }
+  }
+  template <bool kAll>
+  __device__ __forceinline__ void send(const Round &r, uint32_t bits) const {
+#pragma unroll
+    for (int q = 0; q < 8; ++q)
+      if (kAll || ((bits >> q) & 1u)) {
+        double acc[KB];
+#pragma unroll
+        for (int i = 0; i < KB; ++i) acc[i] = (double)r.v[q][i];
+        flush(r.cl[q], acc);
+      }
+  }
+  // Rows that are alone in their half -- with many clusters, nearly all of them: eight per round in a fixed
+  // order, shuffles and loads for all eight whether they are in `set` or not, the next round's in flight while
+  // this round's reductions are issued, and no test per row when all eight go (the usual case).  The decider
+  // warps share their schedulers with the epilogue warps, which keep the ALU pipe busy: every instruction saved
+  // here is worth several cycles, to this warp and to them.
+  __device__ __forceinline__ void send_some(const Round &r, uint32_t bits) const {
+    if (bits == 0xFFu) send<true>(r, bits);
+    else if (bits) send<false>(r, bits);
+  }
+  __device__ __forceinline__ void solos(uint32_t set, uint32_t key, int row0) const {
+    const uint32_t at = rows + (uint32_t)row0 * 128u + chunk16;
+    if (KB <= 2) {  // two sets of registers taking turns
+      Round a, b;
+      load(a, at, key, 0);
+      load(b, at + 1024u, key, 1);
+      send_some(a, set & 0xFFu);
+      load(a, at + 2048u, key, 2);
+      send_some(b, (set >> 8) & 0xFFu);
+      load(b, at + 3072u, key, 3);
+      send_some(a, (set >> 16) & 0xFFu);
+      send_some(b, set >> 24);
+    } else {  // wider rows: one round at a time (registers); their tiles take long enough
+#pragma unroll 1
+      for (int g = 0; g < 4; ++g, set >>= 8) {
+        Round a;
+        load(a, at + 1024u * g, key, g);
+        send_some(a, set & 0xFFu);
+      }
+    }
+  }
+};
+
+template <int KB, bool kFull>
+__device__ __forceinline__ void pair_add_rows(const unsigned char *rows, int row0, const uint32_t (&key)[2], double *sums,
+                                              int d, int lane) {
+  const uint32_t full = 0xFFFFFFFFu;
+  const PairRowAdder<KB, kFull> t{smem_u32(rows) + ((uint32_t)lane & 3u) * 4u, ((uint32_t)lane >> 2) << 4,
+                                  reinterpret_cast<char *>(sums + lane), (uint32_t)d * 8u, (KB - 1) * 32 + lane < d};
+  const uint32_t mask0 = __match_any_sync(full, key[0]), mask1 = __match_any_sync(full, key[1]);
+  const uint32_t below = (1u << lane) - 1u;
+  const bool live0 = !(key[0] >> 31), live1 = !(key[1] >> 31);
+  const bool alone0 = (mask0 & (mask0 - 1)) == 0, alone1 = (mask1 & (mask1 - 1)) == 0;
+  uint32_t lead0 = __ballot_sync(full, live0 && !alone0 && !(mask0 & below));
+  uint32_t lead1 = __ballot_sync(full, live1 && !alone1 && !(mask1 & below));
+  const uint32_t solo0 = __ballot_sync(full, live0 && alone0);
+  uint32_t solo1 = __ballot_sync(full, live1 && alone1);
+  while (lead0) {  // clusters with several rows in the first half: theirs in the second half join them
+    const int b = __ffs(lead0) - 1;
+    lead0 &= lead0 - 1;
+    const uint32_t cl = __shfl_sync(full, key[0], b);
+    uint32_t mem0 = __shfl_sync(full, mask0, b);
+    uint32_t mem1 = __ballot_sync(full, key[1] == cl);
+    lead1 &= ~mem1;
+    solo1 &= ~mem1;
+    double acc[KB];
+#pragma unroll
+    for (int i = 0; i < KB; ++i) acc[i] = 0.0;
+    for (; mem0; mem0 &= mem0 - 1) t.add(row0 + __ffs(mem0) - 1, acc);
+    for (; mem1; mem1 &= mem1 - 1) t.add(row0 + 32 + __ffs(mem1) - 1, acc);
+    t.flush(cl, acc);
+  }
+  while (lead1) {
+    const int b = __ffs(lead1) - 1;
+    lead1 &= lead1 - 1;
+    const uint32_t cl = __shfl_sync(full, key[1], b);
+    uint32_t mem1 = __shfl_sync(full, mask1, b);
+    double acc[KB];
+#pragma unroll
+    for (int i = 0; i < KB; ++i) acc[i] = 0.0;
+    for (; mem1; mem1 &= mem1 - 1) t.add(row0 + 32 + __ffs(mem1) - 1, acc);
+    t.flush(cl, acc);
+  }
+  if (solo0) t.solos(solo0, key[0], row0);
+  if (solo1) t.solos(solo1, key[1], row0 + 32);
+}
+
+// K3's rows in the fused form: the re-checked points were left out above; a warp per flagged point adds its row.
+__global__ void __launch_bounds__(256) flagged_sums_kernel(const float *__restrict__ pts, int d,
+                                                           const int32_t *__restrict__ flag_list,
+                                                           const unsigned int *__restrict__ flag_count,
+                                                           const int32_t *__restrict__ assign, double *__restrict__ sums) {
+  const unsigned int nflag = *flag_count;
+  const int lane = threadIdx.x & 31;
+  const unsigned int warps = gridDim.x * (blockDim.x >> 5);
+  for (unsigned int f = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); f < nflag; f += warps) {
+    const long long p = flag_list[f];
+    const float *row = pts + (size_t)p * d;
+    double *out = sums + (size_t)assign[p] * d;
+    for (int j = lane; j < d; j += 32) atomicAdd(out + j, (double)__ldg(row + j));
+  }
+}
+
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
     tensor_assign_pair_kernel(const __grid_constant__ CUtensorMap map_x, const __grid_constant__ CUtensorMap map_c,
                               const TensorArgs a) {
@@ -548,15 +706,16 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
       (reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   const int kblocks = (a.d + kBlockK - 1) / kBlockK;
   const int ntiles_n = a.k_pad / kPairN;
-  unsigned char *a_res = smem;                                   // [2][kblocks] x 16 KiB: my 128 points, double-buffered
+  unsigned char *a_res = smem;                                   // [abufs][kblocks] x 16 KiB: my 128 points, two or three tiles
   const size_t a_bytes = (size_t)kblocks * kABytes;              // (the next tile's rows land while this one is scored)
-  unsigned char *a_aug = a_res + 2 * a_bytes;                    // the constant |c|^2 tile
+  const int n_abufs = a.abufs;
+  unsigned char *a_aug = a_res + n_abufs * a_bytes;              // the constant |c|^2 tile
   const int kStages = a.stages;
   unsigned char *b_stage = a_aug + kABytes;                  // stages x 16 KiB: my 128 of the tile's 256 centroid rows
   uint64_t *bars = reinterpret_cast<uint64_t *>(b_stage + (size_t)kStages * kBBytes);
   uint64_t *full = bars, *empty = bars + kMaxStages;
-  uint64_t *a_full = bars + 2 * kMaxStages, *a_empty = a_full + 2;
-  uint64_t *t_full = a_empty + 2, *t_empty = t_full + 2;
+  uint64_t *a_full = bars + 2 * kMaxStages, *a_empty = a_full + 3;
+  uint64_t *t_full = a_empty + 3, *t_empty = t_full + 2;
   uint64_t *dec_full = t_empty + 2, *dec_empty = dec_full + 2;  // epilogue -> decider warps, per tile parity (local to each CTA)
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(dec_empty + 2);
   float4 *const xchg = reinterpret_cast<float4 *>(tmem_slot + 4);  // [2 parities][4 column groups][128 rows]
@@ -567,9 +726,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-    for (int b = 0; b < 2; ++b) {
+    for (int b = 0; b < 3; ++b) {
       mbar_init(&a_full[b], 1);
       mbar_init(&a_empty[b], 1 + kDeciderWarps);
+    }
+    for (int b = 0; b < 2; ++b) {
       mbar_init(&t_full[b], 1);
       mbar_init(&t_empty[b], 2 * kEpiWarps);
       mbar_init(&dec_full[b], kEpiWarps);
@@ -599,12 +760,12 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 
   if (warp == kTmaWarp) {
     // ===== TMA producer: in BOTH CTAs; every byte is counted on the leader's barriers =====
-    uint32_t stage = 0, phase = 0, a_phase[2] = {0, 0};
+    uint32_t stage = 0, phase = 0, a_phase = 0;  // bit ab = phase of point-tile buffer ab
     int ab = 0;
     Trace tr{(HGM_TRC(a) && blockIdx.x == 0 && lane == 0) ? HGM_TRC(a) : nullptr, 0};
     for (long long tm = pair0; tm < tiles; tm += npairs) {
       tr(1, (int)tm);
-      mbar_wait(&a_empty[ab], a_phase[ab] ^ 1);
+      mbar_wait(&a_empty[ab], ((a_phase >> ab) & 1u) ^ 1u);
       tr(2, (int)tm);
       if (elect_one()) {
         if (leader) mbar_expect_tx(&a_full[ab], 2 * kblocks * kABytes);
@@ -613,8 +774,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
                            (int)(tm * 2 * kPairRows + rank * kPairRows), &a_full[ab]);
       }
       __syncwarp();
-      a_phase[ab] ^= 1;
-      ab ^= 1;
+      a_phase ^= 1u << ab;
+      if (++ab == n_abufs) ab = 0;
       for (int tn = 0; tn < ntiles_n; ++tn)
         for (int kb = 0; kb <= kblocks; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
@@ -632,14 +793,14 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
     // ===== MMA issuer: the leader CTA only; commits are multicast to both CTAs =====
     if (leader) {
       const uint64_t a_desc0 = umma_desc(a_res, 0), aug_desc = umma_desc(a_aug, 0), b_desc0 = umma_desc(b_stage, 0);
-      uint32_t stage = 0, phase = 0, a_phase[2] = {0, 0}, t_phase[2] = {0, 0};
+      uint32_t stage = 0, phase = 0, a_phase = 0, t_phase[2] = {0, 0};
       int buf = 0, ab = 0;
       Trace tr{(HGM_TRC(a) && blockIdx.x == 0 && lane == 0) ? HGM_TRC(a) + 1024 : nullptr, 0};
       for (long long tm = pair0; tm < tiles; tm += npairs) {
         tr(1, (int)tm);
-        mbar_wait(&a_full[ab], a_phase[ab]);
+        mbar_wait(&a_full[ab], (a_phase >> ab) & 1u);
         tr(2, (int)tm);
-        a_phase[ab] ^= 1;
+        a_phase ^= 1u << ab;
         const uint64_t a_desc_tile = a_desc0 + (uint64_t)(ab * (a_bytes >> 4));
         for (int tn = 0; tn < ntiles_n; ++tn) {
           mbar_wait(&t_empty[buf], t_phase[buf] ^ 1);
@@ -679,7 +840,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
         }
         if (elect_one()) umma_commit_pair(&a_empty[ab]);
         __syncwarp();
-        ab ^= 1;
+        if (++ab == n_abufs) ab = 0;
       }
     }
   } else if (warp >= kFirstEpiWarp) {
@@ -746,7 +907,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
     const int dw = warp - kAllocWarp;
     const float cmax = __uint_as_float(*a.cmax_bits);
     uint32_t d_phase[2] = {0, 0};
-    int par = 0;  // also the A buffer of the tile
+    int par = 0, ab = 0;  // the tile's exchange slots and its buffer of rows
     for (long long tm = pair0; tm < tiles; tm += npairs) {
       mbar_wait_backoff(&dec_full[par], d_phase[par], 100);
       d_phase[par] ^= 1;
@@ -756,7 +917,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
         const int r = dw * 64 + lane + 32 * j;
         float acc = 0.f;
         for (int kb = 0; kb < kblocks; ++kb) {
-          const float4 *tile = reinterpret_cast<const float4 *>(a_res + par * a_bytes + (size_t)kb * kABytes);
+          const float4 *tile = reinterpret_cast<const float4 *>(a_res + ab * a_bytes + (size_t)kb * kABytes);
 #pragma unroll
           for (int ch = 0; ch < 8; ++ch) {
             const float4 v = tile[r * 8 + (ch ^ (r % 8))];
@@ -766,7 +927,8 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
         xn[j] = acc;
       }
       __syncwarp();
-      if (lane == 0) mbar_arrive(&a_empty[par]);  // this buffer of rows may be reloaded (the MMAs committed theirs already)
+      if (!a.sums && lane == 0) mbar_arrive(&a_empty[ab]);  // this buffer of rows may be reloaded (the MMAs committed theirs already)
+      uint32_t key[2];  // fused sums: a decided row carries its cluster, any other row a value no row shares
 #pragma unroll
       for (int j = 0; j < 2; ++j) {
         const int row = dw * 64 + lane + 32 * j;
@@ -779,6 +941,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
           if (o.x < best) { best = o.x; best_tile = __float_as_int(o.z); win_group = g; }  // a tie keeps the lower columns
         }
         const long long p = tm * 2 * kPairRows + (long long)rank * kPairRows + row;
+        key[j] = 0x80000000u | (uint32_t)(32 * j + lane);
         if (p < a.n) {
           const int bidx = best_tile * kPairN + win_group * 64 + (int)(__float_as_uint(best) & 0x3Fu);
           const float xnorm = sqrtf(xn[j]);
@@ -787,12 +950,34 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
           a.assign[p] = bidx;
           if (second - best > thr) {
             if (!HGM_DBG(a)) atomicAdd(a.lcounts + bidx, 1u);
+            key[j] = (uint32_t)bidx;
           } else if (!HGM_DBG(a)) {
             const unsigned int slot = atomicAdd(a.flag_count, 1u);
             a.flag_list[slot] = (int32_t)p;
           }
         }
       }
+      if (a.sums) {
+        const unsigned char *rows = a_res + ab * a_bytes;
+        if (a.d == kblocks * 32) {
+          switch (kblocks) {
+            case 1: pair_add_rows<1, true>(rows, dw * 64, key, a.sums, a.d, lane); break;
+            case 2: pair_add_rows<2, true>(rows, dw * 64, key, a.sums, a.d, lane); break;
+            case 3: pair_add_rows<3, true>(rows, dw * 64, key, a.sums, a.d, lane); break;
+            default: pair_add_rows<4, true>(rows, dw * 64, key, a.sums, a.d, lane); break;
+          }
+        } else {
+          switch (kblocks) {
+            case 1: pair_add_rows<1, false>(rows, dw * 64, key, a.sums, a.d, lane); break;
+            case 2: pair_add_rows<2, false>(rows, dw * 64, key, a.sums, a.d, lane); break;
+            case 3: pair_add_rows<3, false>(rows, dw * 64, key, a.sums, a.d, lane); break;
+            default: pair_add_rows<4, false>(rows, dw * 64, key, a.sums, a.d, lane); break;
+          }
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&a_empty[ab]);  // only now: the sums read the rows from shared memory
+      }
+      if (++ab == n_abufs) ab = 0;
       __syncwarp();
       if (lane == 0) mbar_arrive(&dec_empty[par]);
       par ^= 1;
@@ -1101,9 +1286,9 @@ size_t tensor_smem_bytes(int d, int stages) {
   const int kblocks = (d + kBlockK - 1) / kBlockK;
   return (size_t)2 * kblocks * kABytes + kABytes + (size_t)stages * kBBytes + 512 + 4 * kTileM * 16 + 1024;
 }
-size_t tensor_pair_smem_bytes(int d, int stages) {
+size_t tensor_pair_smem_bytes(int d, int stages, int abufs = 2) {
   const int kblocks = (d + kBlockK - 1) / kBlockK;
-  return (size_t)2 * kblocks * kABytes + kABytes + (size_t)stages * kBBytes + 512 + 2 * 4 * kPairRows * 16 + 1024;
+  return (size_t)abufs * kblocks * kABytes + kABytes + (size_t)stages * kBBytes + 512 + 2 * 4 * kPairRows * 16 + 1024;
 }
 int tensor_stages(int d, size_t smem_optin) {
   int stages = kMaxStages;
@@ -1226,7 +1411,8 @@ cudaError_t launch_tensor_map(const float *d_pts, int64_t n, int d, const float 
                               const unsigned int *d_cmax_bits, int32_t *d_assign, int32_t *d_flag_list,
                               unsigned int *d_flag_count, unsigned int *d_meta, int32_t *d_order, double *d_sums,
                               unsigned long long *d_counts, int sm_count, size_t smem_optin, cudaStream_t s,
-                              cudaEvent_t *phase) {
+                              cudaEvent_t *phase, int *launches) {
+  if (launches) *launches = 0;
   if (n <= 0) return cudaSuccess;
   if (n > 0x7FFFFFFFll) return cudaErrorInvalidValue;
   if ((reinterpret_cast<uintptr_t>(d_pts) & 15) != 0 || !d_assign) return cudaErrorInvalidValue;
@@ -1245,17 +1431,35 @@ cudaError_t launch_tensor_map(const float *d_pts, int64_t n, int d, const float 
   // 14.3 vs 16.7 ms for 8 M); the single-CTA kernel keeps d <= 32, where a point tile is one K-block.
   // hgm_set_tensor_form overrides (parity tests of both forms, comparison runs).
   const int form = g_tensor_form.load();
-  const bool pair = sm_count >= 2 && (form == HGM_TENSOR_FORM_AUTO ? d > 32 : form == HGM_TENSOR_FORM_PAIR);
+  const bool pair = sm_count >= 2 && (form == HGM_TENSOR_FORM_AUTO ? d > 32 : form >= HGM_TENSOR_FORM_PAIR);
+  // Where the sums are made: inside K2 (the pair form's deciders add each decided row while it is in shared memory)
+  // when a tile is scored for longer than its two decider warps need for their 128 rows, else by K4's second pass
+  // over the rows.  Measured per row and SM (tools/profile_map.py --tensor-form 3 / 4, one box): the deciders take
+  // 0.275 ns at d = 64, 0.41 at d = 96, 0.42 at d = 128 whatever k is; the scores take 0.27 ns per 1024 centroids at
+  // d = 64, 0.30 at d = 96, 0.33 at d = 128.  Fused wins from k = 1024 at d <= 64 (11.75 vs 12.63 ms for 40 M rows;
+  // k = 2048: 10.3 vs 11.4 for 20 M) and from k = 2048 above (d = 128, k = 4096: 11.08 vs 11.73 ms for 8 M), and
+  // loses below (d = 64, k = 512: 11.0 vs 9.05; d = 96, k = 1024: 8.30 vs 8.12).
+  const int kb_rows = (d + kBlockK - 1) / kBlockK;
+  const bool fused = pair && (form == HGM_TENSOR_FORM_PAIR_FUSED ||
+                              (form != HGM_TENSOR_FORM_PAIR_SEGMENTED && k_pad >= (kb_rows <= 2 ? 1024 : 2048)));
   int stages = tensor_stages(d, smem_optin);
+  // A third buffer of rows when the sums are fused and six B stages still fit (d <= 64): the deciders then hold a tile's
+  // rows while TWO later tiles are scored, and their reductions never delay the next load.
+  int abufs = 2;
   if (pair) {
+    if (fused && tensor_pair_smem_bytes(d, 6, 3) <= smem_optin) abufs = 3;
+#ifdef HGM_EXPERIMENTS
+    if (const char *v = getenv("HGM_TENSOR_ABUFS")) abufs = atoi(v) == 3 ? 3 : 2;
+#endif
     stages = kMaxStages;
-    while (stages > 2 && tensor_pair_smem_bytes(d, stages) > smem_optin) --stages;
+    while (stages > 2 && tensor_pair_smem_bytes(d, stages, abufs) > smem_optin) --stages;
   }
-  const size_t smem = pair ? tensor_pair_smem_bytes(d, stages) : tensor_smem_bytes(d, stages);  // incl. 1 KiB to align the base
+  const size_t smem = pair ? tensor_pair_smem_bytes(d, stages, abufs) : tensor_smem_bytes(d, stages);  // incl. 1 KiB to align the base
   e = pair ? cudaFuncSetAttribute(tensor_assign_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
            : cudaFuncSetAttribute(tensor_assign_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  TensorArgs a{(long long)n, k, k_pad, d, stages, ~0x3Fu, nullptr, 0, d_cmax_bits, d_pts, d_meta, d_assign, d_flag_list, d_flag_count};
+  TensorArgs a{(long long)n, k, k_pad, d, stages, ~0x3Fu, nullptr, 0, d_cmax_bits, d_pts, d_meta, d_assign, d_flag_list, d_flag_count,
+               fused ? d_sums : nullptr, abufs};
 #ifdef HGM_EXPERIMENTS
   if (const char *v = getenv("HGM_TENSOR_DEBUG")) a.debug = atoi(v);
 #endif
@@ -1310,7 +1514,14 @@ cudaError_t launch_tensor_map(const float *d_pts, int64_t n, int d, const float 
     if ((e = cudaGetLastError()) != cudaSuccess) return e;
   }
   if (phase) cudaEventRecord(phase[2], s);
-  e = launch_segmented_sums(d_pts, n, d, k, d_assign, d_meta, d_order, d_sums, d_counts, sm_count, s);
+  if (launches) *launches = fused ? 6 : 7;  // K2, K3's three, then offsets + K3's rows, or offsets + order + segmented sums
+  if (fused) {  // the counts join the partials; only K3's rows are still to be added
+    cluster_offsets_kernel<<<1, 1024, 0, s>>>(d_meta, k, d_counts);
+    flagged_sums_kernel<<<sm_count * 4, 256, 0, s>>>(d_pts, d, d_flag_list, d_flag_count, d_assign, d_sums);
+    e = cudaGetLastError();
+  } else {
+    e = launch_segmented_sums(d_pts, n, d, k, d_assign, d_meta, d_order, d_sums, d_counts, sm_count, s);
+  }
   if (phase) cudaEventRecord(phase[3], s);
   return e;
 }

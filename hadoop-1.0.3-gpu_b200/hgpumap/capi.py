@@ -21,6 +21,7 @@ FMT_F32LE, FMT_F32BE, FMT_TEXT, FMT_SEQ_F32BE, FMT_SEQ_F32LE = 0, 1, 2, 3, 4
 KERNEL_AUTO, KERNEL_EXACT, KERNEL_GRID2D, KERNEL_TENSOR, KERNEL_GRID2D_SORT = 0, 1, 2, 3, 4
 GRID2D_FORM_NONE, GRID2D_FORM_FIXED_POINT, GRID2D_FORM_SORT = 0, 1, 2
 TENSOR_FORM_AUTO, TENSOR_FORM_SINGLE, TENSOR_FORM_PAIR = 0, 1, 2
+TENSOR_FORM_PAIR_FUSED, TENSOR_FORM_PAIR_SEGMENTED = 3, 4  # pair kernel with the sums inside it / by the second pass
 
 _PKG_ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 _LIB = None

@@ -115,6 +115,8 @@ int hgm_last_kernel(hgm_ctx *ctx, int32_t *kernel);
 #define HGM_TENSOR_FORM_AUTO 0
 #define HGM_TENSOR_FORM_SINGLE 1
 #define HGM_TENSOR_FORM_PAIR 2
+#define HGM_TENSOR_FORM_PAIR_FUSED 3      /* pair kernel, per-cluster sums always made inside it */
+#define HGM_TENSOR_FORM_PAIR_SEGMENTED 4  /* pair kernel, per-cluster sums always by the segmented reduction (K4) */
 int hgm_set_tensor_form(int32_t form);
 /* Diagnostics build only (`make CHECKED=1`): how many shared-memory indices / centroid ids of the d == 2 kernels
  * missed their bound since the library was loaded, and the source line of the first.  HGM_EINVAL in the product build. */

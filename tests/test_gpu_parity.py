@@ -26,7 +26,9 @@ def slot():
 def tensor_form(slot):
     """Force one form of the tcgen05 score kernel for a test; AUTO again afterwards."""
     def force(name):
-        slot.set_tensor_form({"single": capi.TENSOR_FORM_SINGLE, "pair": capi.TENSOR_FORM_PAIR}[name])
+        slot.set_tensor_form({"single": capi.TENSOR_FORM_SINGLE, "pair": capi.TENSOR_FORM_PAIR,
+                              "pair_fused": capi.TENSOR_FORM_PAIR_FUSED,
+                              "pair_segmented": capi.TENSOR_FORM_PAIR_SEGMENTED}[name])
     yield force
     slot.set_tensor_form(capi.TENSOR_FORM_AUTO)
 
@@ -288,11 +290,12 @@ def test_idempotent_and_centroid_update_roundtrip(slot, oracle):
                                    (64, 129, 255), (64, 256, 256), (64, 256, 1), (64, 100, 3001), (32, 9, 2000),
                                    (128, 8, 1000), (16, 200, 3000), (48, 64, 3001), (100, 300, 2500),
                                    (8, 1024, 4000), (20, 128, 2999), (124, 40, 1000), (36, 70, 777)])
-@pytest.mark.parametrize("form", ["single", "pair"])
+@pytest.mark.parametrize("form", ["single", "pair", "pair_fused", "pair_segmented"])
 def test_tensor_path_matches_oracle(slot, oracle, tensor_form, form, d, k, n):
     """BASELINE config 4/5 shapes at test size: assignments bit-exact through the TF32 GEMM +
     FP32 re-check, counts exact, sums within tolerance -- in both forms of K2 (one CTA per tile,
-    and the cta_group::2 pair; the library picks by shape, hgm_set_tensor_form forces one)."""
+    and the cta_group::2 pair; the library picks by shape, hgm_set_tensor_form forces one) and, for the
+    pair, with the per-cluster sums made inside K2 and by K4's second pass ("pair" picks by k)."""
     tensor_form(form)
     pts, cent = cases.general_d(n, d, k, seed=d + k)
     run_case(slot, oracle, pts, cent, capi.KERNEL_TENSOR)
@@ -318,6 +321,24 @@ def test_tensor_path_decides_almost_everything_on_the_tensor_cores(slot, oracle,
     np.testing.assert_array_equal(assign, oracle.assign(pts, dup))
     assert slot.last_rechecks() >= counts[0] > 0
     slot.set_kernel(capi.KERNEL_AUTO)
+
+
+@pytest.mark.parametrize("d,k,n,hot", [(64, 1024, 30011, 3), (64, 512, 20001, 1), (128, 600, 9001, 2), (100, 300, 7001, 5),
+                                       (36, 20, 5003, 2)])
+@pytest.mark.parametrize("form", ["pair_fused", "pair_segmented"])
+def test_tensor_path_sums_on_skewed_clusters(slot, oracle, tensor_form, form, d, k, n, hot):
+    """A few clusters hold most of the points, so that every 64-row window of a tile has many rows of one
+    cluster: the fused form adds those up in registers (groups within a half, merged across the halves)
+    before they leave as one reduction per cluster -- the sums must not notice.  One cluster alone gets
+    every point in the last case."""
+    tensor_form(form)
+    rng = np.random.default_rng(d * 1000 + k)
+    _, cent = cases.general_d(16, d, k, seed=d + k + 1)
+    which = np.where(rng.random(n) < 0.8, rng.integers(0, hot, n), rng.integers(0, k, n))
+    pts = (cent[which] + rng.normal(0, 0.5, size=(n, d))).astype(np.float32)
+    run_case(slot, oracle, pts, cent, capi.KERNEL_TENSOR)
+    one = (cent[np.full(3000, k - 1)] + rng.normal(0, 0.5, size=(3000, d))).astype(np.float32)
+    run_case(slot, oracle, one, cent, capi.KERNEL_TENSOR)
 
 
 def test_tensor_path_is_the_default_for_gemm_shapes(slot, oracle):

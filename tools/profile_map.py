@@ -23,6 +23,7 @@ def main():
     ap.add_argument("--launches", type=int, default=6)
     ap.add_argument("--data", default="blobs")
     ap.add_argument("--lib", default=None, help="another build of libhgpumap.so (same-box A/B runs)")
+    ap.add_argument("--tensor-form", type=int, default=0, help="HGM_TENSOR_FORM_* (0 auto, 3 pair with fused sums, 4 pair with K4)")
     args = ap.parse_args()
     import torch
 
@@ -36,6 +37,7 @@ def main():
     slot = capi.GpuMapSlot(0)
     if args.kernel:
         slot.set_kernel(args.kernel)
+    slot.set_tensor_form(args.tensor_form)
     slot.set_centroids(synth.perturb(synth.SEED_CENTROIDS, centres))
     points = torch.empty(n * d, dtype=torch.float32, device=dev)
     if args.data == "blobs":
@@ -54,6 +56,8 @@ def main():
     _, counts = slot.read_partials()
     assert int(counts.sum()) == n
     print(f"kernel family {slot.last_kernel()}, {n} points, d={d}, k={k}: map ms per launch {np.round(times, 4).tolist()}")
+    if d > 2:
+        print(f"  last launch: K2 / K3 / sums ms {np.round(slot.last_tensor_phases(), 3).tolist()}, {slot.last_rechecks()} rows re-checked")
     slot.close()
 
 
