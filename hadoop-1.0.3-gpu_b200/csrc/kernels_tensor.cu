@@ -908,8 +908,11 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
     const float cmax = __uint_as_float(*a.cmax_bits);
     uint32_t d_phase[2] = {0, 0};
     int par = 0, ab = 0;  // the tile's exchange slots and its buffer of rows
+    Trace tr{(HGM_TRC(a) && blockIdx.x == 0 && dw == 0 && lane == 0) ? HGM_TRC(a) + 3072 : nullptr, 0};
     for (long long tm = pair0; tm < tiles; tm += npairs) {
+      tr(1, (int)tm);
       mbar_wait_backoff(&dec_full[par], d_phase[par], 100);
+      tr(2, (int)tm);
       d_phase[par] ^= 1;
       float xn[2];
 #pragma unroll
@@ -927,6 +930,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
         xn[j] = acc;
       }
       __syncwarp();
+      tr(3, (int)tm);
       if (!a.sums && lane == 0) mbar_arrive(&a_empty[ab]);  // this buffer of rows may be reloaded (the MMAs committed theirs already)
       uint32_t key[2];  // fused sums: a decided row carries its cluster, any other row a value no row shares
 #pragma unroll
@@ -957,6 +961,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
           }
         }
       }
+      tr(4, (int)tm);
       if (a.sums) {
         const unsigned char *rows = a_res + ab * a_bytes;
         if (a.d == kblocks * 32) {
@@ -976,6 +981,7 @@ __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(&a_empty[ab]);  // only now: the sums read the rows from shared memory
+        tr(5, (int)tm);
       }
       if (++ab == n_abufs) ab = 0;
       __syncwarp();
@@ -1472,16 +1478,16 @@ cudaError_t launch_tensor_map(const float *d_pts, int64_t n, int d, const float 
 #endif
     if (trace_path) {
       long long *d_trace = nullptr;
-      if (cudaMalloc(&d_trace, 3 * 1024 * 8) == cudaSuccess) {
-        cudaMemsetAsync(d_trace, 0, 3 * 1024 * 8, s);
+      if (cudaMalloc(&d_trace, 4 * 1024 * 8) == cudaSuccess) {
+        cudaMemsetAsync(d_trace, 0, 4 * 1024 * 8, s);
         a.trace = d_trace;
         tensor_assign_pair_kernel<<<(int)(2 * pairs), kThreads, smem, s>>>(map_x, map_c, a);
         cudaStreamSynchronize(s);
-        static long long h_trace[3 * 1024];
+        static long long h_trace[4 * 1024];
         cudaMemcpy(h_trace, d_trace, sizeof h_trace, cudaMemcpyDeviceToHost);
         cudaFree(d_trace);
         if (FILE *f = fopen(trace_path, "w")) {
-          for (int role = 0; role < 3; ++role)
+          for (int role = 0; role < 4; ++role)
             for (int i = 0; i < 512 && h_trace[role * 1024 + 2 * i + 1]; ++i)
               fprintf(f, "%d %lld %lld %lld\n", role, h_trace[role * 1024 + 2 * i] >> 32,
                       h_trace[role * 1024 + 2 * i] & 0xffffffffll, h_trace[role * 1024 + 2 * i + 1]);
