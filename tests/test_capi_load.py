@@ -75,3 +75,15 @@ def test_bad_arguments_are_rejected_without_a_device():
     assert lib.hgm_set_centroids(None, None, 1, 1) == -22
     assert b"NULL" in lib.hgm_last_error(None)
     assert lib.hgm_synth_centres(1, 0, 2, None) == -22
+
+
+def test_tensor_form_constants_match_the_header():
+    """hgpumap/capi.py mirrors include/hgpumap.h: a form added on one side only would be rejected as HGM_EINVAL."""
+    import re
+
+    from hgpumap import capi
+
+    text = open(os.path.join(os.path.dirname(__file__), "..", "include", "hgpumap.h")).read()
+    header = {m.group(1): int(m.group(2)) for m in re.finditer(r"#define HGM_(TENSOR_FORM_\w+) (\d+)", text)}
+    assert header == {name: getattr(capi, name) for name in header}
+    assert sorted(header.values()) == list(range(len(header)))
