@@ -413,6 +413,7 @@ int hgm_device_count(int *count) {
 const char *hgm_last_error(hgm_ctx *ctx) { return ctx ? ctx->err : g_err; }
 
 int hgm_open(int device_id, hgm_ctx **out) {
+  HGM_RANGE("hgm_open");
   if (!out) return fail(nullptr, HGM_EINVAL, "out is NULL");
   *out = nullptr;
   int ndev = 0;
@@ -487,6 +488,7 @@ void hgm_close(hgm_ctx *c) {
 }
 
 int hgm_set_centroids(hgm_ctx *c, const float *centroids, int32_t k, int32_t d) {
+  HGM_RANGE("hgm_set_centroids");
   NEED_CTX(c);
   if (!centroids || k <= 0 || d <= 0) return fail(c, HGM_EINVAL, "need centroids, k > 0, d > 0");
   if ((int64_t)k * d > (int64_t(1) << 28)) return fail(c, HGM_EINVAL, "k*d too large");
@@ -592,6 +594,7 @@ int hgm_reset_partials(hgm_ctx *c) {
 }
 
 int hgm_map_device(hgm_ctx *c, const float *d_points, int64_t n, int32_t *d_assign) {
+  HGM_RANGE("hgm_map_device");
   NEED_CTX(c);
   if (!c->d_partials) return fail(c, HGM_EINVAL, "hgm_set_centroids has not been called");
   if (n < 0 || (n > 0 && !d_points)) return fail(c, HGM_EINVAL, "bad points argument");
@@ -607,6 +610,7 @@ int hgm_map_device(hgm_ctx *c, const float *d_points, int64_t n, int32_t *d_assi
 }
 
 int hgm_read_partials(hgm_ctx *c, double *sums, int64_t *counts) {
+  HGM_RANGE("hgm_read_partials");
   NEED_CTX(c);
   if (!c->d_partials) return fail(c, HGM_EINVAL, "hgm_set_centroids has not been called");
   if (!sums || !counts) return fail(c, HGM_EINVAL, "sums and counts are required");
@@ -1380,6 +1384,7 @@ static int open_split_file(hgm_ctx *c, const char *path, int64_t offset, int64_t
 
 int hgm_map_split(hgm_ctx *c, const void *host_bytes, size_t nbytes, int32_t fmt, double *sums,
                   int64_t *counts, int32_t *assign, int64_t *n_points_out) {
+  HGM_RANGE("hgm_map_split");
   NEED_CTX(c);
   if (nbytes > 0 && !host_bytes) return fail(c, HGM_EINVAL, "host_bytes is NULL");
   SplitSource src;
@@ -1394,6 +1399,7 @@ int hgm_map_split(hgm_ctx *c, const void *host_bytes, size_t nbytes, int32_t fmt
 
 int hgm_map_file(hgm_ctx *c, const char *path, int64_t offset, int64_t length, int32_t fmt,
                  double *sums, int64_t *counts, int32_t *assign, int64_t *n_points_out) {
+  HGM_RANGE("hgm_map_file");
   NEED_CTX(c);
   if (fmt == HGM_FMT_SEQ_F32BE || fmt == HGM_FMT_SEQ_F32LE)
     return map_seq_file(c, path, offset, length, fmt == HGM_FMT_SEQ_F32BE, sums, counts, assign, n_points_out);
@@ -1466,6 +1472,7 @@ static int cache_store(hgm_ctx *c, int64_t split_id, SplitSource &src, int32_t f
 }
 
 int hgm_cache_put(hgm_ctx *c, int64_t split_id, const void *host_bytes, size_t nbytes, int32_t fmt) {
+  HGM_RANGE("hgm_cache_put");
   NEED_CTX(c);
   if (nbytes > 0 && !host_bytes) return fail(c, HGM_EINVAL, "host_bytes is NULL");
   SplitSource src;
@@ -1479,6 +1486,7 @@ int hgm_cache_put(hgm_ctx *c, int64_t split_id, const void *host_bytes, size_t n
 }
 
 int hgm_cache_put_file(hgm_ctx *c, int64_t split_id, const char *path, int64_t offset, int64_t length, int32_t fmt) {
+  HGM_RANGE("hgm_cache_put_file");
   NEED_CTX(c);
   if (fmt == HGM_FMT_SEQ_F32BE || fmt == HGM_FMT_SEQ_F32LE)
     return cache_seq_file(c, split_id, path, offset, length, fmt == HGM_FMT_SEQ_F32BE);
@@ -1491,6 +1499,7 @@ int hgm_cache_put_file(hgm_ctx *c, int64_t split_id, const char *path, int64_t o
 }
 
 int hgm_cache_map(hgm_ctx *c, int64_t split_id, int32_t *d_assign, int64_t *n_points_out) {
+  HGM_RANGE("hgm_cache_map");
   NEED_CTX(c);
   auto it = c->cache.find(split_id);
   if (it == c->cache.end()) return fail(c, HGM_EINVAL, "split %lld is not in the cache", (long long)split_id);
@@ -1503,6 +1512,7 @@ static int map_cached(hgm_ctx *c, std::vector<const hgm_ctx::CachedSplit *> &ord
                       int32_t *n_launch_groups_out);
 
 int hgm_cache_map_all(hgm_ctx *c, int64_t *n_points_out, int32_t *n_launch_groups_out) {
+  HGM_RANGE("hgm_cache_map_all");
   NEED_CTX(c);
   if (!c->d_partials) return fail(c, HGM_EINVAL, "hgm_set_centroids has not been called");
   std::vector<const hgm_ctx::CachedSplit *> order;
@@ -1513,6 +1523,7 @@ int hgm_cache_map_all(hgm_ctx *c, int64_t *n_points_out, int32_t *n_launch_group
 
 int hgm_cache_map_many(hgm_ctx *c, const int64_t *split_ids, int32_t n_ids, int64_t *n_points_out,
                        int32_t *n_launch_groups_out) {
+  HGM_RANGE("hgm_cache_map_many");
   NEED_CTX(c);
   if (!c->d_partials) return fail(c, HGM_EINVAL, "hgm_set_centroids has not been called");
   if (n_ids < 0 || (n_ids > 0 && !split_ids)) return fail(c, HGM_EINVAL, "bad split id list");

@@ -275,6 +275,7 @@ int hgm_peer_close(hgm_ctx *c) {
 }
 
 int hgm_allreduce_partials(hgm_ctx *c) {
+  HGM_RANGE("hgm_allreduce_partials");
   int dev, k, d;
   cudaStream_t st;
   void **slot;

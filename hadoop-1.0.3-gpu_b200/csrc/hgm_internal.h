@@ -8,6 +8,20 @@
 
 #include "../../include/hgpumap.h"
 
+// NVTX ranges on the entry points a trace of a map task should show (the fork's ad-hoc
+// wall-clock LOG.info timers, mapred/MapTask.java:443,451, pipes/PipesGPUMapRunner.java:110-112).  Header-only NVTX 3:
+// without a tool attached a range is one load and a branch.
+#include <nvtx3/nvToolsExt.h>
+namespace hgm {
+struct NvtxRange {
+  explicit NvtxRange(const char *name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+  NvtxRange(const NvtxRange &) = delete;
+  NvtxRange &operator=(const NvtxRange &) = delete;
+};
+}  // namespace hgm
+#define HGM_RANGE(name) ::hgm::NvtxRange hgm_nvtx_range_(name)
+
 namespace hgm {
 
 // ---- arithmetic contract ------------------------------------
