@@ -470,6 +470,10 @@ def run_extras(args, torch, dist, slot, stream, dev, rank, world, points, centre
                                        "K4_counts_and_rechecked_rows" if fused else "K4_segmented_sums": phases[2]},
                          "rechecked_points": flagged, "achieved_tflops": tf,
                          "roofline_frac_tf32_measured_in_run": tf / tf32, "tf32_tflops_cublas_in_run": tf32,
+                         # cuBLAS's 8192^3 TF32 GEMM is a measured yardstick, not the pipe's ceiling (the kernel can pass it:
+                         # it also multiplies the |c|^2 K-block, (d + 32) / d more flops than counted here); the nominal
+                         # dense TF32 rate (half of the 2.25 PFLOP/s bf16 figure) is the other denominator
+                         "roofline_frac_tf32_nominal": tf / 1125.0, "tf32_tflops_nominal": 1125.0,
                          "roofline_frac_bf16_sustained": tf / bf16 if bf16 else None, "bf16_tflops_sustained": bf16,
                          "recheck_sensitivity": []}
             else:
