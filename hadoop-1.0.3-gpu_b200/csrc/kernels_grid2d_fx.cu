@@ -301,16 +301,18 @@ __global__ void __launch_bounds__(S::kThreads, 1)
     return full;
   };
 
-  const long long ntiles = (n + kTile - 1) / kTile;
-  const long long tile_stride = (long long)gridDim.x * S::kWarps;
-  long long tile = (long long)blockIdx.x * S::kWarps + warp;
+  // Tiles are counted in 32 bits (the launcher refuses more than 2^31 of them) and the warp's read pointer is advanced
+  // from tile to tile: the 64-bit index arithmetic per tile was a tenth of the loop's instructions.
+  const int ntiles = (int)((n + kTile - 1) / kTile), full_tiles = (int)(n / kTile);
+  const int tile_stride = (int)gridDim.x * S::kWarps;
+  int tile = (int)blockIdx.x * S::kWarps + warp;
   int qn = 0;  // points in this warp's queue
 
   // lane owns the point pairs (i*32 + lane), i = 0..kPPT/2-1, of its warp's tile
-  auto load_tile = [&](long long tl, float4 (&buf)[kPPT / 2]) {
-    const long long base = tl * kTile;
-    const float *src = pts + 2 * base + 4 * lane;
-    if (base + kTile <= n) {
+  const float *src = pts + 2 * ((long long)tile * kTile) + 4 * lane;  // this lane's first pair of the warp's current tile
+  const long long src_step = 2ll * kTile * tile_stride;
+  auto load_tile = [&](int tl, float4 (&buf)[kPPT / 2]) {
+    if (tl < full_tiles) {
 #pragma unroll
       for (int i = 0; i < kPPT / 2; ++i) {
         if (kVec4) {
@@ -324,7 +326,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
         }
       }
     } else {
-      const int live = (int)(n - base);
+      const int live = (int)(n - (long long)tl * kTile);
 #pragma unroll
       for (int i = 0; i < kPPT / 2; ++i) {
         const int local = 2 * (i * 32 + lane);
@@ -347,18 +349,20 @@ __global__ void __launch_bounds__(S::kThreads, 1)
   for (;;) {
     // the flag is read by the whole warp at once; the vote makes the loop condition warp-uniform by construction
     while (tile < ntiles && !__any_sync(0xFFFFFFFFu, *flag != 0)) {
-      const long long base = tile * kTile;
-      const int live = (int)min((long long)kTile, n - base);
+      const bool whole = tile < full_tiles;
+      const long long base = (long long)tile * kTile;
+      const int live = whole ? kTile : (int)(n - base);
       float xs[kPPT], ys[kPPT];
 #pragma unroll
       for (int i = 0; i < kPPT / 2; ++i) {
         xs[2 * i] = buf[i].x; ys[2 * i] = buf[i].y; xs[2 * i + 1] = buf[i].z; ys[2 * i + 1] = buf[i].w;
       }
       tile += tile_stride;
+      src += src_step;
       if (tile < ntiles) load_tile(tile, buf);  // the next tile's loads fly while this one is worked on
 
       uint32_t seen = 0u;  // OR of the counts found: any bit at or above kFlushAt = a word is at the threshold
-      if (live == kTile)
+      if (whole)
         fx_work_tile<S, kAssign, true, 0>(table_s, g, fx, acc_lane, (uint32_t)k, queue, qindex, assign, base, live, lane, lt_mask, xs, ys, qn, seen);
       else
         fx_work_tile<S, kAssign, false, 0>(table_s, g, fx, acc_lane, (uint32_t)k, queue, qindex, assign, base, live, lane, lt_mask, xs, ys, qn, seen);
@@ -368,7 +372,7 @@ __global__ void __launch_bounds__(S::kThreads, 1)
         seen |= settle(qn, 32, base);
         __syncwarp();
       }
-      if (live == kTile)
+      if (whole)
         fx_work_tile<S, kAssign, true, kPPT / 2>(table_s, g, fx, acc_lane, (uint32_t)k, queue, qindex, assign, base, live, lane, lt_mask, xs, ys, qn, seen);
       else
         fx_work_tile<S, kAssign, false, kPPT / 2>(table_s, g, fx, acc_lane, (uint32_t)k, queue, qindex, assign, base, live, lane, lt_mask, xs, ys, qn, seen);
@@ -457,6 +461,7 @@ cudaError_t launch_fx(const float *d_pts, int64_t n, const float *d_cent, int k,
   cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   const long long ntiles = (n + S::kTile - 1) / S::kTile;
+  if (ntiles > 0x7FF00000ll) return cudaErrorInvalidValue;  // the kernel counts tiles in 32 bits (5.5e11 points: 4.4 TB)
   const long long want = (ntiles + S::kWarps - 1) / S::kWarps;
   const int grid = (int)(want < sm_count ? want : sm_count);
   kern<<<grid, S::kThreads, smem, s>>>(d_pts, (long long)n, d_cent, k, g, fx, d_table, d_cand, outer, d_sums, d_counts,
