@@ -38,6 +38,13 @@ def tensor_case(d, k, n, seed):
     return pts, cent
 
 
+def skewed_rows(d, k, n, seed):
+    rng = np.random.default_rng(seed)
+    _, cent = cases.general_d(16, d, k, seed)
+    which = np.where(rng.random(n) < 0.8, rng.integers(0, 3, n), rng.integers(0, k, n))
+    return (cent[which] + rng.normal(0, 0.5, size=(n, d))).astype(np.float32), cent
+
+
 CASES = {
     "grid2d_fx": lambda s, o: run(s, o, *cases.blobs(50001, 2, 128, seed=3), capi.KERNEL_GRID2D),
     "grid2d_fx_no_assign": lambda s, o: run(s, o, *cases.blobs(50001, 2, 128, seed=4), capi.KERNEL_GRID2D, want_assign=False),
@@ -53,6 +60,11 @@ CASES = {
     "tensor_single_d64": lambda s, o: run(s, o, *tensor_case(64, 256, 4097, 11), capi.KERNEL_TENSOR, capi.TENSOR_FORM_SINGLE),
     "tensor_pair_d64": lambda s, o: run(s, o, *tensor_case(64, 1024, 6001, 12), capi.KERNEL_TENSOR, capi.TENSOR_FORM_PAIR),
     "tensor_pair_d128": lambda s, o: run(s, o, *tensor_case(128, 512, 3001, 13), capi.KERNEL_TENSOR, capi.TENSOR_FORM_PAIR),
+    # the per-cluster sums made by the pair kernel's decider warps (three point-tile buffers at d = 64), forced at a small k,
+    # and on rows that mostly share three clusters (the in-register merge before the reductions)
+    "tensor_pair_fused_d64": lambda s, o: run(s, o, *tensor_case(64, 300, 20011, 14), capi.KERNEL_TENSOR, capi.TENSOR_FORM_PAIR_FUSED),
+    "tensor_pair_fused_d100_skew": lambda s, o: run(s, o, *skewed_rows(100, 300, 9001, 15), capi.KERNEL_TENSOR, capi.TENSOR_FORM_PAIR_FUSED),
+    "tensor_pair_segmented_d64": lambda s, o: run(s, o, *tensor_case(64, 1024, 6001, 16), capi.KERNEL_TENSOR, capi.TENSOR_FORM_PAIR_SEGMENTED),
 }
 
 
